@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""bench.py -- SCREAM scene-renderer hot path on B200 (BASELINE.json metric: depth images/s, Gpoints/s,
+% of HBM roofline).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl ours|reference]
+
+Workload (BASELINE.json configs[1]): the renderer's share of one adversarial 3DMatch
+training step for B pairs per GPU, n = m = 10,000 points, 6 canonical views, w = 64, rho = 24:
+    fake:  forward with winner map (src requires grad)  ->  backward with a N(0,1) upstream gradient
+    real:  forward with the GT pose [R|t] fused on the source cloud, no winner map
+(train_3d_match.py:186-201).  One step renders B * 2 poses * 6 views * 2 clouds = 24 B depth images.
+
+--impl reference times the reference's CPU implementation (the torch restatement in oracle/, bit-identical
+to /root/reference/models/render.py as verified by oracle/make_golden.py; /root/reference does not exist
+on the GPU box) on all host cores, each step a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_PTS, V, W_IMG, RHO = 10_000, 6, 64, 24
+METRIC, UNIT = "depth_images_per_sec", "images/s"
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# --------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# --------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, c in zip(names, r[2:6]) if c.lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# synthetic cfg2 batch (host, pinned)
+# --------------------------------------------------------------------------------------------
+def make_batch(B: int, seed: int):
+    """B pairs of unit-ball clouds (3DMatch normalisation, three_d_match.py:183-190) + GT poses."""
+    from scream_b200 import synth
+    rng = np.random.default_rng(seed)
+    d = rng.standard_normal((B * 2 * N_PTS, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    xyz = d * (rng.random((B * 2 * N_PTS, 1), dtype=np.float32) ** np.float32(1 / 3))
+    pose = np.stack([synth.random_pose(seed * 100003 + b) for b in range(B)])
+    offs = np.arange(2 * B + 1, dtype=np.int64) * N_PTS
+    grad = rng.standard_normal((B, V, 2, W_IMG, W_IMG), dtype=np.float32)
+    return (torch.from_numpy(np.ascontiguousarray(xyz)), torch.from_numpy(offs),
+            torch.from_numpy(np.ascontiguousarray(pose)), torch.from_numpy(grad))
+
+
+def algorithmic_bytes(B: int):
+    """SURVEY.md 8d.  fwd: V*12*(n+m) + V*2*w^2*4 (+ the same again for the int32 winner map);
+    bwd: V*2*w^2*8 + 12*(n+m)."""
+    pts, img = 2 * N_PTS, V * 2 * W_IMG * W_IMG * 4
+    fwd_fake = B * (V * 12 * pts + 2 * img)
+    fwd_real = B * (V * 12 * pts + img)
+    bwd = B * (2 * img + 12 * pts)
+    return fwd_fake, fwd_real, bwd
+
+
+# --------------------------------------------------------------------------------------------
+# CPU reference arm / cpu_baseline (the ONLY place bench.py executes oracle/)
+# --------------------------------------------------------------------------------------------
+def cpu_reference_step(step: int, seed: int = 77):
+    """One bounded sample of the workload on the host: ONE pair, ONE of the six views (cycling with the
+    step), fake forward+backward and real forward -> 4 depth images.  Cost is exactly linear in views."""
+    from oracle import render_oracle as orc
+    from scream_b200 import synth
+    src = torch.from_numpy(synth.unit_ball(N_PTS, seed))
+    tgt = torch.from_numpy(synth.unit_ball(N_PTS, seed + 1))
+    pose = torch.from_numpy(synth.random_pose(seed + 2))
+    euler = [orc.canonical_eulers("muti")[step % V]]
+    g = torch.from_numpy(np.random.default_rng(seed).standard_normal((1, 2, W_IMG, W_IMG)).astype(np.float32))
+    t0 = time.perf_counter()
+    s = src.clone().requires_grad_(True)
+    fake = orc.forward_dense(s, tgt, RHO, W_IMG, euler)            # render.py:61-73, with autograd
+    fake.backward(g)
+    with torch.no_grad():
+        real = orc.forward_dense(orc.apply_pose(pose[:, :3].contiguous(), pose[:, 3:4].contiguous(), src),
+                                 tgt, RHO, W_IMG, euler)
+    dt = time.perf_counter() - t0
+    return dt, 4, float(real.sum())
+
+
+def run_reference(args, rank: int):
+    if rank != 0:
+        return
+    threads = torch.get_num_threads()
+    budget = 240.0
+    t_start = time.perf_counter()
+    for i in range(args.warmup):
+        cpu_reference_step(i)
+        if time.perf_counter() - t_start > budget / 3:
+            break
+    total, imgs, done = 0.0, 0, 0
+    for i in range(args.steps):
+        dt, n, _ = cpu_reference_step(i)
+        total += dt; imgs += n; done += 1
+        if time.perf_counter() - t_start > budget:
+            break
+    val = imgs / total
+    sample = "per step: 1 pair (n=m=10000), 1 of the 6 views, fake fwd+bwd + real fwd = 4 depth images"
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": done, "warmup": args.warmup, "ms_per_step": 1e3 * total / done, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(args.batch), "gpu_launches": 0,
+            "gpoints_per_sec": val * N_PTS / 1e9,
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def config_dict(B: int):
+    return {"workload": "cfg2: 3DMatch training-batch render, fake fwd(+winner)+bwd and real(posed) fwd",
+            "pairs_per_gpu": B, "n_src": N_PTS, "n_tgt": N_PTS, "views": V, "w": W_IMG, "rho": RHO,
+            "images_per_step_per_gpu": 24 * B, "cache": "inputs+outputs per step exceed the 126 MB L2 (B>=512)",
+            "parallelism": "items sharded over GPUs, no data-path collective"}
+
+
+# --------------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------------
+def run_ours(args, rank: int, local_rank: int, world: int):
+    import torch.distributed as dist
+    from scream_b200.render import render_batch, view_matrices, RegistrationRender
+    from scream_b200 import _lib
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    _lib.load()
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    B = args.batch
+    views = view_matrices(RegistrationRender(RHO, W_IMG, device="cpu").eulers).to(dev)
+    h_xyz, h_offs, h_pose, h_grad = [t.pin_memory() for t in make_batch(B, 1234 + rank)]
+    xyz, offs, pose, grad = [t.to(dev) for t in (h_xyz, h_offs, h_pose, h_grad)]
+    max_item = 2 * N_PTS
+    dense = args.dense
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    def step_device(rec=None):
+        """fake fwd(+winner) -> bwd -> real fwd, inputs resident in HBM."""
+        x = xyz.detach().requires_grad_(True)
+        if rec is not None:
+            e = [ev() for _ in range(6)]; e[0].record()
+        fake, _, _ = render_batch(x, offs, views, RHO, W_IMG, dense=dense, need_winner=True, max_item_pts=max_item)
+        if rec is not None:
+            e[1].record(); e[2].record()
+        fake.backward(grad)
+        if rec is not None:
+            e[3].record(); e[4].record()
+        with torch.no_grad():
+            real, _, _ = render_batch(xyz, offs, views, RHO, W_IMG, pose=pose, dense=dense, need_winner=False,
+                                      max_item_pts=max_item)
+        if rec is not None:
+            e[5].record(); rec.append(e)
+        return fake, real, x.grad
+
+    h_fake = torch.empty((B, V, 2, W_IMG, W_IMG), dtype=torch.float32).pin_memory()
+    h_real = torch.empty_like(h_fake).pin_memory()
+    h_gxyz = torch.empty_like(h_xyz).pin_memory()
+
+    def step_e2e():
+        """Same step through the public API from HOST buffers: H2D of the step's inputs, D2H of its results."""
+        x = h_xyz.to(dev, non_blocking=True).requires_grad_(True)
+        p = h_pose.to(dev, non_blocking=True)
+        g = h_grad.to(dev, non_blocking=True)
+        fake, _, _ = render_batch(x, offs, views, RHO, W_IMG, dense=dense, need_winner=True, max_item_pts=max_item)
+        fake.backward(g)
+        with torch.no_grad():
+            real, _, _ = render_batch(x.detach(), offs, views, RHO, W_IMG, pose=p, dense=dense, need_winner=False,
+                                      max_item_pts=max_item)
+        h_fake.copy_(fake.detach(), non_blocking=True)
+        h_real.copy_(real, non_blocking=True)
+        h_gxyz.copy_(x.grad, non_blocking=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, rec=None):
+        barrier()
+        e0, e1 = ev(), ev()
+        e0.record()
+        for _ in range(steps):
+            fn(rec) if rec is not None else fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    rec = []
+    ms = timed(step_device, args.steps, rec)
+    clocks = sampler.stop() if rank == 0 else None
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+
+    imgs_step = 24 * B * world
+    value = imgs_step * args.steps / (ms / 1e3)
+    e2e = imgs_step * args.steps / (ms_e2e / 1e3)
+    # per-launch durations of the forward sequence (rank 0, CUDA events on the launching stream)
+    t_fake = float(np.mean([e[0].elapsed_time(e[1]) for e in rec]))
+    t_bwd = float(np.mean([e[2].elapsed_time(e[3]) for e in rec]))
+    t_real = float(np.mean([e[4].elapsed_time(e[5]) for e in rec]))
+    b_fake, b_real, b_bwd = algorithmic_bytes(B)
+    peak, peak_src = peaks()
+    ach = (b_fake + b_real) / ((t_fake + t_real) / 1e3) / 1e9
+    if rank != 0:
+        return
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(B),
+            "gpoints_per_sec": value * N_PTS / 1e9,
+            "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": int(h_xyz.numel() * 4 + h_pose.numel() * 4 + h_grad.numel() * 4),
+                    "d2h_bytes_per_step": int(h_fake.numel() * 4 * 2 + h_gxyz.numel() * 4)},
+            "gpu_launches": args.steps * 7,
+            "kernel": "dense" if dense else "culled",
+            "roofline": {"bound": "hbm", "kernel": "forward render (z-range + splat/max kernels of one forward call)",
+                         "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                         "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": {"fwd_fake": b_fake, "fwd_real": b_real, "bwd": b_bwd},
+                         "ms_per_launch": {"fwd_fake": t_fake, "bwd": t_bwd, "fwd_real": t_real}},
+            "clocks": clocks}
+    if world == 1 and not args.no_cpu:
+        t0 = time.perf_counter()
+        cpu_reference_step(0)                      # warm-up
+        tot, n = 0.0, 0
+        for i in range(1, 7):
+            dt, k, _ = cpu_reference_step(i)
+            tot += dt; n += k
+            if time.perf_counter() - t0 > 30:
+                break
+        line["cpu_baseline"] = {"value": n / tot, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                                "sample": f"{n // 4} x (1 pair n=m=10000, 1 view, fake fwd+bwd + real fwd); "
+                                          "oracle/render_oracle.py = torch-CPU restatement, bit-identical to reference render.py"}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=512, help="pairs per GPU per step")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--dense", action="store_true", help="force the dense exact kernel")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_ours(args, rank, local_rank, world)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

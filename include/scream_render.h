@@ -1,0 +1,115 @@
+/* scream_render.h -- C ABI of libscream_render.so (B200 / sm_100a scene renderer).
+ *
+ * Drop-in boundary for ONE hot path of xujiabo/SCREAM: the scene renderer
+ *   /root/reference/models/render.py:8-73  (class RegistrationRender: __init__, render, forward)
+ * and the autograd backward it implies (no source lines; defined by torch.max / exp / matmul at
+ * render.py:31,42-49,68-69).  The reference has no FFI -- its "operator API" is that nn.Module --
+ * so each entry point below cites the reference lines it replaces; the Python module
+ * scream_b200/render.py binds them through ctypes and keeps the reference's call signature.
+ *
+ * Conventions
+ *   - every function returns 0 on success and a negative SCREAM_E_* code on failure; nothing throws,
+ *     nothing calls exit(); scream_last_error() returns a thread-local message for the last failure.
+ *   - all data pointers are DEVICE pointers unless the name ends in _host.
+ *   - the caller owns every buffer.  The library allocates nothing; scratch space is a caller-provided
+ *     workspace whose size comes from scream_render_workspace_bytes().
+ *   - all work is enqueued on the given stream; no call synchronises the device or the host
+ *     (the *_host convenience entry points are the exception and say so).
+ *   - thread-safe for concurrent calls that use distinct streams and distinct workspaces.
+ *
+ * Layout
+ *   xyz    [total_pts,3] fp32 row-major (12 B per point, the layout of the reference's [n,3] tensors).
+ *   offs   [2B+1] int64 CSR offsets into xyz, in points: item b owns the SOURCE cloud
+ *          [offs[2b], offs[2b+1]) and the TARGET cloud [offs[2b+1], offs[2b+2]).  This is
+ *          torch.cat([src_pred, tgt_pcd]) of render.py:63 for every item of a batch.
+ *   pose   [B,3,4] fp32 [R|t] or NULL.  Applied to the SOURCE cloud only, before the view rotation:
+ *          the caller-side rigid transform of the "real" render, train_3d_match.py:198-199,
+ *          train_kitti.py:193-194 (fl(sgemm-chain) then a separately rounded + t).
+ *   views  [V,3,3] fp32 view rotations = torch.Tensor(Rotation.from_euler('zyx', e).as_matrix()),
+ *          render.py:67 (built on the host by the Python module with the same scipy call).
+ *   imgs   [B,V,2,w,w] fp32: channel 0 = source cloud, 1 = target cloud (render.py:46,49,59).
+ *   winner [B,V,2,w,w] int32: cloud-local index of the arg-max point of every pixel (lowest index on
+ *          ties, 0 for an all-zero pixel -- torch.max(dim=0) semantics), or NULL.
+ *   zrange [B,V,2] fp32: (zmin, zmax) of the rotated depth over BOTH clouds of the item (render.py:30-31).
+ */
+#ifndef SCREAM_RENDER_H_
+#define SCREAM_RENDER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SCREAM_ABI_VERSION 2
+
+/* error codes */
+#define SCREAM_OK            0
+#define SCREAM_E_ARG        -1   /* bad argument (NULL pointer, w % 64 != 0, B/V <= 0, ...) */
+#define SCREAM_E_WORKSPACE  -2   /* workspace too small or NULL */
+#define SCREAM_E_CUDA       -3   /* a CUDA runtime call or launch failed; see scream_last_error() */
+#define SCREAM_E_UNSUPPORTED -4  /* a size beyond what this build handles */
+
+/* flags */
+#define SCREAM_F_RAW        1u   /* imgs = un-normalised max in [0,1] (render.py:59, RegistrationRender.render)
+                                    instead of (img-0.5)/0.5 (render.py:69, RegistrationRender.forward) */
+#define SCREAM_F_DENSE      2u   /* force the dense exact kernel (every point x every pixel); default is the
+                                    culled exact kernel, which returns bit-identical results */
+
+/* opaque CUDA stream handle (cudaStream_t / CUstream) */
+typedef void *scream_stream_t;
+
+int scream_abi_version(void);
+const char *scream_last_error(void);
+
+/* Bytes of scratch the forward/backward calls need for a batch of B items, V views, image side w and
+ * total_pts points in all.  (No reference counterpart: the reference lets torch allocate N x 4096
+ * temporaries, render.py:42.) */
+int scream_render_workspace_bytes(int B, int V, int w, int64_t total_pts, size_t *out_bytes);
+
+/* Forward render of a batch: replaces RegistrationRender.forward / .render, render.py:27-73, for B
+ * independent (source, target) pairs in one launch sequence.
+ *   rho: the reference's rho (render.py:10,43); the weight is exp(-d2/2 * (float)(rho*rho)).
+ *   w:   image side, w % 64 == 0 (render.py:33-34,55).
+ *   winner may be NULL (inference / "real" render); zrange may be NULL.
+ *   max_item_pts: an upper bound of n+m over the items (sizes the z-range grid without reading offs on
+ *   the host); 0 = unknown, total_pts is used.
+ */
+int scream_render_forward(const float *xyz, const int64_t *offs, int64_t total_pts, int64_t max_item_pts,
+                          const float *pose, const float *views,
+                          int B, int V, int w, double rho, unsigned flags,
+                          float *imgs, int32_t *winner, float *zrange,
+                          void *ws, size_t ws_bytes, scream_stream_t stream);
+
+/* Backward: replaces the autograd graph of render.py:27-73.  Scatters
+ * grad_imgs [B,V,2,w,w] through the saved winner map to grad_xyz [total_pts,3] (overwritten: the
+ * callee zero-fills it first).  With a pose, the source gradient is w.r.t. the PRE-pose coordinates.
+ * flags must be the forward call's (SCREAM_F_RAW changes the 1/0.5 output scale). */
+int scream_render_backward(const float *xyz, const int64_t *offs, int64_t total_pts, int64_t max_item_pts,
+                           const float *pose, const float *views,
+                           int B, int V, int w, double rho, unsigned flags,
+                           const float *grad_imgs, const int32_t *winner, const float *zrange,
+                           float *grad_xyz,
+                           void *ws, size_t ws_bytes, scream_stream_t stream);
+
+/* Transform stage only (testing / parity of the "index path"): rotated coordinates [B? no: total_pts
+ * per view] rotated [V,total_pts,3], pv [V,total_pts] (render.py:31), zrange [B,V,2].  Any output may
+ * be NULL.  Bit-exact against the reference for clouds of >= 16 points (sgemm op order). */
+int scream_render_transform(const float *xyz, const int64_t *offs, int64_t total_pts, int64_t max_item_pts,
+                            const float *pose, const float *views, int B, int V,
+                            float *rotated, float *pv, float *zrange,
+                            void *ws, size_t ws_bytes, scream_stream_t stream);
+
+/* Host-buffer convenience entry point (end-to-end path: H2D copies, forward, D2H copies, one stream
+ * synchronise).  All pointers are HOST pointers; device staging is allocated per call and freed.
+ * device < 0 uses the current device. */
+int scream_render_forward_host(const float *xyz_host, const int64_t *offs_host,
+                               const float *pose_host, const float *views_host,
+                               int B, int V, int w, double rho, unsigned flags,
+                               float *imgs_host, int32_t *winner_host, float *zrange_host, int device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SCREAM_RENDER_H_ */

@@ -1,0 +1,200 @@
+// scream_render.cu -- C ABI of libscream_render.so (see include/scream_render.h).
+// Build: scream_b200/csrc/build.py  (nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=false)
+#include "../../include/scream_render.h"
+#include "common.cuh"
+#include "transform.cuh"
+#include "forward_dense.cuh"
+#include "backward.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+using namespace scream;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap; va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                         \
+    do { cudaError_t e_ = (expr);                                                              \
+         if (e_ != cudaSuccess) return fail(SCREAM_E_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); } while (0)
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct WsLayout { size_t zenc_off, total; };
+
+WsLayout ws_layout(int B, int V, int /*w*/, int64_t /*total_pts*/) {
+    WsLayout L;
+    L.zenc_off = 0;
+    L.total = align_up((size_t)B * V * 2 * sizeof(unsigned), 256);
+    return L;
+}
+
+int check_common(const void* xyz, const void* offs, const void* views, int B, int V, int w, double rho,
+                 int64_t total_pts) {
+    if (!xyz || !offs || !views) return fail(SCREAM_E_ARG, "xyz/offs/views must not be NULL");
+    if (B <= 0 || V <= 0) return fail(SCREAM_E_ARG, "B and V must be positive (B=%d V=%d)", B, V);
+    if (w < 64 || w % 64 != 0) return fail(SCREAM_E_ARG, "w must be a positive multiple of 64 (render.py:33-34), got %d", w);
+    if (w > 4096) return fail(SCREAM_E_UNSUPPORTED, "w=%d exceeds 4096", w);
+    if (!(rho == rho) || rho == 0.0) return fail(SCREAM_E_ARG, "rho must be a non-zero number");
+    if (total_pts <= 0) return fail(SCREAM_E_ARG, "total_pts must be positive");
+    if ((long long)B * V * 2 * ((long long)w * w / 256) > 2147483647LL)
+        return fail(SCREAM_E_UNSUPPORTED, "B*V*w*w too large for one launch");
+    return 0;
+}
+
+// stage 1: z range of every (item, view) into ws (encoded)
+int launch_zrange(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts, const float* pose,
+                  const float* views, int B, int V, unsigned* zenc, cudaStream_t st) {
+    const int pairs = B * V;
+    zrange_init_kernel<<<(pairs + 255) / 256, 256, 0, st>>>(zenc, pairs);
+    if (max_item_pts <= 0 || max_item_pts > total_pts) max_item_pts = total_pts;
+    const int64_t chunks = (max_item_pts + ZR_PTS_PER_CTA - 1) / ZR_PTS_PER_CTA;
+    if (chunks > 2147483647LL || B > 65535) return fail(SCREAM_E_UNSUPPORTED, "batch too large for the z-range grid");
+    zrange_kernel<<<dim3((unsigned)chunks, (unsigned)B), ZR_THREADS, 0, st>>>(xyz, offs, pose, views, V, zenc);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int scream_abi_version(void) { return SCREAM_ABI_VERSION; }
+const char* scream_last_error(void) { return g_err; }
+
+int scream_render_workspace_bytes(int B, int V, int w, int64_t total_pts, size_t* out_bytes) {
+    if (!out_bytes) return fail(SCREAM_E_ARG, "out_bytes is NULL");
+    if (B <= 0 || V <= 0 || w <= 0 || total_pts < 0) return fail(SCREAM_E_ARG, "bad sizes");
+    *out_bytes = ws_layout(B, V, w, total_pts).total;
+    return 0;
+}
+
+int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
+                          const float* pose, const float* views,
+                          int B, int V, int w, double rho, unsigned flags,
+                          float* imgs, int32_t* winner, float* zrange,
+                          void* ws, size_t ws_bytes, scream_stream_t stream)
+{
+    if (int rc = check_common(xyz, offs, views, B, V, w, rho, total_pts)) return rc;
+    if (!imgs) return fail(SCREAM_E_ARG, "imgs is NULL");
+    const WsLayout L = ws_layout(B, V, w, total_pts);
+    if (!ws || ws_bytes < L.total) return fail(SCREAM_E_WORKSPACE, "workspace needs %zu bytes, got %zu", L.total, ws_bytes);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned* zenc = reinterpret_cast<unsigned*>((char*)ws + L.zenc_off);
+    if (int rc = launch_zrange(xyz, offs, total_pts, max_item_pts, pose, views, B, V, zenc, st)) return rc;
+
+    FwdParams P;
+    P.xyz = xyz; P.offs = offs; P.pose = pose; P.views = views; P.zenc = zenc;
+    P.B = B; P.V = V; P.w = w;
+    const float rho2 = (float)(rho * rho);           // tensor * python scalar -> scalar cast to fp32
+    P.negk = -rho2 * 0.5f; P.inv_negk = 1.0f / P.negk;
+    P.flags = flags; P.imgs = imgs; P.winner = winner; P.zrange = zrange;
+    const long long grid = (long long)B * V * 2 * (w * w / FD_TILE);
+    forward_dense_kernel<<<(unsigned)grid, FD_THREADS, 0, st>>>(P);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_render_backward(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t /*max_item_pts*/,
+                           const float* pose, const float* views,
+                           int B, int V, int w, double rho, unsigned flags,
+                           const float* grad_imgs, const int32_t* winner, const float* zrange,
+                           float* grad_xyz, void* /*ws*/, size_t /*ws_bytes*/, scream_stream_t stream)
+{
+    if (int rc = check_common(xyz, offs, views, B, V, w, rho, total_pts)) return rc;
+    if (!grad_imgs || !winner || !zrange || !grad_xyz) return fail(SCREAM_E_ARG, "grad_imgs/winner/zrange/grad_xyz must not be NULL");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaMemsetAsync(grad_xyz, 0, (size_t)total_pts * 3 * sizeof(float), st));
+    BwdParams P;
+    P.xyz = xyz; P.offs = offs; P.pose = pose; P.views = views;
+    P.B = B; P.V = V; P.w = w;
+    P.negk = -(float)(rho * rho) * 0.5f;
+    P.flags = flags; P.grad_imgs = grad_imgs; P.winner = winner; P.zrange = zrange; P.grad_xyz = grad_xyz;
+    const long long grid = (long long)B * V * 2 * (w * w / BW_THREADS);
+    backward_scatter_kernel<<<(unsigned)grid, BW_THREADS, 0, st>>>(P);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_render_transform(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
+                            const float* pose, const float* views, int B, int V,
+                            float* rotated, float* pv, float* zrange,
+                            void* ws, size_t ws_bytes, scream_stream_t stream)
+{
+    if (int rc = check_common(xyz, offs, views, B, V, 64, 1.0, total_pts)) return rc;
+    const WsLayout L = ws_layout(B, V, 64, total_pts);
+    if (!ws || ws_bytes < L.total) return fail(SCREAM_E_WORKSPACE, "workspace needs %zu bytes, got %zu", L.total, ws_bytes);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned* zenc = reinterpret_cast<unsigned*>((char*)ws + L.zenc_off);
+    if (int rc = launch_zrange(xyz, offs, total_pts, max_item_pts, pose, views, B, V, zenc, st)) return rc;
+    if (zrange) zrange_decode_kernel<<<(B * V * 2 + 255) / 256, 256, 0, st>>>(zenc, zrange, B * V * 2);
+    if (rotated || pv) {
+        const int64_t mi = (max_item_pts <= 0 || max_item_pts > total_pts) ? total_pts : max_item_pts;
+        const int64_t chunks = (mi + 255) / 256;
+        transform_dump_kernel<<<dim3((unsigned)chunks, (unsigned)B), 256, 0, st>>>(
+            xyz, offs, total_pts, pose, views, V, zenc, rotated, pv);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_render_forward_host(const float* xyz_host, const int64_t* offs_host,
+                               const float* pose_host, const float* views_host,
+                               int B, int V, int w, double rho, unsigned flags,
+                               float* imgs_host, int32_t* winner_host, float* zrange_host, int device)
+{
+    if (!xyz_host || !offs_host || !views_host || !imgs_host) return fail(SCREAM_E_ARG, "NULL host pointer");
+    if (B <= 0 || V <= 0) return fail(SCREAM_E_ARG, "B and V must be positive");
+    if (device >= 0) CUDA_TRY(cudaSetDevice(device));
+    const int64_t total = offs_host[2 * B];
+    int64_t max_item = 0;
+    for (int b = 0; b < B; ++b) max_item = offs_host[2 * b + 2] - offs_host[2 * b] > max_item ? offs_host[2 * b + 2] - offs_host[2 * b] : max_item;
+    if (int rc = check_common(xyz_host, offs_host, views_host, B, V, w, rho, total)) return rc;
+    const size_t n_img = (size_t)B * V * 2 * w * w;
+    size_t ws_bytes = 0;
+    scream_render_workspace_bytes(B, V, w, total, &ws_bytes);
+    // one device slab: xyz | offs | pose | views | imgs | winner | zrange | ws
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+    const size_t o_xyz = take((size_t)total * 12), o_offs = take((size_t)(2 * B + 1) * 8),
+                 o_pose = take((size_t)B * 48), o_views = take((size_t)V * 36), o_imgs = take(n_img * 4),
+                 o_win = take(n_img * 4), o_zr = take((size_t)B * V * 8), o_ws = take(ws_bytes);
+    char* d = nullptr;
+    cudaStream_t st;
+    CUDA_TRY(cudaMalloc(&d, off));
+    cudaError_t e = cudaStreamCreate(&st);
+    if (e != cudaSuccess) { cudaFree(d); return fail(SCREAM_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+    int rc = 0;
+    auto run = [&]() -> int {
+        CUDA_TRY(cudaMemcpyAsync(d + o_xyz, xyz_host, (size_t)total * 12, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d + o_offs, offs_host, (size_t)(2 * B + 1) * 8, cudaMemcpyHostToDevice, st));
+        if (pose_host) CUDA_TRY(cudaMemcpyAsync(d + o_pose, pose_host, (size_t)B * 48, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(d + o_views, views_host, (size_t)V * 36, cudaMemcpyHostToDevice, st));
+        int r = scream_render_forward((const float*)(d + o_xyz), (const int64_t*)(d + o_offs), total, max_item,
+                                      pose_host ? (const float*)(d + o_pose) : nullptr, (const float*)(d + o_views),
+                                      B, V, w, rho, flags, (float*)(d + o_imgs),
+                                      winner_host ? (int32_t*)(d + o_win) : nullptr, (float*)(d + o_zr),
+                                      d + o_ws, ws_bytes, (scream_stream_t)st);
+        if (r) return r;
+        CUDA_TRY(cudaMemcpyAsync(imgs_host, d + o_imgs, n_img * 4, cudaMemcpyDeviceToHost, st));
+        if (winner_host) CUDA_TRY(cudaMemcpyAsync(winner_host, d + o_win, n_img * 4, cudaMemcpyDeviceToHost, st));
+        if (zrange_host) CUDA_TRY(cudaMemcpyAsync(zrange_host, d + o_zr, (size_t)B * V * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        return 0;
+    };
+    rc = run();
+    cudaStreamDestroy(st);
+    cudaFree(d);
+    return rc;
+}
+
+}  // extern "C"

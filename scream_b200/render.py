@@ -1,0 +1,223 @@
+"""Drop-in scene renderer: the reference's `RegistrationRender` (models/render.py:8-73) on B200.
+
+Same constructor, same mutable attributes (`rho`, `w`, `pix_xy`, `eulers` -- read at CALL time, because
+train_kitti.py:47-48 mutates them after construction), same `forward(src_pred, tgt_pcd) -> [V,2,w,w]`
+and `render(x, src_n) -> [2,w,w]`, differentiable w.r.t. both clouds, no parameters and no buffers
+(`state_dict() == {}`).  Behind it: torch custom ops `scream::render_fwd` / `scream::render_bwd` that
+call the C ABI of libscream_render.so (include/scream_render.h) on the current CUDA stream.
+There is no CPU path: CPU tensors raise.
+
+`render_batch` is the batched entry point (B pairs, CSR offsets, optional per-item GT pose): one launch
+sequence for a whole training batch, which the reference cannot do (pointnet.py:39-40 asserts batch 1).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+from scipy.spatial.transform import Rotation
+from torch import nn
+
+from . import _lib
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _require_cuda(*ts: torch.Tensor) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("scream_b200 renders on CUDA only (no CPU fallback): got a %s tensor" % t.device)
+
+
+def _stream_ptr(dev: torch.device) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+# ----------------------------------------------------------------------------------------------
+# custom ops
+# ----------------------------------------------------------------------------------------------
+@torch.library.custom_op("scream::render_fwd", mutates_args=())
+def render_fwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tensor], views: torch.Tensor,
+               w: int, rho: float, flags: int, want_winner: bool, max_item_pts: int
+               ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    _require_cuda(xyz, offs, pose, views)
+    lib = _lib.load()
+    assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.dim() == 2 and xyz.shape[1] == 3
+    assert offs.dtype == torch.int64 and offs.is_contiguous() and offs.numel() % 2 == 1
+    assert views.dtype == torch.float32 and views.is_contiguous() and views.shape[1:] == (3, 3)
+    B, V, total = (offs.numel() - 1) // 2, views.shape[0], xyz.shape[0]
+    if pose is not None:
+        assert pose.dtype == torch.float32 and pose.is_contiguous() and pose.shape == (B, 3, 4)
+    dev = xyz.device
+    with torch.cuda.device(dev):
+        imgs = torch.empty((B, V, 2, w, w), dtype=torch.float32, device=dev)
+        winner = torch.empty((B, V, 2, w, w) if want_winner else (0,), dtype=torch.int32, device=dev)
+        zrange = torch.empty((B, V, 2), dtype=torch.float32, device=dev)
+        nws = _lib.workspace_bytes(B, V, w, total)
+        ws = torch.empty((nws,), dtype=torch.uint8, device=dev)
+        rc = lib.scream_render_forward(_ptr(xyz), _ptr(offs), total, max_item_pts, _ptr(pose), _ptr(views),
+                                       B, V, w, float(rho), flags, _ptr(imgs),
+                                       _ptr(winner) if want_winner else None, _ptr(zrange),
+                                       _ptr(ws), nws, _stream_ptr(dev))
+    _lib.check(rc, "scream_render_forward")
+    return imgs, winner, zrange
+
+
+@render_fwd.register_fake
+def _(xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts):
+    B, V = (offs.numel() - 1) // 2, views.shape[0]
+    return (xyz.new_empty((B, V, 2, w, w)),
+            xyz.new_empty((B, V, 2, w, w) if want_winner else (0,), dtype=torch.int32),
+            xyz.new_empty((B, V, 2)))
+
+
+@torch.library.custom_op("scream::render_bwd", mutates_args=())
+def render_bwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tensor], views: torch.Tensor,
+               w: int, rho: float, flags: int, grad_imgs: torch.Tensor, winner: torch.Tensor,
+               zrange: torch.Tensor, max_item_pts: int) -> torch.Tensor:
+    _require_cuda(xyz, offs, pose, views, grad_imgs, winner, zrange)
+    lib = _lib.load()
+    B, V, total = (offs.numel() - 1) // 2, views.shape[0], xyz.shape[0]
+    assert winner.numel() == B * V * 2 * w * w, "forward was run without a winner map"
+    grad_imgs = grad_imgs.contiguous().float()
+    dev = xyz.device
+    with torch.cuda.device(dev):
+        grad_xyz = torch.empty_like(xyz)
+        rc = lib.scream_render_backward(_ptr(xyz), _ptr(offs), total, max_item_pts, _ptr(pose), _ptr(views),
+                                        B, V, w, float(rho), flags, _ptr(grad_imgs), _ptr(winner),
+                                        _ptr(zrange), _ptr(grad_xyz), None, 0, _stream_ptr(dev))
+    _lib.check(rc, "scream_render_backward")
+    return grad_xyz
+
+
+@render_bwd.register_fake
+def _(xyz, offs, pose, views, w, rho, flags, grad_imgs, winner, zrange, max_item_pts):
+    return torch.empty_like(xyz)
+
+
+def _setup_ctx(ctx, inputs, output):
+    xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts = inputs
+    _, winner, zrange = output
+    if pose is not None:
+        ctx.save_for_backward(xyz, offs, pose, views, winner, zrange)
+    else:
+        ctx.save_for_backward(xyz, offs, views, winner, zrange)
+    ctx.has_pose = pose is not None
+    ctx.cfg = (w, rho, flags, max_item_pts)
+
+
+def _backward(ctx, g_imgs, g_winner, g_zrange):
+    if ctx.has_pose:
+        xyz, offs, pose, views, winner, zrange = ctx.saved_tensors
+    else:
+        xyz, offs, views, winner, zrange = ctx.saved_tensors
+        pose = None
+    w, rho, flags, max_item_pts = ctx.cfg
+    g = torch.ops.scream.render_bwd(xyz, offs, pose, views, w, rho, flags, g_imgs, winner, zrange, max_item_pts)
+    return g, None, None, None, None, None, None, None, None
+
+
+render_fwd.register_autograd(_backward, setup_context=_setup_ctx)
+
+
+# ----------------------------------------------------------------------------------------------
+# host-side helpers (a1 / a5 of SURVEY.md section 8)
+# ----------------------------------------------------------------------------------------------
+def view_matrices(eulers: Sequence[Sequence[float]]) -> torch.Tensor:
+    """[V,3,3] fp32 on the host, the reference's own conversion (render.py:67)."""
+    return torch.stack([torch.Tensor(Rotation.from_euler("zyx", e).as_matrix()) for e in eulers], dim=0)
+
+
+def make_offsets(sizes: Sequence[Tuple[int, int]]) -> torch.Tensor:
+    """CSR offsets [2B+1] int64 (host) for a list of (n_src, n_tgt)."""
+    flat = np.asarray(sizes, dtype=np.int64).reshape(-1)
+    return torch.from_numpy(np.concatenate([[0], np.cumsum(flat)]).astype(np.int64))
+
+
+def render_batch(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho, w: int,
+                 pose: Optional[torch.Tensor] = None, raw: bool = False, dense: bool = False,
+                 need_winner: Optional[bool] = None, max_item_pts: int = 0):
+    """Render B pairs at once.  xyz [total,3] fp32 cuda, offs [2B+1] int64 cuda, views [V,3,3] fp32 cuda,
+    pose [B,3,4] or None.  Returns (imgs [B,V,2,w,w], winner int32 or empty, zrange [B,V,2])."""
+    if w < 64 or w % 64:
+        raise ValueError("w must be a positive multiple of 64 (render.py:33-34,55)")
+    if need_winner is None:
+        need_winner = torch.is_grad_enabled() and xyz.requires_grad
+    flags = (_lib.F_RAW if raw else 0) | (_lib.F_DENSE if dense else 0)
+    return torch.ops.scream.render_fwd(xyz, offs, pose, views, int(w), float(rho), int(flags),
+                                       bool(need_winner), int(max_item_pts))
+
+
+class RegistrationRender(nn.Module):
+    """B200 drop-in for models/render.py:8-73."""
+
+    def __init__(self, rho, w, view="muti", device="cuda:0"):
+        super().__init__()
+        self.rho, self.w = rho, w
+        dev = torch.device(device)           # the reference hard-codes cuda:0 (render.py:12)
+        i, j = np.arange(w * w) // w, np.arange(w * w) % w
+        pix_xy = torch.from_numpy(np.concatenate([j.reshape(-1, 1), i.reshape(-1, 1)], axis=1)).float()
+        # kept for API compatibility (render.py:15-16); the kernels recompute the centres exactly
+        self.pix_xy = ((pix_xy - w // 2 + 0.5) / (w // 2)).to(dev) if dev.type == "cuda" and torch.cuda.is_available() \
+            else (pix_xy - w // 2 + 0.5) / (w // 2)
+        if view == "muti":
+            self.eulers = [np.array([0, 0, 0]), np.array([0, np.pi / 2, 0]), np.array([0, np.pi, 0]),
+                           np.array([0, np.pi * 3 / 2, 0]),
+                           np.array([0, 0, np.pi / 2]), np.array([0, 0, np.pi * 3 / 2])]
+        else:
+            self.eulers = [np.array([0, 0, 0])]
+        self._cache = {}
+
+    # -- small device-side caches (views by euler content, offsets by sizes) -------------------
+    def _views(self, dev) -> torch.Tensor:
+        key = ("v", str(dev), np.asarray(self.eulers, dtype=np.float64).tobytes())
+        hit = self._cache.get(key)
+        if hit is None:
+            hit = view_matrices(self.eulers).to(dev)
+            self._cache = {k: v for k, v in self._cache.items() if k[0] != "v" or k[1] != str(dev)}
+            self._cache[key] = hit
+        return hit
+
+    def _offsets(self, n: int, m: int, dev) -> torch.Tensor:
+        key = ("o", str(dev), n, m)
+        hit = self._cache.get(key)
+        if hit is None:
+            if len(self._cache) > 64:
+                self._cache.clear()
+            hit = torch.tensor([0, n, n + m], dtype=torch.int64).to(dev)
+            self._cache[key] = hit
+        return hit
+
+    def _call(self, src, tgt, views, raw):
+        if src.dim() != 2 or tgt.dim() != 2 or src.shape[1] != 3 or tgt.shape[1] != 3:
+            raise ValueError("expected [n,3] and [m,3] point tensors")
+        if src.shape[0] == 0 or tgt.shape[0] == 0:
+            raise RuntimeError("max(): cannot reduce over an empty cloud (render.py:46,49)")
+        xyz = torch.cat([src.float(), tgt.float()], dim=0)         # render.py:63
+        n, m = src.shape[0], tgt.shape[0]
+        imgs, _, _ = render_batch(xyz, self._offsets(n, m, xyz.device), views, self.rho, self.w,
+                                  raw=raw, max_item_pts=n + m)
+        return imgs[0]
+
+    def render(self, x, src_n):
+        """[2,w,w] un-normalised image of already-rotated points x [N,3] (render.py:27-59)."""
+        _require_cuda(x)
+        eye = self._cache.get(("eye", str(x.device)))
+        if eye is None:
+            eye = torch.eye(3, dtype=torch.float32, device=x.device).unsqueeze(0).contiguous()
+            self._cache[("eye", str(x.device))] = eye
+        return self._call(x[:src_n], x[src_n:], eye, raw=True)[0]
+
+    def forward(self, src_pred, tgt_pcd):
+        """[V,2,w,w] fp32 in [-1,1) (render.py:61-73)."""
+        _require_cuda(src_pred, tgt_pcd)
+        return self._call(src_pred, tgt_pcd, self._views(src_pred.device), raw=False)
+
+    # no parameters / buffers: keep checkpoints of the enclosing model loadable
+    def __getstate__(self):
+        st = dict(self.__dict__)
+        st["_cache"] = {}
+        return st

@@ -1,0 +1,45 @@
+import ctypes
+import glob
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+def golden_names():
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+
+
+def load_golden(name):
+    with np.load(os.path.join(GOLDEN_DIR, name + ".npz")) as z:
+        return {k: z[k] for k in z.files}
+
+
+@pytest.fixture(scope="session")
+def c_oracle():
+    """The plain-C oracle (oracle/render_oracle.c), built on demand.  Test infrastructure only."""
+    so = os.path.join(ROOT, "oracle", "libscream_oracle.so")
+    src = os.path.join(ROOT, "oracle", "render_oracle.c")
+    if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
+    lib = ctypes.CDLL(so)
+    F, I, L = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64
+    lib.scream_oracle_forward.argtypes = [F, L, F, L, F, F, I, I, ctypes.c_double, F, F, F, F, F]
+    lib.scream_oracle_forward.restype = I
+    lib.scream_oracle_transform.argtypes = [F, L, F, L, F, F, I, F, F, F]
+    lib.scream_oracle_transform.restype = I
+    lib.scream_oracle_backward.argtypes = [F, L, F, L, F, F, I, I, ctypes.c_double, F, F, F, F, F]
+    lib.scream_oracle_backward.restype = I
+    return lib

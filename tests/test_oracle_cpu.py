@@ -1,0 +1,131 @@
+"""CPU suite: the oracles against the golden vectors frozen from the EXECUTED reference
+(oracle/make_golden.py), and the known-answer micro cases of SURVEY.md section 4."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_names, load_golden
+from oracle import render_oracle as orc
+from oracle_utils import c_backward, c_forward, c_transform
+
+NAMES = golden_names()
+
+
+def test_golden_present():
+    assert len(NAMES) >= 7
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_torch_oracle_matches_golden(name):
+    g = load_golden(name)
+    src, tgt = torch.from_numpy(g["src"]), torch.from_numpy(g["tgt"])
+    pose = torch.from_numpy(g["pose"]) if "pose" in g else None
+    r = orc.forward_instrumented(src, tgt, float(g["rho"]), int(g["w"]), torch.from_numpy(g["views"]), pose=pose)
+    assert np.array_equal(r["imgs"].numpy(), g["imgs"])          # bit-exact vs the executed reference
+    assert np.array_equal(r["idx"].numpy(), g["idx"])
+    assert np.array_equal(r["zrange"].numpy(), g["zrange"])
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_view_matrices_match_golden(name):
+    g = load_golden(name)
+    assert np.array_equal(orc.view_matrices(list(g["eulers"])).numpy(), g["views"])
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_c_oracle_matches_golden(name, c_oracle):
+    g = load_golden(name)
+    w, rho = int(g["w"]), float(g["rho"])
+    r = c_forward(c_oracle, g["src"], g["tgt"], g["views"], rho, w, g.get("pose"))
+    assert np.array_equal(r["zrange"], g["zrange"])
+    want = g["val"].astype(np.float64)
+    err = np.abs(r["val"].astype(np.float64) - want)
+    assert (err <= 1e-6 * want + 1e-37).all()
+    bad = r["idx"] != g["idx"]
+    # winners may differ only at near-ties of the reference (top-2 gap within a few ulp)
+    gap = (g["val"] - g["second"])[bad]
+    assert (gap <= 4e-6 * g["val"][bad] + 1e-37).all(), f"{bad.sum()} winner mismatches beyond near-ties"
+
+
+@pytest.mark.parametrize("name", ["cfg2_shell_real", "cfg3_kitti_bev"])
+def test_c_transform_bit_exact_vs_torch(name, c_oracle):
+    """rotation / pose / zrange / pv: the scalar restatement equals ATen bit for bit (N >= 16)."""
+    g = load_golden(name)
+    src, tgt = torch.from_numpy(g["src"]), torch.from_numpy(g["tgt"])
+    views = torch.from_numpy(g["views"])
+    if "pose" in g:
+        p = torch.from_numpy(g["pose"])
+        src = orc.apply_pose(p[:, :3].contiguous(), p[:, 3:4].contiguous(), src)
+    pts = torch.cat([src, tgt], 0)
+    rot, pv, zr = c_transform(c_oracle, g["src"], g["tgt"], g["views"], g.get("pose"))
+    for v in range(views.shape[0]):
+        x = orc.rotate(views[v], pts)
+        assert np.array_equal(x.numpy(), rot[v])
+        pvt, zmin, zmax = orc.depth_weights(x)
+        assert np.array_equal(pvt.numpy(), pv[v])
+        assert zr[v, 0] == np.float32(zmin) and zr[v, 1] == np.float32(zmax)
+
+
+@pytest.mark.parametrize("name", [n for n in NAMES if "grad_out" in load_golden(n)])
+def test_c_backward_matches_reference_autograd(name, c_oracle):
+    g = load_golden(name)
+    gs, gt = c_backward(c_oracle, g["src"], g["tgt"], g["views"], float(g["rho"]), int(g["w"]),
+                        g["grad_out"], g["idx"], g["zrange"], g.get("pose"))
+    scale = max(np.abs(g["grad_src"]).max(), np.abs(g["grad_tgt"]).max())
+    assert np.abs(gs - g["grad_src"]).max() <= 1e-5 * scale
+    assert np.abs(gt - g["grad_tgt"]).max() <= 1e-5 * scale
+
+
+# ---- known-answer micro cases (hand-computable) ----------------------------------------------
+def _pad(points, n=16, far=(5.0, 5.0, 0.0)):
+    """N >= 16 keeps the sgemm op order; padding points are far outside the image."""
+    pts = list(points) + [far] * (n - len(points))
+    return np.asarray(pts, dtype=np.float32)
+
+
+def test_point_on_pixel_centre_gives_pv(c_oracle):
+    w, half = 64, 32
+    cx = (10 - half + 0.5) / half
+    cy = (20 - half + 0.5) / half
+    src = _pad([(cx, cy, 0.25), (0.9, 0.9, 1.0), (-0.9, -0.9, -1.0)])
+    tgt = _pad([(0.0, 0.0, 0.0)])
+    eye = np.eye(3, dtype=np.float32)[None]
+    r = c_forward(c_oracle, src, tgt, eye, 24, w)
+    pv = np.float32(1) - (np.float32(0.25) - np.float32(-1)) / np.float32(2)
+    assert r["val"][0, 0, 20, 10] == pv and r["idx"][0, 0, 20, 10] == 0
+    t = orc.forward_instrumented(torch.from_numpy(src), torch.from_numpy(tgt), 24, w, torch.from_numpy(eye))
+    assert t["val"][0, 0, 20, 10].item() == pv
+
+
+def test_tie_goes_to_lower_index_and_far_pixels_are_zero(c_oracle):
+    w, half = 64, 32
+    cx = (30 - half + 0.5) / half
+    cy = (31 - half + 0.5) / half
+    d = 0.01
+    src = _pad([(cx - d, cy, 0.0), (cx + d, cy, 0.0), (0.0, -0.95, 1.0), (0.0, 0.95, -1.0)])
+    tgt = _pad([(0.5, 0.5, 0.5)])
+    eye = np.eye(3, dtype=np.float32)[None]
+    for r in (c_forward(c_oracle, src, tgt, eye, 24, w),
+              {k: v.numpy() for k, v in orc.forward_instrumented(torch.from_numpy(src), torch.from_numpy(tgt), 24, w,
+                                                                  torch.from_numpy(eye)).items()}):
+        assert r["idx"][0, 0, 31, 30] == 0                  # equidistant, equal z -> lower index
+        assert r["val"][0, 0, 0, 0] == 0 and r["idx"][0, 0, 0, 0] == 0   # beyond sqrt(208)/rho from everything
+        assert r["imgs"][0, 0, 0, 0] == -1.0
+
+
+def test_farthest_point_has_zero_weight(c_oracle):
+    src = _pad([(0.0, 0.0, 1.0), (0.3, 0.3, -1.0)], far=(0.3, 0.3, -1.0))
+    tgt = _pad([(0.1, 0.1, 0.0)], far=(0.1, 0.1, 0.0))
+    _, pv, zr = c_transform(c_oracle, src, tgt, np.eye(3, dtype=np.float32)[None])
+    assert pv[0, 0] == 0.0 and pv[0, 1] == 1.0 and zr[0, 0] == -1 and zr[0, 1] == 1
+
+
+def test_views_are_independent_and_w128_is_row_blocks():
+    """V views = V single-view calls; a w=128 render equals its four 4096-pixel chunks (render.py:33-41)."""
+    g = load_golden("cfg4_opengg_w128")
+    src, tgt = torch.from_numpy(g["src"][:400]), torch.from_numpy(g["tgt"])
+    six = orc.canonical_eulers("muti")
+    full = orc.forward_dense(src, tgt, 36, 128, six)
+    for v in (0, 3):
+        one = orc.forward_dense(src, tgt, 36, 128, [six[v]])
+        assert torch.equal(full[v], one[0])

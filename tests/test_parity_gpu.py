@@ -1,0 +1,180 @@
+"""GPU parity suite (-m gpu): the CUDA path, called through the C ABI / the drop-in module, against the
+oracle (golden vectors frozen from the executed reference + the C oracle on fresh seeded inputs)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_names, load_golden
+from oracle_utils import c_backward, c_forward, c_transform, check_images
+from scream_b200 import _lib, synth
+from scream_b200.render import RegistrationRender, make_offsets, render_batch, view_matrices
+
+pytestmark = pytest.mark.gpu
+NAMES = golden_names()
+DEV = "cuda:0"
+
+
+def gpu_forward(src, tgt, views, rho, w, pose=None, dense=False, winner=True):
+    xyz = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV)
+    offs = make_offsets([(len(src), len(tgt))]).to(DEV)
+    p = None if pose is None else torch.from_numpy(np.ascontiguousarray(pose))[None].contiguous().to(DEV)
+    v = torch.from_numpy(np.ascontiguousarray(views)).to(DEV)
+    val, idx, zr = render_batch(xyz, offs, v, rho, w, pose=p, raw=True, dense=dense, need_winner=winner)
+    imgs, _, _ = render_batch(xyz, offs, v, rho, w, pose=p, raw=False, dense=dense, need_winner=False)
+    return dict(val=val[0].cpu().numpy(), idx=idx[0].cpu().numpy() if winner else None,
+                zrange=zr[0].cpu().numpy(), imgs=imgs[0].cpu().numpy())
+
+
+def oracle_pair_value(c_oracle, src, tgt, views, rho, w, pose, idx_map):
+    """Oracle value of the (pixel, point) pairs named by a winner map (for near-tie adjudication)."""
+    rot, pv, _ = c_transform(c_oracle, src, tgt, views, pose)
+    n = len(src)
+    half = w // 2
+    cen = ((np.arange(w, dtype=np.float32) - np.float32(half)) + np.float32(0.5)) / np.float32(half)
+
+    def f(sel):
+        out = []
+        for v, c, i, j in zip(*np.nonzero(sel)):
+            k = int(idx_map[v, c, i, j]) + (n if c else 0)
+            dx = np.float32(rot[v, k, 0] - cen[j]); dy = np.float32(rot[v, k, 1] - cen[i])
+            d2 = np.float32(np.float32(dx * dx) + np.float32(dy * dy))
+            a = np.float32(np.float32(-d2 / np.float32(2)) * np.float32(rho * rho))
+            out.append(np.float32(pv[v, k] * np.float32(np.exp(np.float64(a)))))
+        return np.asarray(out, dtype=np.float32)
+    return f
+
+
+@pytest.mark.parametrize("dense", [True, False])
+@pytest.mark.parametrize("name", NAMES)
+def test_forward_matches_golden(name, dense, c_oracle):
+    g = load_golden(name)
+    w, rho = int(g["w"]), float(g["rho"])
+    r = gpu_forward(g["src"], g["tgt"], g["views"], rho, w, g.get("pose"), dense=dense)
+    assert np.array_equal(r["zrange"], g["zrange"])                       # bit-exact z range
+    pvf = oracle_pair_value(c_oracle, g["src"], g["tgt"], g["views"], rho, w, g.get("pose"), r["idx"])
+    check_images(r["val"], r["idx"], g["val"], g["idx"], g["second"], pvf)
+    assert np.abs(r["imgs"] - g["imgs"]).max() <= 2e-6                    # normalised output, abs
+
+
+@pytest.mark.parametrize("name", ["cfg2_shell_real", "cfg3_kitti_bev", "cfg4_opengg_w64"])
+def test_transform_stage_bit_exact(name, c_oracle):
+    g = load_golden(name)
+    lib = _lib.load()
+    src, tgt = g["src"], g["tgt"]
+    N, V = len(src) + len(tgt), g["views"].shape[0]
+    xyz = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV)
+    offs = make_offsets([(len(src), len(tgt))]).to(DEV)
+    views = torch.from_numpy(g["views"]).to(DEV)
+    pose = torch.from_numpy(g["pose"])[None].contiguous().to(DEV) if "pose" in g else None
+    rot = torch.empty((V, N, 3), device=DEV); pv = torch.empty((V, N), device=DEV); zr = torch.empty((1, V, 2), device=DEV)
+    nws = _lib.workspace_bytes(1, V, 64, N)
+    ws = torch.empty(nws, dtype=torch.uint8, device=DEV)
+    rc = lib.scream_render_transform(xyz.data_ptr(), offs.data_ptr(), N, N, None if pose is None else pose.data_ptr(),
+                                     views.data_ptr(), 1, V, rot.data_ptr(), pv.data_ptr(), zr.data_ptr(),
+                                     ws.data_ptr(), nws, torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "transform")
+    want_rot, want_pv, want_zr = c_transform(c_oracle, src, tgt, g["views"], g.get("pose"))
+    assert np.array_equal(rot.cpu().numpy(), want_rot)
+    assert np.array_equal(pv.cpu().numpy(), want_pv)
+    assert np.array_equal(zr[0].cpu().numpy(), want_zr)
+
+
+@pytest.mark.parametrize("name", [n for n in NAMES if "grad_out" in load_golden(n)])
+def test_backward_matches_reference_autograd(name):
+    g = load_golden(name)
+    w, rho = int(g["w"]), float(g["rho"])
+    r = RegistrationRender(rho if rho != int(rho) else int(rho), w, device=DEV)
+    r.eulers = list(g["eulers"])
+    s = torch.from_numpy(g["src"]).to(DEV).requires_grad_(True)
+    t = torch.from_numpy(g["tgt"]).to(DEV).requires_grad_(True)
+    imgs = r(s, t)
+    assert imgs.shape == g["imgs"].shape and imgs.is_contiguous() and imgs.dtype == torch.float32
+    assert np.abs(imgs.detach().cpu().numpy() - g["imgs"]).max() <= 2e-6
+    imgs.backward(torch.from_numpy(g["grad_out"]).to(DEV))
+    scale = max(np.abs(g["grad_src"]).max(), np.abs(g["grad_tgt"]).max())
+    assert np.abs(s.grad.cpu().numpy() - g["grad_src"]).max() <= 1e-5 * scale
+    assert np.abs(t.grad.cpu().numpy() - g["grad_tgt"]).max() <= 1e-5 * scale
+
+
+def test_module_render_and_attribute_mutation(c_oracle):
+    """render(x, src_n) on pre-rotated points; rho / eulers mutated after construction (train_kitti.py:47-48)."""
+    g = load_golden("cfg3_kitti_bev")
+    r = RegistrationRender(24, 64, device=DEV)
+    r.rho = 48
+    r.eulers = [np.array([0, np.pi, 0])]
+    out = r(torch.from_numpy(g["src"]).to(DEV), torch.from_numpy(g["tgt"]).to(DEV))
+    assert out.shape == (1, 2, 64, 64)
+    assert np.abs(out.cpu().numpy() - g["imgs"]).max() <= 2e-6
+    rot, _, _ = c_transform(c_oracle, g["src"], g["tgt"], g["views"])
+    raw = r.render(torch.from_numpy(rot[0]).to(DEV), len(g["src"]))
+    assert raw.shape == (2, 64, 64)
+    want = g["val"][0].astype(np.float64)
+    assert (np.abs(raw.cpu().numpy() - want) <= 1e-6 * want + 1e-37).all()
+    assert r.state_dict() == {}
+
+
+def test_noncontiguous_inputs_and_batch_equals_singles():
+    """Batched CSR render == per-item renders, bit for bit; inputs may be strided views (pointnet.py:65)."""
+    views = view_matrices(RegistrationRender(24, 64, device="cpu").eulers).to(DEV)
+    sizes = [(300, 280), (17, 450), (512, 16)]
+    clouds = [(synth.unit_ball(n, 100 + i), synth.room_shell(m, 200 + i)) for i, (n, m) in enumerate(sizes)]
+    xyz = torch.from_numpy(np.concatenate([np.concatenate(c, 0) for c in clouds], 0)).to(DEV)
+    offs = make_offsets(sizes).to(DEV)
+    imgs, win, zr = render_batch(xyz, offs, views, 24, 64, need_winner=True)
+    r = RegistrationRender(24, 64, device=DEV)
+    for b, (s, t) in enumerate(clouds):
+        big = torch.zeros((len(s), 6), device=DEV)
+        big[:, ::2] = torch.from_numpy(s).to(DEV)
+        one = r(big[:, ::2], torch.from_numpy(t).to(DEV))
+        assert torch.equal(one, imgs[b])
+
+
+@pytest.mark.parametrize("cfg", [("ball", 5000, 4800, 24, 64), ("slab", 6000, 6100, 48, 64), ("grid", 0, 0, 36, 128)])
+def test_fresh_inputs_against_c_oracle(cfg, c_oracle):
+    kind, n, m, rho, w = cfg
+    if kind == "ball":
+        src, tgt = synth.unit_ball(n, 901), synth.unit_ball(m, 902)
+        views = view_matrices(RegistrationRender(24, 64, device="cpu").eulers).numpy()[:3]
+    elif kind == "slab":
+        src, tgt = synth.kitti_slab(n, 903), synth.kitti_slab(m, 904)
+        views = view_matrices([np.array([0, np.pi, 0])]).numpy()
+    else:
+        src, tgt = synth.opengg_patch(100, 905)
+        views = np.eye(3, dtype=np.float32)[None]
+    want = c_forward(c_oracle, src, tgt, views, rho, w)
+    for dense in (True, False):
+        r = gpu_forward(src, tgt, views, rho, w, dense=dense)
+        assert np.array_equal(r["zrange"], want["zrange"])
+        pvf = oracle_pair_value(c_oracle, src, tgt, views, rho, w, None, r["idx"])
+        check_images(r["val"], r["idx"], want["val"], want["idx"], want["second"], pvf, rtol=2e-6)
+
+
+def test_culled_equals_dense_bitwise_at_full_size():
+    """Size-independent property at BASELINE cfg2 size: the culled kernel returns exactly what the dense one does."""
+    views = view_matrices(RegistrationRender(24, 64, device="cpu").eulers).to(DEV)
+    sizes = [(10000, 10000), (10000, 9000)]
+    parts = [synth.unit_ball(10000, 1), synth.unit_ball(10000, 2), synth.room_shell(10000, 3), synth.room_shell(9000, 4)]
+    xyz = torch.from_numpy(np.concatenate(parts, 0)).to(DEV)
+    offs = make_offsets(sizes).to(DEV)
+    pose = torch.from_numpy(np.stack([synth.random_pose(5), synth.random_pose(6)])).to(DEV)
+    a = render_batch(xyz, offs, views, 24, 64, pose=pose, raw=True, dense=True, need_winner=True)
+    b = render_batch(xyz, offs, views, 24, 64, pose=pose, raw=True, dense=False, need_winner=True)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+
+
+def test_host_entry_point(c_oracle):
+    g = load_golden("cfg1_ball_single")
+    lib = _lib.load()
+    src, tgt = g["src"], g["tgt"]
+    xyz = np.ascontiguousarray(np.concatenate([src, tgt], 0))
+    offs = make_offsets([(len(src), len(tgt))]).numpy()
+    V, w = g["views"].shape[0], int(g["w"])
+    imgs = np.empty((1, V, 2, w, w), np.float32); win = np.empty((1, V, 2, w, w), np.int32); zr = np.empty((1, V, 2), np.float32)
+    views = np.ascontiguousarray(g["views"])
+    rc = lib.scream_render_forward_host(xyz.ctypes.data, offs.ctypes.data, None, views.ctypes.data, 1, V, w,
+                                        float(g["rho"]), 0, imgs.ctypes.data, win.ctypes.data, zr.ctypes.data, 0)
+    _lib.check(rc, "forward_host")
+    assert np.abs(imgs[0] - g["imgs"]).max() <= 2e-6
+    assert np.array_equal(zr[0], g["zrange"])
+    assert (win[0] != g["idx"]).mean() < 1e-3
