@@ -4,6 +4,7 @@
 #include "common.cuh"
 #include "transform.cuh"
 #include "forward_dense.cuh"
+#include "forward_culled.cuh"
 #include "backward.cuh"
 
 #include <cstdarg>
@@ -98,8 +99,19 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
     const float rho2 = (float)(rho * rho);           // tensor * python scalar -> scalar cast to fp32
     P.negk = -rho2 * 0.5f; P.inv_negk = 1.0f / P.negk;
     P.flags = flags; P.imgs = imgs; P.winner = winner; P.zrange = zrange;
-    const long long grid = (long long)B * V * 2 * (w * w / FD_TILE);
-    forward_dense_kernel<<<(unsigned)grid, FD_THREADS, 0, st>>>(P);
+    if (flags & SCREAM_F_DENSE) {
+        const long long grid = (long long)B * V * 2 * (w * w / FD_TILE);
+        forward_dense_kernel<<<(unsigned)grid, FD_THREADS, 0, st>>>(P);
+    } else {
+        static thread_local int attr_dev = -1;
+        int dev = 0;
+        CUDA_TRY(cudaGetDevice(&dev));
+        if (attr_dev != dev) {
+            CUDA_TRY(cudaFuncSetAttribute(forward_culled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FC_SMEM));
+            attr_dev = dev;
+        }
+        forward_culled_kernel<<<(unsigned)((long long)B * V * 2), FC_THREADS, FC_SMEM, st>>>(P);
+    }
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

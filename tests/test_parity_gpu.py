@@ -178,3 +178,41 @@ def test_host_entry_point(c_oracle):
     assert np.abs(imgs[0] - g["imgs"]).max() <= 2e-6
     assert np.array_equal(zr[0], g["zrange"])
     assert (win[0] != g["idx"]).mean() < 1e-3
+
+
+CULL_CASES = [
+    # (n, m, rho, w, scale, kind)
+    (30000, 13000, 24, 64, 1.0, "ball"),        # more than one shared-memory batch (12288 points)
+    (2000, 2500, 24, 64, 1.0, "shell"),         # sparse, realistic 3DMatch density
+    (5000, 36, 36, 128, 1.0, "grid"),           # OpenGG w=128, regular grid: exact ties
+    (10000, 36, 72, 256, 1.0, "grid"),          # OpenGG w=256
+    (4000, 4000, 24, 64, 1.8, "ball"),          # points far outside [-1,1]^2 (clamped cells)
+    (3000, 3000, 3, 64, 1.0, "ball"),           # very wide Gaussians: windows cover the whole grid
+    (64, 16, 48, 64, 0.3, "ball"),              # tiny cloud, mostly empty image
+    (20000, 20000, 48, 64, 1.0, "slab"),        # KITTI
+]
+
+
+@pytest.mark.parametrize("case", CULL_CASES)
+def test_culled_equals_dense_bitwise(case):
+    n, m, rho, w, scale, kind = case
+    if kind == "ball":
+        src, tgt = synth.unit_ball(n, 11) * np.float32(scale), synth.unit_ball(m, 12) * np.float32(scale)
+    elif kind == "shell":
+        src, tgt = synth.room_shell(n, 13), synth.room_shell(m, 14)
+    elif kind == "slab":
+        src, tgt = synth.kitti_slab(n, 15), synth.kitti_slab(m, 16)
+    else:
+        side = int(round(n ** 0.5))
+        src, tgt = synth.opengg_patch(side, 17)
+    views = torch.from_numpy(np.concatenate([view_matrices(RegistrationRender(24, 64, device="cpu").eulers).numpy()[:3],
+                                             synth.random_views(2, 5)], 0)).to(DEV)
+    xyz = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV)
+    offs = make_offsets([(len(src), len(tgt))]).to(DEV)
+    a = render_batch(xyz, offs, views, rho, w, raw=True, dense=True, need_winner=True)
+    b = render_batch(xyz, offs, views, rho, w, raw=True, dense=False, need_winner=True)
+    assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
+    assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
+    assert torch.equal(a[2], b[2])
+    c = render_batch(xyz, offs, views, rho, w, raw=False, dense=False, need_winner=False)
+    assert torch.equal(c[0], (a[0] - 0.5) / 0.5)
