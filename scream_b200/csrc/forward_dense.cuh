@@ -26,8 +26,10 @@ struct FwdParams {
 };
 
 __device__ __forceinline__ float zero_or_cull(float best, float inv_negk) {
-    // best == +-0: contributions with exp argument below -106 are exactly 0 and can never win
-    if (best == 0.0f) return __fmul_rn(-106.0f, inv_negk);
+    // best == +-0: contributions with exp argument below -106 are exactly 0 and can never win or tie.
+    // The same radius is used while best is (near-)denormal: there fp32 has no relative precision, so a
+    // log-domain margin cannot prove "strictly below"; only "exactly zero" can.
+    if (best >= 0.0f && best < 1e-37f) return __fmul_rn(-106.0f, inv_negk);
     return cull_d2(best, inv_negk);
 }
 
