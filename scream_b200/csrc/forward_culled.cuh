@@ -1,25 +1,35 @@
 // forward_culled.cuh -- culled exact forward: the product kernel.
 //
 // Same result, bit for bit, as forward_dense.cuh (and so as render.py:39-49): for every pixel the max
-// over the cloud of pv_i * exp(-d2/2*rho^2) with the lowest index on ties -- but a (point, pixel) pair
-// is only evaluated when it can still win.  One CTA renders one (item, view, cloud) image:
+// over the cloud of  val = pv_i * exp(-d2/2*rho^2)  with the lowest index on ties -- but almost no
+// (point, pixel) pair is ever evaluated.  One CTA renders one (item, view, cloud) image.
 //
-//   P1  transform (pose, view rotation, pv) every point of the cloud, bin it into a G x G grid of
-//       cells over [-1,1]^2 (clamped), shared-memory histogram; the atomic's return value is the
-//       point's rank inside its cell.
+// Search domain.  With k = rho^2/2 and c_i = -ln(pv_i)/k >= 0 the value is exp(-k * s), s = d2 + c_i,
+// so the winner of a pixel is the point of minimum "score" s (a power diagram).  The search runs on the
+// score (two FMAs per pair, no exp); exp() is evaluated once per pixel, for the point that won, in the
+// reference's op order.  fp32 rounding can reorder two points only when their scores agree to ~1e-6
+// relative: every pixel therefore tracks the runner-up score as well, and a pixel whose two best scores
+// are within a (5x over-estimated) margin -- or whose value is in the denormal range, where fp32 has no
+// relative precision -- is re-done by an exact pass that evaluates the reference expression for every
+// point inside the margin and applies the (value, lowest index) order directly.
+//
+//   P1  transform (pose, view rotation) every point, bin it into a 64 x 64 grid of cells over
+//       [-1,1]^2 (clamped), shared-memory histogram; the atomic's return value is the rank in the cell.
 //   P2  exclusive scan of the histogram -> cell start offsets (row-major: a run of cells in one grid
 //       row is one contiguous run of records).
-//   P3  counting-sort scatter of (x', y') / pv / index records into shared memory (SoA).
-//   P4  gather: a thread owns 4 horizontally adjacent pixels and searches the cells around them in
-//       growing square windows.  A window only has to reach as far as cull_d2(best) (common.cuh): a
-//       point farther than that from the pixel has a value strictly below the pixel's current best.
-//       Inside a window every record costs one 8-byte shared load and a squared-distance test per pixel;
-//       exp() is only evaluated for the few survivors.
+//   P3  counting-sort scatter of (x', y', c, index) records into shared memory (SoA).
+//   P4  per 64 x 64 pixel tile:
+//       A  lane per pixel, 3 x 3 cells around the pixel: best / runner-up score.  Resolved when the best
+//          score (+margin) is smaller than the squared distance to the edge of the window (a point
+//          outside the window has s >= d2 > best).  ~90 % of the pixels of a dense cloud end here.
+//       C  the rest (compacted into a queue): disc scan -- grid rows outwards from the pixel, per-row
+//          column span from the circle equation, radius^2 = best score so far (+margin), capped where
+//          exp() underflows to exactly zero -- then, if flagged, the exact pass over the same disc.
 //   Clouds larger than the shared-memory capacity are rendered in batches; the per-pixel best is carried
 //   through the output buffers (max is associative; earlier batches hold the lower indices).
 #pragma once
 #include "common.cuh"
-#include "forward_dense.cuh"   // FwdParams, zero_or_cull
+#include "forward_dense.cuh"   // FwdParams
 
 namespace scream {
 
@@ -28,43 +38,158 @@ constexpr int FC_PPT = 24;                               // points per thread pe
 constexpr int FC_CAP = FC_THREADS * FC_PPT;              // 12288 points per batch
 constexpr int FC_G = 64;                                 // cell grid side
 constexpr int FC_CELLS = FC_G * FC_G;
-constexpr size_t FC_SMEM = (size_t)(FC_CELLS + 1) * 4 + (size_t)FC_CAP * (8 + 4 + 4) + 64;
+constexpr int FC_TILE = 64;                              // pixel tile side of P4
+constexpr int FC_TPIX = FC_TILE * FC_TILE;
+constexpr float FC_CELLS_PER_NDC = (float)(FC_G / 2);
+constexpr float FC_EXP_ZERO = 108.0f;                    // k*s beyond this: value is exactly +0
+constexpr float FC_EXP_DENORM = 80.0f;                   // k*s beyond this: treat as denormal zone
+constexpr float FC_EXP_MINUS1 = 18.1f;                   // k*s beyond this: (val-0.5)/0.5 == -1 exactly
 
-struct Rect { int j0, j1, i0, i1; };
+// shared-memory carve-up (bytes)
+constexpr size_t FC_OFF_XY = 0;
+constexpr size_t FC_OFF_C = FC_OFF_XY + (size_t)FC_CAP * 8;
+constexpr size_t FC_OFF_IDX = FC_OFF_C + (size_t)FC_CAP * 4;
+constexpr size_t FC_OFF_START = FC_OFF_IDX + (size_t)FC_CAP * 4;             // u16 [CELLS + 8]
+constexpr size_t FC_OFF_SCRATCH = FC_OFF_START + (size_t)(FC_CELLS + 8) * 2; // u32 hist[CELLS+4] | u16 cand[TPIX], queue[TPIX]
+constexpr size_t FC_SMEM = FC_OFF_SCRATCH + (size_t)(FC_CELLS + 4) * 4;
+
+struct FcShared {
+    const float2* xy; const float* c; const int* idx; const unsigned short* start;
+};
 
 __device__ __forceinline__ int cell_of(float x) {
     // fl(fl(x + 1) * G/2), clamped; NaN -> 0
-    float u = __fmul_rn(__fadd_rn(x, 1.0f), (float)(FC_G / 2));
+    float u = __fmul_rn(__fadd_rn(x, 1.0f), FC_CELLS_PER_NDC);
     u = fminf(fmaxf(u, 0.0f), (float)(FC_G - 1));
     return (int)u;                                       // u >= 0: truncation == floor
 }
 
-// cells that can hold a point within `rc` cells of the pixel-centre span [ul, ur] x {uv}
-__device__ __forceinline__ Rect window(float ul, float ur, float uv, float rc) {
-    Rect W;
-    W.j0 = max(0, (int)floorf(ul - rc)); W.j1 = min(FC_G - 1, (int)floorf(ur + rc));
-    W.i0 = max(0, (int)floorf(uv - rc)); W.i1 = min(FC_G - 1, (int)floorf(uv + rc));
-    return W;
+// radius in cells of a squared NDC radius (inflated: covers the rounding of cell_of and of the sqrt)
+__device__ __forceinline__ float radius_cells(float r2) {
+    float r = __fmul_rn(sqrtf(r2), FC_CELLS_PER_NDC);
+    return __fmaf_rn(r, 1e-4f, r) + 1e-3f;
 }
 
-// radius in cells (inflated: covers the <= 4e-6-cell rounding of cell_of and of the sqrt)
-__device__ __forceinline__ float radius_cells(float t2) {
-    float r = __fmul_rn(sqrtf(t2), (float)(FC_G / 2));
-    return fminf(__fmaf_rn(r, 1e-4f, r) + 1e-3f, (float)(2 * FC_G));
+// score margin inside which two points may swap order through fp32 rounding (5x the analysed bound)
+__device__ __forceinline__ float score_margin(float s, float inv_k) {
+    return __fmaf_rn(s, 4e-6f, __fmul_rn(3e-6f, inv_k));
+}
+
+struct PixelGeom { float cx, cy, ux, uy; };              // centre in NDC and in cell coordinates
+
+__device__ __forceinline__ float score_of(const FcShared& S, int s, const PixelGeom& g) {
+    const float2 q = S.xy[s];
+    const float dx = __fsub_rn(q.x, g.cx), dy = __fsub_rn(q.y, g.cy);
+    return __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, S.c[s]));
+}
+
+// column span [j0, j1] of grid row i inside the disc of radius rc (cells) around (ux, uy); false if empty
+__device__ __forceinline__ bool row_span(int i, int ci, float fy, int d, bool up, float ux, float rc, int& j0, int& j1) {
+    if (i < 0 || i >= FC_G) return false;
+    // distance from the pixel centre to the band [i, i+1]
+    const float dist = d == 0 ? 0.0f : (up ? __fadd_rn(fy, (float)(d - 1)) : __fsub_rn((float)d, fy));
+    const float h2 = __fmaf_rn(rc, rc, -__fmul_rn(dist, dist));
+    if (!(h2 >= 0.0f)) return false;
+    const float hw = sqrtf(h2) + 1e-3f;
+    j0 = max(0, (int)floorf(ux - hw));
+    j1 = min(FC_G - 1, (int)floorf(ux + hw));
+    (void)ci;
+    return j0 <= j1;
+}
+
+// Disc scan, score domain.  On entry s1 is an upper bound of the best score (or +inf) and r2cap the
+// largest squared radius that can matter.  On exit s1/a1 = best score / its record, s2 = runner-up.
+__device__ __forceinline__ void disc_find(const FcShared& S, const PixelGeom& g, float r2cap, float inv_k,
+                                          float& s1, float& s2, int& a1)
+{
+    const int ci = (int)g.uy;
+    const float fy = __fsub_rn(g.uy, (float)ci);
+    float r2 = fminf(r2cap, s1 + score_margin(s1, inv_k));
+    float rc = radius_cells(r2);
+    s1 = INFINITY; s2 = INFINITY; a1 = -1;
+    for (int d = 0; d < FC_G; ++d) {
+        const bool up_live = (d == 0) || (__fadd_rn(fy, (float)(d - 1)) <= rc);
+        const bool dn_live = (d > 0) && (__fsub_rn((float)d, fy) <= rc);
+        if (!up_live && !dn_live) break;
+        for (int side = 0; side < 2; ++side) {
+            if (side == 1 && d == 0) break;
+            const int i = side ? ci + d : ci - d;
+            int j0, j1;
+            if (!row_span(i, ci, fy, d, side == 0, g.ux, rc, j0, j1)) continue;
+            const int b = S.start[i * FC_G + j0], e = S.start[i * FC_G + j1 + 1];
+            bool improved = false;
+            for (int s = b; s < e; ++s) {
+                const float sc = score_of(S, s, g);
+                s2 = fminf(s2, fmaxf(sc, s1));
+                if (sc < s1) { s1 = sc; a1 = s; improved = true; }
+            }
+            if (improved) {
+                r2 = fminf(r2, s1 + score_margin(s1, inv_k));
+                rc = radius_cells(r2);
+            }
+        }
+    }
+}
+
+// exact value of record s at pixel g: the reference expression, pv recomputed from the point itself
+struct ExactCtx {
+    const float* xyz; int64_t lo; const float* R; const float* pose; bool posed;
+    float zmin, range, negk;
+};
+__device__ __forceinline__ float exact_value(const FcShared& S, const ExactCtx& E, int s, const PixelGeom& g, int& id) {
+    id = S.idx[s];
+    const float* q = E.xyz + (size_t)(E.lo + id) * 3;
+    float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+    if (E.posed) apply_pose(E.pose, x, y, z);
+    const float pv = depth_weight(rot_row(E.R + 6, x, y, z), E.zmin, E.range);
+    const float2 r = S.xy[s];
+    return pair_value(pair_d2(r.x, r.y, g.cx, g.cy), pv, E.negk);
+}
+
+// Exact pass: every record with score <= s_thr is evaluated with the reference expression.
+__device__ __forceinline__ void disc_exact(const FcShared& S, const ExactCtx& E, const PixelGeom& g, float s_thr,
+                                           float& best, int& arg)
+{
+    const int ci = (int)g.uy;
+    const float fy = __fsub_rn(g.uy, (float)ci);
+    const float rc = radius_cells(s_thr);
+    for (int d = 0; d < FC_G; ++d) {
+        const bool up_live = (d == 0) || (__fadd_rn(fy, (float)(d - 1)) <= rc);
+        const bool dn_live = (d > 0) && (__fsub_rn((float)d, fy) <= rc);
+        if (!up_live && !dn_live) break;
+        for (int side = 0; side < 2; ++side) {
+            if (side == 1 && d == 0) break;
+            const int i = side ? ci + d : ci - d;
+            int j0, j1;
+            if (!row_span(i, ci, fy, d, side == 0, g.ux, rc, j0, j1)) continue;
+            const int b = S.start[i * FC_G + j0], e = S.start[i * FC_G + j1 + 1];
+            for (int s = b; s < e; ++s) {
+                if (score_of(S, s, g) <= s_thr) {
+                    int id;
+                    const float val = exact_value(S, E, s, g, id);
+                    if (val > best || (val == best && id < arg)) { best = val; arg = id; }
+                }
+            }
+        }
+    }
 }
 
 __global__ void __launch_bounds__(FC_THREADS, 1)
 forward_culled_kernel(FwdParams P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    unsigned* s_start = reinterpret_cast<unsigned*>(smem_raw);                    // [CELLS + 1]
-    float2* s_xy = reinterpret_cast<float2*>(smem_raw + ((FC_CELLS + 1) * 4 + 15) / 16 * 16);
-    float* s_pv = reinterpret_cast<float*>(s_xy + FC_CAP);
-    int* s_idx = reinterpret_cast<int*>(s_pv + FC_CAP);
+    float2* s_xy = reinterpret_cast<float2*>(smem_raw + FC_OFF_XY);
+    float* s_c = reinterpret_cast<float*>(smem_raw + FC_OFF_C);
+    int* s_idx = reinterpret_cast<int*>(smem_raw + FC_OFF_IDX);
+    unsigned short* s_start = reinterpret_cast<unsigned short*>(smem_raw + FC_OFF_START);
+    unsigned* s_hist = reinterpret_cast<unsigned*>(smem_raw + FC_OFF_SCRATCH);
+    unsigned short* s_cand = reinterpret_cast<unsigned short*>(smem_raw + FC_OFF_SCRATCH);
+    unsigned short* s_queue = s_cand + FC_TPIX;
     __shared__ float s_R[9], s_pose[12];
     __shared__ unsigned s_warp_tot[FC_THREADS / 32];
+    __shared__ unsigned s_qn;
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
     const int w = P.w, npix = w * w, half = w / 2;
     int bid = blockIdx.x;
     const int c = bid % 2; bid /= 2;
@@ -82,7 +207,11 @@ forward_culled_kernel(FwdParams P)
     const float range = z_range(zmin, zmax);
     const size_t img_off = (((size_t)b * P.V + v) * 2 + c) * npix;
     const bool raw = P.flags & 1u;
-    const float cells_per_ndc = (float)(FC_G / 2);
+    const float inv_k = -P.inv_negk;                      // 1/k, k = rho^2/2
+    const float s_zero = __fmul_rn(FC_EXP_ZERO, inv_k);   // scores beyond: value exactly 0
+    // scores beyond s_far cannot change the OUTPUT: all of them when the value is exactly zero; with the
+    // normalised output and no winner map, already when val <= 2^-26 ((val-0.5)/0.5 rounds to -1).
+    const bool minus1_ok = !raw && P.winner == nullptr;
 
     if (P.zrange && c == 0 && tid == 0) {
         P.zrange[((size_t)b * P.V + v) * 2] = zmin;
@@ -90,14 +219,19 @@ forward_culled_kernel(FwdParams P)
     }
     __syncthreads();
 
+    FcShared S; S.xy = s_xy; S.c = s_c; S.idx = s_idx; S.start = s_start;
+    ExactCtx E; E.xyz = P.xyz; E.lo = lo; E.R = s_R; E.pose = s_pose; E.posed = posed;
+    E.zmin = zmin; E.range = range; E.negk = P.negk;
+
     int batch = 0;
     int64_t c0 = lo;
     do {                                                 // at least one pass, so empty clouds still write
         const int cnt = (int)max((int64_t)0, min((int64_t)FC_CAP, hi - c0));
         const bool last = c0 + cnt >= hi;
+        E.lo = lo;                                        // record indices are cloud-local
 
         // ---------------- P1: transform + histogram -------------------------------------------
-        for (int t = tid; t <= FC_CELLS; t += FC_THREADS) s_start[t] = 0u;
+        for (int t = tid; t < FC_CELLS + 4; t += FC_THREADS) s_hist[t] = 0u;
         __syncthreads();
         unsigned packed[FC_PPT];
 #pragma unroll
@@ -110,7 +244,7 @@ forward_culled_kernel(FwdParams P)
                 if (posed) apply_pose(s_pose, x, y, z);
                 const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z);
                 const int cell = cell_of(yr) * FC_G + cell_of(xr);
-                const unsigned rank = atomicAdd(&s_start[cell], 1u);
+                const unsigned rank = atomicAdd(&s_hist[cell], 1u);
                 packed[k] = ((unsigned)cell << 16) | (rank & 0xFFFFu);       // cnt <= 12288 < 65536
             }
         }
@@ -121,14 +255,14 @@ forward_culled_kernel(FwdParams P)
             constexpr int PER = FC_CELLS / FC_THREADS;                       // 8 consecutive cells per thread
             unsigned loc[PER], sum = 0;
 #pragma unroll
-            for (int k = 0; k < PER; ++k) { loc[k] = s_start[tid * PER + k]; sum += loc[k]; }
+            for (int k = 0; k < PER; ++k) { loc[k] = s_hist[tid * PER + k]; sum += loc[k]; }
             unsigned inc = sum;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 unsigned o = __shfl_up_sync(0xFFFFFFFFu, inc, d);
-                if ((tid & 31) >= d) inc += o;
+                if (lane >= d) inc += o;
             }
-            if ((tid & 31) == 31) s_warp_tot[tid >> 5] = inc;
+            if (lane == 31) s_warp_tot[tid >> 5] = inc;
             __syncthreads();
             if (tid < 32) {
                 unsigned t = tid < FC_THREADS / 32 ? s_warp_tot[tid] : 0u, ti = t;
@@ -142,8 +276,8 @@ forward_culled_kernel(FwdParams P)
             __syncthreads();
             unsigned run = s_warp_tot[tid >> 5] + inc - sum;
 #pragma unroll
-            for (int k = 0; k < PER; ++k) { s_start[tid * PER + k] = run; run += loc[k]; }
-            if (tid == FC_THREADS - 1) s_start[FC_CELLS] = run;
+            for (int k = 0; k < PER; ++k) { s_start[tid * PER + k] = (unsigned short)run; run += loc[k]; }
+            if (tid == FC_THREADS - 1) s_start[FC_CELLS] = (unsigned short)run;
         }
         __syncthreads();
 
@@ -156,100 +290,110 @@ forward_culled_kernel(FwdParams P)
                 float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
                 if (posed) apply_pose(s_pose, x, y, z);
                 const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z), zr = rot_row(s_R + 6, x, y, z);
-                const unsigned pos = s_start[packed[k] >> 16] + (packed[k] & 0xFFFFu);
+                const unsigned pos = (unsigned)s_start[packed[k] >> 16] + (packed[k] & 0xFFFFu);
                 s_xy[pos] = make_float2(xr, yr);
-                s_pv[pos] = depth_weight(zr, zmin, range);
+                // c = -ln(pv)/k >= 0; pv == 0 -> +inf (never wins); pv < 0 (rounding corner) -> NaN (never wins)
+                s_c[pos] = __fmul_rn(logf(depth_weight(zr, zmin, range)), P.inv_negk);
                 s_idx[pos] = (int)(c0 - lo) + j;
             }
         }
         __syncthreads();
 
-        // ---------------- P4: per-pixel window search -----------------------------------------
-        const int groups_per_row = w / FD_PX;
-        for (int g = tid; g < npix / FD_PX; g += FC_THREADS) {
-            const int row = g / groups_per_row, col0 = (g % groups_per_row) * FD_PX;
-            const float cy = pixel_centre(row, half);
-            float cx[FD_PX], best[FD_PX], t2[FD_PX];
-            int arg[FD_PX];
-            const size_t o = img_off + (size_t)row * w + col0;
-            if (batch == 0) {
-#pragma unroll
-                for (int u = 0; u < FD_PX; ++u) { best[u] = 0.0f; arg[u] = 0; }
-            } else {
-                const float4 pb = *reinterpret_cast<const float4*>(P.imgs + o);
-                best[0] = pb.x; best[1] = pb.y; best[2] = pb.z; best[3] = pb.w;
-                if (P.winner) {
-                    const int4 pa = *reinterpret_cast<const int4*>(P.winner + o);
-                    arg[0] = pa.x; arg[1] = pa.y; arg[2] = pa.z; arg[3] = pa.w;
-                } else {
-                    arg[0] = arg[1] = arg[2] = arg[3] = -1;
-                }
-            }
-            float t2max = 0.0f;
-#pragma unroll
-            for (int u = 0; u < FD_PX; ++u) {
-                cx[u] = pixel_centre(col0 + u, half);
-                t2[u] = zero_or_cull(best[u], P.inv_negk);
-                t2max = fmaxf(t2max, t2[u]);
-            }
-            const float ul = __fmul_rn(__fadd_rn(cx[0], 1.0f), cells_per_ndc);
-            const float ur = __fmul_rn(__fadd_rn(cx[FD_PX - 1], 1.0f), cells_per_ndc);
-            const float uv = __fmul_rn(__fadd_rn(cy, 1.0f), cells_per_ndc);
+        // ---------------- P4: per-pixel search, one 64 x 64 pixel tile at a time ---------------
+        const int tiles_side = w / FC_TILE;
+        for (int tile = 0; tile < tiles_side * tiles_side; ++tile) {
+            const int trow0 = (tile / tiles_side) * FC_TILE, tcol0 = (tile % tiles_side) * FC_TILE;
+            if (tid == 0) s_qn = 0u;
+            __syncthreads();
 
-            Rect done; done.j0 = 1; done.j1 = 0; done.i0 = 1; done.i1 = 0;   // empty
-            float r = 1.0f;
-            while (cnt > 0) {
-                const float need = radius_cells(t2max);
-                const float rr = fminf(r, need);
-                const Rect W = window(ul, ur, uv, rr);
-                for (int i = W.i0; i <= W.i1; ++i) {
-                    const bool inside = i >= done.i0 && i <= done.i1;
-                    // up to two runs of cells in this grid row: left of / right of the finished rectangle
-                    for (int part = 0; part < 2; ++part) {
-                        int ja, jb;
-                        if (!inside) { if (part) break; ja = W.j0; jb = W.j1; }
-                        else if (part == 0) { ja = W.j0; jb = done.j0 - 1; }
-                        else { ja = done.j1 + 1; jb = W.j1; }
-                        if (ja > jb) continue;
-                        const int s0 = (int)s_start[i * FC_G + ja], s1 = (int)s_start[i * FC_G + jb + 1];
-                        for (int s = s0; s < s1; ++s) {
-                            const float2 q = s_xy[s];
-                            const float dy = __fsub_rn(q.y, cy), dy2 = __fmul_rn(dy, dy);
-#pragma unroll
-                            for (int u = 0; u < FD_PX; ++u) {
-                                const float dx = __fsub_rn(q.x, cx[u]);
-                                const float d2 = __fadd_rn(__fmul_rn(dx, dx), dy2);
-                                if (d2 <= t2[u]) {
-                                    const float val = pair_value(d2, s_pv[s], P.negk);
-                                    const int id = s_idx[s];
-                                    if (val > best[u] || (val == best[u] && id < arg[u])) {
-                                        best[u] = val; arg[u] = id;
-                                        t2[u] = zero_or_cull(val, P.inv_negk);
-                                        t2max = fmaxf(fmaxf(t2[0], t2[1]), fmaxf(t2[2], t2[3]));
-                                    }
-                                }
-                            }
-                        }
+            // ---- phase A: 3 x 3 cells, lane per pixel ----
+            for (int pl = tid; pl < FC_TPIX; pl += FC_THREADS) {
+                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                PixelGeom g;
+                g.cx = pixel_centre(col, half); g.cy = pixel_centre(row, half);
+                g.ux = __fmul_rn(__fadd_rn(g.cx, 1.0f), FC_CELLS_PER_NDC);
+                g.uy = __fmul_rn(__fadd_rn(g.cy, 1.0f), FC_CELLS_PER_NDC);
+                const int ci = (int)g.uy, cj = (int)g.ux;
+                const float fx = g.ux - (float)cj, fy = g.uy - (float)ci;
+                const float edge = fminf(fminf(fx, 1.0f - fx), fminf(fy, 1.0f - fy));
+                const float cov = __fmul_rn(1.0f + edge, 1.0f / FC_CELLS_PER_NDC);
+                const float cov2 = __fmul_rn(__fmul_rn(cov, cov), 0.99999f);
+                const int j0 = max(cj - 1, 0), j1 = min(cj + 1, FC_G - 1);
+                float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
+                for (int i = max(ci - 1, 0); i <= min(ci + 1, FC_G - 1); ++i) {
+                    const int rb = s_start[i * FC_G + j0], re = s_start[i * FC_G + j1 + 1];
+                    for (int s = rb; s < re; ++s) {
+                        const float sc = score_of(S, s, g);
+                        s2 = fminf(s2, fmaxf(sc, s1));
+                        if (sc < s1) { s1 = sc; a1 = s; }
                     }
                 }
-                done = W;
-                if (rr >= radius_cells(t2max)) break;
-                r = __fmul_rn(r, 2.0f);
+                const float m = score_margin(s1, inv_k);
+                const bool resolved = (s1 + m < cov2) && (s2 > s1 + m) && (__fmul_rn(s1, -P.negk) < FC_EXP_DENORM);
+                s_cand[pl] = (unsigned short)(a1 < 0 ? 0xFFFF : a1);
+                if (resolved) {
+                    int id;
+                    float val = exact_value(S, E, a1, g, id);
+                    const size_t o = img_off + (size_t)row * w + col;
+                    if (batch > 0) {
+                        const float pb = P.imgs[o];
+                        if (!(val > pb)) { val = pb; id = P.winner ? P.winner[o] : 0; }
+                    }
+                    P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
+                    if (P.winner) P.winner[o] = id;
+                }
+                const unsigned um = __ballot_sync(0xFFFFFFFFu, !resolved);
+                if (um) {
+                    unsigned base = 0;
+                    if (lane == 0) base = atomicAdd(&s_qn, (unsigned)__popc(um));
+                    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                    if (!resolved) s_queue[base + __popc(um & ((1u << lane) - 1u))] = (unsigned short)pl;
+                }
             }
+            __syncthreads();
 
-            float out[FD_PX];
-#pragma unroll
-            for (int u = 0; u < FD_PX; ++u)
-                out[u] = (raw || !last) ? best[u] : __fmul_rn(__fsub_rn(best[u], 0.5f), 2.0f);
-            *reinterpret_cast<float4*>(P.imgs + o) = make_float4(out[0], out[1], out[2], out[3]);
-            if (P.winner) {
-                const int none = (hi > lo) ? 0 : -1;
-                *reinterpret_cast<int4*>(P.winner + o) = make_int4(arg[0] + none, arg[1] + none, arg[2] + none, arg[3] + none);
+            // ---- phase C: disc scan for the unresolved pixels ----
+            const int qn = (int)s_qn;
+            for (int qi = tid; qi < qn; qi += FC_THREADS) {
+                const int pl = s_queue[qi];
+                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                PixelGeom g;
+                g.cx = pixel_centre(col, half); g.cy = pixel_centre(row, half);
+                g.ux = __fmul_rn(__fadd_rn(g.cx, 1.0f), FC_CELLS_PER_NDC);
+                g.uy = __fmul_rn(__fadd_rn(g.cy, 1.0f), FC_CELLS_PER_NDC);
+                const size_t o = img_off + (size_t)row * w + col;
+                float prev = 0.0f; int prev_id = 0;
+                if (batch > 0) { prev = P.imgs[o]; prev_id = P.winner ? P.winner[o] : 0; }
+                // nothing beyond r2cap can change the output of this pixel
+                float r2cap = s_zero;
+                if (minus1_ok) r2cap = fminf(r2cap, __fmul_rn(FC_EXP_MINUS1, inv_k));
+                const int cand = s_cand[pl];
+                float s1 = cand == 0xFFFF ? INFINITY : score_of(S, cand, g), s2; int a1;
+                disc_find(S, g, r2cap, inv_k, s1, s2, a1);
+                float val = 0.0f; int id = 0;
+                if (a1 >= 0 && s1 <= r2cap) {
+                    const float m = score_margin(s1, inv_k);
+                    const bool denorm = __fmul_rn(s1, -P.negk) >= FC_EXP_DENORM;
+                    if (!denorm && s2 > s1 + m) {
+                        val = exact_value(S, E, a1, g, id);
+                    } else {
+                        disc_exact(S, E, g, denorm ? s_zero : s1 + m, val, id);
+                    }
+                    if (val == 0.0f) id = 0;              // all-zero pixel: torch.max returns index 0
+                }
+                if (batch > 0 && !(val > prev)) { val = prev; id = prev_id; }
+                P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
+                if (P.winner) P.winner[o] = id;
             }
+            __syncthreads();
         }
-        __syncthreads();
         c0 += cnt; ++batch;
     } while (c0 < hi);
+
+    // empty cloud: the reference would raise; the batched C ABI writes the background and winner -1
+    if (hi <= lo && P.winner) {
+        for (int p = tid; p < npix; p += FC_THREADS) P.winner[img_off + p] = -1;
+    }
 }
 
 }  // namespace scream
