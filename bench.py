@@ -32,6 +32,7 @@ sys.path.insert(0, ROOT)
 
 N_PTS, V, W_IMG, RHO = 10_000, 6, 64, 24
 METRIC, UNIT = "depth_images_per_sec", "images/s"
+CLOUD = "unit_ball"
 
 
 def peaks():
@@ -80,13 +81,17 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------
 # synthetic cfg2 batch (host, pinned)
 # --------------------------------------------------------------------------------------------
-def make_batch(B: int, seed: int):
-    """B pairs of unit-ball clouds (3DMatch normalisation, three_d_match.py:183-190) + GT poses."""
+def make_batch(B: int, seed: int, cloud: str = "ball"):
+    """B pairs of unit-ball clouds (3DMatch normalisation, three_d_match.py:183-190) + GT poses.
+    cloud="shell": the SURVEY 8d realism variant (points on the faces of a random box, sigma 0.003)."""
     from scream_b200 import synth
     rng = np.random.default_rng(seed)
-    d = rng.standard_normal((B * 2 * N_PTS, 3)).astype(np.float32)
-    d /= np.linalg.norm(d, axis=1, keepdims=True)
-    xyz = d * (rng.random((B * 2 * N_PTS, 1), dtype=np.float32) ** np.float32(1 / 3))
+    if cloud == "shell":
+        xyz = np.concatenate([synth.room_shell(N_PTS, seed * 7919 + i) for i in range(2 * B)], 0)
+    else:
+        d = rng.standard_normal((B * 2 * N_PTS, 3)).astype(np.float32)
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        xyz = d * (rng.random((B * 2 * N_PTS, 1), dtype=np.float32) ** np.float32(1 / 3))
     pose = np.stack([synth.random_pose(seed * 100003 + b) for b in range(B)])
     offs = np.arange(2 * B + 1, dtype=np.int64) * N_PTS
     grad = rng.standard_normal((B, V, 2, W_IMG, W_IMG), dtype=np.float32)
@@ -158,7 +163,7 @@ def run_reference(args, rank: int):
 
 def config_dict(B: int):
     return {"workload": "cfg2: 3DMatch training-batch render, fake fwd(+winner)+bwd and real(posed) fwd",
-            "pairs_per_gpu": B, "n_src": N_PTS, "n_tgt": N_PTS, "views": V, "w": W_IMG, "rho": RHO,
+            "pairs_per_gpu": B, "cloud": CLOUD, "n_src": N_PTS, "n_tgt": N_PTS, "views": V, "w": W_IMG, "rho": RHO,
             "images_per_step_per_gpu": 24 * B, "cache": "inputs+outputs per step exceed the 126 MB L2 (B>=512)",
             "parallelism": "items sharded over GPUs, no data-path collective"}
 
@@ -177,7 +182,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     torch.cuda.set_device(dev)
     B = args.batch
     views = view_matrices(RegistrationRender(RHO, W_IMG, device="cpu").eulers).to(dev)
-    h_xyz, h_offs, h_pose, h_grad = [t.pin_memory() for t in make_batch(B, 1234 + rank)]
+    h_xyz, h_offs, h_pose, h_grad = [t.pin_memory() for t in make_batch(B, 1234 + rank, args.cloud)]
     xyz, offs, pose, grad = [t.to(dev) for t in (h_xyz, h_offs, h_pose, h_grad)]
     max_item = 2 * N_PTS
     dense = args.dense
@@ -301,7 +306,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dense", action="store_true", help="force the dense exact kernel")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cloud", default="ball", choices=["ball", "shell"], help="synthetic cloud family (cfg2 default: ball)")
     args = ap.parse_args()
+    global CLOUD
+    CLOUD = "unit_ball" if args.cloud == "ball" else "room_shell"
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -33,8 +33,8 @@
 
 namespace scream {
 
-constexpr int FC_THREADS = 512;
-constexpr int FC_PPT = 24;                               // points per thread per batch
+constexpr int FC_THREADS = 1024;
+constexpr int FC_PPT = 12;                               // points per thread per batch
 constexpr int FC_CAP = FC_THREADS * FC_PPT;              // 12288 points per batch
 constexpr int FC_G = 64;                                 // cell grid side
 constexpr int FC_CELLS = FC_G * FC_G;
@@ -55,6 +55,7 @@ constexpr size_t FC_SMEM = FC_OFF_SCRATCH + (size_t)(FC_CELLS + 4) * 4;
 
 struct FcShared {
     const float2* xy; const float* c; const int* idx; const unsigned short* start;
+    const unsigned long long* rowmask; const unsigned long long* blockmask;   // cell occupancy: per grid row, per 4 rows
 };
 
 __device__ __forceinline__ int cell_of(float x) {
@@ -83,52 +84,9 @@ __device__ __forceinline__ float score_of(const FcShared& S, int s, const PixelG
     return __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, S.c[s]));
 }
 
-// column span [j0, j1] of grid row i inside the disc of radius rc (cells) around (ux, uy); false if empty
-__device__ __forceinline__ bool row_span(int i, int ci, float fy, int d, bool up, float ux, float rc, int& j0, int& j1) {
-    if (i < 0 || i >= FC_G) return false;
-    // distance from the pixel centre to the band [i, i+1]
-    const float dist = d == 0 ? 0.0f : (up ? __fadd_rn(fy, (float)(d - 1)) : __fsub_rn((float)d, fy));
-    const float h2 = __fmaf_rn(rc, rc, -__fmul_rn(dist, dist));
-    if (!(h2 >= 0.0f)) return false;
-    const float hw = sqrtf(h2) + 1e-3f;
-    j0 = max(0, (int)floorf(ux - hw));
-    j1 = min(FC_G - 1, (int)floorf(ux + hw));
-    (void)ci;
-    return j0 <= j1;
-}
-
-// Disc scan, score domain.  On entry s1 is an upper bound of the best score (or +inf) and r2cap the
-// largest squared radius that can matter.  On exit s1/a1 = best score / its record, s2 = runner-up.
-__device__ __forceinline__ void disc_find(const FcShared& S, const PixelGeom& g, float r2cap, float inv_k,
-                                          float& s1, float& s2, int& a1)
-{
-    const int ci = (int)g.uy;
-    const float fy = __fsub_rn(g.uy, (float)ci);
-    float r2 = fminf(r2cap, s1 + score_margin(s1, inv_k));
-    float rc = radius_cells(r2);
-    s1 = INFINITY; s2 = INFINITY; a1 = -1;
-    for (int d = 0; d < FC_G; ++d) {
-        const bool up_live = (d == 0) || (__fadd_rn(fy, (float)(d - 1)) <= rc);
-        const bool dn_live = (d > 0) && (__fsub_rn((float)d, fy) <= rc);
-        if (!up_live && !dn_live) break;
-        for (int side = 0; side < 2; ++side) {
-            if (side == 1 && d == 0) break;
-            const int i = side ? ci + d : ci - d;
-            int j0, j1;
-            if (!row_span(i, ci, fy, d, side == 0, g.ux, rc, j0, j1)) continue;
-            const int b = S.start[i * FC_G + j0], e = S.start[i * FC_G + j1 + 1];
-            bool improved = false;
-            for (int s = b; s < e; ++s) {
-                const float sc = score_of(S, s, g);
-                s2 = fminf(s2, fmaxf(sc, s1));
-                if (sc < s1) { s1 = sc; a1 = s; improved = true; }
-            }
-            if (improved) {
-                r2 = fminf(r2, s1 + score_margin(s1, inv_k));
-                rc = radius_cells(r2);
-            }
-        }
-    }
+// bits j0..j1 (inclusive) of a 64-column occupancy word
+__device__ __forceinline__ unsigned long long col_mask(int j0, int j1) {
+    return ((~0ull) >> (63 - j1)) & ((~0ull) << j0);
 }
 
 // exact value of record s at pixel g: the reference expression, pv recomputed from the point itself
@@ -146,31 +104,71 @@ __device__ __forceinline__ float exact_value(const FcShared& S, const ExactCtx& 
     return pair_value(pair_d2(r.x, r.y, g.cx, g.cy), pv, E.negk);
 }
 
-// Exact pass: every record with score <= s_thr is evaluated with the reference expression.
-__device__ __forceinline__ void disc_exact(const FcShared& S, const ExactCtx& E, const PixelGeom& g, float s_thr,
-                                           float& best, int& arg)
+// Disc scan around pixel g: 4-row blocks of the cell grid outwards from the pixel's row, an occupancy
+// bit-mask test per block and per row (empty space costs a few instructions per 4 rows), then the
+// records of the row's column span from the circle equation.
+//   EXACT == false (score domain): on entry s1 is an upper bound of the best score (or +inf) and r2 the
+//     largest squared radius that can matter; the radius shrinks to the best score (+margin) as records
+//     are found.  On exit s1/a1 = best score / its record, s2 = runner-up score.
+//   EXACT == true: every record with score <= r2 is evaluated with the reference expression and the
+//     (value, lowest index) order is applied directly to best/arg.
+template <bool EXACT>
+__device__ __forceinline__ void disc_scan(const FcShared& S, const ExactCtx& E, const PixelGeom& g, float r2, float inv_k,
+                                          float& s1, float& s2, int& a1, float& best, int& arg)
 {
     const int ci = (int)g.uy;
-    const float fy = __fsub_rn(g.uy, (float)ci);
-    const float rc = radius_cells(s_thr);
-    for (int d = 0; d < FC_G; ++d) {
-        const bool up_live = (d == 0) || (__fadd_rn(fy, (float)(d - 1)) <= rc);
-        const bool dn_live = (d > 0) && (__fsub_rn((float)d, fy) <= rc);
-        if (!up_live && !dn_live) break;
+    const int bi = ci >> 2;
+    const float s_thr = r2;
+    float rc = radius_cells(r2);
+    if (!EXACT) { s1 = INFINITY; s2 = INFINITY; a1 = -1; }
+    for (int db = 0; db < FC_G / 4; ++db) {
+        bool live = false;
         for (int side = 0; side < 2; ++side) {
-            if (side == 1 && d == 0) break;
-            const int i = side ? ci + d : ci - d;
-            int j0, j1;
-            if (!row_span(i, ci, fy, d, side == 0, g.ux, rc, j0, j1)) continue;
-            const int b = S.start[i * FC_G + j0], e = S.start[i * FC_G + j1 + 1];
-            for (int s = b; s < e; ++s) {
-                if (score_of(S, s, g) <= s_thr) {
-                    int id;
-                    const float val = exact_value(S, E, s, g, id);
-                    if (val > best || (val == best && id < arg)) { best = val; arg = id; }
+            if (side == 1 && db == 0) break;
+            const int B = side ? bi + db : bi - db;
+            if (B < 0 || B >= FC_G / 4) continue;
+            const float bdist = db == 0 ? 0.0f : (side ? __fsub_rn((float)(4 * B), g.uy) : __fsub_rn(g.uy, (float)(4 * B + 4)));
+            if (bdist > rc) continue;
+            live = true;
+            const int jlo = max(0, (int)floorf(g.ux - rc)), jhi = min(FC_G - 1, (int)floorf(g.ux + rc));
+            if (jlo > jhi) continue;
+            const unsigned long long cm = col_mask(jlo, jhi);
+            if ((S.blockmask[B] & cm) == 0ull) continue;
+            for (int t = 0; t < 4; ++t) {
+                const int i = side ? 4 * B + t : 4 * B + 3 - t;               // nearest row of the block first
+                const float dist = i == ci ? 0.0f : (i < ci ? __fsub_rn(g.uy, (float)(i + 1)) : __fsub_rn((float)i, g.uy));
+                if (dist > rc) continue;
+                if ((S.rowmask[i] & cm) == 0ull) continue;
+                const float h2 = __fmaf_rn(rc, rc, -__fmul_rn(dist, dist));
+                const float hw = sqrtf(fmaxf(h2, 0.0f)) + 1e-3f;
+                const int j0 = max(0, (int)floorf(g.ux - hw)), j1 = min(FC_G - 1, (int)floorf(g.ux + hw));
+                if (j0 > j1) continue;
+                const int rb = S.start[i * FC_G + j0], re = S.start[i * FC_G + j1 + 1];
+                if (EXACT) {
+#pragma unroll 1
+                    for (int s = rb; s < re; ++s) {
+                        if (score_of(S, s, g) <= s_thr) {
+                            int id;
+                            const float val = exact_value(S, E, s, g, id);
+                            if (val > best || (val == best && id < arg)) { best = val; arg = id; }
+                        }
+                    }
+                } else {
+                    bool improved = false;
+#pragma unroll 1
+                    for (int s = rb; s < re; ++s) {
+                        const float sc = score_of(S, s, g);
+                        s2 = fminf(s2, fmaxf(sc, s1));
+                        if (sc < s1) { s1 = sc; a1 = s; improved = true; }
+                    }
+                    if (improved) {
+                        r2 = fminf(r2, s1 + score_margin(s1, inv_k));
+                        rc = radius_cells(r2);
+                    }
                 }
             }
         }
+        if (!live) break;
     }
 }
 
@@ -187,7 +185,9 @@ forward_culled_kernel(FwdParams P)
     unsigned short* s_queue = s_cand + FC_TPIX;
     __shared__ float s_R[9], s_pose[12];
     __shared__ unsigned s_warp_tot[FC_THREADS / 32];
-    __shared__ unsigned s_qn;
+    __shared__ unsigned s_qfar, s_qnear, s_qhead;
+    __shared__ unsigned long long s_rowmask[FC_G], s_blockmask[FC_G / 4];
+    __shared__ unsigned char s_ring[FC_CELLS];            // Chebyshev distance (cells) to the nearest occupied cell
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int w = P.w, npix = w * w, half = w / 2;
@@ -212,6 +212,7 @@ forward_culled_kernel(FwdParams P)
     // scores beyond s_far cannot change the OUTPUT: all of them when the value is exactly zero; with the
     // normalised output and no winner map, already when val <= 2^-26 ((val-0.5)/0.5 rounds to -1).
     const bool minus1_ok = !raw && P.winner == nullptr;
+    const float r2cap_all = minus1_ok ? fminf(s_zero, __fmul_rn(FC_EXP_MINUS1, inv_k)) : s_zero;
 
     if (P.zrange && c == 0 && tid == 0) {
         P.zrange[((size_t)b * P.V + v) * 2] = zmin;
@@ -220,6 +221,7 @@ forward_culled_kernel(FwdParams P)
     __syncthreads();
 
     FcShared S; S.xy = s_xy; S.c = s_c; S.idx = s_idx; S.start = s_start;
+    S.rowmask = s_rowmask; S.blockmask = s_blockmask;
     ExactCtx E; E.xyz = P.xyz; E.lo = lo; E.R = s_R; E.pose = s_pose; E.posed = posed;
     E.zmin = zmin; E.range = range; E.negk = P.negk;
 
@@ -252,7 +254,7 @@ forward_culled_kernel(FwdParams P)
 
         // ---------------- P2: exclusive scan over the cells -----------------------------------
         {
-            constexpr int PER = FC_CELLS / FC_THREADS;                       // 8 consecutive cells per thread
+            constexpr int PER = FC_CELLS / FC_THREADS;                       // 4 consecutive cells per thread
             unsigned loc[PER], sum = 0;
 #pragma unroll
             for (int k = 0; k < PER; ++k) { loc[k] = s_hist[tid * PER + k]; sum += loc[k]; }
@@ -281,7 +283,22 @@ forward_culled_kernel(FwdParams P)
         }
         __syncthreads();
 
-        // ---------------- P3: scatter records into cell order ---------------------------------
+        // ---------------- P3: occupancy masks + scatter of the records into cell order ---------
+        if (tid < (FC_G / 4) * 32) {                      // warp wq builds rows 4wq..4wq+3
+            const int wq = tid >> 5;
+            unsigned long long bm = 0ull;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int i = 4 * wq + t;
+                const unsigned short* st = s_start + i * FC_G;
+                const unsigned lo32 = __ballot_sync(0xFFFFFFFFu, st[lane + 1] != st[lane]);
+                const unsigned hi32 = __ballot_sync(0xFFFFFFFFu, st[lane + 33] != st[lane + 32]);
+                const unsigned long long rm = ((unsigned long long)hi32 << 32) | lo32;
+                if (lane == 0) s_rowmask[i] = rm;
+                bm |= rm;
+            }
+            if (lane == 0) s_blockmask[wq] = bm;
+        }
 #pragma unroll
         for (int k = 0; k < FC_PPT; ++k) {
             if (packed[k] != 0xFFFFFFFFu) {
@@ -299,11 +316,40 @@ forward_culled_kernel(FwdParams P)
         }
         __syncthreads();
 
+        // ---------------- P3b: Chebyshev distance transform of the cell occupancy -------------
+        // h[i][j] = distance to the nearest occupied cell of row i (bit tricks on the row mask), then
+        // ring[i][j] = min_i' max(|i-i'|, h[i'][j]), rows outwards with early exit.  Lets empty space be
+        // classified without touching the records: a pixel whose ring is >= 2 has nothing in its 3 x 3
+        // window, and its nearest point is at least (ring - 1 + edge) cells away.
+        {
+            unsigned char* s_h = reinterpret_cast<unsigned char*>(s_queue);      // scratch until phase A
+            for (int cell = tid; cell < FC_CELLS; cell += FC_THREADS) {
+                const int i = cell >> 6, j = cell & 63;
+                const unsigned long long m = s_rowmask[i];
+                const unsigned long long ml = m & ((2ull << j) - 1ull), mr = m >> j;
+                int h = FC_G;
+                if (ml) h = j - (63 - __clzll((long long)ml));
+                if (mr) h = min(h, __ffsll((long long)mr) - 1);
+                s_h[cell] = (unsigned char)h;
+            }
+            __syncthreads();
+            for (int cell = tid; cell < FC_CELLS; cell += FC_THREADS) {
+                const int i = cell >> 6;
+                int best = s_h[cell];
+                for (int d = 1; d < best; ++d) {
+                    if (i - d >= 0) best = min(best, max(d, (int)s_h[cell - d * FC_G]));
+                    if (i + d < FC_G) best = min(best, max(d, (int)s_h[cell + d * FC_G]));
+                }
+                s_ring[cell] = (unsigned char)best;
+            }
+            __syncthreads();
+        }
+
         // ---------------- P4: per-pixel search, one 64 x 64 pixel tile at a time ---------------
         const int tiles_side = w / FC_TILE;
         for (int tile = 0; tile < tiles_side * tiles_side; ++tile) {
             const int trow0 = (tile / tiles_side) * FC_TILE, tcol0 = (tile % tiles_side) * FC_TILE;
-            if (tid == 0) s_qn = 0u;
+            if (tid == 0) { s_qfar = 0u; s_qnear = 0u; s_qhead = 0u; }
             __syncthreads();
 
             // ---- phase A: 3 x 3 cells, lane per pixel ----
@@ -320,8 +366,13 @@ forward_culled_kernel(FwdParams P)
                 const float cov2 = __fmul_rn(__fmul_rn(cov, cov), 0.99999f);
                 const int j0 = max(cj - 1, 0), j1 = min(cj + 1, FC_G - 1);
                 float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
-                for (int i = max(ci - 1, 0); i <= min(ci + 1, FC_G - 1); ++i) {
+                const int ring = s_ring[ci * FC_G + cj];
+                // nothing nearer than (ring - 1 + edge) cells: beyond the radius that can change the output?
+                const float dlb = __fmul_rn((float)(ring - 1) + edge, 1.0f / FC_CELLS_PER_NDC);
+                const bool blank = ring >= 2 && __fmul_rn(__fmul_rn(dlb, dlb), 0.99999f) > r2cap_all;
+                for (int i = max(ci - 1, 0); ring < 2 && i <= min(ci + 1, FC_G - 1); ++i) {
                     const int rb = s_start[i * FC_G + j0], re = s_start[i * FC_G + j1 + 1];
+#pragma unroll 1
                     for (int s = rb; s < re; ++s) {
                         const float sc = score_of(S, s, g);
                         s2 = fminf(s2, fmaxf(sc, s1));
@@ -331,6 +382,13 @@ forward_culled_kernel(FwdParams P)
                 const float m = score_margin(s1, inv_k);
                 const bool resolved = (s1 + m < cov2) && (s2 > s1 + m) && (__fmul_rn(s1, -P.negk) < FC_EXP_DENORM);
                 s_cand[pl] = (unsigned short)(a1 < 0 ? 0xFFFF : a1);
+                if (blank) {                              // background: value 0 (index 0), or what earlier batches found
+                    const size_t o = img_off + (size_t)row * w + col;
+                    float val = 0.0f; int id = 0;
+                    if (batch > 0) { val = P.imgs[o]; id = P.winner ? P.winner[o] : 0; }
+                    P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
+                    if (P.winner) P.winner[o] = id;
+                }
                 if (resolved) {
                     int id;
                     float val = exact_value(S, E, a1, g, id);
@@ -342,20 +400,33 @@ forward_culled_kernel(FwdParams P)
                     P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
                     if (P.winner) P.winner[o] = id;
                 }
-                const unsigned um = __ballot_sync(0xFFFFFFFFu, !resolved);
-                if (um) {
-                    unsigned base = 0;
-                    if (lane == 0) base = atomicAdd(&s_qn, (unsigned)__popc(um));
-                    base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                    if (!resolved) s_queue[base + __popc(um & ((1u << lane) - 1u))] = (unsigned short)pl;
+                // unresolved pixels: "far" ones (nothing within the window: the expensive scans) are queued
+                // from the front, the rest from the back; phase C drains front to back.
+                const bool far = !resolved && !blank && a1 < 0, near = !resolved && a1 >= 0;
+                const unsigned fm = __ballot_sync(0xFFFFFFFFu, far), nm = __ballot_sync(0xFFFFFFFFu, near);
+                if (fm | nm) {
+                    unsigned fb = 0, nb = 0;
+                    if (lane == 0) {
+                        if (fm) fb = atomicAdd(&s_qfar, (unsigned)__popc(fm));
+                        if (nm) nb = atomicAdd(&s_qnear, (unsigned)__popc(nm));
+                    }
+                    fb = __shfl_sync(0xFFFFFFFFu, fb, 0); nb = __shfl_sync(0xFFFFFFFFu, nb, 0);
+                    const unsigned lt = (1u << lane) - 1u;
+                    if (far) s_queue[fb + __popc(fm & lt)] = (unsigned short)pl;
+                    if (near) s_queue[FC_TPIX - 1 - (nb + __popc(nm & lt))] = (unsigned short)pl;
                 }
             }
             __syncthreads();
 
             // ---- phase C: disc scan for the unresolved pixels ----
-            const int qn = (int)s_qn;
-            for (int qi = tid; qi < qn; qi += FC_THREADS) {
-                const int pl = s_queue[qi];
+            const int nfar = (int)s_qfar, qn = nfar + (int)s_qnear;
+            for (;;) {
+                int qi = 0;
+                if (lane == 0) qi = (int)atomicAdd(&s_qhead, 32u);
+                qi = __shfl_sync(0xFFFFFFFFu, qi, 0) + lane;
+                if (qi - lane >= qn) break;
+                if (qi >= qn) continue;
+                const int pl = qi < nfar ? s_queue[qi] : s_queue[FC_TPIX - 1 - (qi - nfar)];
                 const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
                 PixelGeom g;
                 g.cx = pixel_centre(col, half); g.cy = pixel_centre(row, half);
@@ -365,19 +436,26 @@ forward_culled_kernel(FwdParams P)
                 float prev = 0.0f; int prev_id = 0;
                 if (batch > 0) { prev = P.imgs[o]; prev_id = P.winner ? P.winner[o] : 0; }
                 // nothing beyond r2cap can change the output of this pixel
-                float r2cap = s_zero;
-                if (minus1_ok) r2cap = fminf(r2cap, __fmul_rn(FC_EXP_MINUS1, inv_k));
+                const float r2cap = r2cap_all;
                 const int cand = s_cand[pl];
                 float s1 = cand == 0xFFFF ? INFINITY : score_of(S, cand, g), s2; int a1;
-                disc_find(S, g, r2cap, inv_k, s1, s2, a1);
                 float val = 0.0f; int id = 0;
+                disc_scan<false>(S, E, g, fminf(r2cap, s1 + score_margin(s1, inv_k)), inv_k, s1, s2, a1, val, id);
                 if (a1 >= 0 && s1 <= r2cap) {
-                    const float m = score_margin(s1, inv_k);
-                    const bool denorm = __fmul_rn(s1, -P.negk) >= FC_EXP_DENORM;
-                    if (!denorm && s2 > s1 + m) {
+                    // scores within s_thr of the best may swap order through rounding.  In the denormal
+                    // range the value is a multiple of 2^-149: two values closer than ~8 of those may tie
+                    // or swap, i.e. scores within -ln(1 - u)/k <= 1.5 u/k, u = 8 * 2^-149 * e^(k s1);
+                    // from u >= 1/2 on (the last ~2.5 e-folds above zero) everything non-zero is evaluated.
+                    float s_thr = s1 + score_margin(s1, inv_k);
+                    const float e1 = __fmul_rn(s1, -P.negk);
+                    if (e1 >= FC_EXP_DENORM) {
+                        const float lu = e1 - 101.2f;                 // ln u
+                        s_thr = lu >= -0.7f ? s_zero : s_thr + 1.5f * expf(lu) * inv_k;
+                    }
+                    if (s2 > s_thr) {
                         val = exact_value(S, E, a1, g, id);
                     } else {
-                        disc_exact(S, E, g, denorm ? s_zero : s1 + m, val, id);
+                        disc_scan<true>(S, E, g, fminf(s_thr, s_zero), inv_k, s1, s2, a1, val, id);
                     }
                     if (val == 0.0f) id = 0;              // all-zero pixel: torch.max returns index 0
                 }
