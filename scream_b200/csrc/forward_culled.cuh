@@ -155,8 +155,43 @@ __device__ __forceinline__ void disc_scan(const FcShared& S, const ExactCtx& E, 
                     }
                 } else {
                     bool improved = false;
+                    int rb2 = rb;
+                    if (s1 == INFINITY) {
+                        // no bound yet: take the occupied cell of this row nearest to the pixel's column first,
+                        // so the rest of the (possibly long) span is cut by the radius it gives
+                        const unsigned long long rm = S.rowmask[i] & col_mask(j0, j1);
+                        const int cj = min(max((int)g.ux, j0), j1);
+                        const unsigned long long ml = rm & ((2ull << cj) - 1ull), mr = rm >> cj;
+                        int jn = -1;
+                        if (ml) jn = 63 - __clzll((long long)ml);
+                        if (mr) { const int jr = cj + __ffsll((long long)mr) - 1; if (jn < 0 || jr - cj < cj - jn) jn = jr; }
+                        if (jn >= 0) {
+                            const int nb = S.start[i * FC_G + jn], ne = S.start[i * FC_G + jn + 1];
 #pragma unroll 1
-                    for (int s = rb; s < re; ++s) {
+                            for (int s = nb; s < ne; ++s) {
+                                const float sc = score_of(S, s, g);
+                                if (sc < s1) { s1 = sc; }
+                            }
+                            // radius from this bound; the full span below re-visits the cell (s1/s2/a1 stay consistent)
+                            const float r2n = fminf(r2, s1 + score_margin(s1, inv_k));
+                            const float rcn = radius_cells(r2n);
+                            const float h2n = __fmaf_rn(rcn, rcn, -__fmul_rn(dist, dist));
+                            const float hwn = sqrtf(fmaxf(h2n, 0.0f)) + 1e-3f;
+                            const int j0n = max(j0, (int)floorf(g.ux - hwn)), j1n = min(j1, (int)floorf(g.ux + hwn));
+                            rb2 = S.start[i * FC_G + j0n];
+                            const int re2 = S.start[i * FC_G + j1n + 1];
+                            s1 = INFINITY;
+#pragma unroll 1
+                            for (int s = rb2; s < re2; ++s) {
+                                const float sc = score_of(S, s, g);
+                                s2 = fminf(s2, fmaxf(sc, s1));
+                                if (sc < s1) { s1 = sc; a1 = s; improved = true; }
+                            }
+                            rb2 = re;                     // span done
+                        }
+                    }
+#pragma unroll 1
+                    for (int s = rb2; s < re; ++s) {
                         const float sc = score_of(S, s, g);
                         s2 = fminf(s2, fmaxf(sc, s1));
                         if (sc < s1) { s1 = sc; a1 = s; improved = true; }
