@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define SCREAM_ABI_VERSION 2
+#define SCREAM_ABI_VERSION 3
 
 /* error codes */
 #define SCREAM_OK            0
@@ -56,6 +56,10 @@ extern "C" {
                                     instead of (img-0.5)/0.5 (render.py:69, RegistrationRender.forward) */
 #define SCREAM_F_DENSE      2u   /* force the dense exact kernel (every point x every pixel); default is the
                                     culled exact kernel, which returns bit-identical results */
+
+#define SCREAM_F_ZRANGE_IN  4u   /* zrange [B,V,2] is an INPUT: the depth range of render.py:30-31 was reduced by the
+                                    caller (point-sharded clouds: every shard must normalise with the range of
+                                    the WHOLE cloud, scream_b200/shard.py); the z-range kernel is skipped */
 
 /* opaque CUDA stream handle (cudaStream_t / CUstream) */
 typedef void *scream_stream_t;
@@ -72,7 +76,8 @@ int scream_render_workspace_bytes(int B, int V, int w, int64_t total_pts, size_t
  * independent (source, target) pairs in one launch sequence.
  *   rho: the reference's rho (render.py:10,43); the weight is exp(-d2/2 * (float)(rho*rho)).
  *   w:   image side, w % 64 == 0 (render.py:33-34,55).
- *   winner may be NULL (inference / "real" render); zrange may be NULL.
+ *   winner may be NULL (inference / "real" render); zrange may be NULL (output), or, with
+ *   SCREAM_F_ZRANGE_IN, must hold the (zmin, zmax) pairs to use.
  *   max_item_pts: an upper bound of n+m over the items (sizes the z-range grid without reading offs on
  *   the host); 0 = unknown, total_pts is used.
  */

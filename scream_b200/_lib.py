@@ -11,10 +11,11 @@ import threading
 
 from .csrc import build as _build
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 F_RAW = 1
 F_DENSE = 2
+F_ZRANGE_IN = 4
 
 _lock = threading.Lock()
 _lib = None

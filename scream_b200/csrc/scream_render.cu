@@ -91,14 +91,17 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
     if (!ws || ws_bytes < L.total) return fail(SCREAM_E_WORKSPACE, "workspace needs %zu bytes, got %zu", L.total, ws_bytes);
     cudaStream_t st = (cudaStream_t)stream;
     unsigned* zenc = reinterpret_cast<unsigned*>((char*)ws + L.zenc_off);
-    if (int rc = launch_zrange(xyz, offs, total_pts, max_item_pts, pose, views, B, V, zenc, st)) return rc;
+    if (flags & SCREAM_F_ZRANGE_IN) {
+        if (!zrange) return fail(SCREAM_E_ARG, "SCREAM_F_ZRANGE_IN needs a zrange buffer");
+        zrange_encode_kernel<<<(B * V * 2 + 255) / 256, 256, 0, st>>>(zrange, zenc, B * V * 2);
+    } else if (int rc = launch_zrange(xyz, offs, total_pts, max_item_pts, pose, views, B, V, zenc, st)) return rc;
 
     FwdParams P;
     P.xyz = xyz; P.offs = offs; P.pose = pose; P.views = views; P.zenc = zenc;
     P.B = B; P.V = V; P.w = w;
     const float rho2 = (float)(rho * rho);           // tensor * python scalar -> scalar cast to fp32
     P.negk = -rho2 * 0.5f; P.inv_negk = 1.0f / P.negk;
-    P.flags = flags; P.imgs = imgs; P.winner = winner; P.zrange = zrange;
+    P.flags = flags; P.imgs = imgs; P.winner = winner; P.zrange = (flags & SCREAM_F_ZRANGE_IN) ? nullptr : zrange;
     if (flags & SCREAM_F_DENSE) {
         const long long grid = (long long)B * V * 2 * (w * w / FD_TILE);
         forward_dense_kernel<<<(unsigned)grid, FD_THREADS, 0, st>>>(P);

@@ -80,6 +80,12 @@ zrange_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ offs,
     }
 }
 
+// caller-supplied zrange floats [B][V][2] -> zenc (SCREAM_F_ZRANGE_IN)
+__global__ void zrange_encode_kernel(const float* __restrict__ zrange, unsigned* __restrict__ zenc, int count) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) zenc[i] = enc_f32(zrange[i]);
+}
+
 // decode zenc -> zrange floats [B][V][2]
 __global__ void zrange_decode_kernel(const unsigned* __restrict__ zenc, float* __restrict__ zrange, int count) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -41,9 +41,10 @@ def _stream_ptr(dev: torch.device) -> int:
 # ----------------------------------------------------------------------------------------------
 @torch.library.custom_op("scream::render_fwd", mutates_args=())
 def render_fwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tensor], views: torch.Tensor,
-               w: int, rho: float, flags: int, want_winner: bool, max_item_pts: int
+               w: int, rho: float, flags: int, want_winner: bool, max_item_pts: int,
+               zrange_in: Optional[torch.Tensor] = None
                ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    _require_cuda(xyz, offs, pose, views)
+    _require_cuda(xyz, offs, pose, views, zrange_in)
     lib = _lib.load()
     assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.dim() == 2 and xyz.shape[1] == 3
     assert offs.dtype == torch.int64 and offs.is_contiguous() and offs.numel() % 2 == 1
@@ -55,7 +56,12 @@ def render_fwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tenso
     with torch.cuda.device(dev):
         imgs = torch.empty((B, V, 2, w, w), dtype=torch.float32, device=dev)
         winner = torch.empty((B, V, 2, w, w) if want_winner else (0,), dtype=torch.int32, device=dev)
-        zrange = torch.empty((B, V, 2), dtype=torch.float32, device=dev)
+        if zrange_in is not None:                 # point-sharded clouds: the range of the WHOLE cloud (shard.py)
+            assert zrange_in.shape == (B, V, 2) and zrange_in.dtype == torch.float32
+            zrange = zrange_in.contiguous().clone()
+            flags |= _lib.F_ZRANGE_IN
+        else:
+            zrange = torch.empty((B, V, 2), dtype=torch.float32, device=dev)
         nws = _lib.workspace_bytes(B, V, w, total)
         ws = torch.empty((nws,), dtype=torch.uint8, device=dev)
         rc = lib.scream_render_forward(_ptr(xyz), _ptr(offs), total, max_item_pts, _ptr(pose), _ptr(views),
@@ -67,7 +73,7 @@ def render_fwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tenso
 
 
 @render_fwd.register_fake
-def _(xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts):
+def _(xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts, zrange_in=None):
     B, V = (offs.numel() - 1) // 2, views.shape[0]
     return (xyz.new_empty((B, V, 2, w, w)),
             xyz.new_empty((B, V, 2, w, w) if want_winner else (0,), dtype=torch.int32),
@@ -99,7 +105,7 @@ def _(xyz, offs, pose, views, w, rho, flags, grad_imgs, winner, zrange, max_item
 
 
 def _setup_ctx(ctx, inputs, output):
-    xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts = inputs
+    xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts, _zr_in = inputs
     _, winner, zrange = output
     if pose is not None:
         ctx.save_for_backward(xyz, offs, pose, views, winner, zrange)
@@ -117,7 +123,7 @@ def _backward(ctx, g_imgs, g_winner, g_zrange):
         pose = None
     w, rho, flags, max_item_pts = ctx.cfg
     g = torch.ops.scream.render_bwd(xyz, offs, pose, views, w, rho, flags, g_imgs, winner, zrange, max_item_pts)
-    return g, None, None, None, None, None, None, None, None
+    return g, None, None, None, None, None, None, None, None, None
 
 
 render_fwd.register_autograd(_backward, setup_context=_setup_ctx)
@@ -139,16 +145,69 @@ def make_offsets(sizes: Sequence[Tuple[int, int]]) -> torch.Tensor:
 
 def render_batch(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho, w: int,
                  pose: Optional[torch.Tensor] = None, raw: bool = False, dense: bool = False,
-                 need_winner: Optional[bool] = None, max_item_pts: int = 0):
+                 need_winner: Optional[bool] = None, max_item_pts: int = 0,
+                 zrange_in: Optional[torch.Tensor] = None):
     """Render B pairs at once.  xyz [total,3] fp32 cuda, offs [2B+1] int64 cuda, views [V,3,3] fp32 cuda,
-    pose [B,3,4] or None.  Returns (imgs [B,V,2,w,w], winner int32 or empty, zrange [B,V,2])."""
+    pose [B,3,4] or None; zrange_in [B,V,2]: use this depth range instead of reducing it (point-sharded
+    clouds, scream_b200/shard.py).  Returns (imgs [B,V,2,w,w], winner int32 or empty, zrange [B,V,2])."""
     if w < 64 or w % 64:
         raise ValueError("w must be a positive multiple of 64 (render.py:33-34,55)")
     if need_winner is None:
         need_winner = torch.is_grad_enabled() and xyz.requires_grad
     flags = (_lib.F_RAW if raw else 0) | (_lib.F_DENSE if dense else 0)
     return torch.ops.scream.render_fwd(xyz, offs, pose, views, int(w), float(rho), int(flags),
-                                       bool(need_winner), int(max_item_pts))
+                                       bool(need_winner), int(max_item_pts), zrange_in)
+
+
+def depth_range(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, pose: Optional[torch.Tensor] = None,
+                max_item_pts: int = 0) -> torch.Tensor:
+    """[B,V,2] (zmin, zmax) of the rotated depth over both clouds of every item (render.py:30-31), on the
+    device, no host sync.  Used by the point-sharded path (shard.py) before the cross-rank min/max."""
+    _require_cuda(xyz, offs, views, pose)
+    lib = _lib.load()
+    B, V, total = (offs.numel() - 1) // 2, views.shape[0], xyz.shape[0]
+    dev = xyz.device
+    with torch.cuda.device(dev):
+        zr = torch.empty((B, V, 2), dtype=torch.float32, device=dev)
+        nws = _lib.workspace_bytes(B, V, 64, total)
+        ws = torch.empty((nws,), dtype=torch.uint8, device=dev)
+        rc = lib.scream_render_transform(_ptr(xyz), _ptr(offs), total, int(max_item_pts), _ptr(pose), _ptr(views),
+                                         B, V, None, None, _ptr(zr), _ptr(ws), nws, _stream_ptr(dev))
+    _lib.check(rc, "scream_render_transform")
+    return zr
+
+
+def render_cloud_point_sharded(src_local: torch.Tensor, tgt_local: torch.Tensor, src_offset: int, tgt_offset: int,
+                               views: torch.Tensor, rho, w: int, group=None):
+    """One giant pair, points sharded over the ranks of `group` (BASELINE config 5; shard.py has the
+    protocol).  Every rank passes its rows and their global offsets; all ranks get the same
+    (imgs [V,2,w,w], val, winner_global int64, zrange [V,2]), bit-identical to the unsharded render."""
+    from . import shard
+    dev = src_local.device
+
+    def pair(src, tgt):
+        xyz = torch.cat([src.float(), tgt.float()], 0).contiguous()
+        offs = torch.tensor([0, src.shape[0], src.shape[0] + tgt.shape[0]], dtype=torch.int64, device=dev)
+        return xyz, offs
+
+    def range_fn(src, tgt):
+        xyz, offs = pair(src, tgt)
+        if xyz.shape[0] == 0:
+            z = torch.empty((views.shape[0], 2), dtype=torch.float32, device=dev)
+            z[:, 0], z[:, 1] = float("inf"), float("-inf")
+            return z
+        return depth_range(xyz, offs, views)[0]
+
+    def render_fn(src, tgt, zr):
+        xyz, offs = pair(src, tgt)
+        if xyz.shape[0] == 0:
+            V = views.shape[0]
+            return (torch.zeros((V, 2, w, w), device=dev), torch.full((V, 2, w, w), -1, dtype=torch.int32, device=dev))
+        val, win, _ = render_batch(xyz, offs, views, rho, w, raw=True, need_winner=True, zrange_in=zr[None].contiguous())
+        return val[0], win[0]
+
+    with torch.no_grad():
+        return shard.render_cloud_point_sharded(src_local, tgt_local, src_offset, tgt_offset, range_fn, render_fn, group)
 
 
 class RegistrationRender(nn.Module):

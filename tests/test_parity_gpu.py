@@ -216,3 +216,34 @@ def test_culled_equals_dense_bitwise(case):
     assert torch.equal(a[2], b[2])
     c = render_batch(xyz, offs, views, rho, w, raw=False, dense=False, need_winner=False)
     assert torch.equal(c[0], (a[0] - 0.5) / 0.5)
+
+
+def test_point_sharded_merge_equals_unsharded():
+    """SURVEY 8e, giant-cloud mode emulated on one GPU: two point shards rendered with the depth range of the
+    whole cloud (SCREAM_F_ZRANGE_IN), merged through the int64 keys -> bit-identical to the unsharded render."""
+    from scream_b200 import shard
+    from scream_b200.render import depth_range
+    src, tgt = synth.unit_ball(9001, 41), synth.room_shell(7003, 42)
+    views = torch.from_numpy(synth.random_views(3, 9)).to(DEV)
+    xyz = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV)
+    offs = make_offsets([(len(src), len(tgt))]).to(DEV)
+    val, win, zr = render_batch(xyz, offs, views, 24, 64, raw=True, need_winner=True)
+    assert torch.equal(depth_range(xyz, offs, views), zr)
+    keys, zrs = [], []
+    world = 3
+    spans = [(shard.balanced_slice(len(src), r, world), shard.balanced_slice(len(tgt), r, world)) for r in range(world)]
+    for (slo, shi), (tlo, thi) in spans:
+        x = torch.from_numpy(np.concatenate([src[slo:shi], tgt[tlo:thi]], 0)).to(DEV)
+        o = make_offsets([(shi - slo, thi - tlo)]).to(DEV)
+        zrs.append(depth_range(x, o, views))
+    zr_all = torch.stack([torch.stack(zrs)[..., 0].min(0)[0], torch.stack(zrs)[..., 1].max(0)[0]], -1)
+    assert torch.equal(zr_all, zr)
+    for (slo, shi), (tlo, thi) in spans:
+        x = torch.from_numpy(np.concatenate([src[slo:shi], tgt[tlo:thi]], 0)).to(DEV)
+        o = make_offsets([(shi - slo, thi - tlo)]).to(DEV)
+        v, wn, _ = render_batch(x, o, views, 24, 64, raw=True, need_winner=True, zrange_in=zr_all)
+        off = torch.tensor([slo, tlo], device=DEV).view(1, 1, 2, 1, 1)
+        keys.append(shard.pack_keys(v, wn.long() + off))
+    v2, i2 = shard.unpack_keys(torch.stack(keys).max(0)[0])
+    assert torch.equal(v2, val)
+    assert torch.equal(i2, win.long())
