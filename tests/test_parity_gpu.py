@@ -247,3 +247,30 @@ def test_point_sharded_merge_equals_unsharded():
     v2, i2 = shard.unpack_keys(torch.stack(keys).max(0)[0])
     assert torch.equal(v2, val)
     assert torch.equal(i2, win.long())
+
+
+def test_host_pipeline_equals_render_batch():
+    """scream_b200.pipeline.StepPipeline (chunks over CUDA streams, pinned host buffers) == one render_batch call."""
+    from scream_b200.pipeline import StepPipeline
+    sizes = [(700, 650), (512, 300), (40, 900), (1000, 1000), (333, 77)]
+    V, w, rho = 6, 64, 24
+    views = view_matrices(RegistrationRender(rho, w, device="cpu").eulers)
+    parts = []
+    for i, (n, m) in enumerate(sizes):
+        parts += [synth.unit_ball(n, 300 + i), synth.room_shell(m, 400 + i)]
+    h_xyz = torch.from_numpy(np.concatenate(parts, 0)).pin_memory()
+    h_pose = torch.from_numpy(np.stack([synth.random_pose(50 + i) for i in range(len(sizes))])).pin_memory()
+    h_grad = torch.from_numpy(np.random.default_rng(3).standard_normal((len(sizes), V, 2, w, w)).astype(np.float32)).pin_memory()
+    o_fake, o_real = torch.empty_like(h_grad).pin_memory(), torch.empty_like(h_grad).pin_memory()
+    o_g = torch.empty_like(h_xyz).pin_memory()
+    pipe = StepPipeline(sizes, views, rho, w, DEV, chunk_pairs=2, n_streams=3)
+    pipe.run(h_xyz, h_pose, h_grad, o_fake, o_real, o_g)
+    pipe.synchronize()
+    x = h_xyz.to(DEV).requires_grad_(True)
+    offs = make_offsets(sizes).to(DEV)
+    fake, _, _ = render_batch(x, offs, views.to(DEV), rho, w, need_winner=True)
+    fake.backward(h_grad.to(DEV))
+    real, _, _ = render_batch(x.detach(), offs, views.to(DEV), rho, w, pose=h_pose.to(DEV), need_winner=False)
+    assert torch.equal(o_fake, fake.detach().cpu())
+    assert torch.equal(o_real, real.cpu())
+    assert np.abs(o_g.numpy() - x.grad.cpu().numpy()).max() <= 1e-5 * np.abs(x.grad.cpu().numpy()).max()   # atomics order
