@@ -16,6 +16,7 @@ ABI_VERSION = 3
 F_RAW = 1
 F_DENSE = 2
 F_ZRANGE_IN = 4
+F_NOSTREAM = 8
 
 _lock = threading.Lock()
 _lib = None

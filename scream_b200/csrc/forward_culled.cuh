@@ -237,6 +237,15 @@ forward_culled_kernel(FwdParams P)
 
     const ItemSpan sp = item_span(P.offs, b);
     const int64_t lo = c ? sp.tgt0 : sp.src0, hi = c ? sp.end : sp.tgt0;
+    // giant clouds (forward_stream.cuh): render the survivor list of this image instead of the whole cloud,
+    // unless the list overflowed.  npts = number of points to render, pidx(j) = cloud-local index of the j-th.
+    const int* surv = nullptr;
+    int64_t npts = hi - lo;
+    if (P.surv != nullptr) {
+        const size_t img = ((size_t)b * P.V + v) * 2 + c;
+        const unsigned ns = P.surv_cnt[img];
+        if (ns <= (unsigned)P.surv_cap) { surv = P.surv + img * (size_t)P.surv_cap; npts = (int64_t)ns; }
+    }
     const float zmin = dec_f32(P.zenc[((size_t)b * P.V + v) * 2]);
     const float zmax = dec_f32(P.zenc[((size_t)b * P.V + v) * 2 + 1]);
     const float range = z_range(zmin, zmax);
@@ -261,10 +270,10 @@ forward_culled_kernel(FwdParams P)
     E.zmin = zmin; E.range = range; E.negk = P.negk;
 
     int batch = 0;
-    int64_t c0 = lo;
+    int64_t c0 = 0;                                      // position in the point list of this image
     do {                                                 // at least one pass, so empty clouds still write
-        const int cnt = (int)max((int64_t)0, min((int64_t)FC_CAP, hi - c0));
-        const bool last = c0 + cnt >= hi;
+        const int cnt = (int)max((int64_t)0, min((int64_t)FC_CAP, npts - c0));
+        const bool last = c0 + cnt >= npts;
         E.lo = lo;                                        // record indices are cloud-local
 
         // ---------------- P1: transform + histogram -------------------------------------------
@@ -276,7 +285,8 @@ forward_culled_kernel(FwdParams P)
             const int j = k * FC_THREADS + tid;
             packed[k] = 0xFFFFFFFFu;
             if (j < cnt) {
-                const float* q = P.xyz + (size_t)(c0 + j) * 3;
+                const int64_t pi = surv ? (int64_t)__ldg(surv + c0 + j) : c0 + j;
+                const float* q = P.xyz + (size_t)(lo + pi) * 3;
                 float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
                 if (posed) apply_pose(s_pose, x, y, z);
                 const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z);
@@ -338,7 +348,8 @@ forward_culled_kernel(FwdParams P)
         for (int k = 0; k < FC_PPT; ++k) {
             if (packed[k] != 0xFFFFFFFFu) {
                 const int j = k * FC_THREADS + tid;
-                const float* q = P.xyz + (size_t)(c0 + j) * 3;
+                const int64_t pi = surv ? (int64_t)__ldg(surv + c0 + j) : c0 + j;
+                const float* q = P.xyz + (size_t)(lo + pi) * 3;
                 float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
                 if (posed) apply_pose(s_pose, x, y, z);
                 const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z), zr = rot_row(s_R + 6, x, y, z);
@@ -346,7 +357,7 @@ forward_culled_kernel(FwdParams P)
                 s_xy[pos] = make_float2(xr, yr);
                 // c = -ln(pv)/k >= 0; pv == 0 -> +inf (never wins); pv < 0 (rounding corner) -> NaN (never wins)
                 s_c[pos] = __fmul_rn(logf(depth_weight(zr, zmin, range)), P.inv_negk);
-                s_idx[pos] = (int)(c0 - lo) + j;
+                s_idx[pos] = (int)pi;
             }
         }
         __syncthreads();
@@ -428,9 +439,10 @@ forward_culled_kernel(FwdParams P)
                     int id;
                     float val = exact_value(S, E, a1, g, id);
                     const size_t o = img_off + (size_t)row * w + col;
-                    if (batch > 0) {
+                    if (batch > 0) {                      // merge with the earlier batches: (value, lowest index)
                         const float pb = P.imgs[o];
-                        if (!(val > pb)) { val = pb; id = P.winner ? P.winner[o] : 0; }
+                        const int pid = P.winner ? P.winner[o] : 0;
+                        if (!(val > pb || (val == pb && id < pid))) { val = pb; id = pid; }
                     }
                     P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
                     if (P.winner) P.winner[o] = id;
@@ -494,14 +506,14 @@ forward_culled_kernel(FwdParams P)
                     }
                     if (val == 0.0f) id = 0;              // all-zero pixel: torch.max returns index 0
                 }
-                if (batch > 0 && !(val > prev)) { val = prev; id = prev_id; }
+                if (batch > 0 && !(val > prev || (val == prev && id < prev_id))) { val = prev; id = prev_id; }
                 P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
                 if (P.winner) P.winner[o] = id;
             }
             __syncthreads();
         }
         c0 += cnt; ++batch;
-    } while (c0 < hi);
+    } while (c0 < npts);
 
     // empty cloud: the reference would raise; the batched C ABI writes the background and winner -1
     if (hi <= lo && P.winner) {

@@ -23,6 +23,7 @@ struct FwdParams {
     float negk, inv_negk;
     unsigned flags;
     float* imgs; int32_t* winner; float* zrange;
+    const int* surv; const unsigned* surv_cnt; int surv_cap;   // survivor lists of the giant-cloud path, or nullptr
 };
 
 __device__ __forceinline__ float zero_or_cull(float best, float inv_negk) {

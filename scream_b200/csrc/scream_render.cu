@@ -5,8 +5,10 @@
 #include "transform.cuh"
 #include "forward_dense.cuh"
 #include "forward_culled.cuh"
+#include "forward_stream.cuh"
 #include "backward.cuh"
 
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -30,12 +32,31 @@ int fail(int code, const char* fmt, ...) {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-struct WsLayout { size_t zenc_off, total; };
+struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, total; bool stream; int surv_cap; };
 
-WsLayout ws_layout(int B, int V, int /*w*/, int64_t /*total_pts*/) {
+// The giant-cloud pre-filter (forward_stream.cuh) is used when the AVERAGE item reaches FS_MIN_AVG_PTS points
+// (decided from B and total_pts alone, so the workspace query and the forward call agree) and w == 64.
+bool stream_eligible(int B, int w, int64_t total_pts) {
+    return w == 64 && total_pts >= FS_MIN_AVG_PTS * (int64_t)B;
+}
+
+WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
     WsLayout L;
-    L.zenc_off = 0;
-    L.total = align_up((size_t)B * V * 2 * sizeof(unsigned), 256);
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+    L.zenc_off = take((size_t)B * V * 2 * sizeof(unsigned));
+    L.stream = stream_eligible(B, w, total_pts);
+    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = 0;
+    // rim cells of a solid cloud pass the cell-level test wholesale (~2-3 % of the points): keep room for 1/16
+    L.surv_cap = (int)std::min<int64_t>(std::max<int64_t>(FS_SURV_MIN, total_pts / 16), 1 << 26);
+    if (L.stream) {
+        const size_t imgs = (size_t)B * V * 2;
+        L.seed_off = take(imgs * FC_CELLS * sizeof(unsigned));
+        L.cnt_off = take(imgs * sizeof(unsigned));          // directly after seed: one memset clears both
+        L.thr_off = take(imgs * FC_CELLS * sizeof(float2));     // (eff, thr) per cell
+        L.surv_off = take(imgs * (size_t)L.surv_cap * sizeof(int));
+    }
+    L.total = off;
     return L;
 }
 
@@ -102,6 +123,38 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
     const float rho2 = (float)(rho * rho);           // tensor * python scalar -> scalar cast to fp32
     P.negk = -rho2 * 0.5f; P.inv_negk = 1.0f / P.negk;
     P.flags = flags; P.imgs = imgs; P.winner = winner; P.zrange = (flags & SCREAM_F_ZRANGE_IN) ? nullptr : zrange;
+    P.surv = nullptr; P.surv_cnt = nullptr; P.surv_cap = 0;
+    // giant clouds: seed z-buffer -> bounds -> filter, then the culled kernel renders the survivors
+    const int zero_radius = (int)ceilf(sqrtf(FC_EXP_ZERO / (0.5f * rho2)) * FC_CELLS_PER_NDC) + 1;
+    if (L.stream && !(flags & (SCREAM_F_DENSE | SCREAM_F_NOSTREAM)) && zero_radius <= 32) {
+        StreamParams S;
+        S.xyz = xyz; S.offs = offs; S.pose = pose; S.views = views; S.zenc = zenc; S.B = B; S.V = V; S.negk = P.negk;
+        S.seed = reinterpret_cast<unsigned*>((char*)ws + L.seed_off);
+        S.bnd = reinterpret_cast<float2*>((char*)ws + L.thr_off);
+        S.surv_cnt = reinterpret_cast<unsigned*>((char*)ws + L.cnt_off);
+        S.surv = reinterpret_cast<int*>((char*)ws + L.surv_off); S.surv_cap = L.surv_cap;
+        CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
+        const int64_t mi = (max_item_pts <= 0 || max_item_pts > total_pts) ? total_pts : max_item_pts;
+        const int64_t chunks = (mi + FS_CHUNK - 1) / FS_CHUNK;
+        if (B > 65535) return fail(SCREAM_E_UNSUPPORTED, "batch too large for the stream grid");
+        {
+            static thread_local int bound_attr_dev = -1;
+            int dev = 0;
+            CUDA_TRY(cudaGetDevice(&dev));
+            if (bound_attr_dev != dev) {
+                CUDA_TRY(cudaFuncSetAttribute(stream_bound_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_BOUND_SMEM(32)));
+                CUDA_TRY(cudaFuncSetAttribute(stream_seed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_SEED_SMEM));
+                CUDA_TRY(cudaFuncSetAttribute(stream_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_FILTER_SMEM));
+                bound_attr_dev = dev;
+            }
+        }
+        if (chunks > 2147483647LL || V > 65535 * 2) return fail(SCREAM_E_UNSUPPORTED, "cloud too large for the stream grid");
+        stream_seed_kernel<<<dim3((unsigned)chunks, (unsigned)((V + FS_VPC - 1) / FS_VPC), (unsigned)B), FS_THREADS, FS_SEED_SMEM, st>>>(S);
+        stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM(zero_radius), st>>>(S, zero_radius);
+        stream_filter_kernel<<<dim3((unsigned)((mi + FS_FILTER_CHUNK - 1) / FS_FILTER_CHUNK), (unsigned)((V + FS_VPC_FILTER - 1) / FS_VPC_FILTER), (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
+        CUDA_TRY(cudaGetLastError());
+        P.surv = S.surv; P.surv_cnt = S.surv_cnt; P.surv_cap = L.surv_cap;
+    }
     if (flags & SCREAM_F_DENSE) {
         const long long grid = (long long)B * V * 2 * (w * w / FD_TILE);
         forward_dense_kernel<<<(unsigned)grid, FD_THREADS, 0, st>>>(P);
@@ -146,7 +199,8 @@ int scream_render_transform(const float* xyz, const int64_t* offs, int64_t total
                             void* ws, size_t ws_bytes, scream_stream_t stream)
 {
     if (int rc = check_common(xyz, offs, views, B, V, 64, 1.0, total_pts)) return rc;
-    const WsLayout L = ws_layout(B, V, 64, total_pts);
+    WsLayout L = ws_layout(B, V, 64, total_pts);
+    L.total = align_up((size_t)B * V * 2 * sizeof(unsigned), 256);      // only the encoded z range is used here
     if (!ws || ws_bytes < L.total) return fail(SCREAM_E_WORKSPACE, "workspace needs %zu bytes, got %zu", L.total, ws_bytes);
     cudaStream_t st = (cudaStream_t)stream;
     unsigned* zenc = reinterpret_cast<unsigned*>((char*)ws + L.zenc_off);

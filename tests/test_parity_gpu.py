@@ -274,3 +274,40 @@ def test_host_pipeline_equals_render_batch():
     assert torch.equal(o_fake, fake.detach().cpu())
     assert torch.equal(o_real, real.cpu())
     assert np.abs(o_g.numpy() - x.grad.cpu().numpy()).max() <= 1e-5 * np.abs(x.grad.cpu().numpy()).max()   # atomics order
+
+
+GIANT_CASES = [
+    # (n, m, rho, kind, V)
+    (260000, 140000, 24, "ball", 3),            # solid ball: the filter keeps a few thousand points per image
+    (150000, 150000, 24, "shell", 2),           # surfaces + large empty margins (far pixels, unknown-zone thresholds)
+    (200000, 100000, 48, "slab", 2),            # KITTI-like
+    (120000, 90000, 24, "ballx", 2),            # points outside [-1,1]^2 (clamped cells must not seed)
+]
+
+
+@pytest.mark.parametrize("case", GIANT_CASES)
+def test_giant_cloud_stream_filter_is_exact(case):
+    """BASELINE config 5 path: seed z-buffer -> bounds -> filter -> render of the survivors must give the same bits
+    as rendering every batch of the cloud (SCREAM_F_NOSTREAM), values and winner maps."""
+    n, m, rho, kind, V = case
+    if kind == "ball":
+        src, tgt = synth.unit_ball(n, 21), synth.unit_ball(m, 22)
+    elif kind == "ballx":
+        src, tgt = synth.unit_ball(n, 23) * np.float32(1.4), synth.unit_ball(m, 24) * np.float32(1.2)
+    elif kind == "shell":
+        src, tgt = synth.room_shell(n, 25), synth.room_shell(m, 26)
+    else:
+        src, tgt = synth.kitti_slab(n, 27), synth.kitti_slab(m, 28)
+    views = torch.from_numpy(np.concatenate([np.eye(3, dtype=np.float32)[None], synth.random_views(V - 1, 7)], 0)).to(DEV)
+    xyz = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV)
+    offs = make_offsets([(n, m)]).to(DEV)
+    pose = torch.from_numpy(synth.random_pose(3))[None].contiguous().to(DEV)
+    for p in (None, pose):
+        a = render_batch(xyz, offs, views, rho, 64, pose=p, raw=True, need_winner=True, no_stream=True)
+        b = render_batch(xyz, offs, views, rho, 64, pose=p, raw=True, need_winner=True)
+        assert torch.equal(a[2], b[2])
+        assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
+        assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
+    c = render_batch(xyz, offs, views, rho, 64, need_winner=False)
+    d = render_batch(xyz, offs, views, rho, 64, need_winner=False, no_stream=True)
+    assert torch.equal(c[0], d[0])
