@@ -182,7 +182,7 @@ def test_host_entry_point(c_oracle):
 
 CULL_CASES = [
     # (n, m, rho, w, scale, kind)
-    (30000, 13000, 24, 64, 1.0, "ball"),        # more than one shared-memory batch (12288 points)
+    (30000, 13000, 24, 64, 1.0, "ball"),        # more than one shared-memory batch (10240 points)
     (2000, 2500, 24, 64, 1.0, "shell"),         # sparse, realistic 3DMatch density
     (5000, 36, 36, 128, 1.0, "grid"),           # OpenGG w=128, regular grid: exact ties
     (10000, 36, 72, 256, 1.0, "grid"),          # OpenGG w=256
@@ -190,6 +190,8 @@ CULL_CASES = [
     (3000, 3000, 3, 64, 1.0, "ball"),           # very wide Gaussians: windows cover the whole grid
     (64, 16, 48, 64, 0.3, "ball"),              # tiny cloud, mostly empty image
     (20000, 20000, 48, 64, 1.0, "slab"),        # KITTI
+    (3000, 700, 24, 192, 1.0, "ball"),          # w/2 = 96 is not a power of two (pixel centres by IEEE division)
+    (300, 8, 6, 64, 0.5, "ball"),               # wide Gaussians over a tiny cloud: every disc spans many rows
 ]
 
 
