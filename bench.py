@@ -308,8 +308,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dense", action="store_true", help="force the dense exact kernel")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--chunk", type=int, default=32, help="pairs per chunk of the host-buffer pipeline (e2e leg)")
-    ap.add_argument("--streams", type=int, default=4, help="CUDA streams of the host-buffer pipeline (e2e leg)")
+    ap.add_argument("--chunk", type=int, default=37, help="pairs per chunk of the host-buffer pipeline (e2e leg)")
+    ap.add_argument("--streams", type=int, default=6, help="CUDA streams of the host-buffer pipeline (e2e leg)")
     ap.add_argument("--cloud", default="ball", choices=["ball", "shell"], help="synthetic cloud family (cfg2 default: ball)")
     args = ap.parse_args()
     global CLOUD

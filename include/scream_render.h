@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define SCREAM_ABI_VERSION 3
+#define SCREAM_ABI_VERSION 4
 
 /* error codes */
 #define SCREAM_OK            0
@@ -108,6 +108,13 @@ int scream_render_transform(const float *xyz, const int64_t *offs, int64_t total
                             const float *pose, const float *views, int B, int V,
                             float *rotated, float *pv, float *zrange,
                             void *ws, size_t ws_bytes, scream_stream_t stream);
+
+/* Depth images -> colour strip: replaces utils.py:81-91 (deep_to_img) applied to every view and the
+ * np.concatenate(..., axis=1) of train_3d_match.py:212-213, train_kitti.py:211-212, visualize_depth_image.py:27-28.
+ *   imgs [B,V,2,w,w] fp32, the forward call's normalised output;  rgb [B, w, V*w, 3] uint8: view v of item b occupies
+ *   columns [v*w, (v+1)*w).  Component order is the reference's (it hands the array to cv2 as is).
+ * The reference shows / writes the strip with cv2 (imshow is unavailable on this box); here it stays a device buffer. */
+int scream_depth_to_rgb8(const float *imgs, int B, int V, int w, unsigned char *rgb, scream_stream_t stream);
 
 /* Host-buffer convenience entry point (end-to-end path: H2D copies, forward, D2H copies, one stream
  * synchronise).  All pointers are HOST pointers; device staging is allocated per call and freed.

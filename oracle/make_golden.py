@@ -86,8 +86,40 @@ def freeze(name, src, tgt, rho, w, eulers, pose=None, grad=False, view="muti"):
           f"max={v.max():.4f} zero_px={(v == 0).mean():.3f}")
 
 
+def reference_function(path, name, namespace):
+    """Execute ONE unmodified top-level function of a reference file whose module cannot be imported here
+    (utils.py imports open3d): its source segment is compiled as is, in a namespace holding its globals."""
+    import ast
+    src = open(path).read()
+    node = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == name)
+    exec(compile(ast.get_source_segment(src, node), path, "exec"), namespace)
+    return namespace[name]
+
+
+def freeze_colorize():
+    """tests/golden/colorize_strip.npz: the reference's deep_to_img (utils.py:81-91) run on rendered views."""
+    from oracle import colorize_oracle as col
+    ref_fn = reference_function("/root/reference/utils.py", "deep_to_img", {"torch": torch, "np": np})
+    g = np.load(os.path.join(OUT, "cfg2_ball_fake.npz"))
+    imgs = g["imgs"].copy()                                   # [6,2,64,64] from the executed reference renderer
+    rng = np.random.default_rng(3)
+    extra = rng.uniform(-1, 1, (2, 2, 64, 64)).astype(np.float32)
+    extra[0, 1, :32] = extra[0, 0, :32]                       # exact ties between the channels
+    extra[1, :, :8] = np.float32(-1.0)                        # background in both channels
+    imgs = np.concatenate([imgs, extra], 0)
+    t = torch.from_numpy(imgs).permute(0, 2, 3, 1)            # train_3d_match.py:212
+    want = np.concatenate([ref_fn(t[j]) for j in range(t.shape[0])], axis=1)     # :213, reference code verbatim
+    got = col.views_to_strip(imgs)
+    assert want.dtype == np.uint8 and np.array_equal(want, got), "colorize restatement differs from the reference"
+    np.savez_compressed(os.path.join(OUT, "colorize_strip.npz"), imgs=imgs, strip=want)
+    print(f"wrote colorize_strip: imgs {imgs.shape} -> strip {want.shape}, restatement == reference")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--only-colorize" in sys.argv:
+        freeze_colorize()
+        return
     torch.manual_seed(0)
     six = orc.canonical_eulers("muti")
     one = orc.canonical_eulers("single")
@@ -106,6 +138,7 @@ def main():
     freeze("cfg4_opengg_w128", dsm, dem, 36, 128, one, view="single")
     # sparse cloud: most pixels are far from every point (exact zeros, denormals)
     freeze("sparse_far_pixels", synth.unit_ball(40, 51) * np.float32(0.2), synth.unit_ball(16, 52), 48, 64, six)
+    freeze_colorize()
 
 
 if __name__ == "__main__":

@@ -7,6 +7,7 @@
 #include "forward_culled.cuh"
 #include "forward_stream.cuh"
 #include "backward.cuh"
+#include "colorize.cuh"
 
 #include <algorithm>
 #include <cstdarg>
@@ -212,6 +213,18 @@ int scream_render_transform(const float* xyz, const int64_t* offs, int64_t total
         transform_dump_kernel<<<dim3((unsigned)chunks, (unsigned)B), 256, 0, st>>>(
             xyz, offs, total_pts, pose, views, V, zenc, rotated, pv);
     }
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_depth_to_rgb8(const float* imgs, int B, int V, int w, unsigned char* rgb, scream_stream_t stream)
+{
+    if (!imgs || !rgb) return fail(SCREAM_E_ARG, "imgs/rgb must not be NULL");
+    if (B <= 0 || V <= 0 || w <= 0) return fail(SCREAM_E_ARG, "B, V and w must be positive");
+    const long long total = (long long)B * V * w * w;
+    const long long grid = (total + CZ_THREADS - 1) / CZ_THREADS;
+    if (grid > 2147483647LL) return fail(SCREAM_E_UNSUPPORTED, "B*V*w*w too large for one launch");
+    depth_to_rgb8_kernel<<<(unsigned)grid, CZ_THREADS, 0, (cudaStream_t)stream>>>(imgs, B, V, w, rgb);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

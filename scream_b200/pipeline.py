@@ -24,7 +24,7 @@ from .render import make_offsets
 
 class StepPipeline:
     def __init__(self, sizes: Sequence[Tuple[int, int]], views: torch.Tensor, rho, w: int, device,
-                 chunk_pairs: int = 32, n_streams: int = 4, dense: bool = False):
+                 chunk_pairs: int = 37, n_streams: int = 6, dense: bool = False):
         if not torch.cuda.is_available():
             raise RuntimeError("scream_b200 renders on CUDA only (no CPU fallback)")
         _lib.load()

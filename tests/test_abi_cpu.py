@@ -16,7 +16,7 @@ from scream_b200.render import RegistrationRender, make_offsets, view_matrices
 def declared_symbols():
     text = open(os.path.join(ROOT, "include", "scream_render.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(scream_[a-z_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(scream_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_header_symbols_all_exported():
