@@ -29,7 +29,8 @@ namespace scream {
 
 constexpr int FS_THREADS = 1024;                        // S1: one CTA per SM (128 KB of tiles), 32 warps
 constexpr int FS_FILTER_THREADS = 1024;
-constexpr int FS_FILTER_CHUNK = 65536;                   // points per CTA task of S3 (amortises staging the bounds)
+constexpr int FS_FILTER_CHUNK_MAX = 131072;              // points per CTA task of S3 (amortises staging the thresholds)
+constexpr int FS_FILTER_CHUNK_MIN = 8192;
 constexpr int FS_CHUNK = 32768;                          // points per CTA task
 constexpr int FS_SURV_MIN = 4 * FC_CAP;                  // survivors kept per image: at least 49152, else total_pts / 16
 constexpr int64_t FS_MIN_AVG_PTS = 4 * FC_CAP;           // stream path when total_pts / B reaches this
@@ -43,10 +44,12 @@ struct StreamParams {
     unsigned* seed;                                      // [B][V][2][4096] uint bits of float >= 0 (S1), then eff (S2; -1 = unknown)
     float2* bnd;                                         // [B][V][2][4096] (eff, thr) written by S2, read by S3
     int* surv; unsigned* surv_cnt; int surv_cap;         // [B][V][2][surv_cap], [B][V][2]
+    int seed_stride;                                     // S1 seeds from every seed_stride-th chunk of the cloud (any subset is a valid lower bound)
+    int filter_chunk;                                    // points per CTA task of S3
 };
 
 constexpr int FS_VPC = 4;                                // views per CTA task of S1 (a point is loaded once for all of them)
-constexpr int FS_VPC_FILTER = 2;                         // ... of S3: 2 views x 2 clouds x 32 KB of bounds staged in shared memory
+constexpr int FS_VPC_FILTER = 5;                         // ... of S3: 5 views x 2 clouds x 16 KB of pv thresholds staged in shared memory
 constexpr float FS_PV_ABS = 4e-7f;                       // |1 - (z-zmin)*rcp(range) - pv_exact| (two roundings + rcp) stays below this
 
 // fast exp for bounds only: ex2.approx(a * log2e), error <= 2 + 1.16|a| ulp (|a| <= 108: < 1.6e-5 relative)
@@ -100,7 +103,7 @@ stream_seed_kernel(StreamParams P)
     __shared__ float s_pose[12];
     const int v0 = blockIdx.y * FS_VPC, nv = min(FS_VPC, P.V - v0), b = blockIdx.z;
     const ItemSpan sp = item_span(P.offs, b);
-    const int64_t base = sp.src0 + (int64_t)blockIdx.x * FS_CHUNK;
+    const int64_t base = sp.src0 + (int64_t)blockIdx.x * P.seed_stride * FS_CHUNK;
     if (base >= sp.end) return;
     const int tid = threadIdx.x;
     stream_load_views(P, b, v0, nv, s_view);
@@ -217,96 +220,147 @@ stream_bound_kernel(StreamParams P, int radius)
 }
 
 // ---- S3: filter --------------------------------------------------------------------------------
-// grid (chunks of FS_FILTER_CHUNK, ceil(V / FS_VPC_FILTER), B).  The (eff, thr) bounds of the CTA's views are staged
-// in shared memory: the per-point lookup is a random 8-byte read, which L1 serves at one sector per cycle.
-constexpr int FS_LIST_CAP = 5120;                        // survivors a CTA collects per image before it appends them in one piece
-constexpr size_t FS_FILTER_SMEM = (size_t)FS_VPC_FILTER * 2 * (FC_CELLS * sizeof(float2) + FS_LIST_CAP * sizeof(int));
+// grid (ceil(V / FS_VPC_FILTER), chunks of P.filter_chunk points, B): the view groups of one chunk run back to back, so
+// the chunk is read from HBM once and from L2 afterwards.
+// Two steps.  (1) A point of cell a can only survive if its pv reaches  L[a] = min(eff[a] / FS_UP, thr[a])  (its value is
+// at most pv: the Gaussian weight is <= 1).  L (one float per cell and image) is staged in shared memory for 5 views x 2
+// clouds; per point and view this costs three float4 shared loads, ~30 FP32 ops and one random shared load.  The points
+// that pass (the front layer and the rim of the cloud, a few per cent) are pushed on a shared-memory queue, one ballot per
+// warp (every warp owns a queue; no block barrier in the loop).  (2) Whenever a warp's queue fills, and at the end, the warp processes its entries with all lanes busy: the full test
+// against (eff, thr) from global memory, then one global atomic per warp and image to reserve list space.
+constexpr int FS_WQ = 384;                               // queue entries per warp: (image of the CTA) << 20 | point of the chunk
+constexpr size_t FS_FILTER_SMEM = (size_t)FS_VPC_FILTER * 2 * FC_CELLS * sizeof(float) + (size_t)(FS_FILTER_THREADS / 32) * FS_WQ * sizeof(unsigned);
+static_assert(FS_WQ > 32 * FS_VPC_FILTER && FS_FILTER_CHUNK_MAX <= (1 << 20), "queue layout");
 
-__global__ void __launch_bounds__(FS_FILTER_THREADS)
+struct StreamViewPacked { float4 rx, ry, rz; };          // (R0..2, zmin), (R3..5, rcp_range), (R6..8, -)
+
+__device__ __forceinline__ float ex2_ftz(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// the transform S1 and S3 share (same arithmetic as stream_point(): they must agree on the home cell)
+struct FilterPoint { float ux, uy, pv_hi, cj, cr; bool inside; int cell; };
+__device__ __forceinline__ FilterPoint filter_point(float x, float y, float z, const StreamViewPacked& W) {
+    FilterPoint f;
+    f.ux = __fmaf_rn(__fmaf_rn(W.rx.z, z, __fmaf_rn(W.rx.y, y, __fmul_rn(W.rx.x, x))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+    f.uy = __fmaf_rn(__fmaf_rn(W.ry.z, z, __fmaf_rn(W.ry.y, y, __fmul_rn(W.ry.x, x))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+    const float zr = __fmaf_rn(W.rz.z, z, __fmaf_rn(W.rz.y, y, __fmul_rn(W.rz.x, x)));
+    f.pv_hi = __fmaf_rn(-(zr - W.rx.w), W.ry.w, 1.0f) + FS_PV_ABS;
+    const float fj = floorf(f.ux), fi = floorf(f.uy);
+    f.cj = fminf(fmaxf(fj, 0.0f), (float)(FC_G - 1)); f.cr = fminf(fmaxf(fi, 0.0f), (float)(FC_G - 1));
+    f.inside = (f.cj == fj) && (f.cr == fi);             // really inside its cell (not clamped, not NaN)
+    f.cell = (int)f.cr * FC_G + (int)f.cj;
+    return f;
+}
+
+__global__ void __launch_bounds__(FS_FILTER_THREADS, 1)
 stream_filter_kernel(StreamParams P)
 {
-    extern __shared__ float2 s_bnd[];                    // [FS_VPC_FILTER][2][4096], then int s_list[FS_VPC_FILTER * 2][FS_LIST_CAP]
-    int* s_list = reinterpret_cast<int*>(s_bnd + FS_VPC_FILTER * 2 * FC_CELLS);
-    __shared__ unsigned s_cnt[FS_VPC_FILTER * 2], s_base[FS_VPC_FILTER * 2];
-    __shared__ StreamView s_view[FS_VPC_FILTER];
+    extern __shared__ float s_L[];                       // [FS_VPC_FILTER][2][4096], then unsigned s_q[32 warps][FS_WQ]
+    unsigned* s_q = reinterpret_cast<unsigned*>(s_L + FS_VPC_FILTER * 2 * FC_CELLS);
+    __shared__ StreamViewPacked s_view[FS_VPC_FILTER];
     __shared__ float s_pose[12];
-    const int v0 = blockIdx.y * FS_VPC_FILTER, nv = min(FS_VPC_FILTER, P.V - v0), b = blockIdx.z;
+    const int v0 = blockIdx.x * FS_VPC_FILTER, nv = min(FS_VPC_FILTER, P.V - v0), b = blockIdx.z;
     const ItemSpan sp = item_span(P.offs, b);
-    const int64_t base = sp.src0 + (int64_t)blockIdx.x * FS_FILTER_CHUNK;
+    const int64_t base = sp.src0 + (int64_t)blockIdx.y * P.filter_chunk;
     if (base >= sp.end) return;
     const int tid = threadIdx.x, lane = tid & 31;
-    stream_load_views(P, b, v0, nv, s_view);
-    if (P.pose && tid < 12) s_pose[tid] = P.pose[(size_t)b * 12 + tid];
-    if (tid < FS_VPC_FILTER * 2) s_cnt[tid] = 0u;
-    {
-        const float4* src = reinterpret_cast<const float4*>(P.bnd + ((size_t)b * P.V + v0) * 2 * FC_CELLS);
-        float4* dst = reinterpret_cast<float4*>(s_bnd);
-        for (int t = tid; t < nv * FC_CELLS; t += FS_FILTER_THREADS) dst[t] = __ldg(src + t);      // 2 clouds x 4096 float2 = 4096 float4 per view
+    if (tid < nv) {
+        const int v = v0 + tid;
+        const float* R = P.views + (size_t)v * 9;
+        const float zmin = dec_f32(P.zenc[((size_t)b * P.V + v) * 2]), zmax = dec_f32(P.zenc[((size_t)b * P.V + v) * 2 + 1]);
+        s_view[tid].rx = make_float4(R[0], R[1], R[2], zmin);
+        s_view[tid].ry = make_float4(R[3], R[4], R[5], 1.0f / z_range(zmin, zmax));
+        s_view[tid].rz = make_float4(R[6], R[7], R[8], 0.0f);
+    }
+    const bool has_pose = P.pose != nullptr;
+    if (has_pose && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    const size_t img0 = ((size_t)b * P.V + v0) * 2;
+    const float2* bnd0 = P.bnd + img0 * FC_CELLS;
+    for (int t = tid; t < nv * 2 * FC_CELLS; t += FS_FILTER_THREADS) {
+        const float2 bd = __ldg(bnd0 + t);               // (eff, thr); eff: -1 unknown, 0 exactly zero -> L <= 0: everything passes
+        s_L[t] = fminf(bd.x * (1.0f / FS_UP) * (1.0f - 1e-5f), bd.y);   // weight <= 1 + 2^-22 (ex2.approx)
     }
     __syncthreads();
     const float negkc = P.negk / (FC_CELLS_PER_NDC * FC_CELLS_PER_NDC);
-    const int64_t stop = min(sp.end, base + FS_FILTER_CHUNK);
-    const int64_t iters = (stop - base + FS_FILTER_THREADS - 1) / FS_FILTER_THREADS;
-    for (int64_t it = 0; it < iters; ++it) {
-        const int64_t gi = base + it * FS_FILTER_THREADS + tid;
-        const bool live = gi < stop;
-        const int c = live && gi >= sp.tgt0;
+    const float negkc2 = negkc * 1.4426950408889634f;   // exp(a) = 2^(a log2 e)
+    // flushing tiny weights to zero is only safe when the weight AT THE HOME PIXEL (d2c <= 1/2 cell^2) cannot be tiny
+    const bool ftz_ok = negkc * 0.5f > -60.0f;
+    const int npts = (int)min((int64_t)P.filter_chunk, sp.end - base);
+    const int split = (int)min((int64_t)npts, max((int64_t)0, sp.tgt0 - base));     // points [0, split) are source points
+
+    // step 2 (per warp): the queued (image, point) pairs of this warp, all lanes busy
+    unsigned* wq = s_q + (tid >> 5) * FS_WQ;
+    int wcount = 0;                                      // warp-uniform
+    auto drain = [&]() {
+        for (int t0 = 0; t0 < wcount; t0 += 32) {
+            const int t = t0 + lane;
+            bool keep = false; int l = 0, li = 0;
+            if (t < wcount) {
+                const unsigned e = wq[t];
+                l = (int)(e >> 20);
+                const int pi = (int)(e & 0xFFFFFu);
+                const int c = l & 1;
+                const float* q = P.xyz + (size_t)(base + pi) * 3;
+                float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+                if (has_pose && c == 0) apply_pose(s_pose, x, y, z);
+                const FilterPoint f = filter_point(x, y, z, s_view[l >> 1]);
+                li = (int)(base + pi - (c ? sp.tgt0 : sp.src0));
+                keep = true;
+                if (f.inside) {
+                    const float2 bd = __ldg(bnd0 + (size_t)l * FC_CELLS + f.cell);
+                    const float fx = f.ux - f.cj - 0.5f, fy = f.uy - f.cr - 0.5f;
+                    const float d2c = __fmaf_rn(fx, fx, fy * fy);
+                    const float wgt = ftz_ok ? ex2_ftz(d2c * negkc2) : exp_fast(d2c * negkc);
+                    keep = (f.pv_hi * wgt * FS_UP >= bd.x) || (f.pv_hi >= bd.y);
+                }
+            }
+            const unsigned km = __ballot_sync(0xFFFFFFFFu, keep);
+            if (keep) {                                  // one global atomic per warp and image
+                const unsigned peers = __match_any_sync(km, l);
+                const int leader = __ffs(peers) - 1;
+                unsigned gp = 0;
+                if (lane == leader) gp = atomicAdd(&P.surv_cnt[img0 + l], (unsigned)__popc(peers));
+                gp = __shfl_sync(peers, gp, leader) + __popc(peers & ((1u << lane) - 1u));
+                if (gp < (unsigned)P.surv_cap) P.surv[(img0 + l) * (size_t)P.surv_cap + gp] = li;
+            }
+            __syncwarp();
+        }
+        wcount = 0;
+    };
+
+    // step 1: every point of the chunk against the pv thresholds of the CTA's views.  No block barrier in the loop: every
+    // warp owns a queue (its fill level lives in a register) and drains it on its own.
+    const unsigned lt = (1u << lane) - 1u;
+    for (int p0 = 0; p0 < npts; p0 += FS_FILTER_THREADS) {
+        const int pi = p0 + tid;
+        const bool live = pi < npts;
+        const int c = pi >= split;
         float x = 0.f, y = 0.f, z = 0.f;
         if (live) {
-            const float* q = P.xyz + (size_t)gi * 3;
-            x = __ldcs(q); y = __ldcs(q + 1); z = __ldcs(q + 2);
-            if (P.pose != nullptr && c == 0) apply_pose(s_pose, x, y, z);
+            const float* q = P.xyz + (size_t)(base + pi) * 3;
+            x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2);
+            if (has_pose && c == 0) apply_pose(s_pose, x, y, z);
         }
+        const float floor_pv = live ? 0.0f : INFINITY;  // dead lanes never pass
+        const float* Lc = s_L + c * FC_CELLS;
+        const unsigned ebase = ((unsigned)c << 20) | (unsigned)pi;
         for (int vv = 0; vv < nv; ++vv) {
-            const size_t img0 = ((size_t)b * P.V + v0 + vv) * 2;
-            bool keep = false;
-            if (live) {
-                const StreamPoint pt = stream_point(x, y, z, s_view[vv]);
-                const float pv_hi = pt.pv + FS_PV_ABS;
-                if (pv_hi > 0.0f) {
-                    const float2 bd = s_bnd[(vv * 2 + c) * FC_CELLS + pt.cell];                // (eff, thr)
-                    // points outside [-1,1]^2 (clamped into border cells) never seed and are never dropped: S2's
-                    // "exactly zero" pixels are only zero for the points inside
-                    keep = !pt.inside || (pv_hi * home_weight(pt, negkc) * FS_UP >= bd.x) || (pv_hi >= bd.y);
-                }
-            }
-            const unsigned any = __ballot_sync(0xFFFFFFFFu, keep);
-            if (any == 0u) continue;
-            // a warp straddles at most the src/tgt boundary: one ballot per cloud.  Survivors go to the CTA's
-            // shared-memory list of the image (one shared atomic per warp); what does not fit goes straight to global.
-#pragma unroll
-            for (int cc = 0; cc < 2; ++cc) {
-                const unsigned m = __ballot_sync(0xFFFFFFFFu, keep && c == cc);
-                if (m) {
-                    const int l = vv * 2 + cc;
-                    unsigned pos = 0;
-                    if (lane == 0) pos = atomicAdd(&s_cnt[l], (unsigned)__popc(m));
-                    pos = __shfl_sync(0xFFFFFFFFu, pos, 0) + __popc(m & ((1u << lane) - 1u));
-                    if (keep && c == cc) {
-                        const int li = (int)(gi - (cc ? sp.tgt0 : sp.src0));
-                        if (pos < (unsigned)FS_LIST_CAP) s_list[l * FS_LIST_CAP + pos] = li;
-                        else {
-                            const unsigned gp = atomicAdd(&P.surv_cnt[img0 + cc], 1u);
-                            if (gp < (unsigned)P.surv_cap) P.surv[(img0 + cc) * (size_t)P.surv_cap + gp] = li;
-                        }
-                    }
-                }
+            const FilterPoint f = filter_point(x, y, z, s_view[vv]);
+            const float lim = f.inside ? Lc[vv * 2 * FC_CELLS + f.cell] : 0.0f;    // clamped points are never dropped here
+            const bool pass = f.pv_hi > floor_pv && f.pv_hi >= lim;
+            const unsigned pm = __ballot_sync(0xFFFFFFFFu, pass);
+            if (pm) {
+                if (pass) wq[wcount + __popc(pm & lt)] = ebase + ((unsigned)vv << 21);
+                wcount += __popc(pm);
             }
         }
+        if (wcount > FS_WQ - 32 * FS_VPC_FILTER) { __syncwarp(); drain(); }      // one more round always fits
     }
-    __syncthreads();
-    if (tid < nv * 2) {
-        const unsigned n = min(s_cnt[tid], (unsigned)FS_LIST_CAP);
-        s_cnt[tid] = n;
-        s_base[tid] = n ? atomicAdd(&P.surv_cnt[((size_t)b * P.V + v0) * 2 + tid], n) : 0u;
-    }
-    __syncthreads();
-    for (int l = 0; l < nv * 2; ++l) {
-        const unsigned n = s_cnt[l], gb = s_base[l];
-        int* dst = P.surv + (((size_t)b * P.V + v0) * 2 + l) * (size_t)P.surv_cap;
-        for (unsigned t = tid; t < n; t += FS_FILTER_THREADS)
-            if (gb + t < (unsigned)P.surv_cap) dst[gb + t] = s_list[l * FS_LIST_CAP + t];
-    }
+    __syncwarp();
+    drain();
 }
 
 }  // namespace scream

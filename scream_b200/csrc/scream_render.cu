@@ -136,8 +136,16 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         S.surv = reinterpret_cast<int*>((char*)ws + L.surv_off); S.surv_cap = L.surv_cap;
         CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
         const int64_t mi = (max_item_pts <= 0 || max_item_pts > total_pts) ? total_pts : max_item_pts;
-        const int64_t chunks = (mi + FS_CHUNK - 1) / FS_CHUNK;
-        if (B > 65535) return fail(SCREAM_E_UNSUPPORTED, "batch too large for the stream grid");
+        // S1 seeds from a subset of the cloud (about 4 M points per item: ~1000 per pixel): any subset gives valid bounds
+        S.seed_stride = (int)std::min<int64_t>(std::max<int64_t>(mi / (4 << 20), 1), 64);
+        const int64_t chunks = ((mi + FS_CHUNK - 1) / FS_CHUNK + S.seed_stride - 1) / S.seed_stride;
+        // S3: chunks small enough to fill the GPU (>= ~4 CTAs per SM over all view groups), large enough to amortise staging
+        const int vgroups = (V + FS_VPC_FILTER - 1) / FS_VPC_FILTER;
+        int64_t fchunk = mi * vgroups * B / (4 * 148);
+        fchunk = std::min<int64_t>(std::max<int64_t>(fchunk / FS_FILTER_THREADS * FS_FILTER_THREADS, FS_FILTER_CHUNK_MIN), FS_FILTER_CHUNK_MAX);
+        S.filter_chunk = (int)fchunk;
+        const int64_t fchunks = (mi + fchunk - 1) / fchunk;
+        if (B > 65535 || fchunks > 65535) return fail(SCREAM_E_UNSUPPORTED, "batch or cloud too large for the stream grid");
         {
             static thread_local int bound_attr_dev = -1;
             int dev = 0;
@@ -152,7 +160,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         if (chunks > 2147483647LL || V > 65535 * 2) return fail(SCREAM_E_UNSUPPORTED, "cloud too large for the stream grid");
         stream_seed_kernel<<<dim3((unsigned)chunks, (unsigned)((V + FS_VPC - 1) / FS_VPC), (unsigned)B), FS_THREADS, FS_SEED_SMEM, st>>>(S);
         stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM(zero_radius), st>>>(S, zero_radius);
-        stream_filter_kernel<<<dim3((unsigned)((mi + FS_FILTER_CHUNK - 1) / FS_FILTER_CHUNK), (unsigned)((V + FS_VPC_FILTER - 1) / FS_VPC_FILTER), (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
+        stream_filter_kernel<<<dim3((unsigned)vgroups, (unsigned)fchunks, (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
         CUDA_TRY(cudaGetLastError());
         P.surv = S.surv; P.surv_cnt = S.surv_cnt; P.surv_cap = L.surv_cap;
     }

@@ -60,4 +60,5 @@ def test_rendered_views_to_ppm(tmp_path):
     path = tmp_path / "views.ppm"
     write_ppm(str(path), strip)
     raw = open(path, "rb").read()
-    assert raw.startswith(b"P6\n384 64\n255\n") and len(raw) == 15 + 64 * 384 * 3
+    head = b"P6\n384 64\n255\n"
+    assert raw.startswith(head) and len(raw) == len(head) + 64 * 384 * 3
