@@ -245,6 +245,10 @@ forward_culled_kernel(FwdParams P)
         const size_t img = ((size_t)b * P.V + v) * 2 + c;
         const unsigned ns = P.surv_cnt[img];
         if (ns <= (unsigned)P.surv_cap) { surv = P.surv + img * (size_t)P.surv_cap; npts = (int64_t)ns; }
+        else if (P.surv1 != nullptr) {
+            const unsigned n1 = P.surv1_cnt[img];
+            if (n1 <= (unsigned)P.surv1_cap) { surv = P.surv1 + img * (size_t)P.surv1_cap; npts = (int64_t)n1; }
+        }
     }
     const float zmin = dec_f32(P.zenc[((size_t)b * P.V + v) * 2]);
     const float zmax = dec_f32(P.zenc[((size_t)b * P.V + v) * 2 + 1]);

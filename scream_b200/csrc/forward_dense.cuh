@@ -23,7 +23,8 @@ struct FwdParams {
     float negk, inv_negk;
     unsigned flags;
     float* imgs; int32_t* winner; float* zrange;
-    const int* surv; const unsigned* surv_cnt; int surv_cap;   // survivor lists of the giant-cloud path, or nullptr
+    const int* surv; const unsigned* surv_cnt; int surv_cap;   // survivor lists of the giant-cloud path (last filter round), or nullptr
+    const int* surv1; const unsigned* surv1_cnt; int surv1_cap; // first-round lists: used for an image whose last-round list overflowed
 };
 
 __device__ __forceinline__ float zero_or_cull(float best, float inv_negk) {

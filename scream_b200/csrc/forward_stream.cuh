@@ -4,22 +4,16 @@
 // This is north_star's "projection + z-buffer" stage: a per-pixel atomicMax on float bits, staged
 // through a shared-memory image tile.
 //
-//   S1 seed    every point -> its home cell (the cell of the 64 x 64 grid that holds it; for w == 64 a cell
-//              is a pixel) -> value at that pixel, rounded DOWN -> atomicMax on the uint bits of the value
-//              (monotone for values >= 0) in a shared-memory tile, flushed to the global seed image.
-//              seed[q] is the value of a real point at pixel q, hence a lower bound of the pixel's max.
-//   S2 bound   per image: eff[q]  = max(seed[q], max_q' seed[q'] * exp(-k dmax^2(q',q)))   (lower bound of
-//              the max at q, also for pixels no point calls home), and the per-cell admission threshold
-//              thr[a] = min_{q != a} eff[q] * exp(+k dmin^2(a,q)):  a point of cell a can only reach
-//              eff[q] at another pixel q if its pv is at least thr[a]  (val <= pv * exp(-k dmin^2)).
-//   S3 filter  every point again: it survives iff its value at its home pixel (rounded UP) reaches
-//              eff[home], or its pv reaches thr[home cell].  Survivors (cloud-local indices) are appended
-//              to a per-image list.  Every point that attains a pixel's maximum survives -- including all
-//              points that tie -- so rendering the survivors is bit-identical to rendering the cloud.
+//   S1 seed    a sample of the points -> home cell (the cell of the 64 x 64 grid that holds the point; for w == 64 a cell
+//              is a pixel) -> value at that pixel -> 64-bit atomicMax (value bits, point index) in a shared-memory tile,
+//              flushed to the global seed image: per cell, one real point that does well at the cell's own pixel.
+//   S2 bound   per image, in the score domain (s = d^2 + c, c = -ln(pv)/k): U(q) = best seed score at every pixel, its
+//              squared-distance transform T at the cell corners, and a per-cell pv threshold (details at the kernel).
+//   S3 filter  every point: it survives iff it may reach U at some pixel -- a per-cell pv threshold first, then the
+//              per-point test with the corner values of its cell.  Survivors (cloud-local indices) are appended to a
+//              per-image list.  Every point that attains a pixel's maximum survives, including all points that tie.
 //   S4 render  forward_culled_kernel on the survivor lists (FwdParams::surv*); an image whose list
 //              overflowed is rendered from the full cloud in batches (correct, slow).
-// dmax / dmin: largest / smallest distance between a point anywhere in cell q' (resp. a) and the pixel
-// centre of cell q: per axis |delta| + 1/2 resp. max(0, |delta| - 1/2) cells.
 #pragma once
 #include "common.cuh"
 #include "forward_dense.cuh"
@@ -41,15 +35,20 @@ struct StreamParams {
     const float* xyz; const int64_t* offs; const float* pose; const float* views; const unsigned* zenc;
     int B, V;
     float negk;                                          // -rho^2/2
-    unsigned* seed;                                      // [B][V][2][4096] uint bits of float >= 0 (S1), then eff (S2; -1 = unknown)
-    float2* bnd;                                         // [B][V][2][4096] (eff, thr) written by S2, read by S3
-    int* surv; unsigned* surv_cnt; int surv_cap;         // [B][V][2][surv_cap], [B][V][2]
-    int seed_stride;                                     // S1 seeds from every seed_stride-th chunk of the cloud (any subset is a valid lower bound)
+    unsigned long long* seed;                            // [B][V][2][4096]  (value bits << 32 | cloud-local index) of the cell's seed point (S1)
+    float* lpv;                                          // [B][V][2][4096]  pv a point of the cell needs at least (S2 -> S3 step 1)
+    float4* win;                                         // [B][V][2][4096][8] per cell, one 128-byte line: U of the 5 x 5 pixels around it (row-major,
+                                                         //   -inf outside the image), then T_far at its 4 corners, 3 pads (S2 -> S3 step 2)
+    int* surv; unsigned* surv_cnt; int surv_cap;         // [B][V][2][surv_cap], [B][V][2]   survivors of the first round
+    int* surv2; unsigned* surv2_cnt; int surv2_cap;      // ... of the second round (re-seeded from the first round's survivors)
+    int seed_stride;                                     // S1 seeds from every seed_stride-th chunk of the cloud (any subset gives valid bounds)
     int filter_chunk;                                    // points per CTA task of S3
+    unsigned long long* stats;                           // [2] diagnostics: (point, view) pairs that passed step 1 / step 2 of S3
 };
 
-constexpr int FS_VPC = 4;                                // views per CTA task of S1 (a point is loaded once for all of them)
+constexpr int FS_VPC = 2;                                // views per CTA task of S1 (2 views x 2 clouds x 32 KB of 64-bit tiles)
 constexpr int FS_VPC_FILTER = 5;                         // ... of S3: 5 views x 2 clouds x 16 KB of pv thresholds staged in shared memory
+constexpr int FS_TC = (FC_G + 1) * (FC_G + 1);           // cell corners per image
 constexpr float FS_PV_ABS = 4e-7f;                       // |1 - (z-zmin)*rcp(range) - pv_exact| (two roundings + rcp) stays below this
 
 // fast exp for bounds only: ex2.approx(a * log2e), error <= 2 + 1.16|a| ulp (|a| <= 108: < 1.6e-5 relative)
@@ -63,7 +62,7 @@ struct StreamPoint { float pv, d2c; int cell; bool inside; };
 // transform for BOUNDS: the renderer's rotation, pv through a reciprocal multiply (|error| <= FS_PV_ABS, applied in
 // the safe direction by the callers), home cell = floor of the cell coordinate (clamped like the renderer's grid) and
 // d2c = squared distance, in cells^2, to the pixel centre of that cell (w == 64: pixel = cell).  The cell function
-// need not be bit-identical to the renderer's: S1 and S3 share it, and the bounds of S2 carry 1e-4 of slack.
+// need not be bit-identical to the renderer's: S1 and S3 share it, and the bounds of S2 carry slack.
 __device__ __forceinline__ StreamPoint stream_point(float x, float y, float z, const StreamView& W) {
     StreamPoint sp;
     const float ux = __fmaf_rn(rot_row(W.R, x, y, z), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
@@ -92,13 +91,15 @@ __device__ __forceinline__ void stream_load_views(const StreamParams& P, int b, 
 }
 
 // ---- S1: seed ----------------------------------------------------------------------------------
-// grid (chunks, ceil(V / FS_VPC), B).
-constexpr size_t FS_SEED_SMEM = (size_t)FS_VPC * 2 * FC_CELLS * sizeof(unsigned);
+// grid (chunks, ceil(V / FS_VPC), B).  Per cell and image: the sampled point with the best value at the cell's own pixel,
+// as a 64-bit key (value bits, cloud-local index): atomicMax keeps value and identity together.  The value only ranks
+// the candidates of a cell; S2 re-evaluates the chosen point exactly.
+constexpr size_t FS_SEED_SMEM = (size_t)FS_VPC * 2 * FC_CELLS * sizeof(unsigned long long);
 
 __global__ void __launch_bounds__(FS_THREADS)
 stream_seed_kernel(StreamParams P)
 {
-    extern __shared__ unsigned s_tile[];                 // [FS_VPC][2][4096]
+    extern __shared__ unsigned long long s_tile[];       // [FS_VPC][2][4096]
     __shared__ StreamView s_view[FS_VPC];
     __shared__ float s_pose[12];
     const int v0 = blockIdx.y * FS_VPC, nv = min(FS_VPC, P.V - v0), b = blockIdx.z;
@@ -108,12 +109,13 @@ stream_seed_kernel(StreamParams P)
     const int tid = threadIdx.x;
     stream_load_views(P, b, v0, nv, s_view);
     if (P.pose && tid < 12) s_pose[tid] = P.pose[(size_t)b * 12 + tid];
-    for (int t = tid; t < nv * 2 * FC_CELLS; t += FS_THREADS) s_tile[t] = 0u;
+    for (int t = tid; t < nv * 2 * FC_CELLS; t += FS_THREADS) s_tile[t] = 0ull;
     __syncthreads();
     const float negkc = P.negk / (FC_CELLS_PER_NDC * FC_CELLS_PER_NDC);
     const int64_t stop = min(sp.end, base + FS_CHUNK);
     for (int64_t gi = base + tid; gi < stop; gi += FS_THREADS) {
         const int c = gi >= sp.tgt0;
+        const unsigned li = (unsigned)(gi - (c ? sp.tgt0 : sp.src0));
         const float* q = P.xyz + (size_t)gi * 3;
         float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
         if (P.pose != nullptr && c == 0) apply_pose(s_pose, x, y, z);
@@ -121,113 +123,203 @@ stream_seed_kernel(StreamParams P)
             const StreamPoint pt = stream_point(x, y, z, s_view[vv]);
             const float pv_lo = pt.pv - FS_PV_ABS;
             if (!(pv_lo > 0.0f) || !pt.inside) continue;     // clamped points may be anywhere outside: they cannot seed
-            const float val = pv_lo * home_weight(pt, negkc) * FS_DOWN;
+            const float val = pv_lo * home_weight(pt, negkc);
             const unsigned bits = __float_as_uint(val);
-            unsigned* slot = &s_tile[(vv * 2 + c) * FC_CELLS + pt.cell];
-            if (val > 0.0f && bits > *slot) atomicMax(slot, bits);
+            unsigned long long* slot = &s_tile[(vv * 2 + c) * FC_CELLS + pt.cell];
+            if (val > 0.0f && bits > (unsigned)(*reinterpret_cast<volatile unsigned long long*>(slot) >> 32))
+                atomicMax(slot, ((unsigned long long)bits << 32) | li);
         }
     }
     __syncthreads();
-    unsigned* out = P.seed + ((size_t)b * P.V + v0) * 2 * FC_CELLS;
+    unsigned long long* out = P.seed + ((size_t)b * P.V + v0) * 2 * FC_CELLS;
     for (int t = tid; t < nv * 2 * FC_CELLS; t += FS_THREADS) {
-        const unsigned bits = s_tile[t];
-        if (bits != 0u && bits > out[t]) atomicMax(&out[t], bits);
+        const unsigned long long key = s_tile[t];
+        if (key != 0ull && key > out[t]) atomicMax(&out[t], key);
     }
 }
 
-// ---- S2: per-image bounds ----------------------------------------------------------------------
-// grid (V * 2, B), 1024 threads, 4 cells per thread.  Both bounds are separable in the two grid axes
-// (exp(-k(dx^2+dy^2)) = exp(-k dx^2) exp(-k dy^2), and max / min distribute over the product of non-negative
-// factors), so each is a column pass followed by a row pass over a window of `radius` cells: O(4096 * radius)
-// per image instead of O(4096 * radius^2).  The own cell is excluded from thr[a] exactly: the column pass
-// leaves out the own row, and the row pass adds the own row without the own column.
-constexpr size_t FS_BOUND_SMEM(int radius) { return (size_t)4 * FC_CELLS * sizeof(float) + (size_t)3 * (radius + 1) * sizeof(float); }
+// Slack of the score tests (NDC^2).  Two points whose VALUES the renderer may order either way have scores within
+// 4.8e-7 s + 6e-7 / k of each other (rounding of d2, of the exp argument, expf <= 2 ulp, the final product).  Everything
+// proportional to s -- that, and the rounding of U, of the two transform passes, of the interpolation and of the point's
+// cell position (together < 1.3e-6 s) -- is covered by rounding U UP by 6e-6 (U(q) is the score at stake at the critical
+// pixel); pv is rounded in the safe direction on both sides.  What is left is the additive part:
+__device__ __forceinline__ float stream_slack(float inv_k) { return __fmaf_rn(2e-6f, inv_k, 1e-10f); }
+
+// ---- S2: per-image bounds, in the score domain -----------------------------------------------------
+// With k = rho^2/2 and c_i = -ln(pv_i)/k the value of point i at pixel q is exp(-k s_i(q)), s_i(q) = |x_i - q|^2 + c_i,
+// so "point i reaches the best value seen at q" reads  s_i(q) <= U(q)  -- no exp, no underflow.
+//   U(q)  = min over the seed points (exact positions, c rounded up) of s_seed(q), capped where the value is exactly 0:
+//           an upper bound of the minimum score at pixel q.  Ring search outwards from the pixel's cell with early exit.
+//   T(X)  = min_q |X - q|^2 - U(q)  at the 65 x 65 cell CORNERS X: a squared-distance transform, separable, exact.
+//           Point i can reach U at some pixel iff T(x_i) <= -c_i.  m(x) = T(x) - |x|^2 is a minimum of affine functions,
+//           hence concave, so inside a cell it lies above the bilinear interpolation of its corner values:
+//               T(x) >= bilerp(T corners)(t) - h^2 (t_x (1 - t_x) + t_y (1 - t_y)),   t = position in the cell, h = cell size
+//           (exact whenever one pixel q is the minimiser over the whole cell, which is the rule away from the cloud).
+//           This is the per-POINT test of S3 step 2: four floats per cell, no cell-level slack on the point's position.
+//   lpv[a] = exp(-k Cmax[a]),  Cmax[a] = h^2/2 - min(T at the 4 corners of a): no point of cell a with pv below it passes
+//           the per-point test -- the cheap per-cell threshold of S3 step 1.
+// grid (V * 2, B), 1024 threads.
+constexpr size_t FS_BOUND_SMEM = (size_t)FC_CELLS * sizeof(float4) + (size_t)FC_CELLS * sizeof(float)
+                               + (size_t)2 * (FC_G + 1) * FC_G * sizeof(float) + (size_t)FS_TC * sizeof(float);
 
 __global__ void __launch_bounds__(1024)
-stream_bound_kernel(StreamParams P, int radius)
+stream_bound_kernel(StreamParams P)
 {
-    extern __shared__ float s_dyn[];
-    float* s_seed = s_dyn;                               // seed, later E (eff as used by the threshold pass)
-    float* s_a = s_dyn + FC_CELLS;                       // column pass of eff, later column pass of thr
-    float* s_u = s_dyn + 2 * FC_CELLS;                   // column pass of the distance to the nearest seeded cell
-    float* s_eff = s_dyn + 3 * FC_CELLS;
-    float* t_max = s_dyn + 4 * FC_CELLS;                 // exp(-k ((d + 1/2) cell)^2)
-    float* t_min = t_max + radius + 1;                   // exp(+k (max(d - 1/2, 0) cell)^2), capped (finite)
-    float* t_d2 = t_min + radius + 1;                    // (max(d - 1/2, 0) cell)^2
-    const int vc = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
-    const size_t img = ((size_t)b * P.V * 2 + vc) * FC_CELLS;
-    const float cell = 1.0f / FC_CELLS_PER_NDC;
-    for (int d = tid; d <= radius; d += 1024) {
-        const float hi = ((float)d + 0.5f) * cell, lo = fmaxf((float)d - 0.5f, 0.0f) * cell;
-        t_max[d] = expf(hi * hi * P.negk) * (1.0f - 1e-4f);                     // accurate exp: denormals kept
-        t_min[d] = fminf(expf(-lo * lo * P.negk) * (1.0f - 1e-4f), 3.0e38f);
-        t_d2[d] = lo * lo;
-    }
-    for (int t = tid; t < FC_CELLS; t += 1024) s_seed[t] = __uint_as_float(P.seed[img + t]);
+    extern __shared__ float4 s_seedpt[];                 // [4096] (x', y', c_up, -) of the cell's seed; c = +inf: none
+    float* s_U = reinterpret_cast<float*>(s_seedpt + FC_CELLS);          // [4096]
+    float* s_A = s_U + FC_CELLS;                                         // [65][64] row pass
+    float* s_E = s_A + (FC_G + 1) * FC_G;                                // [65][64] row pass without the 4 columns around X
+    float* s_T = s_E + (FC_G + 1) * FC_G;                                // [65][65]
+    __shared__ float s_R[9], s_pose[12];
+    const int vc = blockIdx.x, v = vc >> 1, c = vc & 1, b = blockIdx.y, tid = threadIdx.x;
+    const size_t img = ((size_t)b * P.V + v) * 2 + c;
+    if (tid < 9) s_R[tid] = P.views[(size_t)v * 9 + tid];
+    const bool posed = P.pose != nullptr && c == 0;
+    if (posed && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    const ItemSpan sp = item_span(P.offs, b);
+    const int64_t lo = c ? sp.tgt0 : sp.src0;
+    const float zmin = dec_f32(P.zenc[((size_t)b * P.V + v) * 2]), zmax = dec_f32(P.zenc[((size_t)b * P.V + v) * 2 + 1]);
+    const float rcp_range = 1.0f / z_range(zmin, zmax);
+    const float inv_k = -1.0f / P.negk;
+    const float h = 1.0f / FC_CELLS_PER_NDC;
+    const float s_zero_up = FC_EXP_ZERO * inv_k * (1.0f + 1e-4f);       // scores beyond: value exactly 0
     __syncthreads();
-    const float zero_d2 = FC_EXP_ZERO / (-P.negk) * 1.001f;                      // NDC^2 beyond which a value is exactly 0
 
-    // eff, column pass
-    for (int q = tid; q < FC_CELLS; q += 1024) {
-        const int i = q >> 6, j = q & 63;
-        float a = 0.0f, u = INFINITY;
-        for (int i2 = max(0, i - radius); i2 <= min(FC_G - 1, i + radius); ++i2) {
-            const float sd = s_seed[i2 * FC_G + j];
-            if (sd > 0.0f) { const int d = abs(i2 - i); a = fmaxf(a, sd * t_max[d]); u = fminf(u, t_d2[d]); }
+    // seed points, exactly placed
+    for (int cell = tid; cell < FC_CELLS; cell += 1024) {
+        const unsigned long long key = P.seed[img * FC_CELLS + cell];
+        float4 sd = make_float4(0.f, 0.f, INFINITY, 0.f);
+        if (key != 0ull) {
+            const float* q = P.xyz + (size_t)(lo + (int64_t)(unsigned)(key & 0xFFFFFFFFull)) * 3;
+            float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+            if (posed) apply_pose(s_pose, x, y, z);
+            const float pv_lo = __fmaf_rn(-(rot_row(s_R + 6, x, y, z) - zmin), rcp_range, 1.0f) - FS_PV_ABS;
+            if (pv_lo > 0.0f)
+                sd = make_float4(rot_row(s_R, x, y, z), rot_row(s_R + 3, x, y, z),
+                                 fmaxf(-logf(pv_lo) * inv_k, 0.0f) * (1.0f + 1e-5f) + 1e-12f, 0.f);
         }
-        s_a[q] = a; s_u[q] = u;
+        s_seedpt[cell] = sd;
     }
     __syncthreads();
-    // eff, row pass.  -1: unknown (a seeded cell within the zero radius but the bound underflowed), 0: exactly zero
+
+    // U(q): rings of cells around the pixel's own cell, until no farther seed can beat the best so far
     for (int q = tid; q < FC_CELLS; q += 1024) {
         const int i = q >> 6, j = q & 63;
-        float e = s_seed[q], m = INFINITY;
-        for (int j2 = max(0, j - radius); j2 <= min(FC_G - 1, j + radius); ++j2) {
-            const int d = abs(j2 - j);
-            e = fmaxf(e, s_a[i * FC_G + j2] * t_max[d]);
-            m = fminf(m, s_u[i * FC_G + j2] + t_d2[d]);
+        const float qx = ((float)j + 0.5f) * h - 1.0f, qy = ((float)i + 0.5f) * h - 1.0f;      // pixel centre (w == 64), exact
+        float best = s_zero_up;
+        for (int d = 0; d < FC_G; ++d) {
+            const float reach = ((float)d - 0.5f) * h;                       // seeds lie inside their cells
+            if (d > 0 && reach * reach * (1.0f - 1e-5f) >= best) break;
+            const int i0 = i - d, i1 = i + d, j0 = max(j - d, 0), j1 = min(j + d, FC_G - 1);
+            if (i0 >= 0) for (int jj = j0; jj <= j1; ++jj) {
+                const float4 sd = s_seedpt[i0 * FC_G + jj];
+                const float dx = sd.x - qx, dy = sd.y - qy;
+                best = fminf(best, __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, sd.z)));
+            }
+            if (d > 0 && i1 < FC_G) for (int jj = j0; jj <= j1; ++jj) {
+                const float4 sd = s_seedpt[i1 * FC_G + jj];
+                const float dx = sd.x - qx, dy = sd.y - qy;
+                best = fminf(best, __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, sd.z)));
+            }
+            for (int ii = max(i0 + 1, 0); ii <= min(i1 - 1, FC_G - 1); ++ii) {
+                if (j - d >= 0) {
+                    const float4 sd = s_seedpt[ii * FC_G + j - d];
+                    const float dx = sd.x - qx, dy = sd.y - qy;
+                    best = fminf(best, __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, sd.z)));
+                }
+                if (j + d < FC_G) {
+                    const float4 sd = s_seedpt[ii * FC_G + j + d];
+                    const float dx = sd.x - qx, dy = sd.y - qy;
+                    best = fminf(best, __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, sd.z)));
+                }
+            }
         }
-        s_eff[q] = e > 0.0f ? e : (m <= zero_d2 ? -1.0f : 0.0f);
-    }
-    __syncthreads();
-    // E = eff as the threshold pass uses it: unknown -> 0 (admits everything in reach), exactly zero -> +inf (skipped:
-    // the winner of an all-zero pixel is index 0 whatever the points)
-    for (int q = tid; q < FC_CELLS; q += 1024) {
-        const float e = s_eff[q];
-        s_seed[q] = e > 0.0f ? e : (e < 0.0f ? 0.0f : INFINITY);
-    }
-    __syncthreads();
-    // thr, column pass without the own row
-    for (int q = tid; q < FC_CELLS; q += 1024) {
-        const int i = q >> 6, j = q & 63;
-        float h = INFINITY;
-        for (int i2 = max(0, i - radius); i2 <= min(FC_G - 1, i + radius); ++i2)
-            if (i2 != i) h = fminf(h, s_seed[i2 * FC_G + j] * t_min[abs(i2 - i)]);
-        s_a[q] = h;
-    }
-    __syncthreads();
-    // thr, row pass: other rows through s_a (all columns), own row through E (other columns only)
-    for (int q = tid; q < FC_CELLS; q += 1024) {
-        const int i = q >> 6, j = q & 63;
-        float thr = INFINITY;
-        for (int j2 = max(0, j - radius); j2 <= min(FC_G - 1, j + radius); ++j2) {
-            const float f = t_min[abs(j2 - j)];
-            thr = fminf(thr, s_a[i * FC_G + j2] * f);
-            if (j2 != j) thr = fminf(thr, s_seed[i * FC_G + j2] * f);
+        // Denormal range (k U > 80): values are multiples of 2^-149, so scores up to -ln(1 - u)/k <= 1.5 u/k apart
+        // (u = 8 * 2^-149 * e^(k U)) may tie or swap; from u >= 1/2 on every non-zero value may.  Same rule as the
+        // renderer's exact pass (forward_culled.cuh).
+        float up = best * (1.0f + 6e-6f);
+        const float e1 = up * -P.negk;
+        if (e1 >= FC_EXP_DENORM) {
+            const float lu = e1 - 101.2f;
+            up = lu >= -0.7f ? s_zero_up : up + 1.6f * expf(lu) * inv_k;
         }
-        P.bnd[img + q] = make_float2(s_eff[q], thr * (1.0f - 1e-4f));     // eff: -1 unknown, 0 exactly zero
+        s_U[q] = fminf(up, s_zero_up);
+    }
+    __syncthreads();
+
+    // T_far at the corners: pixels outside the 4 x 4 block around corner (Y, X) -- every pixel that is NOT in the 5 x 5
+    // neighbourhood of a cell touching the corner.  Row pass over all / over the far columns, then the column pass.
+    for (int t = tid; t < (FC_G + 1) * FC_G; t += 1024) {
+        const int X = t / FC_G, qy = t % FC_G;
+        float a = INFINITY, e = INFINITY;
+        for (int qx = 0; qx < FC_G; ++qx) {
+            const float dx = ((float)(X - qx) - 0.5f) * h;
+            const float val = __fmaf_rn(dx, dx, -s_U[qy * FC_G + qx]);
+            a = fminf(a, val);
+            if (qx < X - 2 || qx > X + 1) e = fminf(e, val);
+        }
+        s_A[X * FC_G + qy] = a; s_E[X * FC_G + qy] = e;
+    }
+    __syncthreads();
+    for (int t = tid; t < FS_TC; t += 1024) {
+        const int Y = t / (FC_G + 1), X = t % (FC_G + 1);
+        float m = INFINITY;
+        for (int qy = 0; qy < FC_G; ++qy) {
+            const float dy = ((float)(Y - qy) - 0.5f) * h;
+            const bool far_row = qy < Y - 2 || qy > Y + 1;
+            m = fminf(m, __fmaf_rn(dy, dy, far_row ? s_A[X * FC_G + qy] : s_E[X * FC_G + qy]));
+        }
+        s_T[t] = m;
+    }
+    __syncthreads();
+    // per-cell pv threshold: the largest c a point of the cell may have and still pass the per-point test of S3:
+    // near pixels exactly (smallest distance of the cell to the pixel centre), far pixels through the corner bound
+    for (int cell = tid; cell < FC_CELLS; cell += 1024) {
+        const int i = cell >> 6, j = cell & 63;
+        const float tmin = fminf(fminf(s_T[i * (FC_G + 1) + j], s_T[i * (FC_G + 1) + j + 1]),
+                                 fminf(s_T[(i + 1) * (FC_G + 1) + j], s_T[(i + 1) * (FC_G + 1) + j + 1]));
+        float cmax = 0.5f * h * h - tmin;
+        for (int di = -2; di <= 2; ++di) {
+            const int qi = i + di;
+            if (qi < 0 || qi >= FC_G) continue;
+            const float ay = fmaxf(fabsf((float)di) - 0.5f, 0.0f) * h;
+            for (int dj = -2; dj <= 2; ++dj) {
+                const int qj = j + dj;
+                if (qj < 0 || qj >= FC_G) continue;
+                const float ax = fmaxf(fabsf((float)dj) - 0.5f, 0.0f) * h;
+                cmax = fmaxf(cmax, s_U[qi * FC_G + qj] - (ax * ax + ay * ay) * (1.0f - 1e-6f));
+            }
+        }
+        cmax += stream_slack(inv_k);
+        // pv >= exp(-k cmax); cmax < 0: nothing can pass (pv <= 1)
+        P.lpv[img * FC_CELLS + cell] = expf(fmaxf(P.negk * cmax, -120.0f)) * (1.0f - 1e-4f);
+    }
+    // the per-point test reads one 128-byte line per cell: 25 window values of U, 4 corner values of T_far
+    float* win = reinterpret_cast<float*>(P.win + img * (size_t)FC_CELLS * 8);
+    for (int t = tid; t < FC_CELLS * 32; t += 1024) {
+        const int cell = t >> 5, k = t & 31, i = cell >> 6, j = cell & 63;
+        float val = 0.0f;
+        if (k < 25) {
+            const int qi = i + k / 5 - 2, qj = j + k % 5 - 2;
+            val = (qi >= 0 && qi < FC_G && qj >= 0 && qj < FC_G) ? s_U[qi * FC_G + qj] : -INFINITY;
+        } else if (k < 29) {
+            val = s_T[(i + ((k - 25) >> 1)) * (FC_G + 1) + j + ((k - 25) & 1)];
+        }
+        win[t] = val;
     }
 }
 
 // ---- S3: filter --------------------------------------------------------------------------------
 // grid (ceil(V / FS_VPC_FILTER), chunks of P.filter_chunk points, B): the view groups of one chunk run back to back, so
 // the chunk is read from HBM once and from L2 afterwards.
-// Two steps.  (1) A point of cell a can only survive if its pv reaches  L[a] = min(eff[a] / FS_UP, thr[a])  (its value is
-// at most pv: the Gaussian weight is <= 1).  L (one float per cell and image) is staged in shared memory for 5 views x 2
-// clouds; per point and view this costs three float4 shared loads, ~30 FP32 ops and one random shared load.  The points
-// that pass (the front layer and the rim of the cloud, a few per cent) are pushed on a shared-memory queue, one ballot per
-// warp (every warp owns a queue; no block barrier in the loop).  (2) Whenever a warp's queue fills, and at the end, the warp processes its entries with all lanes busy: the full test
-// against (eff, thr) from global memory, then one global atomic per warp and image to reserve list space.
+// Two steps.  (1) A point of cell a can only survive if its pv reaches lpv[a] (S2).  lpv (one float per cell and image) is
+// staged in shared memory for 5 views x 2 clouds; per point and view this costs three float4 shared loads, ~30 FP32 ops and
+// one random shared load.  The points that pass (the front layer and the rim of the cloud, a few per cent) are pushed on a
+// shared-memory queue, one ballot per warp (every warp owns a queue; no block barrier in the loop).  (2) Whenever a warp's
+// queue fills, and at the end, the warp processes its entries with all lanes busy: the per-point test
+// T_lowerbound(x_i) <= -c_i (S2) with the four corner values of the point's cell from global memory, then one global atomic
+// per warp and image to reserve list space.  Every point that attains a pixel's maximum passes -- all points that tie
+// included -- so rendering the survivors is bit-identical to rendering the cloud.
 constexpr int FS_WQ = 384;                               // queue entries per warp: (image of the CTA) << 20 | point of the chunk
 constexpr size_t FS_FILTER_SMEM = (size_t)FS_VPC_FILTER * 2 * FC_CELLS * sizeof(float) + (size_t)(FS_FILTER_THREADS / 32) * FS_WQ * sizeof(unsigned);
 static_assert(FS_WQ > 32 * FS_VPC_FILTER && FS_FILTER_CHUNK_MAX <= (1 << 20), "queue layout");
@@ -255,6 +347,36 @@ __device__ __forceinline__ FilterPoint filter_point(float x, float y, float z, c
     return f;
 }
 
+// The per-point test of S3 (inside points only): may point f reach U at some pixel?  Pixels of the 5 x 5 neighbourhood of
+// its cell exactly, all others through the interpolated corner values of T_far (lower bound, see S2).  One 128-byte line.
+__device__ __forceinline__ bool point_may_win(const FilterPoint& f, const float4* __restrict__ win, float inv_k)
+{
+    const float h = 1.0f / FC_CELLS_PER_NDC;
+    const float c_lo = -logf(f.pv_hi) * inv_k * (1.0f - 1e-5f);          // pv rounded up -> c rounded down
+    const float thr = stream_slack(inv_k) - c_lo;
+    const float4* line = win + (size_t)f.cell * 8;
+    float w[32];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const float4 v = __ldg(line + k);
+        w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
+    }
+    const float tx = f.ux - f.cj, ty = f.uy - f.cr;                      // position in the cell, [0, 1)
+    float best = INFINITY;                                               // min over the window of |x - q|^2 - U(q)
+#pragma unroll
+    for (int di = -2; di <= 2; ++di) {
+        const float dy = (ty - (float)di - 0.5f) * h;
+#pragma unroll
+        for (int dj = -2; dj <= 2; ++dj) {
+            const float dx = (tx - (float)dj - 0.5f) * h;
+            best = fminf(best, __fmaf_rn(dx, dx, dy * dy) - w[(di + 2) * 5 + dj + 2]);
+        }
+    }
+    const float top = __fmaf_rn(tx, w[26] - w[25], w[25]), bot = __fmaf_rn(tx, w[28] - w[27], w[27]);
+    const float tlb = __fmaf_rn(ty, bot - top, top) - h * h * (tx * (1.0f - tx) + ty * (1.0f - ty));
+    return fminf(best, tlb) <= thr;
+}
+
 __global__ void __launch_bounds__(FS_FILTER_THREADS, 1)
 stream_filter_kernel(StreamParams P)
 {
@@ -278,16 +400,10 @@ stream_filter_kernel(StreamParams P)
     const bool has_pose = P.pose != nullptr;
     if (has_pose && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
     const size_t img0 = ((size_t)b * P.V + v0) * 2;
-    const float2* bnd0 = P.bnd + img0 * FC_CELLS;
-    for (int t = tid; t < nv * 2 * FC_CELLS; t += FS_FILTER_THREADS) {
-        const float2 bd = __ldg(bnd0 + t);               // (eff, thr); eff: -1 unknown, 0 exactly zero -> L <= 0: everything passes
-        s_L[t] = fminf(bd.x * (1.0f / FS_UP) * (1.0f - 1e-5f), bd.y);   // weight <= 1 + 2^-22 (ex2.approx)
-    }
+    const float* lpv0 = P.lpv + img0 * FC_CELLS;
+    for (int t = tid; t < nv * 2 * FC_CELLS; t += FS_FILTER_THREADS) s_L[t] = __ldg(lpv0 + t);
     __syncthreads();
-    const float negkc = P.negk / (FC_CELLS_PER_NDC * FC_CELLS_PER_NDC);
-    const float negkc2 = negkc * 1.4426950408889634f;   // exp(a) = 2^(a log2 e)
-    // flushing tiny weights to zero is only safe when the weight AT THE HOME PIXEL (d2c <= 1/2 cell^2) cannot be tiny
-    const bool ftz_ok = negkc * 0.5f > -60.0f;
+    const float inv_k = -1.0f / P.negk;
     const int npts = (int)min((int64_t)P.filter_chunk, sp.end - base);
     const int split = (int)min((int64_t)npts, max((int64_t)0, sp.tgt0 - base));     // points [0, split) are source points
 
@@ -295,6 +411,7 @@ stream_filter_kernel(StreamParams P)
     unsigned* wq = s_q + (tid >> 5) * FS_WQ;
     int wcount = 0;                                      // warp-uniform
     auto drain = [&]() {
+        if (lane == 0 && wcount) atomicAdd(P.stats, (unsigned long long)wcount);
         for (int t0 = 0; t0 < wcount; t0 += 32) {
             const int t = t0 + lane;
             bool keep = false; int l = 0, li = 0;
@@ -308,14 +425,7 @@ stream_filter_kernel(StreamParams P)
                 if (has_pose && c == 0) apply_pose(s_pose, x, y, z);
                 const FilterPoint f = filter_point(x, y, z, s_view[l >> 1]);
                 li = (int)(base + pi - (c ? sp.tgt0 : sp.src0));
-                keep = true;
-                if (f.inside) {
-                    const float2 bd = __ldg(bnd0 + (size_t)l * FC_CELLS + f.cell);
-                    const float fx = f.ux - f.cj - 0.5f, fy = f.uy - f.cr - 0.5f;
-                    const float d2c = __fmaf_rn(fx, fx, fy * fy);
-                    const float wgt = ftz_ok ? ex2_ftz(d2c * negkc2) : exp_fast(d2c * negkc);
-                    keep = (f.pv_hi * wgt * FS_UP >= bd.x) || (f.pv_hi >= bd.y);
-                }
+                keep = !f.inside || point_may_win(f, P.win + (img0 + l) * (size_t)FC_CELLS * 8, inv_k);
             }
             const unsigned km = __ballot_sync(0xFFFFFFFFu, keep);
             if (keep) {                                  // one global atomic per warp and image
@@ -361,6 +471,109 @@ stream_filter_kernel(StreamParams P)
     }
     __syncwarp();
     drain();
+}
+
+// ---- second round: re-seed from the survivors, filter the survivor lists again ------------------------------------
+// The first round's seeds are the best of a SAMPLE, so its survivors are the points that beat the best sample somewhere:
+// about (points per cell) / (samples per cell) per cell and neighbour.  They contain every true winner, hence seeding
+// again from them gives the true per-cell best, and the same exact test then leaves little more than the winners.
+// Both kernels walk one image's list: grid (chunks of FS_R2_CHUNK list entries, V * 2, B).
+constexpr int FS_R2_CHUNK = 32768;
+constexpr unsigned FS_R2_OVERFLOW = 0xFFFFFFFFu;         // surv2_cnt of an image whose first list overflowed
+
+struct Round2Ctx { size_t img; int64_t lo; unsigned n1; bool posed; };
+__device__ __forceinline__ Round2Ctx round2_ctx(const StreamParams& P) {
+    Round2Ctx C;
+    const int vc = blockIdx.y, v = vc >> 1, c = vc & 1, b = blockIdx.z;
+    C.img = ((size_t)b * P.V + v) * 2 + c;
+    const ItemSpan sp = item_span(P.offs, b);
+    C.lo = c ? sp.tgt0 : sp.src0;
+    C.n1 = P.surv_cnt[C.img];
+    C.posed = P.pose != nullptr && c == 0;
+    return C;
+}
+
+__global__ void __launch_bounds__(FS_THREADS)
+stream_reseed_kernel(StreamParams P)
+{
+    __shared__ unsigned long long s_tile[FC_CELLS];
+    __shared__ StreamView s_view;
+    __shared__ float s_pose[12];
+    const Round2Ctx C = round2_ctx(P);
+    if (C.n1 > (unsigned)P.surv_cap || (unsigned)blockIdx.x * FS_R2_CHUNK >= C.n1) return;
+    const int tid = threadIdx.x, b = blockIdx.z, v = blockIdx.y >> 1;
+    stream_load_views(P, b, v, 1, &s_view);
+    if (C.posed && tid < 12) s_pose[tid] = P.pose[(size_t)b * 12 + tid];
+    for (int t = tid; t < FC_CELLS; t += FS_THREADS) s_tile[t] = 0ull;
+    __syncthreads();
+    const float negkc = P.negk / (FC_CELLS_PER_NDC * FC_CELLS_PER_NDC);
+    const int* list = P.surv + C.img * (size_t)P.surv_cap;
+    const unsigned stop = min(C.n1, (blockIdx.x + 1u) * FS_R2_CHUNK);
+    for (unsigned t = blockIdx.x * FS_R2_CHUNK + tid; t < stop; t += FS_THREADS) {
+        const unsigned li = (unsigned)__ldg(list + t);
+        const float* q = P.xyz + (size_t)(C.lo + li) * 3;
+        float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+        if (C.posed) apply_pose(s_pose, x, y, z);
+        const StreamPoint pt = stream_point(x, y, z, s_view);
+        const float pv_lo = pt.pv - FS_PV_ABS;
+        if (!(pv_lo > 0.0f) || !pt.inside) continue;
+        const float val = pv_lo * home_weight(pt, negkc);
+        const unsigned bits = __float_as_uint(val);
+        unsigned long long* slot = &s_tile[pt.cell];
+        if (val > 0.0f && bits > (unsigned)(*reinterpret_cast<volatile unsigned long long*>(slot) >> 32))
+            atomicMax(slot, ((unsigned long long)bits << 32) | li);
+    }
+    __syncthreads();
+    unsigned long long* out = P.seed + C.img * FC_CELLS;
+    for (int t = tid; t < FC_CELLS; t += FS_THREADS) {
+        const unsigned long long key = s_tile[t];
+        if (key != 0ull && key > out[t]) atomicMax(&out[t], key);
+    }
+}
+
+__global__ void __launch_bounds__(FS_THREADS)
+stream_refilter_kernel(StreamParams P)
+{
+    __shared__ StreamViewPacked s_view;
+    __shared__ float s_pose[12];
+    const Round2Ctx C = round2_ctx(P);
+    if (C.n1 > (unsigned)P.surv_cap) {                    // first list incomplete: no second list either
+        if (blockIdx.x == 0 && threadIdx.x == 0) P.surv2_cnt[C.img] = FS_R2_OVERFLOW;
+        return;
+    }
+    if ((unsigned)blockIdx.x * FS_R2_CHUNK >= C.n1) return;
+    const int tid = threadIdx.x, lane = tid & 31, b = blockIdx.z, v = blockIdx.y >> 1;
+    if (tid == 0) {
+        const float* R = P.views + (size_t)v * 9;
+        const float zmin = dec_f32(P.zenc[((size_t)b * P.V + v) * 2]), zmax = dec_f32(P.zenc[((size_t)b * P.V + v) * 2 + 1]);
+        s_view.rx = make_float4(R[0], R[1], R[2], zmin);
+        s_view.ry = make_float4(R[3], R[4], R[5], 1.0f / z_range(zmin, zmax));
+        s_view.rz = make_float4(R[6], R[7], R[8], 0.0f);
+    }
+    if (C.posed && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    __syncthreads();
+    const float inv_k = -1.0f / P.negk;
+    const int* list = P.surv + C.img * (size_t)P.surv_cap;
+    const unsigned first = blockIdx.x * FS_R2_CHUNK, stop = min(C.n1, first + FS_R2_CHUNK);
+    for (unsigned t0 = first + (tid - lane); t0 < stop; t0 += FS_THREADS) {
+        const unsigned t = t0 + lane;
+        bool keep = false; int li = 0;
+        if (t < stop) {
+            li = __ldg(list + t);
+            const float* q = P.xyz + (size_t)(C.lo + li) * 3;
+            float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+            if (C.posed) apply_pose(s_pose, x, y, z);
+            const FilterPoint f = filter_point(x, y, z, s_view);
+            keep = f.pv_hi > 0.0f && (!f.inside || point_may_win(f, P.win + C.img * (size_t)FC_CELLS * 8, inv_k));
+        }
+        const unsigned km = __ballot_sync(0xFFFFFFFFu, keep);
+        if (km) {
+            unsigned gp = 0;
+            if (lane == 0) gp = atomicAdd(&P.surv2_cnt[C.img], (unsigned)__popc(km));
+            gp = __shfl_sync(0xFFFFFFFFu, gp, 0) + __popc(km & ((1u << lane) - 1u));
+            if (keep && gp < (unsigned)P.surv2_cap) P.surv2[C.img * (size_t)P.surv2_cap + gp] = li;
+        }
+    }
 }
 
 }  // namespace scream

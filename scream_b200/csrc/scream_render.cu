@@ -33,7 +33,7 @@ int fail(int code, const char* fmt, ...) {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, total; bool stream; int surv_cap; };
+struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, surv2_off, total; bool stream; int surv_cap, surv2_cap; };
 
 // The giant-cloud pre-filter (forward_stream.cuh) is used when the AVERAGE item reaches FS_MIN_AVG_PTS points
 // (decided from B and total_pts alone, so the workspace query and the forward call agree) and w == 64.
@@ -47,15 +47,17 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
     L.zenc_off = take((size_t)B * V * 2 * sizeof(unsigned));
     L.stream = stream_eligible(B, w, total_pts);
-    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = 0;
+    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = 0;
+    L.surv2_cap = 1 << 18;
     // rim cells of a solid cloud pass the cell-level test wholesale (~2-3 % of the points): keep room for 1/16
     L.surv_cap = (int)std::min<int64_t>(std::max<int64_t>(FS_SURV_MIN, total_pts / 16), 1 << 26);
     if (L.stream) {
         const size_t imgs = (size_t)B * V * 2;
-        L.seed_off = take(imgs * FC_CELLS * sizeof(unsigned));
-        L.cnt_off = take(imgs * sizeof(unsigned));          // directly after seed: one memset clears both
-        L.thr_off = take(imgs * FC_CELLS * sizeof(float2));     // (eff, thr) per cell
+        L.seed_off = take(imgs * FC_CELLS * sizeof(unsigned long long));    // (value bits, point) seed keys
+        L.cnt_off = take(imgs * 2 * sizeof(unsigned) + 64); // round-1 and round-2 counters + 2 diagnostic u64, directly after seed: one memset clears all
+        L.thr_off = take(imgs * (size_t)FC_CELLS * 33 * sizeof(float));     // per cell: one 128-byte line of the per-point test, then lpv
         L.surv_off = take(imgs * (size_t)L.surv_cap * sizeof(int));
+        L.surv2_off = take(imgs * (size_t)L.surv2_cap * sizeof(int));
     }
     L.total = off;
     return L;
@@ -125,15 +127,20 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
     P.negk = -rho2 * 0.5f; P.inv_negk = 1.0f / P.negk;
     P.flags = flags; P.imgs = imgs; P.winner = winner; P.zrange = (flags & SCREAM_F_ZRANGE_IN) ? nullptr : zrange;
     P.surv = nullptr; P.surv_cnt = nullptr; P.surv_cap = 0;
+    P.surv1 = nullptr; P.surv1_cnt = nullptr; P.surv1_cap = 0;
     // giant clouds: seed z-buffer -> bounds -> filter, then the culled kernel renders the survivors
     const int zero_radius = (int)ceilf(sqrtf(FC_EXP_ZERO / (0.5f * rho2)) * FC_CELLS_PER_NDC) + 1;
     if (L.stream && !(flags & (SCREAM_F_DENSE | SCREAM_F_NOSTREAM)) && zero_radius <= 32) {
         StreamParams S;
         S.xyz = xyz; S.offs = offs; S.pose = pose; S.views = views; S.zenc = zenc; S.B = B; S.V = V; S.negk = P.negk;
-        S.seed = reinterpret_cast<unsigned*>((char*)ws + L.seed_off);
-        S.bnd = reinterpret_cast<float2*>((char*)ws + L.thr_off);
+        S.seed = reinterpret_cast<unsigned long long*>((char*)ws + L.seed_off);
+        S.win = reinterpret_cast<float4*>((char*)ws + L.thr_off);
+        S.lpv = reinterpret_cast<float*>(S.win + (size_t)B * V * 2 * FC_CELLS * 8);
         S.surv_cnt = reinterpret_cast<unsigned*>((char*)ws + L.cnt_off);
         S.surv = reinterpret_cast<int*>((char*)ws + L.surv_off); S.surv_cap = L.surv_cap;
+        S.surv2_cnt = S.surv_cnt + (size_t)B * V * 2;
+        S.stats = reinterpret_cast<unsigned long long*>((char*)ws + L.cnt_off + align_up((size_t)B * V * 4 * sizeof(unsigned), 8));
+        S.surv2 = reinterpret_cast<int*>((char*)ws + L.surv2_off); S.surv2_cap = L.surv2_cap;
         CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
         const int64_t mi = (max_item_pts <= 0 || max_item_pts > total_pts) ? total_pts : max_item_pts;
         // S1 seeds from a subset of the cloud (about 4 M points per item: ~1000 per pixel): any subset gives valid bounds
@@ -151,7 +158,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
             int dev = 0;
             CUDA_TRY(cudaGetDevice(&dev));
             if (bound_attr_dev != dev) {
-                CUDA_TRY(cudaFuncSetAttribute(stream_bound_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_BOUND_SMEM(32)));
+                CUDA_TRY(cudaFuncSetAttribute(stream_bound_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_BOUND_SMEM));
                 CUDA_TRY(cudaFuncSetAttribute(stream_seed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_SEED_SMEM));
                 CUDA_TRY(cudaFuncSetAttribute(stream_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_FILTER_SMEM));
                 bound_attr_dev = dev;
@@ -159,10 +166,26 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         }
         if (chunks > 2147483647LL || V > 65535 * 2) return fail(SCREAM_E_UNSUPPORTED, "cloud too large for the stream grid");
         stream_seed_kernel<<<dim3((unsigned)chunks, (unsigned)((V + FS_VPC - 1) / FS_VPC), (unsigned)B), FS_THREADS, FS_SEED_SMEM, st>>>(S);
-        stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM(zero_radius), st>>>(S, zero_radius);
+        stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM, st>>>(S);
         stream_filter_kernel<<<dim3((unsigned)vgroups, (unsigned)fchunks, (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
+        // second round: seeds from the survivors (the true per-cell best), bounds again, survivor lists filtered again.
+        // Pays once the first round's seeds are a thin sample of the cloud (its survivors grow with the stride).
+        const bool round2 = S.seed_stride >= 4;
+        if (round2) {
+            const unsigned r2chunks = (unsigned)((std::min<int64_t>(mi, L.surv_cap) + FS_R2_CHUNK - 1) / FS_R2_CHUNK);
+            CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.cnt_off - L.seed_off, st));
+            const dim3 g2(r2chunks, (unsigned)(V * 2), (unsigned)B);
+            stream_reseed_kernel<<<g2, FS_THREADS, 0, st>>>(S);
+            stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM, st>>>(S);
+            stream_refilter_kernel<<<g2, FS_THREADS, 0, st>>>(S);
+        }
         CUDA_TRY(cudaGetLastError());
-        P.surv = S.surv; P.surv_cnt = S.surv_cnt; P.surv_cap = L.surv_cap;
+        if (round2) {
+            P.surv = S.surv2; P.surv_cnt = S.surv2_cnt; P.surv_cap = L.surv2_cap;
+            P.surv1 = S.surv; P.surv1_cnt = S.surv_cnt; P.surv1_cap = L.surv_cap;
+        } else {
+            P.surv = S.surv; P.surv_cnt = S.surv_cnt; P.surv_cap = L.surv_cap;
+        }
     }
     if (flags & SCREAM_F_DENSE) {
         const long long grid = (long long)B * V * 2 * (w * w / FD_TILE);

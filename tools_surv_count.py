@@ -1,0 +1,25 @@
+"""Diagnostics (GPU): survivor counts of the giant-cloud filter rounds vs the number of distinct winners.
+    python tools_surv_count.py <n_points> [views]"""
+import sys, numpy as np, torch
+sys.path.insert(0,'/root/repo')
+from scream_b200 import _lib, synth
+from scream_b200.render import make_offsets
+n=int(sys.argv[1]); V=int(sys.argv[2]) if len(sys.argv)>2 else 8
+dev=torch.device('cuda:0'); rng=np.random.default_rng(5)
+d=rng.standard_normal((n,3)).astype(np.float32); d/=np.linalg.norm(d,axis=1,keepdims=True)
+xyz=torch.from_numpy(d*(rng.random((n,1),dtype=np.float32)**np.float32(1/3))).to(dev)
+offs=make_offsets([(n//2,n-n//2)]).to(dev); views=torch.from_numpy(synth.random_views(V,5)).to(dev)
+lib=_lib.load(); nws=_lib.workspace_bytes(1,V,64,n); ws=torch.zeros(nws,dtype=torch.uint8,device=dev)
+imgs=torch.empty((1,V,2,64,64),device=dev); win=torch.empty((1,V,2,64,64),dtype=torch.int32,device=dev); zr=torch.empty((1,V,2),device=dev)
+rc=lib.scream_render_forward(xyz.data_ptr(),offs.data_ptr(),n,n,None,views.data_ptr(),1,V,64,24.0,1,imgs.data_ptr(),win.data_ptr(),zr.data_ptr(),ws.data_ptr(),nws,torch.cuda.current_stream().cuda_stream)
+torch.cuda.synchronize(); assert rc==0
+al=lambda x:(x+255)//256*256
+cnt_off=al(V*2*4)+al(V*2*4096*8)
+cnt=ws[cnt_off:cnt_off+V*2*4].view(torch.int32).cpu().numpy()
+cnt2=ws[cnt_off+V*2*4:cnt_off+V*2*8].view(torch.int32).cpu().numpy()
+print("n",n,"round-1 survivors per image: mean",cnt.mean(),"max",cnt.max(),"frac of cloud",cnt.mean()/(n/2))
+st=ws[cnt_off+(V*2*8+7)//8*8:cnt_off+(V*2*8+7)//8*8+16].view(torch.int64).cpu().numpy()
+print("   step-1 passes (point,view pairs):",int(st[0]),"=",st[0]/(n*V),"of all pairs")
+print("   round-2 survivors per image: mean",cnt2.mean(),"max",cnt2.max())
+# how many survivors actually win a pixel
+w=win[0].cpu().numpy(); print("distinct winners per image (mean)", np.mean([len(np.unique(w[v,c])) for v in range(V) for c in range(2)]))
