@@ -161,6 +161,43 @@ def run_reference(args, rank: int):
     print(json.dumps(line), flush=True)
 
 
+def streaming_leg(dev, peak_gbs: float, n: int = 100_000_000, n_views: int = 64, steps: int = 5):
+    """BASELINE.json configs[4] on one GPU (the regime where HBM is the roofline the metric names): one pair of n/2 +
+    n/2 unit-ball points, 64 random views, w = 64, rho = 24, forward with winner maps, inputs resident in HBM
+    (1.2 GB: ten times the L2).  Reported beside the cfg2 headline; SURVEY 8d's per-view accounting V*12*N + V*2*w^2*8."""
+    from scream_b200 import synth
+    from scream_b200.render import render_batch, make_offsets
+    g = torch.Generator(device=dev).manual_seed(1234 + 5)
+    d = torch.randn((n, 3), generator=g, device=dev)
+    d /= d.norm(dim=1, keepdim=True)
+    xyz = (d * torch.rand((n, 1), generator=g, device=dev) ** (1.0 / 3.0)).contiguous()
+    del d
+    offs = make_offsets([(n // 2, n - n // 2)]).to(dev)
+    views = torch.from_numpy(synth.random_views(n_views, 5)).to(dev)
+    run = lambda: render_batch(xyz, offs, views, RHO, W_IMG, need_winner=True, max_item_pts=n)
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out = run()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    alg = n_views * 12 * n + n_views * 2 * W_IMG * W_IMG * 8
+    res = {"workload": "cfg5: one pair, 100 M points x 64 views, fwd + winner maps, giant-cloud path (exact pre-filter + culled render)",
+           "n_points": n, "views": n_views, "ms_per_step": ms, "steps": steps,
+           "gpoint_views_per_sec": n_views * n / ms / 1e6, "images_per_sec": 2 * n_views / ms * 1e3,
+           "roofline": {"bound": "hbm", "achieved": alg / ms / 1e6, "peak": peak_gbs, "unit": "GB/s",
+                        "frac": alg / ms / 1e6 / peak_gbs, "algorithmic_bytes_per_step": alg,
+                        "note": "per-view accounting (SURVEY 8d); the strict compulsory traffic is 12*N per pass over the cloud"},
+           "checksum": float(out[0].sum())}
+    del xyz, out
+    torch.cuda.empty_cache()
+    return res
+
+
 def config_dict(B: int):
     return {"workload": "cfg2: 3DMatch training-batch render, fake fwd(+winner)+bwd and real(posed) fwd",
             "pairs_per_gpu": B, "cloud": CLOUD, "n_src": N_PTS, "n_tgt": N_PTS, "views": V, "w": W_IMG, "rho": RHO,
@@ -284,6 +321,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                          "algorithmic_bytes_per_launch": {"fwd_fake": b_fake, "fwd_real": b_real, "bwd": b_bwd},
                          "ms_per_launch": {"fwd_fake": t_fake, "bwd": t_bwd, "fwd_real": t_real}},
             "clocks": clocks}
+    if world == 1 and not args.no_stream_leg:
+        line["streaming"] = streaming_leg(dev, peak)
     if world == 1 and not args.no_cpu:
         t0 = time.perf_counter()
         cpu_reference_step(0)                      # warm-up
@@ -308,6 +347,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dense", action="store_true", help="force the dense exact kernel")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-stream-leg", action="store_true", help="skip the cfg5 streaming-regime leg (N=1 only)")
     ap.add_argument("--chunk", type=int, default=37, help="pairs per chunk of the host-buffer pipeline (e2e leg)")
     ap.add_argument("--streams", type=int, default=6, help="CUDA streams of the host-buffer pipeline (e2e leg)")
     ap.add_argument("--cloud", default="ball", choices=["ball", "shell"], help="synthetic cloud family (cfg2 default: ball)")

@@ -64,6 +64,9 @@ extern "C" {
 #define SCREAM_F_NOSTREAM   8u   /* giant clouds (average item >= 49152 points, w == 64): skip the streaming pre-filter and
                                     render every batch of the cloud (testing / diagnostics; same bits, slower) */
 
+#define SCREAM_F_THINSEED  16u   /* giant clouds: seed the pre-filter from every 4th chunk only and always run its second
+                                    round, as clouds of >= 16 M points do by themselves (testing; same bits) */
+
 /* opaque CUDA stream handle (cudaStream_t / CUstream) */
 typedef void *scream_stream_t;
 

@@ -17,6 +17,7 @@ F_RAW = 1
 F_DENSE = 2
 F_ZRANGE_IN = 4
 F_NOSTREAM = 8
+F_THINSEED = 16
 
 _lock = threading.Lock()
 _lib = None

@@ -146,7 +146,7 @@ def make_offsets(sizes: Sequence[Tuple[int, int]]) -> torch.Tensor:
 def render_batch(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho, w: int,
                  pose: Optional[torch.Tensor] = None, raw: bool = False, dense: bool = False,
                  need_winner: Optional[bool] = None, max_item_pts: int = 0,
-                 zrange_in: Optional[torch.Tensor] = None, no_stream: bool = False):
+                 zrange_in: Optional[torch.Tensor] = None, no_stream: bool = False, thin_seed: bool = False):
     """Render B pairs at once.  xyz [total,3] fp32 cuda, offs [2B+1] int64 cuda, views [V,3,3] fp32 cuda,
     pose [B,3,4] or None; zrange_in [B,V,2]: use this depth range instead of reducing it (point-sharded
     clouds, scream_b200/shard.py).  Returns (imgs [B,V,2,w,w], winner int32 or empty, zrange [B,V,2])."""
@@ -154,7 +154,8 @@ def render_batch(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho
         raise ValueError("w must be a positive multiple of 64 (render.py:33-34,55)")
     if need_winner is None:
         need_winner = torch.is_grad_enabled() and xyz.requires_grad
-    flags = (_lib.F_RAW if raw else 0) | (_lib.F_DENSE if dense else 0) | (_lib.F_NOSTREAM if no_stream else 0)
+    flags = (_lib.F_RAW if raw else 0) | (_lib.F_DENSE if dense else 0) | (_lib.F_NOSTREAM if no_stream else 0) \
+        | (_lib.F_THINSEED if thin_seed else 0)
     return torch.ops.scream.render_fwd(xyz, offs, pose, views, int(w), float(rho), int(flags),
                                        bool(need_winner), int(max_item_pts), zrange_in)
 

@@ -310,6 +310,10 @@ def test_giant_cloud_stream_filter_is_exact(case):
         assert torch.equal(a[2], b[2])
         assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
         assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
+        # thin seeds + the second filter round (what clouds of >= 16 M points get): same bits again
+        t = render_batch(xyz, offs, views, rho, 64, pose=p, raw=True, need_winner=True, thin_seed=True)
+        assert torch.equal(a[0], t[0]), f"thin seed: values differ at {(a[0] != t[0]).sum().item()} pixels"
+        assert torch.equal(a[1], t[1]), f"thin seed: winners differ at {(a[1] != t[1]).sum().item()} pixels"
     c = render_batch(xyz, offs, views, rho, 64, need_winner=False)
     d = render_batch(xyz, offs, views, rho, 64, need_winner=False, no_stream=True)
     assert torch.equal(c[0], d[0])
