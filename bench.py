@@ -136,6 +136,15 @@ def cpu_reference_step(step: int, seed: int = 77):
 def run_reference(args, rank: int):
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1: give the reference every host core this process may use
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    if torch.get_num_threads() < avail and "SCREAM_REF_THREADS" not in os.environ:
+        torch.set_num_threads(avail)
+    elif "SCREAM_REF_THREADS" in os.environ:
+        torch.set_num_threads(int(os.environ["SCREAM_REF_THREADS"]))
     threads = torch.get_num_threads()
     budget = 240.0
     t_start = time.perf_counter()
