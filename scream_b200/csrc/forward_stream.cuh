@@ -457,10 +457,19 @@ stream_filter_kernel(StreamParams P)
         const float floor_pv = live ? 0.0f : INFINITY;  // dead lanes never pass
         const float* Lc = s_L + c * FC_CELLS;
         const unsigned ebase = ((unsigned)c << 20) | (unsigned)pi;
-        for (int vv = 0; vv < nv; ++vv) {
-            const FilterPoint f = filter_point(x, y, z, s_view[vv]);
-            const float lim = f.inside ? Lc[vv * 2 * FC_CELLS + f.cell] : 0.0f;    // clamped points are never dropped here
-            const bool pass = f.pv_hi > floor_pv && f.pv_hi >= lim;
+#pragma unroll
+        for (int vv = 0; vv < FS_VPC_FILTER; ++vv) {
+            if (vv >= nv) break;
+            // the transform of filter_point() / stream_point(), cell by integer floor: inside <=> both in [0, 64)
+            const float4 rx = s_view[vv].rx, ry = s_view[vv].ry, rz = s_view[vv].rz;
+            const float ux = __fmaf_rn(__fmaf_rn(rx.z, z, __fmaf_rn(rx.y, y, __fmul_rn(rx.x, x))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+            const float uy = __fmaf_rn(__fmaf_rn(ry.z, z, __fmaf_rn(ry.y, y, __fmul_rn(ry.x, x))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+            const float zr = __fmaf_rn(rz.z, z, __fmaf_rn(rz.y, y, __fmul_rn(rz.x, x)));
+            const float pv_hi = __fmaf_rn(-(zr - rx.w), ry.w, 1.0f) + FS_PV_ABS;
+            const int jj = __float2int_rd(ux), ii = __float2int_rd(uy);
+            const bool inside = (unsigned)(ii | jj) < (unsigned)FC_G;
+            const float lim = Lc[vv * 2 * FC_CELLS + (inside ? ii * FC_G + jj : 0)];
+            const bool pass = pv_hi > floor_pv && (pv_hi >= lim || !inside);        // clamped points are never dropped here
             const unsigned pm = __ballot_sync(0xFFFFFFFFu, pass);
             if (pm) {
                 if (pass) wq[wcount + __popc(pm & lt)] = ebase + ((unsigned)vv << 21);
