@@ -320,9 +320,9 @@ stream_bound_kernel(StreamParams P)
 // T_lowerbound(x_i) <= -c_i (S2) with the four corner values of the point's cell from global memory, then one global atomic
 // per warp and image to reserve list space.  Every point that attains a pixel's maximum passes -- all points that tie
 // included -- so rendering the survivors is bit-identical to rendering the cloud.
-constexpr int FS_WQ = 384;                               // queue entries per warp: (image of the CTA) << 20 | point of the chunk
+constexpr int FS_WQ = 512;                               // queue entries per warp: (image of the CTA) << 20 | point of the chunk
 constexpr size_t FS_FILTER_SMEM = (size_t)FS_VPC_FILTER * 2 * FC_CELLS * sizeof(float) + (size_t)(FS_FILTER_THREADS / 32) * FS_WQ * sizeof(unsigned);
-static_assert(FS_WQ > 32 * FS_VPC_FILTER && FS_FILTER_CHUNK_MAX <= (1 << 20), "queue layout");
+static_assert(FS_WQ > 64 * FS_VPC_FILTER && FS_FILTER_CHUNK_MAX <= (1 << 20), "queue layout");
 
 struct StreamViewPacked { float4 rx, ry, rz; };          // (R0..2, zmin), (R3..5, rcp_range), (R6..8, -)
 
@@ -444,39 +444,47 @@ stream_filter_kernel(StreamParams P)
     // step 1: every point of the chunk against the pv thresholds of the CTA's views.  No block barrier in the loop: every
     // warp owns a queue (its fill level lives in a register) and drains it on its own.
     const unsigned lt = (1u << lane) - 1u;
-    for (int p0 = 0; p0 < npts; p0 += FS_FILTER_THREADS) {
-        const int pi = p0 + tid;
-        const bool live = pi < npts;
-        const int c = pi >= split;
-        float x = 0.f, y = 0.f, z = 0.f;
-        if (live) {
-            const float* q = P.xyz + (size_t)(base + pi) * 3;
-            x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2);
-            if (has_pose && c == 0) apply_pose(s_pose, x, y, z);
+    // two points per thread and round: the view constants are loaded once for both
+    for (int p0 = 0; p0 < npts; p0 += 2 * FS_FILTER_THREADS) {
+        float x[2], y[2], z[2], floor_pv[2]; unsigned ebase[2]; const float* Lc[2];
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int pi = p0 + hh * FS_FILTER_THREADS + tid;
+            const bool live = pi < npts;
+            const int c = pi >= split;
+            x[hh] = 0.f; y[hh] = 0.f; z[hh] = 0.f;
+            if (live) {
+                const float* q = P.xyz + (size_t)(base + pi) * 3;
+                x[hh] = __ldg(q); y[hh] = __ldg(q + 1); z[hh] = __ldg(q + 2);
+                if (has_pose && c == 0) apply_pose(s_pose, x[hh], y[hh], z[hh]);
+            }
+            floor_pv[hh] = live ? 0.0f : INFINITY;       // dead lanes never pass
+            Lc[hh] = s_L + c * FC_CELLS;
+            ebase[hh] = ((unsigned)c << 20) | (unsigned)pi;
         }
-        const float floor_pv = live ? 0.0f : INFINITY;  // dead lanes never pass
-        const float* Lc = s_L + c * FC_CELLS;
-        const unsigned ebase = ((unsigned)c << 20) | (unsigned)pi;
 #pragma unroll
         for (int vv = 0; vv < FS_VPC_FILTER; ++vv) {
             if (vv >= nv) break;
-            // the transform of filter_point() / stream_point(), cell by integer floor: inside <=> both in [0, 64)
             const float4 rx = s_view[vv].rx, ry = s_view[vv].ry, rz = s_view[vv].rz;
-            const float ux = __fmaf_rn(__fmaf_rn(rx.z, z, __fmaf_rn(rx.y, y, __fmul_rn(rx.x, x))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
-            const float uy = __fmaf_rn(__fmaf_rn(ry.z, z, __fmaf_rn(ry.y, y, __fmul_rn(ry.x, x))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
-            const float zr = __fmaf_rn(rz.z, z, __fmaf_rn(rz.y, y, __fmul_rn(rz.x, x)));
-            const float pv_hi = __fmaf_rn(-(zr - rx.w), ry.w, 1.0f) + FS_PV_ABS;
-            const int jj = __float2int_rd(ux), ii = __float2int_rd(uy);
-            const bool inside = (unsigned)(ii | jj) < (unsigned)FC_G;
-            const float lim = Lc[vv * 2 * FC_CELLS + (inside ? ii * FC_G + jj : 0)];
-            const bool pass = pv_hi > floor_pv && (pv_hi >= lim || !inside);        // clamped points are never dropped here
-            const unsigned pm = __ballot_sync(0xFFFFFFFFu, pass);
-            if (pm) {
-                if (pass) wq[wcount + __popc(pm & lt)] = ebase + ((unsigned)vv << 21);
-                wcount += __popc(pm);
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                // the transform of filter_point() / stream_point(), cell by integer floor: inside <=> both in [0, 64)
+                const float ux = __fmaf_rn(__fmaf_rn(rx.z, z[hh], __fmaf_rn(rx.y, y[hh], __fmul_rn(rx.x, x[hh]))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+                const float uy = __fmaf_rn(__fmaf_rn(ry.z, z[hh], __fmaf_rn(ry.y, y[hh], __fmul_rn(ry.x, x[hh]))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+                const float zr = __fmaf_rn(rz.z, z[hh], __fmaf_rn(rz.y, y[hh], __fmul_rn(rz.x, x[hh])));
+                const float pv_hi = __fmaf_rn(-(zr - rx.w), ry.w, 1.0f) + FS_PV_ABS;
+                const int jj = __float2int_rd(ux), ii = __float2int_rd(uy);
+                const bool inside = (unsigned)(ii | jj) < (unsigned)FC_G;
+                const float lim = Lc[hh][vv * 2 * FC_CELLS + (inside ? ii * FC_G + jj : 0)];
+                const bool pass = pv_hi > floor_pv[hh] && (pv_hi >= lim || !inside);    // clamped points are never dropped here
+                const unsigned pm = __ballot_sync(0xFFFFFFFFu, pass);
+                if (pm) {
+                    if (pass) wq[wcount + __popc(pm & lt)] = ebase[hh] + ((unsigned)vv << 21);
+                    wcount += __popc(pm);
+                }
             }
         }
-        if (wcount > FS_WQ - 32 * FS_VPC_FILTER) { __syncwarp(); drain(); }      // one more round always fits
+        if (wcount > FS_WQ - 64 * FS_VPC_FILTER) { __syncwarp(); drain(); }      // one more round always fits
     }
     __syncwarp();
     drain();
