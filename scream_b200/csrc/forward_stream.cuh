@@ -43,11 +43,15 @@ struct StreamParams {
     int* surv2; unsigned* surv2_cnt; int surv2_cap;      // ... of the second round (re-seeded from the first round's survivors)
     int seed_stride;                                     // S1 seeds from every seed_stride-th chunk of the cloud (any subset gives valid bounds)
     int filter_chunk;                                    // points per CTA task of S3
-    unsigned long long* stats;                           // [2] diagnostics: (point, view) pairs that passed step 1 / step 2 of S3
+    unsigned long long* stats;                           // [3] diagnostics: (point, view) pairs that passed the cell test / (unused) / the voxel mask of S3
+    unsigned* bbox;                                      // [B][2][6] per cloud (source posed): max keys of ~enc(min x,y,z), enc(max x,y,z); zero-initialised
+    unsigned char* vox;                                  // [B][view groups][2][vox_g^3] bit vv: a point of the voxel may pass view v0 + vv's cell test
+    int vox_g;                                           // voxels per axis of the cloud's bounding box
 };
 
 constexpr int FS_VPC = 2;                                // views per CTA task of S1 (2 views x 2 clouds x 32 KB of 64-bit tiles)
-constexpr int FS_VPC_FILTER = 5;                         // ... of S3: 5 views x 2 clouds x 16 KB of pv thresholds staged in shared memory
+constexpr int FS_VPC_FILTER = 7;                         // ... of S3: 7 views x 16 KB of one cloud's pv thresholds staged in shared memory
+constexpr int FV_G = 40;                                 // voxels per axis of a cloud's bounding box (S2b): g^3 mask bytes per view group, staged too
 constexpr int FS_TC = (FC_G + 1) * (FC_G + 1);           // cell corners per image
 constexpr float FS_PV_ABS = 4e-7f;                       // |1 - (z-zmin)*rcp(range) - pv_exact| (two roundings + rcp) stays below this
 
@@ -309,20 +313,146 @@ stream_bound_kernel(StreamParams P)
     }
 }
 
+// ---- S2b: voxel masks ----------------------------------------------------------------------------
+// The cell test of S3 costs ~50 instructions per (point, view) and only a few per cent pass.  Most pairs can be refused
+// without looking at the view: a voxel grid over each cloud's bounding box, and per voxel and view one bit -- "some point
+// inside this voxel could pass the cell test" (largest pv over the voxel against the smallest threshold over the cells
+// its projection touches, with slack for every rounding involved; conservative, never exact).  S3 then reads one byte
+// per point and view group and only queues the pairs whose bit is set.
+constexpr int FV_BBOX_THREADS = 256, FV_BBOX_PTS = FV_BBOX_THREADS * 32;
+
+// grid (chunks of FV_BBOX_PTS points, B): bounding box of the source cloud (posed, the arithmetic of every other stage)
+// and of the target cloud.
+__global__ void __launch_bounds__(FV_BBOX_THREADS)
+stream_bbox_kernel(StreamParams P)
+{
+    __shared__ float s_pose[12];
+    __shared__ unsigned s_key[12];
+    const int b = blockIdx.y, tid = threadIdx.x;
+    const ItemSpan sp = item_span(P.offs, b);
+    const int64_t base = sp.src0 + (int64_t)blockIdx.x * FV_BBOX_PTS;
+    if (base >= sp.end) return;
+    if (P.pose && tid < 12) s_pose[tid] = P.pose[(size_t)b * 12 + tid];
+    if (tid >= 32 && tid < 44) s_key[tid - 32] = 0u;
+    __syncthreads();
+    float lo[2][3], hi[2][3];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) { lo[k / 3][k % 3] = INFINITY; hi[k / 3][k % 3] = -INFINITY; }
+    const int64_t stop = min(sp.end, base + FV_BBOX_PTS);
+    for (int64_t gi = base + tid; gi < stop; gi += FV_BBOX_THREADS) {
+        const float* q = P.xyz + (size_t)gi * 3;
+        float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+        if (gi < sp.tgt0) {
+            if (P.pose) apply_pose(s_pose, x, y, z);
+            lo[0][0] = fminf(lo[0][0], x); lo[0][1] = fminf(lo[0][1], y); lo[0][2] = fminf(lo[0][2], z);
+            hi[0][0] = fmaxf(hi[0][0], x); hi[0][1] = fmaxf(hi[0][1], y); hi[0][2] = fmaxf(hi[0][2], z);
+        } else {
+            lo[1][0] = fminf(lo[1][0], x); lo[1][1] = fminf(lo[1][1], y); lo[1][2] = fminf(lo[1][2], z);
+            hi[1][0] = fmaxf(hi[1][0], x); hi[1][1] = fmaxf(hi[1][1], y); hi[1][2] = fmaxf(hi[1][2], z);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const unsigned kl = __reduce_max_sync(0xFFFFFFFFu, ~enc_f32(lo[c][a]));
+            const unsigned kh = __reduce_max_sync(0xFFFFFFFFu, enc_f32(hi[c][a]));
+            if ((tid & 31) == 0) { atomicMax(&s_key[c * 6 + a], kl); atomicMax(&s_key[c * 6 + 3 + a], kh); }
+        }
+    }
+    __syncthreads();
+    if (tid < 12) atomicMax(P.bbox + (size_t)b * 12 + tid, s_key[tid]);
+}
+
+struct VoxelGrid { float lo[3], inv[3]; bool ok; };       // voxel index along a = min(int((p[a] - lo[a]) * inv[a]), g - 1)
+__device__ __forceinline__ VoxelGrid voxel_grid(const unsigned* __restrict__ bb, int g, float* ext) {
+    VoxelGrid G; G.ok = true;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float lo = dec_f32(~bb[a]), hi = dec_f32(bb[3 + a]);
+        const float e = hi - lo;
+        G.ok = G.ok && (e >= 0.0f) && (e < INFINITY);                       // an empty cloud or NaN / inf coordinates: no grid
+        G.lo[a] = lo; G.inv[a] = e > 0.0f ? (float)g / e : 0.0f;
+        if (ext) ext[a] = e;
+    }
+    return G;
+}
+
+// grid (ceil(g^3 / 256), view groups * 2 clouds, B): one thread per voxel, the FS_VPC_FILTER views of the group.
+constexpr int FV_FOOT_MAX = 8;                            // projections wider than this many cells: keep
+
+__global__ void __launch_bounds__(256)
+stream_voxmask_kernel(StreamParams P)
+{
+    __shared__ StreamView s_view[FS_VPC_FILTER];
+    const int g = P.vox_g, nvox = g * g * g;
+    const int grp = blockIdx.y >> 1, c = blockIdx.y & 1, b = blockIdx.z;
+    const int v0 = grp * FS_VPC_FILTER, nv = min(FS_VPC_FILTER, P.V - v0);
+    stream_load_views(P, b, v0, nv, s_view);
+    __syncthreads();
+    const int vox = blockIdx.x * 256 + threadIdx.x;
+    if (vox >= nvox) return;
+    const int groups = (P.V + FS_VPC_FILTER - 1) / FS_VPC_FILTER;
+    unsigned char* out = P.vox + (((size_t)b * groups + grp) * 2 + c) * (size_t)nvox + vox;
+    float ext[3];
+    const VoxelGrid G = voxel_grid(P.bbox + ((size_t)b * 2 + c) * 6, g, ext);
+    if (!G.ok) { *out = 0xFF; return; }
+    const int iv[3] = { vox % g, (vox / g) % g, vox / (g * g) };
+    float cp[3], hs[3], M = 0.0f;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) M = fmaxf(M, fmaxf(fabsf(G.lo[a]), fabsf(G.lo[a] + ext[a])));
+    const float rnd = 2e-6f * M + 1e-30f;                 // rounding of a rotated coordinate, here plus in the per-point transform
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float s = ext[a] / (float)g;
+        cp[a] = G.lo[a] + ((float)iv[a] + 0.5f) * s;
+        hs[a] = 0.5f * s * (1.0f + 1e-3f) + rnd;          // index rounding (<= 2e-5 voxels) and the centre's own rounding
+    }
+    unsigned mask = 0u;
+    for (int vv = 0; vv < nv; ++vv) {
+        const StreamView& W = s_view[vv];
+        const float uxc = __fmaf_rn(rot_row(W.R, cp[0], cp[1], cp[2]), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+        const float uyc = __fmaf_rn(rot_row(W.R + 3, cp[0], cp[1], cp[2]), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+        const float zc = rot_row(W.R + 6, cp[0], cp[1], cp[2]);
+        const float ex = (fabsf(W.R[0]) * hs[0] + fabsf(W.R[1]) * hs[1] + fabsf(W.R[2]) * hs[2] + rnd) * FC_CELLS_PER_NDC + 1e-4f;
+        const float ey = (fabsf(W.R[3]) * hs[0] + fabsf(W.R[4]) * hs[1] + fabsf(W.R[5]) * hs[2] + rnd) * FC_CELLS_PER_NDC + 1e-4f;
+        const float ez = fabsf(W.R[6]) * hs[0] + fabsf(W.R[7]) * hs[1] + fabsf(W.R[8]) * hs[2] + rnd;
+        const float fj0 = floorf(uxc - ex), fj1 = floorf(uxc + ex), fi0 = floorf(uyc - ey), fi1 = floorf(uyc + ey);
+        bool keep = !(fj0 >= 0.0f && fi0 >= 0.0f && fj1 < (float)FC_G && fi1 < (float)FC_G);   // touches the outside (or NaN)
+        keep = keep || fj1 - fj0 >= (float)FV_FOOT_MAX || fi1 - fi0 >= (float)FV_FOOT_MAX;
+        if (!keep) {
+            const float pv_max = __fmaf_rn(-((zc - ez) - W.zmin), W.rcp_range, 1.0f) + (FS_PV_ABS + 1e-6f);
+            const float* L = P.lpv + (((size_t)b * P.V + v0 + vv) * 2 + c) * FC_CELLS;
+            float lim = INFINITY;
+            for (int i = (int)fi0; i <= (int)fi1; ++i)
+                for (int j = (int)fj0; j <= (int)fj1; ++j) lim = fminf(lim, __ldg(L + i * FC_G + j));
+            keep = pv_max >= lim;
+        }
+        if (keep) mask |= 1u << vv;
+    }
+    *out = (unsigned char)mask;
+}
+
 // ---- S3: filter --------------------------------------------------------------------------------
-// grid (ceil(V / FS_VPC_FILTER), chunks of P.filter_chunk points, B): the view groups of one chunk run back to back, so
-// the chunk is read from HBM once and from L2 afterwards.
-// Two steps.  (1) A point of cell a can only survive if its pv reaches lpv[a] (S2).  lpv (one float per cell and image) is
-// staged in shared memory for 5 views x 2 clouds; per point and view this costs three float4 shared loads, ~30 FP32 ops and
-// one random shared load.  The points that pass (the front layer and the rim of the cloud, a few per cent) are pushed on a
-// shared-memory queue, one ballot per warp (every warp owns a queue; no block barrier in the loop).  (2) Whenever a warp's
-// queue fills, and at the end, the warp processes its entries with all lanes busy: the per-point test
-// T_lowerbound(x_i) <= -c_i (S2) with the four corner values of the point's cell from global memory, then one global atomic
-// per warp and image to reserve list space.  Every point that attains a pixel's maximum passes -- all points that tie
-// included -- so rendering the survivors is bit-identical to rendering the cloud.
-constexpr int FS_WQ = 512;                               // queue entries per warp: (image of the CTA) << 20 | point of the chunk
-constexpr size_t FS_FILTER_SMEM = (size_t)FS_VPC_FILTER * 2 * FC_CELLS * sizeof(float) + (size_t)(FS_FILTER_THREADS / 32) * FS_WQ * sizeof(unsigned);
-static_assert(FS_WQ > 64 * FS_VPC_FILTER && FS_FILTER_CHUNK_MAX <= (1 << 20), "queue layout");
+// grid (ceil(V / FS_VPC_FILTER), 2 clouds x chunks of P.filter_chunk points, B): the view groups of one chunk run back
+// to back, so the chunk is read from HBM once and from L2 afterwards.  A CTA works on ONE cloud's points, so it stages
+// that cloud's tables only: the voxel masks of its view group (S2b) and the pv thresholds lpv of its views (S2).
+// Per round a warp takes 32 points:
+//  (0) voxel byte of each point (one shared load) -> the (view, point) pairs whose bit is set go on the warp's pair
+//      queue (one ballot per view);
+//  (1) the queue is worked off 32 pairs at a time, all lanes busy: coordinates by shuffle from the lane that holds the
+//      point, transform, pv against the threshold of the point's cell (one random shared load); pairs that pass (the
+//      front layer and the rim of the cloud, a few per cent) go on the warp's step-2 queue;
+//  (2) whenever that queue fills, and at the end: the per-point test T_lowerbound(x_i) <= -c_i (S2) with the 128-byte
+//      line of the point's cell from global memory, then one global atomic per warp and image to reserve list space.
+// Every point that attains a pixel's maximum passes -- all points that tie included -- so rendering the survivors is
+// bit-identical to rendering the cloud.  No block barrier in the loop (queues are per warp, fill levels in registers).
+constexpr int FS_WQ = 64;                                // step-2 queue entries per warp: view << 21 | cloud << 20 | point of the chunk
+constexpr int FS_Q1 = 256;                               // pair queue per warp, a ring (u16: slot << 8 | view << 5 | lane): < 32 left over + 32 * views per round
+constexpr size_t FS_FILTER_SMEM = (size_t)FS_VPC_FILTER * FC_CELLS * sizeof(float) + (size_t)FV_G * FV_G * FV_G
+                                + (size_t)(FS_FILTER_THREADS / 32) * (FS_WQ * sizeof(unsigned) + FS_Q1 * sizeof(unsigned short) + 2 * 96 * sizeof(float));
+static_assert(FS_WQ >= 64 && FS_FILTER_CHUNK_MAX <= (1 << 20) && FS_VPC_FILTER <= 7 && 32 * FS_VPC_FILTER + 32 <= FS_Q1 &&
+              (FV_G * FV_G * FV_G) % 16 == 0 && FS_FILTER_SMEM <= 225 * 1024, "queue layout, one mask byte per view group, shared memory");
 
 struct StreamViewPacked { float4 rx, ry, rz; };          // (R0..2, zmin), (R3..5, rcp_range), (R6..8, -)
 
@@ -380,14 +510,21 @@ __device__ __forceinline__ bool point_may_win(const FilterPoint& f, const float4
 __global__ void __launch_bounds__(FS_FILTER_THREADS, 1)
 stream_filter_kernel(StreamParams P)
 {
-    extern __shared__ float s_L[];                       // [FS_VPC_FILTER][2][4096], then unsigned s_q[32 warps][FS_WQ]
-    unsigned* s_q = reinterpret_cast<unsigned*>(s_L + FS_VPC_FILTER * 2 * FC_CELLS);
+    extern __shared__ __align__(16) float s_L[];         // [FS_VPC_FILTER][4096] thresholds, voxel bytes, step-2 queues, pair queues
+    unsigned char* s_vox = reinterpret_cast<unsigned char*>(s_L + FS_VPC_FILTER * FC_CELLS);
+    unsigned* s_q = reinterpret_cast<unsigned*>(s_vox + FV_G * FV_G * FV_G);
+    unsigned short* s_q1 = reinterpret_cast<unsigned short*>(s_q + (FS_FILTER_THREADS / 32) * FS_WQ);
+    float* s_ring = reinterpret_cast<float*>(s_q1 + (FS_FILTER_THREADS / 32) * FS_Q1);
     __shared__ StreamViewPacked s_view[FS_VPC_FILTER];
     __shared__ float s_pose[12];
+    __shared__ float s_grid[6];                          // voxel grid of this cloud: lo x,y,z, voxels per unit length x,y,z (S2b)
+    __shared__ bool s_grid_ok;
     const int v0 = blockIdx.x * FS_VPC_FILTER, nv = min(FS_VPC_FILTER, P.V - v0), b = blockIdx.z;
+    const int nchunk = gridDim.y >> 1, c = (int)blockIdx.y >= nchunk;
     const ItemSpan sp = item_span(P.offs, b);
-    const int64_t base = sp.src0 + (int64_t)blockIdx.y * P.filter_chunk;
-    if (base >= sp.end) return;
+    const int64_t cloud0 = c ? sp.tgt0 : sp.src0, cloud1 = c ? sp.end : sp.tgt0;
+    const int64_t base = cloud0 + (int64_t)((int)blockIdx.y - c * nchunk) * P.filter_chunk;
+    if (base >= cloud1) return;
     const int tid = threadIdx.x, lane = tid & 31;
     if (tid < nv) {
         const int v = v0 + tid;
@@ -397,36 +534,50 @@ stream_filter_kernel(StreamParams P)
         s_view[tid].ry = make_float4(R[3], R[4], R[5], 1.0f / z_range(zmin, zmax));
         s_view[tid].rz = make_float4(R[6], R[7], R[8], 0.0f);
     }
-    const bool has_pose = P.pose != nullptr;
-    if (has_pose && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    const bool posed = P.pose != nullptr && c == 0;
+    if (posed && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    if (tid == 64) {
+        const VoxelGrid G = voxel_grid(P.bbox + ((size_t)b * 2 + c) * 6, FV_G, nullptr);
+        for (int a = 0; a < 3; ++a) { s_grid[a] = G.lo[a]; s_grid[3 + a] = G.inv[a]; }
+        s_grid_ok = G.ok;
+    }
     const size_t img0 = ((size_t)b * P.V + v0) * 2;
-    const float* lpv0 = P.lpv + img0 * FC_CELLS;
-    for (int t = tid; t < nv * 2 * FC_CELLS; t += FS_FILTER_THREADS) s_L[t] = __ldg(lpv0 + t);
+    for (int t = tid; t < nv * FC_CELLS; t += FS_FILTER_THREADS)
+        s_L[t] = __ldg(P.lpv + (img0 + (size_t)(t >> 12) * 2 + c) * FC_CELLS + (t & (FC_CELLS - 1)));
+    {
+        const int groups = (P.V + FS_VPC_FILTER - 1) / FS_VPC_FILTER;
+        const uint4* src = reinterpret_cast<const uint4*>(P.vox + (((size_t)b * groups + blockIdx.x) * 2 + c) * (size_t)(FV_G * FV_G * FV_G));
+        uint4* dst = reinterpret_cast<uint4*>(s_vox);
+        for (int t = tid; t < FV_G * FV_G * FV_G / 16; t += FS_FILTER_THREADS) dst[t] = __ldg(src + t);
+    }
     __syncthreads();
     const float inv_k = -1.0f / P.negk;
-    const int npts = (int)min((int64_t)P.filter_chunk, sp.end - base);
-    const int split = (int)min((int64_t)npts, max((int64_t)0, sp.tgt0 - base));     // points [0, split) are source points
+    const int npts = (int)min((int64_t)P.filter_chunk, cloud1 - base);
+    const bool grid_ok = s_grid_ok;
+    const unsigned vmask = (1u << nv) - 1u;              // views of this group
+    const float glx = s_grid[0], gly = s_grid[1], glz = s_grid[2], gix = s_grid[3], giy = s_grid[4], giz = s_grid[5];
 
-    // step 2 (per warp): the queued (image, point) pairs of this warp, all lanes busy
+    // step 2 (per warp): the queued (view, point) pairs of this warp, all lanes busy
     unsigned* wq = s_q + (tid >> 5) * FS_WQ;
     int wcount = 0;                                      // warp-uniform
-    auto drain = [&]() {
-        if (lane == 0 && wcount) atomicAdd(P.stats, (unsigned long long)wcount);
-        for (int t0 = 0; t0 < wcount; t0 += 32) {
-            const int t = t0 + lane;
+    unsigned long long n_cell = 0ull, n_vox = 0ull;      // diagnostics
+    auto drain = [&](bool flush) {                       // the newest 32 entries at a time; a partial batch only when flushing
+        while (wcount >= 32 || (flush && wcount > 0)) {
+            const int t0 = max(wcount - 32, 0), t = t0 + lane;
+            n_cell += (unsigned)(wcount - t0);
             bool keep = false; int l = 0, li = 0;
             if (t < wcount) {
                 const unsigned e = wq[t];
                 l = (int)(e >> 20);
                 const int pi = (int)(e & 0xFFFFFu);
-                const int c = l & 1;
                 const float* q = P.xyz + (size_t)(base + pi) * 3;
                 float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
-                if (has_pose && c == 0) apply_pose(s_pose, x, y, z);
+                if (posed) apply_pose(s_pose, x, y, z);
                 const FilterPoint f = filter_point(x, y, z, s_view[l >> 1]);
-                li = (int)(base + pi - (c ? sp.tgt0 : sp.src0));
+                li = (int)(base + pi - cloud0);
                 keep = !f.inside || point_may_win(f, P.win + (img0 + l) * (size_t)FC_CELLS * 8, inv_k);
             }
+            wcount = t0;
             const unsigned km = __ballot_sync(0xFFFFFFFFu, keep);
             if (keep) {                                  // one global atomic per warp and image
                 const unsigned peers = __match_any_sync(km, l);
@@ -438,56 +589,87 @@ stream_filter_kernel(StreamParams P)
             }
             __syncwarp();
         }
-        wcount = 0;
     };
 
-    // step 1: every point of the chunk against the pv thresholds of the CTA's views.  No block barrier in the loop: every
-    // warp owns a queue (its fill level lives in a register) and drains it on its own.
     const unsigned lt = (1u << lane) - 1u;
-    // two points per thread and round: the view constants are loaded once for both
-    for (int p0 = 0; p0 < npts; p0 += 2 * FS_FILTER_THREADS) {
-        float x[2], y[2], z[2], floor_pv[2]; unsigned ebase[2]; const float* Lc[2];
-#pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-            const int pi = p0 + hh * FS_FILTER_THREADS + tid;
-            const bool live = pi < npts;
-            const int c = pi >= split;
-            x[hh] = 0.f; y[hh] = 0.f; z[hh] = 0.f;
-            if (live) {
-                const float* q = P.xyz + (size_t)(base + pi) * 3;
-                x[hh] = __ldg(q); y[hh] = __ldg(q + 1); z[hh] = __ldg(q + 2);
-                if (has_pose && c == 0) apply_pose(s_pose, x[hh], y[hh], z[hh]);
-            }
-            floor_pv[hh] = live ? 0.0f : INFINITY;       // dead lanes never pass
-            Lc[hh] = s_L + c * FC_CELLS;
-            ebase[hh] = ((unsigned)c << 20) | (unsigned)pi;
+    unsigned short* q1 = s_q1 + (tid >> 5) * FS_Q1;      // ring of (slot << 8 | view << 5 | lane), FIFO
+    float* ring = s_ring + (tid >> 5) * (2 * 96);        // the posed points of this round and the one before: [slot][x,y,z][lane]
+    unsigned q1h = 0u, q1t = 0u;                         // warp-uniform head / tail (free running)
+    int cur_p0 = 0, cur_slot = 0;                        // the round being appended: chunk index of lane 0's point, ring slot
+    unsigned tail1 = 0u;                                 // queue tail when the last round started appending: older pairs live in the slot reused next
+    // step 1 on the oldest 32 pairs of the queue (count < 32 only when the chunk is finished)
+    auto cell_test = [&](int count) {
+        const bool live = lane < count;
+        const unsigned e = live ? (unsigned)q1[(q1h + lane) & (FS_Q1 - 1)] : 0u;
+        q1h += (unsigned)count;
+        const int slot = (int)(e >> 8), vv = (int)(e >> 5) & 7, sl = (int)(e & 31u);
+        const float* pt = ring + slot * 96 + sl;
+        const float px = pt[0], py = pt[32], pz = pt[64];
+        const float4 rx = s_view[vv].rx, ry = s_view[vv].ry, rz = s_view[vv].rz;
+        // the transform of filter_point() / stream_point(), cell by integer floor: inside <=> both in [0, 64)
+        const float ux = __fmaf_rn(__fmaf_rn(rx.z, pz, __fmaf_rn(rx.y, py, __fmul_rn(rx.x, px))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+        const float uy = __fmaf_rn(__fmaf_rn(ry.z, pz, __fmaf_rn(ry.y, py, __fmul_rn(ry.x, px))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+        const float zr = __fmaf_rn(rz.z, pz, __fmaf_rn(rz.y, py, __fmul_rn(rz.x, px)));
+        const float pv_hi = __fmaf_rn(-(zr - rx.w), ry.w, 1.0f) + FS_PV_ABS;
+        const int jj = __float2int_rd(ux), ii = __float2int_rd(uy);
+        const bool inside = (unsigned)(ii | jj) < (unsigned)FC_G;
+        const float lim = s_L[vv * FC_CELLS + (inside ? ii * FC_G + jj : 0)];
+        const bool pass = live && pv_hi > 0.0f && (pv_hi >= lim || !inside);         // clamped points are never dropped here
+        const unsigned pm = __ballot_sync(0xFFFFFFFFu, pass);
+        if (pm) {
+            // the pair's point: entries are at most one round old, the other slot holds the round before
+            if (pass) wq[wcount + __popc(pm & lt)] = ((unsigned)vv << 21) | ((unsigned)c << 20) | (unsigned)(cur_p0 - (slot != cur_slot ? FS_FILTER_THREADS : 0) + sl);
+            wcount += __popc(pm);
         }
-#pragma unroll
-        for (int vv = 0; vv < FS_VPC_FILTER; ++vv) {
-            if (vv >= nv) break;
-            const float4 rx = s_view[vv].rx, ry = s_view[vv].ry, rz = s_view[vv].rz;
-#pragma unroll
-            for (int hh = 0; hh < 2; ++hh) {
-                // the transform of filter_point() / stream_point(), cell by integer floor: inside <=> both in [0, 64)
-                const float ux = __fmaf_rn(__fmaf_rn(rx.z, z[hh], __fmaf_rn(rx.y, y[hh], __fmul_rn(rx.x, x[hh]))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
-                const float uy = __fmaf_rn(__fmaf_rn(ry.z, z[hh], __fmaf_rn(ry.y, y[hh], __fmul_rn(ry.x, x[hh]))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
-                const float zr = __fmaf_rn(rz.z, z[hh], __fmaf_rn(rz.y, y[hh], __fmul_rn(rz.x, x[hh])));
-                const float pv_hi = __fmaf_rn(-(zr - rx.w), ry.w, 1.0f) + FS_PV_ABS;
-                const int jj = __float2int_rd(ux), ii = __float2int_rd(uy);
-                const bool inside = (unsigned)(ii | jj) < (unsigned)FC_G;
-                const float lim = Lc[hh][vv * 2 * FC_CELLS + (inside ? ii * FC_G + jj : 0)];
-                const bool pass = pv_hi > floor_pv[hh] && (pv_hi >= lim || !inside);    // clamped points are never dropped here
-                const unsigned pm = __ballot_sync(0xFFFFFFFFu, pass);
-                if (pm) {
-                    if (pass) wq[wcount + __popc(pm & lt)] = ebase[hh] + ((unsigned)vv << 21);
-                    wcount += __popc(pm);
-                }
-            }
+        if (wcount >= FS_WQ - 32) { __syncwarp(); drain(false); }                   // one more batch always fits
+    };
+    float nx = 0.0f, ny = 0.0f, nz = 0.0f;               // the next round's point, loaded one round ahead
+    if (tid < npts) { const float* q = P.xyz + (size_t)(base + tid) * 3; nx = __ldg(q); ny = __ldg(q + 1); nz = __ldg(q + 2); }
+    for (int p0 = 0, slot = 0; p0 < npts; p0 += FS_FILTER_THREADS, slot ^= 1) {
+        // the slot written below still holds the round before last: pairs of that round must be gone first (rare)
+        if ((int)(tail1 - q1h) > 0) { cell_test((int)min(32u, q1t - q1h)); __syncwarp(); }
+        tail1 = q1t;
+        cur_p0 = p0 + (tid & ~31); cur_slot = slot;
+        // step 0: this lane's point, its voxel byte, the pairs whose bit is set
+        const int pi = p0 + tid;
+        float x = nx, y = ny, z = nz;
+        if (pi + FS_FILTER_THREADS < npts) {
+            const float* q = P.xyz + (size_t)(base + pi + FS_FILTER_THREADS) * 3;
+            nx = __ldg(q); ny = __ldg(q + 1); nz = __ldg(q + 2);
         }
-        if (wcount > FS_WQ - 64 * FS_VPC_FILTER) { __syncwarp(); drain(); }      // one more round always fits
+        unsigned m = 0u;
+        if (pi < npts) {
+            if (posed) apply_pose(s_pose, x, y, z);
+            const int i0 = min((int)((x - glx) * gix), FV_G - 1), i1 = min((int)((y - gly) * giy), FV_G - 1),
+                      i2 = min((int)((z - glz) * giz), FV_G - 1);
+            m = (grid_ok ? (unsigned)s_vox[(i2 * FV_G + i1) * FV_G + i0] : 0xFFu) & vmask;
+        }
+        ring[slot * 96 + lane] = x; ring[slot * 96 + 32 + lane] = y; ring[slot * 96 + 64 + lane] = z;
+        // every lane appends its own pairs: exclusive prefix of the bit counts, then one store per set bit
+        const int cnt = __popc(m);
+        int inc = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (lane >= d) inc += o; }
+        unsigned pos = q1t + (unsigned)(inc - cnt);
+        q1t += (unsigned)__shfl_sync(0xFFFFFFFFu, inc, 31);
+        const unsigned etag = ((unsigned)slot << 8) | (unsigned)lane;
+        while (m) {
+            const int vv = __ffs(m) - 1;
+            m &= m - 1u;
+            q1[pos++ & (FS_Q1 - 1)] = (unsigned short)(etag | ((unsigned)vv << 5));
+        }
+        __syncwarp();
+        while (q1t - q1h >= 32u) cell_test(32);
     }
+    n_vox = q1t;
     __syncwarp();
-    drain();
+    if (q1t != q1h) cell_test((int)(q1t - q1h));
+    __syncwarp();
+    drain(true);
+    if (lane == 0) {
+        if (n_cell) atomicAdd(P.stats, n_cell);
+        if (n_vox) atomicAdd(P.stats + 2, n_vox);
+    }
 }
 
 // ---- second round: re-seed from the survivors, filter the survivor lists again ------------------------------------

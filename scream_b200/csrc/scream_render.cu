@@ -33,7 +33,7 @@ int fail(int code, const char* fmt, ...) {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, surv2_off, total; bool stream; int surv_cap, surv2_cap; };
+struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, surv2_off, vox_off, total; bool stream; int surv_cap, surv2_cap, vox_g; };
 
 // The giant-cloud pre-filter (forward_stream.cuh) is used when the AVERAGE item reaches FS_MIN_AVG_PTS points
 // (decided from B and total_pts alone, so the workspace query and the forward call agree) and w == 64.
@@ -47,17 +47,19 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
     L.zenc_off = take((size_t)B * V * 2 * sizeof(unsigned));
     L.stream = stream_eligible(B, w, total_pts);
-    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = 0;
+    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = L.vox_off = 0;
+    L.vox_g = FV_G;
     L.surv2_cap = 1 << 18;
     // rim cells of a solid cloud pass the cell-level test wholesale (~2-3 % of the points): keep room for 1/16
     L.surv_cap = (int)std::min<int64_t>(std::max<int64_t>(FS_SURV_MIN, total_pts / 16), 1 << 26);
     if (L.stream) {
         const size_t imgs = (size_t)B * V * 2;
         L.seed_off = take(imgs * FC_CELLS * sizeof(unsigned long long));    // (value bits, point) seed keys
-        L.cnt_off = take(imgs * 2 * sizeof(unsigned) + 64); // round-1 and round-2 counters + 2 diagnostic u64, directly after seed: one memset clears all
+        L.cnt_off = take(imgs * 2 * sizeof(unsigned) + 64 + (size_t)B * 12 * sizeof(unsigned)); // round-1 and round-2 counters, 3 diagnostic u64, bounding-box keys; directly after seed: one memset clears all
         L.thr_off = take(imgs * (size_t)FC_CELLS * 33 * sizeof(float));     // per cell: one 128-byte line of the per-point test, then lpv
         L.surv_off = take(imgs * (size_t)L.surv_cap * sizeof(int));
         L.surv2_off = take(imgs * (size_t)L.surv2_cap * sizeof(int));
+        L.vox_off = take((size_t)B * ((V + FS_VPC_FILTER - 1) / FS_VPC_FILTER) * 2 * (size_t)L.vox_g * L.vox_g * L.vox_g);
     }
     L.total = off;
     return L;
@@ -82,9 +84,16 @@ int launch_zrange(const float* xyz, const int64_t* offs, int64_t total_pts, int6
     const int pairs = B * V;
     zrange_init_kernel<<<(pairs + 255) / 256, 256, 0, st>>>(zenc, pairs);
     if (max_item_pts <= 0 || max_item_pts > total_pts) max_item_pts = total_pts;
-    const int64_t chunks = (max_item_pts + ZR_PTS_PER_CTA - 1) / ZR_PTS_PER_CTA;
-    if (chunks > 2147483647LL || B > 65535) return fail(SCREAM_E_UNSUPPORTED, "batch too large for the z-range grid");
-    zrange_kernel<<<dim3((unsigned)chunks, (unsigned)B), ZR_THREADS, 0, st>>>(xyz, offs, pose, views, V, zenc);
+    if (B > 65535) return fail(SCREAM_E_UNSUPPORTED, "batch too large for the z-range grid");
+    if (max_item_pts >= ZW_MIN_PTS && (V + ZW_VPG - 1) / ZW_VPG <= 65535) {
+        const int64_t chunks = (max_item_pts + ZW_PTS_PER_CTA - 1) / ZW_PTS_PER_CTA;
+        zrange_wide_kernel<<<dim3((unsigned)chunks, (unsigned)((V + ZW_VPG - 1) / ZW_VPG), (unsigned)B), ZW_THREADS, 0, st>>>(
+            xyz, offs, pose, views, V, zenc);
+    } else {
+        const int64_t chunks = (max_item_pts + ZR_PTS_PER_CTA - 1) / ZR_PTS_PER_CTA;
+        if (chunks > 2147483647LL) return fail(SCREAM_E_UNSUPPORTED, "cloud too large for the z-range grid");
+        zrange_kernel<<<dim3((unsigned)chunks, (unsigned)B), ZR_THREADS, 0, st>>>(xyz, offs, pose, views, V, zenc);
+    }
     CUDA_TRY(cudaGetLastError());
     return 0;
 }
@@ -141,6 +150,8 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         S.surv2_cnt = S.surv_cnt + (size_t)B * V * 2;
         S.stats = reinterpret_cast<unsigned long long*>((char*)ws + L.cnt_off + align_up((size_t)B * V * 4 * sizeof(unsigned), 8));
         S.surv2 = reinterpret_cast<int*>((char*)ws + L.surv2_off); S.surv2_cap = L.surv2_cap;
+        S.bbox = reinterpret_cast<unsigned*>(S.stats + 8);
+        S.vox = reinterpret_cast<unsigned char*>((char*)ws + L.vox_off); S.vox_g = L.vox_g;
         CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
         const int64_t mi = (max_item_pts <= 0 || max_item_pts > total_pts) ? total_pts : max_item_pts;
         // S1 seeds from a subset of the cloud (about 4 M points per item: ~1000 per pixel): any subset gives valid bounds
@@ -153,7 +164,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         fchunk = std::min<int64_t>(std::max<int64_t>(fchunk / FS_FILTER_THREADS * FS_FILTER_THREADS, FS_FILTER_CHUNK_MIN), FS_FILTER_CHUNK_MAX);
         S.filter_chunk = (int)fchunk;
         const int64_t fchunks = (mi + fchunk - 1) / fchunk;
-        if (B > 65535 || fchunks > 65535) return fail(SCREAM_E_UNSUPPORTED, "batch or cloud too large for the stream grid");
+        if (B > 65535 || fchunks * 2 > 65535) return fail(SCREAM_E_UNSUPPORTED, "batch or cloud too large for the stream grid");
         {
             static thread_local int bound_attr_dev = -1;
             int dev = 0;
@@ -165,10 +176,12 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
                 bound_attr_dev = dev;
             }
         }
-        if (chunks > 2147483647LL || V > 65535 * 2) return fail(SCREAM_E_UNSUPPORTED, "cloud too large for the stream grid");
+        if (chunks > 2147483647LL || V * 2 > 65535 || (mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS > 2147483647LL) return fail(SCREAM_E_UNSUPPORTED, "cloud too large for the stream grid");
         stream_seed_kernel<<<dim3((unsigned)chunks, (unsigned)((V + FS_VPC - 1) / FS_VPC), (unsigned)B), FS_THREADS, FS_SEED_SMEM, st>>>(S);
         stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM, st>>>(S);
-        stream_filter_kernel<<<dim3((unsigned)vgroups, (unsigned)fchunks, (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
+        stream_bbox_kernel<<<dim3((unsigned)((mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS), (unsigned)B), FV_BBOX_THREADS, 0, st>>>(S);
+        stream_voxmask_kernel<<<dim3((unsigned)((L.vox_g * L.vox_g * L.vox_g + 255) / 256), (unsigned)(vgroups * 2), (unsigned)B), 256, 0, st>>>(S);
+        stream_filter_kernel<<<dim3((unsigned)vgroups, (unsigned)(fchunks * 2), (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
         // second round: seeds from the survivors (the true per-cell best), bounds again, survivor lists filtered again.
         // Pays once the first round's seeds are a thin sample of the cloud (its survivors grow with the stride).
         const bool round2 = S.seed_stride >= 4;

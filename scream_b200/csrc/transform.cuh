@@ -80,6 +80,91 @@ zrange_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ offs,
     }
 }
 
+// ---- large clouds (>= ZW_MIN_PTS points in an item): views in registers, points streamed ---------------------
+// grid (chunks, view groups, B).  A thread keeps the z rows and the running min / max of ZW_VPG views in
+// registers and walks ZW_PTS_PER_THREAD points two at a time: per (point, view) 3 FMA-pipe instructions and one
+// three-input FMNMX3 (sm_100), against ~10 in the kernel above.  The cloud is read V / ZW_VPG times (from L2
+// when it fits).  Float min / max order -0 < +0 like the integer keys do, so both kernels give the same bits.
+constexpr int ZW_THREADS = 256;
+constexpr int ZW_VPG = 16;
+constexpr int ZW_PTS_PER_THREAD = 64;
+constexpr int ZW_PTS_PER_CTA = ZW_THREADS * ZW_PTS_PER_THREAD;
+constexpr int64_t ZW_MIN_PTS = 1 << 18;
+
+__device__ __forceinline__ float fmin3(float a, float b, float c) {
+    float r; asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r;
+}
+
+__global__ void __launch_bounds__(ZW_THREADS)
+zrange_wide_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ offs,
+                   const float* __restrict__ pose, const float* __restrict__ views,
+                   int V, unsigned* __restrict__ zenc)
+{
+    const int b = blockIdx.z, v0 = blockIdx.y * ZW_VPG;
+    const ItemSpan sp = item_span(offs, b);
+    const int64_t npts = sp.end - sp.src0;
+    const int64_t base = (int64_t)blockIdx.x * ZW_PTS_PER_CTA;
+    if (base >= npts) return;
+
+    __shared__ unsigned s_min[ZW_VPG], s_max[ZW_VPG];
+    __shared__ float s_pose[12];
+    if (pose && threadIdx.x < 12) s_pose[threadIdx.x] = pose[(size_t)b * 12 + threadIdx.x];
+    if (threadIdx.x < ZW_VPG) { s_min[threadIdx.x] = 0xFFFFFFFFu; s_max[threadIdx.x] = 0u; }
+
+    float r[ZW_VPG][3], lo[ZW_VPG], hi[ZW_VPG];
+#pragma unroll
+    for (int v = 0; v < ZW_VPG; ++v) {
+        const float* R = views + (size_t)min(v0 + v, V - 1) * 9 + 6;     // past the end: the last view again
+        r[v][0] = __ldg(R); r[v][1] = __ldg(R + 1); r[v][2] = __ldg(R + 2);
+        lo[v] = INFINITY; hi[v] = -INFINITY;
+    }
+    __syncthreads();
+
+    const int64_t nsrc = sp.tgt0 - sp.src0;
+    const int64_t end = min(npts, base + ZW_PTS_PER_CTA);
+    // the next pair of points is loaded one iteration ahead (the loop is otherwise bound by the load latency)
+    auto load2 = [&](int64_t i0, float& ax, float& ay, float& az, float& bx, float& by, float& bz) {
+        const int64_t i1 = i0 + ZW_THREADS < end ? i0 + ZW_THREADS : i0;    // odd tail: the same point twice
+        const float* p = xyz + (size_t)(sp.src0 + i0) * 3;
+        const float* q = xyz + (size_t)(sp.src0 + i1) * 3;
+        ax = __ldg(p); ay = __ldg(p + 1); az = __ldg(p + 2);
+        bx = __ldg(q); by = __ldg(q + 1); bz = __ldg(q + 2);
+    };
+    float nax = 0.f, nay = 0.f, naz = 0.f, nbx = 0.f, nby = 0.f, nbz = 0.f;
+    if (base + threadIdx.x < end) load2(base + threadIdx.x, nax, nay, naz, nbx, nby, nbz);
+#pragma unroll 1
+    for (int64_t i0 = base + threadIdx.x; i0 < end; i0 += 2 * ZW_THREADS) {
+        float ax = nax, ay = nay, az = naz, bx = nbx, by = nby, bz = nbz;
+        if (i0 + 2 * ZW_THREADS < end) load2(i0 + 2 * ZW_THREADS, nax, nay, naz, nbx, nby, nbz);
+        if (pose) {
+            const int64_t i1 = i0 + ZW_THREADS < end ? i0 + ZW_THREADS : i0;
+            if (i0 < nsrc) apply_pose(s_pose, ax, ay, az);
+            if (i1 < nsrc) apply_pose(s_pose, bx, by, bz);
+        }
+#pragma unroll
+        for (int v = 0; v < ZW_VPG; ++v) {
+            const float za = rot_row(r[v], ax, ay, az), zb = rot_row(r[v], bx, by, bz);
+            lo[v] = fmin3(lo[v], za, zb);
+            hi[v] = fmax3(hi[v], za, zb);
+        }
+    }
+#pragma unroll
+    for (int v = 0; v < ZW_VPG; ++v) {
+        const unsigned l = __reduce_min_sync(0xFFFFFFFFu, enc_f32(lo[v]));
+        const unsigned h = __reduce_max_sync(0xFFFFFFFFu, enc_f32(hi[v]));
+        if ((threadIdx.x & 31) == 0) { atomicMin(&s_min[v], l); atomicMax(&s_max[v], h); }
+    }
+    __syncthreads();
+    if (threadIdx.x < ZW_VPG && v0 + threadIdx.x < V) {
+        unsigned* z = zenc + ((size_t)b * V + v0 + threadIdx.x) * 2;
+        atomicMin(z, s_min[threadIdx.x]);
+        atomicMax(z + 1, s_max[threadIdx.x]);
+    }
+}
+
 // caller-supplied zrange floats [B][V][2] -> zenc (SCREAM_F_ZRANGE_IN)
 __global__ void zrange_encode_kernel(const float* __restrict__ zrange, unsigned* __restrict__ zenc, int count) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -7,7 +7,7 @@ import torch
 from conftest import golden_names, load_golden
 from oracle_utils import c_backward, c_forward, c_transform, check_images
 from scream_b200 import _lib, synth
-from scream_b200.render import RegistrationRender, make_offsets, render_batch, view_matrices
+from scream_b200.render import RegistrationRender, depth_range, make_offsets, render_batch, view_matrices
 
 pytestmark = pytest.mark.gpu
 NAMES = golden_names()
@@ -317,3 +317,39 @@ def test_giant_cloud_stream_filter_is_exact(case):
     c = render_batch(xyz, offs, views, rho, 64, need_winner=False)
     d = render_batch(xyz, offs, views, rho, 64, need_winner=False, no_stream=True)
     assert torch.equal(c[0], d[0])
+
+
+@pytest.mark.parametrize("posed", [False, True])
+def test_depth_range_of_large_clouds_bit_exact(posed, c_oracle):
+    """Items of >= 2^18 points take the views-in-registers z-range kernel (transform.cuh, zrange_wide_kernel):
+    same bits as the oracle's render.py:30-31, odd point counts and a partial view group included."""
+    n, m, V = (1 << 17) + 12345, (1 << 17) + 40002, 18
+    src, tgt = synth.unit_ball(n, 71), synth.room_shell(m, 72)
+    views = np.concatenate([np.eye(3, dtype=np.float32)[None], synth.random_views(V - 1, 9)], 0)
+    pose = synth.random_pose(11) if posed else None
+    xyz = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV)
+    offs = make_offsets([(n, m)]).to(DEV)
+    zr = depth_range(xyz, offs, torch.from_numpy(views).to(DEV),
+                     None if pose is None else torch.from_numpy(pose)[None].contiguous().to(DEV))
+    _, _, want = c_transform(c_oracle, src, tgt, views, pose)
+    assert np.array_equal(zr[0].cpu().numpy().view(np.uint32), want.view(np.uint32))
+
+
+def test_depth_range_signed_zero_same_in_both_kernels():
+    """min / max over depths that include +0 and -0: the small-cloud kernel (integer keys) and the large-cloud
+    kernel (float FMNMX3) must agree on the sign of a zero extremum (-0 < +0 in both)."""
+    rng = np.random.default_rng(5)
+    views = torch.eye(3, dtype=torch.float32, device=DEV)[None]
+    for sign in (1.0, -1.0):                           # zero is the minimum / the maximum
+        out = []
+        for N in (4096, (1 << 18) + 4096):
+            pts = rng.random((N, 3), dtype=np.float32)
+            pts[:, 2] = sign * (pts[:, 2] + np.float32(0.01))
+            pts[100::977, 2] = np.float32(0.0)
+            pts[101::977, 2] = np.float32(-0.0)
+            pts[101::977, :2] *= np.float32(-1.0)      # fma(1, -0, fma(0, y, 0 * x)) stays -0 only if the inner terms are -0 too
+            xyz = torch.from_numpy(pts).to(DEV)
+            zr = depth_range(xyz, make_offsets([(N // 2, N - N // 2)]).to(DEV), views)
+            out.append(zr[0, 0].cpu().numpy().view(np.uint32).copy())
+        want = 0x80000000 if sign > 0 else 0x00000000
+        assert out[0][0 if sign > 0 else 1] == want and out[1][0 if sign > 0 else 1] == want, (sign, out)

@@ -18,8 +18,9 @@ cnt_off=al(V*2*4)+al(V*2*4096*8)
 cnt=ws[cnt_off:cnt_off+V*2*4].view(torch.int32).cpu().numpy()
 cnt2=ws[cnt_off+V*2*4:cnt_off+V*2*8].view(torch.int32).cpu().numpy()
 print("n",n,"round-1 survivors per image: mean",cnt.mean(),"max",cnt.max(),"frac of cloud",cnt.mean()/(n/2))
-st=ws[cnt_off+(V*2*8+7)//8*8:cnt_off+(V*2*8+7)//8*8+16].view(torch.int64).cpu().numpy()
-print("   step-1 passes (point,view pairs):",int(st[0]),"=",st[0]/(n*V),"of all pairs")
+st=ws[cnt_off+(V*2*8+7)//8*8:cnt_off+(V*2*8+7)//8*8+24].view(torch.int64).cpu().numpy()
+print("   voxel-mask passes (point,view pairs):",int(st[2]),"=",st[2]/(n*V),"of all pairs")
+print("   cell-test passes (point,view pairs):",int(st[0]),"=",st[0]/(n*V),"of all pairs")
 print("   round-2 survivors per image: mean",cnt2.mean(),"max",cnt2.max())
 # how many survivors actually win a pixel
 w=win[0].cpu().numpy(); print("distinct winners per image (mean)", np.mean([len(np.unique(w[v,c])) for v in range(V) for c in range(2)]))
