@@ -37,6 +37,7 @@ struct StreamParams {
     float negk;                                          // -rho^2/2
     unsigned long long* seed;                            // [B][V][2][4096]  (value bits << 32 | cloud-local index) of the cell's seed point (S1)
     float* lpv;                                          // [B][V][2][4096]  pv a point of the cell needs at least (S2 -> S3 step 1)
+    float* uimg;                                         // [B][V][2][4096]  U(q) (S2 -> the exact far test of the second round)
     float4* win;                                         // [B][V][2][4096][8] per cell, one 128-byte line: U of the 5 x 5 pixels around it (row-major,
                                                          //   -inf outside the image), then T_far at its 4 corners, 3 pads (S2 -> S3 step 2)
     int* surv; unsigned* surv_cnt; int surv_cap;         // [B][V][2][surv_cap], [B][V][2]   survivors of the first round
@@ -298,6 +299,7 @@ stream_bound_kernel(StreamParams P)
         // pv >= exp(-k cmax); cmax < 0: nothing can pass (pv <= 1)
         P.lpv[img * FC_CELLS + cell] = expf(fmaxf(P.negk * cmax, -120.0f)) * (1.0f - 1e-4f);
     }
+    for (int q = tid; q < FC_CELLS; q += 1024) P.uimg[img * FC_CELLS + q] = s_U[q];
     // the per-point test reads one 128-byte line per cell: 25 window values of U, 4 corner values of T_far
     float* win = reinterpret_cast<float*>(P.win + img * (size_t)FC_CELLS * 8);
     for (int t = tid; t < FC_CELLS * 32; t += 1024) {
@@ -479,11 +481,14 @@ __device__ __forceinline__ FilterPoint filter_point(float x, float y, float z, c
 
 // The per-point test of S3 (inside points only): may point f reach U at some pixel?  Pixels of the 5 x 5 neighbourhood of
 // its cell exactly, all others through the interpolated corner values of T_far (lower bound, see S2).  One 128-byte line.
-__device__ __forceinline__ bool point_may_win(const FilterPoint& f, const float4* __restrict__ win, float inv_k)
+// Returns 2: it does at a pixel of the window; 1: only the far bound lets it through; 0: it cannot.  thr = the largest
+// |x - q|^2 - U(q) that still passes.
+__device__ __forceinline__ int point_may_win(const FilterPoint& f, const float4* __restrict__ win, float inv_k, float* thr_out = nullptr)
 {
     const float h = 1.0f / FC_CELLS_PER_NDC;
     const float c_lo = -logf(f.pv_hi) * inv_k * (1.0f - 1e-5f);          // pv rounded up -> c rounded down
     const float thr = stream_slack(inv_k) - c_lo;
+    if (thr_out) *thr_out = thr;
     const float4* line = win + (size_t)f.cell * 8;
     float w[32];
 #pragma unroll
@@ -504,7 +509,7 @@ __device__ __forceinline__ bool point_may_win(const FilterPoint& f, const float4
     }
     const float top = __fmaf_rn(tx, w[26] - w[25], w[25]), bot = __fmaf_rn(tx, w[28] - w[27], w[27]);
     const float tlb = __fmaf_rn(ty, bot - top, top) - h * h * (tx * (1.0f - tx) + ty * (1.0f - ty));
-    return fminf(best, tlb) <= thr;
+    return best <= thr ? 2 : (tlb <= thr ? 1 : 0);
 }
 
 __global__ void __launch_bounds__(FS_FILTER_THREADS, 1)
@@ -575,7 +580,7 @@ stream_filter_kernel(StreamParams P)
                 if (posed) apply_pose(s_pose, x, y, z);
                 const FilterPoint f = filter_point(x, y, z, s_view[l >> 1]);
                 li = (int)(base + pi - cloud0);
-                keep = !f.inside || point_may_win(f, P.win + (img0 + l) * (size_t)FC_CELLS * 8, inv_k);
+                keep = !f.inside || point_may_win(f, P.win + (img0 + l) * (size_t)FC_CELLS * 8, inv_k) != 0;
             }
             wcount = t0;
             const unsigned km = __ballot_sync(0xFFFFFFFFu, keep);
@@ -653,10 +658,11 @@ stream_filter_kernel(StreamParams P)
         unsigned pos = q1t + (unsigned)(inc - cnt);
         q1t += (unsigned)__shfl_sync(0xFFFFFFFFu, inc, 31);
         const unsigned etag = ((unsigned)slot << 8) | (unsigned)lane;
-        while (m) {
-            const int vv = __ffs(m) - 1;
-            m &= m - 1u;
-            q1[pos++ & (FS_Q1 - 1)] = (unsigned short)(etag | ((unsigned)vv << 5));
+#pragma unroll
+        for (int vv = 0; vv < FS_VPC_FILTER; ++vv) {     // predicated stores: cheaper than a divergent loop over the set bits
+            const unsigned bit = (m >> vv) & 1u;
+            if (bit) q1[pos & (FS_Q1 - 1)] = (unsigned short)(etag | ((unsigned)vv << 5));
+            pos += bit;
         }
         __syncwarp();
         while (q1t - q1h >= 32u) cell_test(32);
@@ -730,11 +736,16 @@ stream_reseed_kernel(StreamParams P)
     }
 }
 
+// The second filter also settles the points that only the far bound let through (the rim of a solid cloud: the
+// interpolated bound is loose by up to ~h^2/2 there, and the cloud is dense): the whole warp tests one such point against
+// every pixel -- 8 x 8 pixel blocks first (distance to the block against the block's largest U), then the pixels of the
+// blocks that remain.  What is left is little more than the points that win a pixel.
 __global__ void __launch_bounds__(FS_THREADS)
 stream_refilter_kernel(StreamParams P)
 {
     __shared__ StreamViewPacked s_view;
     __shared__ float s_pose[12];
+    __shared__ float s_U[FC_CELLS], s_Ub[64];
     const Round2Ctx C = round2_ctx(P);
     if (C.n1 > (unsigned)P.surv_cap) {                    // first list incomplete: no second list either
         if (blockIdx.x == 0 && threadIdx.x == 0) P.surv2_cnt[C.img] = FS_R2_OVERFLOW;
@@ -750,21 +761,66 @@ stream_refilter_kernel(StreamParams P)
         s_view.rz = make_float4(R[6], R[7], R[8], 0.0f);
     }
     if (C.posed && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    for (int q = tid; q < FC_CELLS; q += FS_THREADS) s_U[q] = __ldg(P.uimg + C.img * FC_CELLS + q);
+    __syncthreads();
+    if (tid < 64) {
+        const int bi = tid >> 3, bj = tid & 7;
+        float m = -INFINITY;
+        for (int k = 0; k < 64; ++k) m = fmaxf(m, s_U[(bi * 8 + (k >> 3)) * FC_G + bj * 8 + (k & 7)]);
+        s_Ub[tid] = m;
+    }
     __syncthreads();
     const float inv_k = -1.0f / P.negk;
+    const float h = 1.0f / FC_CELLS_PER_NDC;
     const int* list = P.surv + C.img * (size_t)P.surv_cap;
     const unsigned first = blockIdx.x * FS_R2_CHUNK, stop = min(C.n1, first + FS_R2_CHUNK);
     for (unsigned t0 = first + (tid - lane); t0 < stop; t0 += FS_THREADS) {
         const unsigned t = t0 + lane;
-        bool keep = false; int li = 0;
+        int code = 0, li = 0; float ux = 0.0f, uy = 0.0f, thr = 0.0f;
         if (t < stop) {
             li = __ldg(list + t);
             const float* q = P.xyz + (size_t)(C.lo + li) * 3;
             float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
             if (C.posed) apply_pose(s_pose, x, y, z);
             const FilterPoint f = filter_point(x, y, z, s_view);
-            keep = f.pv_hi > 0.0f && (!f.inside || point_may_win(f, P.win + C.img * (size_t)FC_CELLS * 8, inv_k));
+            ux = f.ux; uy = f.uy;
+            if (f.pv_hi > 0.0f) code = f.inside ? point_may_win(f, P.win + C.img * (size_t)FC_CELLS * 8, inv_k, &thr) : 2;
         }
+        // the far candidates, one at a time, all lanes on it
+        unsigned todo = __ballot_sync(0xFFFFFFFFu, code == 1);
+        while (todo) {
+            const int sl = __ffs(todo) - 1;
+            todo &= todo - 1u;
+            const float px = __shfl_sync(0xFFFFFFFFu, ux, sl), py = __shfl_sync(0xFFFFFFFFu, uy, sl), pt = __shfl_sync(0xFFFFFFFFu, thr, sl);
+            unsigned blocks[2];
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {                // lane tests blocks lane and lane + 32: pixel centres [8 bj + 0.5, 8 bj + 7.5]
+                const int blk = lane + 32 * r, bi = blk >> 3, bj = blk & 7;
+                const float dx = fmaxf(fmaxf((float)(bj * 8) + 0.5f - px, px - ((float)(bj * 8) + 7.5f)), 0.0f) * h;
+                const float dy = fmaxf(fmaxf((float)(bi * 8) + 0.5f - py, py - ((float)(bi * 8) + 7.5f)), 0.0f) * h;
+                blocks[r] = __ballot_sync(0xFFFFFFFFu, __fmaf_rn(dx, dx, dy * dy) * (1.0f - 1e-5f) - s_Ub[blk] <= pt);
+            }
+            bool hit = false;
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                unsigned bm = blocks[r];
+                while (bm && !hit) {
+                    const int blk = __ffs(bm) - 1 + 32 * r, bi = blk >> 3, bj = blk & 7;
+                    bm &= bm - 1u;
+                    bool any = false;
+#pragma unroll
+                    for (int rr = 0; rr < 2; ++rr) {     // lane tests pixels lane and lane + 32 of the block
+                        const int k = lane + 32 * rr, i = bi * 8 + (k >> 3), j = bj * 8 + (k & 7);
+                        const float dx = (px - ((float)j + 0.5f)) * h, dy = (py - ((float)i + 0.5f)) * h;
+                        // the extra rounding of px - (j + 0.5) (<= 4e-6 cells on >= 2.5 cells) goes to the safe side
+                        any = any || (__fmaf_rn(dx, dx, dy * dy) * (1.0f - 8e-6f) - s_U[i * FC_G + j] <= pt);
+                    }
+                    hit = __any_sync(0xFFFFFFFFu, any);
+                }
+            }
+            if (hit && lane == sl) code = 2;
+        }
+        const bool keep = code == 2;
         const unsigned km = __ballot_sync(0xFFFFFFFFu, keep);
         if (km) {
             unsigned gp = 0;

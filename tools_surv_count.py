@@ -24,3 +24,15 @@ print("   cell-test passes (point,view pairs):",int(st[0]),"=",st[0]/(n*V),"of a
 print("   round-2 survivors per image: mean",cnt2.mean(),"max",cnt2.max())
 # how many survivors actually win a pixel
 w=win[0].cpu().numpy(); print("distinct winners per image (mean)", np.mean([len(np.unique(w[v,c])) for v in range(V) for c in range(2)]))
+# where (in the image plane) the round-2 survivors of image (view 0, source cloud) lie, against the winners
+S1=(n//16 if n//16>49152 else 49152); S1=min(S1,1<<26); S2=1<<18
+thr_off=cnt_off+al(V*2*8+64+48); surv_off=thr_off+al(V*2*4096*34*4); surv2_off=surv_off+al(V*2*S1*4)
+ids=ws[surv2_off:surv2_off+int(cnt2[0])*4].view(torch.int32).long()
+R=views[0]; src=xyz[:n//2]
+def radii(idx):
+    p=src[idx]@R.T; return (p[:,0]**2+p[:,1]**2).sqrt()*32
+edges=torch.tensor([0,24,28,30,31,31.5,31.8,32.5],device=dev)
+rs=radii(ids); rw=radii(torch.unique(win[0,0,0].long()))
+print("radius (pixels) histogram edges",edges.tolist())
+print("  survivors",torch.histc(rs,bins=1,min=0,max=40).item(),[int(((rs>=edges[i])&(rs<edges[i+1])).sum()) for i in range(len(edges)-1)])
+print("  winners  ",[int(((rw>=edges[i])&(rw<edges[i+1])).sum()) for i in range(len(edges)-1)])
