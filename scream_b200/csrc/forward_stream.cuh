@@ -24,7 +24,7 @@ namespace scream {
 constexpr int FS_THREADS = 1024;                        // S1: one CTA per SM (128 KB of tiles), 32 warps
 constexpr int FS_FILTER_THREADS = 1024;
 constexpr int FS_FILTER_CHUNK_MAX = 131072;              // points per CTA task of S3 (amortises staging the thresholds)
-constexpr int FS_FILTER_CHUNK_MIN = 8192;
+constexpr int FS_FILTER_CHUNK_MIN = 2048;
 constexpr int FS_CHUNK = 32768;                          // points per CTA task
 constexpr int FS_SURV_MIN = 4 * FC_CAP;                  // survivors kept per image: at least 49152, else total_pts / 16
 constexpr int64_t FS_MIN_AVG_PTS = 4 * FC_CAP;           // stream path when total_pts / B reaches this
@@ -46,13 +46,13 @@ struct StreamParams {
     int filter_chunk;                                    // points per CTA task of S3
     unsigned long long* stats;                           // [3] diagnostics: (point, view) pairs that passed the cell test / (unused) / the voxel mask of S3
     unsigned* bbox;                                      // [B][2][6] per cloud (source posed): max keys of ~enc(min x,y,z), enc(max x,y,z); zero-initialised
-    unsigned char* vox;                                  // [B][view groups][2][vox_g^3] bit vv: a point of the voxel may pass view v0 + vv's cell test
+    unsigned long long* vox;                             // [B][view groups][2][vox_g^3] bit vv: a point of the voxel may pass view v0 + vv's cell test
     int vox_g;                                           // voxels per axis of the cloud's bounding box
 };
 
 constexpr int FS_VPC = 2;                                // views per CTA task of S1 (2 views x 2 clouds x 32 KB of 64-bit tiles)
-constexpr int FS_VPC_FILTER = 7;                         // ... of S3: 7 views x 16 KB of one cloud's pv thresholds staged in shared memory
-constexpr int FV_G = 40;                                 // voxels per axis of a cloud's bounding box (S2b): g^3 mask bytes per view group, staged too
+constexpr int FS_VPC_FILTER = 64;                        // ... of S3: one 64-bit voxel mask word covers them
+constexpr int FV_G = 64;                                 // voxels per axis of a cloud's bounding box (S2b): g^3 mask words per group of 64 views
 constexpr int FS_TC = (FC_G + 1) * (FC_G + 1);           // cell corners per image
 constexpr float FS_PV_ABS = 4e-7f;                       // |1 - (z-zmin)*rcp(range) - pv_exact| (two roundings + rcp) stays below this
 
@@ -395,10 +395,10 @@ stream_voxmask_kernel(StreamParams P)
     const int vox = blockIdx.x * 256 + threadIdx.x;
     if (vox >= nvox) return;
     const int groups = (P.V + FS_VPC_FILTER - 1) / FS_VPC_FILTER;
-    unsigned char* out = P.vox + (((size_t)b * groups + grp) * 2 + c) * (size_t)nvox + vox;
+    unsigned long long* out = P.vox + (((size_t)b * groups + grp) * 2 + c) * (size_t)nvox + vox;
     float ext[3];
     const VoxelGrid G = voxel_grid(P.bbox + ((size_t)b * 2 + c) * 6, g, ext);
-    if (!G.ok) { *out = 0xFF; return; }
+    if (!G.ok) { *out = ~0ull; return; }
     const int iv[3] = { vox % g, (vox / g) % g, vox / (g * g) };
     float cp[3], hs[3], M = 0.0f;
 #pragma unroll
@@ -410,7 +410,7 @@ stream_voxmask_kernel(StreamParams P)
         cp[a] = G.lo[a] + ((float)iv[a] + 0.5f) * s;
         hs[a] = 0.5f * s * (1.0f + 1e-3f) + rnd;          // index rounding (<= 2e-5 voxels) and the centre's own rounding
     }
-    unsigned mask = 0u;
+    unsigned long long mask = 0ull;
     for (int vv = 0; vv < nv; ++vv) {
         const StreamView& W = s_view[vv];
         const float uxc = __fmaf_rn(rot_row(W.R, cp[0], cp[1], cp[2]), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
@@ -430,31 +430,28 @@ stream_voxmask_kernel(StreamParams P)
                 for (int j = (int)fj0; j <= (int)fj1; ++j) lim = fminf(lim, __ldg(L + i * FC_G + j));
             keep = pv_max >= lim;
         }
-        if (keep) mask |= 1u << vv;
+        if (keep) mask |= 1ull << vv;
     }
-    *out = (unsigned char)mask;
+    *out = mask;
 }
 
 // ---- S3: filter --------------------------------------------------------------------------------
-// grid (ceil(V / FS_VPC_FILTER), 2 clouds x chunks of P.filter_chunk points, B): the view groups of one chunk run back
-// to back, so the chunk is read from HBM once and from L2 afterwards.  A CTA works on ONE cloud's points, so it stages
-// that cloud's tables only: the voxel masks of its view group (S2b) and the pv thresholds lpv of its views (S2).
-// Per round a warp takes 32 points:
-//  (0) voxel byte of each point (one shared load) -> the (view, point) pairs whose bit is set go on the warp's pair
-//      queue (one ballot per view);
-//  (1) the queue is worked off 32 pairs at a time, all lanes busy: coordinates by shuffle from the lane that holds the
-//      point, transform, pv against the threshold of the point's cell (one random shared load); pairs that pass (the
-//      front layer and the rim of the cloud, a few per cent) go on the warp's step-2 queue;
-//  (2) whenever that queue fills, and at the end: the per-point test T_lowerbound(x_i) <= -c_i (S2) with the 128-byte
-//      line of the point's cell from global memory, then one global atomic per warp and image to reserve list space.
+// grid (ceil(V / 64), 2 clouds x chunks of P.filter_chunk points, B).  A CTA works on one cloud's points and (up to) 64
+// views; every point is read once.  Per round a warp takes 32 points:
+//  (0) the 64-bit voxel mask of each point (S2b; one 8-byte load, the tables live in L2) -> the (view, point) pairs whose
+//      bit is set are appended to the warp's pair queue, a ring in shared memory (prefix sum over the lanes' bit counts,
+//      32 views at a time);
+//  (1) the queue is worked off 32 pairs at a time, all lanes busy: coordinates from the warp's point ring, transform,
+//      pv against the threshold of the point's cell (S2; one 4-byte load from L2); pairs that pass (the front layer and
+//      the rim of the cloud, a few per cent) go on the warp's step-2 queue;
+//  (2) whenever that queue holds 32: the per-point test T_lowerbound(x_i) <= -c_i (S2) with the 128-byte line of the
+//      point's cell, then one global atomic per warp and image to reserve list space.
 // Every point that attains a pixel's maximum passes -- all points that tie included -- so rendering the survivors is
 // bit-identical to rendering the cloud.  No block barrier in the loop (queues are per warp, fill levels in registers).
 constexpr int FS_WQ = 64;                                // step-2 queue entries per warp: view << 21 | cloud << 20 | point of the chunk
-constexpr int FS_Q1 = 256;                               // pair queue per warp, a ring (u16: slot << 8 | view << 5 | lane): < 32 left over + 32 * views per round
-constexpr size_t FS_FILTER_SMEM = (size_t)FS_VPC_FILTER * FC_CELLS * sizeof(float) + (size_t)FV_G * FV_G * FV_G
-                                + (size_t)(FS_FILTER_THREADS / 32) * (FS_WQ * sizeof(unsigned) + FS_Q1 * sizeof(unsigned short) + 2 * 96 * sizeof(float));
-static_assert(FS_WQ >= 64 && FS_FILTER_CHUNK_MAX <= (1 << 20) && FS_VPC_FILTER <= 7 && 32 * FS_VPC_FILTER + 32 <= FS_Q1 &&
-              (FV_G * FV_G * FV_G) % 16 == 0 && FS_FILTER_SMEM <= 225 * 1024, "queue layout, one mask byte per view group, shared memory");
+constexpr int FS_Q1 = 2048;                              // pair queue per warp, a ring (u16: slot << 11 | view << 5 | lane): < 32 left over + 32 * 32 per half round
+constexpr size_t FS_FILTER_SMEM = (size_t)(FS_FILTER_THREADS / 32) * (FS_WQ * sizeof(unsigned) + FS_Q1 * sizeof(unsigned short) + 2 * 96 * sizeof(float));
+static_assert(FS_WQ >= 64 && FS_FILTER_CHUNK_MAX <= (1 << 20) && FS_VPC_FILTER == 64 && 32 * 32 + 32 <= FS_Q1, "queue layout, one mask word per view group");
 
 struct StreamViewPacked { float4 rx, ry, rz; };          // (R0..2, zmin), (R3..5, rcp_range), (R6..8, -)
 
@@ -515,9 +512,7 @@ __device__ __forceinline__ int point_may_win(const FilterPoint& f, const float4*
 __global__ void __launch_bounds__(FS_FILTER_THREADS, 1)
 stream_filter_kernel(StreamParams P)
 {
-    extern __shared__ __align__(16) float s_L[];         // [FS_VPC_FILTER][4096] thresholds, voxel bytes, step-2 queues, pair queues
-    unsigned char* s_vox = reinterpret_cast<unsigned char*>(s_L + FS_VPC_FILTER * FC_CELLS);
-    unsigned* s_q = reinterpret_cast<unsigned*>(s_vox + FV_G * FV_G * FV_G);
+    extern __shared__ __align__(16) unsigned s_q[];      // step-2 queues, pair queues, point rings
     unsigned short* s_q1 = reinterpret_cast<unsigned short*>(s_q + (FS_FILTER_THREADS / 32) * FS_WQ);
     float* s_ring = reinterpret_cast<float*>(s_q1 + (FS_FILTER_THREADS / 32) * FS_Q1);
     __shared__ StreamViewPacked s_view[FS_VPC_FILTER];
@@ -540,32 +535,27 @@ stream_filter_kernel(StreamParams P)
         s_view[tid].rz = make_float4(R[6], R[7], R[8], 0.0f);
     }
     const bool posed = P.pose != nullptr && c == 0;
-    if (posed && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
-    if (tid == 64) {
-        const VoxelGrid G = voxel_grid(P.bbox + ((size_t)b * 2 + c) * 6, FV_G, nullptr);
+    if (posed && tid >= 64 && tid < 76) s_pose[tid - 64] = P.pose[(size_t)b * 12 + tid - 64];
+    if (tid == 96) {
+        const VoxelGrid G = voxel_grid(P.bbox + ((size_t)b * 2 + c) * 6, P.vox_g, nullptr);
         for (int a = 0; a < 3; ++a) { s_grid[a] = G.lo[a]; s_grid[3 + a] = G.inv[a]; }
         s_grid_ok = G.ok;
     }
-    const size_t img0 = ((size_t)b * P.V + v0) * 2;
-    for (int t = tid; t < nv * FC_CELLS; t += FS_FILTER_THREADS)
-        s_L[t] = __ldg(P.lpv + (img0 + (size_t)(t >> 12) * 2 + c) * FC_CELLS + (t & (FC_CELLS - 1)));
-    {
-        const int groups = (P.V + FS_VPC_FILTER - 1) / FS_VPC_FILTER;
-        const uint4* src = reinterpret_cast<const uint4*>(P.vox + (((size_t)b * groups + blockIdx.x) * 2 + c) * (size_t)(FV_G * FV_G * FV_G));
-        uint4* dst = reinterpret_cast<uint4*>(s_vox);
-        for (int t = tid; t < FV_G * FV_G * FV_G / 16; t += FS_FILTER_THREADS) dst[t] = __ldg(src + t);
-    }
     __syncthreads();
+    const size_t img0 = ((size_t)b * P.V + v0) * 2;
+    const float* lpv0 = P.lpv + (img0 + c) * FC_CELLS;   // view vv of this cloud: + vv * 2 * FC_CELLS
+    const int vg = P.vox_g, groups = (P.V + FS_VPC_FILTER - 1) / FS_VPC_FILTER;
+    const unsigned long long* vox = P.vox + (((size_t)b * groups + blockIdx.x) * 2 + c) * (size_t)(vg * vg * vg);
     const float inv_k = -1.0f / P.negk;
     const int npts = (int)min((int64_t)P.filter_chunk, cloud1 - base);
     const bool grid_ok = s_grid_ok;
-    const unsigned vmask = (1u << nv) - 1u;              // views of this group
     const float glx = s_grid[0], gly = s_grid[1], glz = s_grid[2], gix = s_grid[3], giy = s_grid[4], giz = s_grid[5];
+    const unsigned long long vmask = nv == 64 ? ~0ull : (1ull << nv) - 1ull;       // views of this group
 
     // step 2 (per warp): the queued (view, point) pairs of this warp, all lanes busy
     unsigned* wq = s_q + (tid >> 5) * FS_WQ;
     int wcount = 0;                                      // warp-uniform
-    unsigned long long n_cell = 0ull, n_vox = 0ull;      // diagnostics
+    unsigned long long n_cell = 0ull;                    // diagnostics
     auto drain = [&](bool flush) {                       // the newest 32 entries at a time; a partial batch only when flushing
         while (wcount >= 32 || (flush && wcount > 0)) {
             const int t0 = max(wcount - 32, 0), t = t0 + lane;
@@ -597,17 +587,17 @@ stream_filter_kernel(StreamParams P)
     };
 
     const unsigned lt = (1u << lane) - 1u;
-    unsigned short* q1 = s_q1 + (tid >> 5) * FS_Q1;      // ring of (slot << 8 | view << 5 | lane), FIFO
+    unsigned short* q1 = s_q1 + (tid >> 5) * FS_Q1;      // ring of (slot << 11 | view << 5 | lane), FIFO
     float* ring = s_ring + (tid >> 5) * (2 * 96);        // the posed points of this round and the one before: [slot][x,y,z][lane]
     unsigned q1h = 0u, q1t = 0u;                         // warp-uniform head / tail (free running)
     int cur_p0 = 0, cur_slot = 0;                        // the round being appended: chunk index of lane 0's point, ring slot
     unsigned tail1 = 0u;                                 // queue tail when the last round started appending: older pairs live in the slot reused next
-    // step 1 on the oldest 32 pairs of the queue (count < 32 only when the chunk is finished)
+    // step 1 on the oldest 32 pairs of the queue (count < 32 only when flushing)
     auto cell_test = [&](int count) {
         const bool live = lane < count;
         const unsigned e = live ? (unsigned)q1[(q1h + lane) & (FS_Q1 - 1)] : 0u;
         q1h += (unsigned)count;
-        const int slot = (int)(e >> 8), vv = (int)(e >> 5) & 7, sl = (int)(e & 31u);
+        const int slot = (int)(e >> 11), vv = (int)(e >> 5) & 63, sl = (int)(e & 31u);
         const float* pt = ring + slot * 96 + sl;
         const float px = pt[0], py = pt[32], pz = pt[64];
         const float4 rx = s_view[vv].rx, ry = s_view[vv].ry, rz = s_view[vv].rz;
@@ -618,7 +608,7 @@ stream_filter_kernel(StreamParams P)
         const float pv_hi = __fmaf_rn(-(zr - rx.w), ry.w, 1.0f) + FS_PV_ABS;
         const int jj = __float2int_rd(ux), ii = __float2int_rd(uy);
         const bool inside = (unsigned)(ii | jj) < (unsigned)FC_G;
-        const float lim = s_L[vv * FC_CELLS + (inside ? ii * FC_G + jj : 0)];
+        const float lim = __ldg(lpv0 + (size_t)vv * (2 * FC_CELLS) + (inside ? ii * FC_G + jj : 0));
         const bool pass = live && pv_hi > 0.0f && (pv_hi >= lim || !inside);         // clamped points are never dropped here
         const unsigned pm = __ballot_sync(0xFFFFFFFFu, pass);
         if (pm) {
@@ -626,7 +616,7 @@ stream_filter_kernel(StreamParams P)
             if (pass) wq[wcount + __popc(pm & lt)] = ((unsigned)vv << 21) | ((unsigned)c << 20) | (unsigned)(cur_p0 - (slot != cur_slot ? FS_FILTER_THREADS : 0) + sl);
             wcount += __popc(pm);
         }
-        if (wcount >= FS_WQ - 32) { __syncwarp(); drain(false); }                   // one more batch always fits
+        if (wcount >= 32) { __syncwarp(); drain(false); }
     };
     float nx = 0.0f, ny = 0.0f, nz = 0.0f;               // the next round's point, loaded one round ahead
     if (tid < npts) { const float* q = P.xyz + (size_t)(base + tid) * 3; nx = __ldg(q); ny = __ldg(q + 1); nz = __ldg(q + 2); }
@@ -635,46 +625,50 @@ stream_filter_kernel(StreamParams P)
         if ((int)(tail1 - q1h) > 0) { cell_test((int)min(32u, q1t - q1h)); __syncwarp(); }
         tail1 = q1t;
         cur_p0 = p0 + (tid & ~31); cur_slot = slot;
-        // step 0: this lane's point, its voxel byte, the pairs whose bit is set
+        // step 0: this lane's point, its voxel mask, the pairs whose bit is set
         const int pi = p0 + tid;
         float x = nx, y = ny, z = nz;
         if (pi + FS_FILTER_THREADS < npts) {
             const float* q = P.xyz + (size_t)(base + pi + FS_FILTER_THREADS) * 3;
             nx = __ldg(q); ny = __ldg(q + 1); nz = __ldg(q + 2);
         }
-        unsigned m = 0u;
+        unsigned long long m = 0ull;
         if (pi < npts) {
             if (posed) apply_pose(s_pose, x, y, z);
-            const int i0 = min((int)((x - glx) * gix), FV_G - 1), i1 = min((int)((y - gly) * giy), FV_G - 1),
-                      i2 = min((int)((z - glz) * giz), FV_G - 1);
-            m = (grid_ok ? (unsigned)s_vox[(i2 * FV_G + i1) * FV_G + i0] : 0xFFu) & vmask;
+            const int i0 = min((int)((x - glx) * gix), vg - 1), i1 = min((int)((y - gly) * giy), vg - 1),
+                      i2 = min((int)((z - glz) * giz), vg - 1);
+            m = (grid_ok ? __ldg(vox + (size_t)((i2 * vg + i1) * vg + i0)) : ~0ull) & vmask;
         }
         ring[slot * 96 + lane] = x; ring[slot * 96 + 32 + lane] = y; ring[slot * 96 + 64 + lane] = z;
-        // every lane appends its own pairs: exclusive prefix of the bit counts, then one store per set bit
-        const int cnt = __popc(m);
-        int inc = cnt;
+        const unsigned etag = ((unsigned)slot << 11) | (unsigned)lane;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (lane >= d) inc += o; }
-        unsigned pos = q1t + (unsigned)(inc - cnt);
-        q1t += (unsigned)__shfl_sync(0xFFFFFFFFu, inc, 31);
-        const unsigned etag = ((unsigned)slot << 8) | (unsigned)lane;
+        for (int half = 0; half < 2; ++half) {           // 32 views at a time: at most 1024 new pairs, < 32 left from before
+            unsigned mh = half ? (unsigned)(m >> 32) : (unsigned)m;
+            if (__any_sync(0xFFFFFFFFu, mh != 0u)) {
+                // every lane appends its own pairs: exclusive prefix of the bit counts, then one store per set bit
+                const int cnt = __popc(mh);
+                int inc = cnt;
 #pragma unroll
-        for (int vv = 0; vv < FS_VPC_FILTER; ++vv) {     // predicated stores: cheaper than a divergent loop over the set bits
-            const unsigned bit = (m >> vv) & 1u;
-            if (bit) q1[pos & (FS_Q1 - 1)] = (unsigned short)(etag | ((unsigned)vv << 5));
-            pos += bit;
+                for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (lane >= d) inc += o; }
+                unsigned pos = q1t + (unsigned)(inc - cnt);
+                q1t += (unsigned)__shfl_sync(0xFFFFFFFFu, inc, 31);
+                while (mh) {
+                    const int vv = __ffs(mh) - 1 + 32 * half;
+                    mh &= mh - 1u;
+                    q1[pos++ & (FS_Q1 - 1)] = (unsigned short)(etag | ((unsigned)vv << 5));
+                }
+                __syncwarp();
+                while (q1t - q1h >= 32u) cell_test(32);
+            }
         }
-        __syncwarp();
-        while (q1t - q1h >= 32u) cell_test(32);
     }
-    n_vox = q1t;
     __syncwarp();
-    if (q1t != q1h) cell_test((int)(q1t - q1h));
+    while (q1t != q1h) cell_test((int)min(32u, q1t - q1h));
     __syncwarp();
     drain(true);
     if (lane == 0) {
         if (n_cell) atomicAdd(P.stats, n_cell);
-        if (n_vox) atomicAdd(P.stats + 2, n_vox);
+        if (q1t) atomicAdd(P.stats + 2, (unsigned long long)q1t);
     }
 }
 

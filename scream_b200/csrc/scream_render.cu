@@ -48,7 +48,7 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
     L.zenc_off = take((size_t)B * V * 2 * sizeof(unsigned));
     L.stream = stream_eligible(B, w, total_pts);
     L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = L.vox_off = 0;
-    L.vox_g = FV_G;
+    L.vox_g = total_pts / B >= (4 << 20) ? FV_G : FV_G / 2;   // ~100+ points per voxel; the mask kernel costs g^3 x V
     L.surv2_cap = 1 << 18;
     // rim cells of a solid cloud pass the cell-level test wholesale (~2-3 % of the points): keep room for 1/16
     L.surv_cap = (int)std::min<int64_t>(std::max<int64_t>(FS_SURV_MIN, total_pts / 16), 1 << 26);
@@ -59,7 +59,7 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
         L.thr_off = take(imgs * (size_t)FC_CELLS * 34 * sizeof(float));     // per cell: one 128-byte line of the per-point test, then lpv, then U
         L.surv_off = take(imgs * (size_t)L.surv_cap * sizeof(int));
         L.surv2_off = take(imgs * (size_t)L.surv2_cap * sizeof(int));
-        L.vox_off = take((size_t)B * ((V + FS_VPC_FILTER - 1) / FS_VPC_FILTER) * 2 * (size_t)L.vox_g * L.vox_g * L.vox_g);
+        L.vox_off = take((size_t)B * ((V + FS_VPC_FILTER - 1) / FS_VPC_FILTER) * 2 * (size_t)L.vox_g * L.vox_g * L.vox_g * sizeof(unsigned long long));
     }
     L.total = off;
     return L;
@@ -152,7 +152,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         S.stats = reinterpret_cast<unsigned long long*>((char*)ws + L.cnt_off + align_up((size_t)B * V * 4 * sizeof(unsigned), 8));
         S.surv2 = reinterpret_cast<int*>((char*)ws + L.surv2_off); S.surv2_cap = L.surv2_cap;
         S.bbox = reinterpret_cast<unsigned*>(S.stats + 8);
-        S.vox = reinterpret_cast<unsigned char*>((char*)ws + L.vox_off); S.vox_g = L.vox_g;
+        S.vox = reinterpret_cast<unsigned long long*>((char*)ws + L.vox_off); S.vox_g = L.vox_g;
         CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
         const int64_t mi = (max_item_pts <= 0 || max_item_pts > total_pts) ? total_pts : max_item_pts;
         // S1 seeds from a subset of the cloud (about 4 M points per item: ~1000 per pixel): any subset gives valid bounds
@@ -161,7 +161,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         const int64_t chunks = ((mi + FS_CHUNK - 1) / FS_CHUNK + S.seed_stride - 1) / S.seed_stride;
         // S3: chunks small enough to fill the GPU (>= ~4 CTAs per SM over all view groups), large enough to amortise staging
         const int vgroups = (V + FS_VPC_FILTER - 1) / FS_VPC_FILTER;
-        int64_t fchunk = mi * vgroups * B / (4 * 148);
+        int64_t fchunk = mi * vgroups * B / (16 * 148);
         fchunk = std::min<int64_t>(std::max<int64_t>(fchunk / FS_FILTER_THREADS * FS_FILTER_THREADS, FS_FILTER_CHUNK_MIN), FS_FILTER_CHUNK_MAX);
         S.filter_chunk = (int)fchunk;
         const int64_t fchunks = (mi + fchunk - 1) / fchunk;
