@@ -36,8 +36,9 @@ struct StreamParams {
     int B, V;
     float negk;                                          // -rho^2/2
     unsigned long long* seed;                            // [B][V][2][4096]  (value bits << 32 | cloud-local index) of the cell's seed point (S1)
-    float* lpv;                                          // [B][V][2][4096]  pv a point of the cell needs at least (S2 -> S3 step 1)
+    float* lpv;                                          // [B][V][2][4096]  pv a point of the cell needs at least (S2 -> S2b voxel masks)
     float* uimg;                                         // [B][V][2][4096]  U(q) (S2 -> the exact far test of the second round)
+    float* lpv9;                                         // [B][V][2][192][192]  the same threshold per third of a cell (S2 -> S3 step 1)
     float4* win;                                         // [B][V][2][4096][8] per cell, one 128-byte line: U of the 5 x 5 pixels around it (row-major,
                                                          //   -inf outside the image), then T_far at its 4 corners, 3 pads (S2 -> S3 step 2)
     int* surv; unsigned* surv_cnt; int surv_cap;         // [B][V][2][surv_cap], [B][V][2]   survivors of the first round
@@ -54,6 +55,7 @@ constexpr int FS_VPC = 2;                                // views per CTA task o
 constexpr int FS_VPC_FILTER = 64;                        // ... of S3: one 64-bit voxel mask word covers them
 constexpr int FV_G = 64;                                 // voxels per axis of a cloud's bounding box (S2b): g^3 mask words per group of 64 views
 constexpr int FS_TC = (FC_G + 1) * (FC_G + 1);           // cell corners per image
+constexpr int FS_SUB = 3;                                // S3 step 1 thresholds per cell and axis (odd: the pixel centre in the middle sub-cell)
 constexpr float FS_PV_ABS = 4e-7f;                       // |1 - (z-zmin)*rcp(range) - pv_exact| (two roundings + rcp) stays below this
 
 // fast exp for bounds only: ex2.approx(a * log2e), error <= 2 + 1.16|a| ulp (|a| <= 108: < 1.6e-5 relative)
@@ -299,6 +301,31 @@ stream_bound_kernel(StreamParams P)
         // pv >= exp(-k cmax); cmax < 0: nothing can pass (pv <= 1)
         P.lpv[img * FC_CELLS + cell] = expf(fmaxf(P.negk * cmax, -120.0f)) * (1.0f - 1e-4f);
     }
+    // the same threshold per THIRD of a cell (3 x 3 sub-cells; the pixel centre lies in the middle one): in a dense cloud
+    // the winner of a pixel sits within a fraction of a pixel of its centre, and the other eight sub-cells refuse outright
+    for (int t = tid; t < FS_SUB * FC_G * FS_SUB * FC_G; t += 1024) {
+        const int i3 = t / (FS_SUB * FC_G), j3 = t % (FS_SUB * FC_G), i = i3 / FS_SUB, j = j3 / FS_SUB;
+        const int sa = j3 - FS_SUB * j, sb = i3 - FS_SUB * i;
+        const float tmin = fminf(fminf(s_T[i * (FC_G + 1) + j], s_T[i * (FC_G + 1) + j + 1]),
+                                 fminf(s_T[(i + 1) * (FC_G + 1) + j], s_T[(i + 1) * (FC_G + 1) + j + 1]));
+        float cmax = 0.5f * h * h - tmin;
+        // the sub-cell's box relative to the cell's pixel centre, in cells, widened by the rounding of the classification
+        const float x0 = (float)sa / FS_SUB - 0.5f - 1e-4f, x1 = (float)(sa + 1) / FS_SUB - 0.5f + 1e-4f;
+        const float y0 = (float)sb / FS_SUB - 0.5f - 1e-4f, y1 = (float)(sb + 1) / FS_SUB - 0.5f + 1e-4f;
+        for (int di = -2; di <= 2; ++di) {
+            const int qi = i + di;
+            if (qi < 0 || qi >= FC_G) continue;
+            const float ay = fmaxf(fmaxf((float)di - y1, y0 - (float)di), 0.0f) * h;
+            for (int dj = -2; dj <= 2; ++dj) {
+                const int qj = j + dj;
+                if (qj < 0 || qj >= FC_G) continue;
+                const float ax = fmaxf(fmaxf((float)dj - x1, x0 - (float)dj), 0.0f) * h;
+                cmax = fmaxf(cmax, s_U[qi * FC_G + qj] - (ax * ax + ay * ay) * (1.0f - 1e-6f));
+            }
+        }
+        cmax += stream_slack(inv_k);
+        P.lpv9[img * (size_t)(FS_SUB * FC_G * FS_SUB * FC_G) + t] = expf(fmaxf(P.negk * cmax, -120.0f)) * (1.0f - 1e-4f);
+    }
     for (int q = tid; q < FC_CELLS; q += 1024) P.uimg[img * FC_CELLS + q] = s_U[q];
     // the per-point test reads one 128-byte line per cell: 25 window values of U, 4 corner values of T_far
     float* win = reinterpret_cast<float*>(P.win + img * (size_t)FC_CELLS * 8);
@@ -543,7 +570,7 @@ stream_filter_kernel(StreamParams P)
     }
     __syncthreads();
     const size_t img0 = ((size_t)b * P.V + v0) * 2;
-    const float* lpv0 = P.lpv + (img0 + c) * FC_CELLS;   // view vv of this cloud: + vv * 2 * FC_CELLS
+    const float* lpv0 = P.lpv9 + (img0 + c) * (size_t)(FS_SUB * FC_G * FS_SUB * FC_G);       // view vv of this cloud: + vv * 2 * that
     const int vg = P.vox_g, groups = (P.V + FS_VPC_FILTER - 1) / FS_VPC_FILTER;
     const unsigned long long* vox = P.vox + (((size_t)b * groups + blockIdx.x) * 2 + c) * (size_t)(vg * vg * vg);
     const float inv_k = -1.0f / P.negk;
@@ -601,14 +628,14 @@ stream_filter_kernel(StreamParams P)
         const float* pt = ring + slot * 96 + sl;
         const float px = pt[0], py = pt[32], pz = pt[64];
         const float4 rx = s_view[vv].rx, ry = s_view[vv].ry, rz = s_view[vv].rz;
-        // the transform of filter_point() / stream_point(), cell by integer floor: inside <=> both in [0, 64)
+        // the transform of filter_point() / stream_point(); sub-cell by integer floor of 3 x the cell coordinate
         const float ux = __fmaf_rn(__fmaf_rn(rx.z, pz, __fmaf_rn(rx.y, py, __fmul_rn(rx.x, px))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
         const float uy = __fmaf_rn(__fmaf_rn(ry.z, pz, __fmaf_rn(ry.y, py, __fmul_rn(ry.x, px))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
         const float zr = __fmaf_rn(rz.z, pz, __fmaf_rn(rz.y, py, __fmul_rn(rz.x, px)));
         const float pv_hi = __fmaf_rn(-(zr - rx.w), ry.w, 1.0f) + FS_PV_ABS;
-        const int jj = __float2int_rd(ux), ii = __float2int_rd(uy);
-        const bool inside = (unsigned)(ii | jj) < (unsigned)FC_G;
-        const float lim = __ldg(lpv0 + (size_t)vv * (2 * FC_CELLS) + (inside ? ii * FC_G + jj : 0));
+        const int j3 = __float2int_rd(ux * (float)FS_SUB), i3 = __float2int_rd(uy * (float)FS_SUB);
+        const bool inside = (unsigned)j3 < (unsigned)(FS_SUB * FC_G) && (unsigned)i3 < (unsigned)(FS_SUB * FC_G);
+        const float lim = __ldg(lpv0 + (size_t)vv * (2 * FS_SUB * FC_G * FS_SUB * FC_G) + (inside ? i3 * (FS_SUB * FC_G) + j3 : 0));
         const bool pass = live && pv_hi > 0.0f && (pv_hi >= lim || !inside);         // clamped points are never dropped here
         const unsigned pm = __ballot_sync(0xFFFFFFFFu, pass);
         if (pm) {

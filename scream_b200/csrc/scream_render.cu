@@ -56,7 +56,7 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
         const size_t imgs = (size_t)B * V * 2;
         L.seed_off = take(imgs * FC_CELLS * sizeof(unsigned long long));    // (value bits, point) seed keys
         L.cnt_off = take(imgs * 2 * sizeof(unsigned) + 64 + (size_t)B * 12 * sizeof(unsigned)); // round-1 and round-2 counters, 3 diagnostic u64, bounding-box keys; directly after seed: one memset clears all
-        L.thr_off = take(imgs * (size_t)FC_CELLS * 34 * sizeof(float));     // per cell: one 128-byte line of the per-point test, then lpv, then U
+        L.thr_off = take(imgs * (size_t)FC_CELLS * (34 + FS_SUB * FS_SUB) * sizeof(float));     // per cell: one 128-byte line of the per-point test, then lpv, U, sub-cell lpv
         L.surv_off = take(imgs * (size_t)L.surv_cap * sizeof(int));
         L.surv2_off = take(imgs * (size_t)L.surv2_cap * sizeof(int));
         L.vox_off = take((size_t)B * ((V + FS_VPC_FILTER - 1) / FS_VPC_FILTER) * 2 * (size_t)L.vox_g * L.vox_g * L.vox_g * sizeof(unsigned long long));
@@ -146,6 +146,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         S.win = reinterpret_cast<float4*>((char*)ws + L.thr_off);
         S.lpv = reinterpret_cast<float*>(S.win + (size_t)B * V * 2 * FC_CELLS * 8);
         S.uimg = S.lpv + (size_t)B * V * 2 * FC_CELLS;
+        S.lpv9 = S.uimg + (size_t)B * V * 2 * FC_CELLS;
         S.surv_cnt = reinterpret_cast<unsigned*>((char*)ws + L.cnt_off);
         S.surv = reinterpret_cast<int*>((char*)ws + L.surv_off); S.surv_cap = L.surv_cap;
         S.surv2_cnt = S.surv_cnt + (size_t)B * V * 2;

@@ -26,7 +26,7 @@ print("   round-2 survivors per image: mean",cnt2.mean(),"max",cnt2.max())
 w=win[0].cpu().numpy(); print("distinct winners per image (mean)", np.mean([len(np.unique(w[v,c])) for v in range(V) for c in range(2)]))
 # where (in the image plane) the round-2 survivors of image (view 0, source cloud) lie, against the winners
 S1=(n//16 if n//16>49152 else 49152); S1=min(S1,1<<26); S2=1<<18
-thr_off=cnt_off+al(V*2*8+64+48); surv_off=thr_off+al(V*2*4096*34*4); surv2_off=surv_off+al(V*2*S1*4)
+thr_off=cnt_off+al(V*2*8+64+48); surv_off=thr_off+al(V*2*4096*43*4); surv2_off=surv_off+al(V*2*S1*4)
 ids=ws[surv2_off:surv2_off+int(cnt2[0])*4].view(torch.int32).long()
 R=views[0]; src=xyz[:n//2]
 def radii(idx):
