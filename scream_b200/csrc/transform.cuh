@@ -6,6 +6,7 @@
 //                     -> device reduction (redux.sync on order-preserving uints + atomics), no host sync
 #pragma once
 #include "common.cuh"
+#include <cuda_pipeline.h>
 
 namespace scream {
 
@@ -88,6 +89,7 @@ zrange_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ offs,
 constexpr int ZW_THREADS = 256;
 constexpr int ZW_VPG = 16;
 constexpr int ZW_PTS_PER_THREAD = 64;
+constexpr int ZW_STAGES = 4;                // cp.async stages per thread (2 points each)
 constexpr int ZW_PTS_PER_CTA = ZW_THREADS * ZW_PTS_PER_THREAD;
 constexpr int64_t ZW_MIN_PTS = 1 << 18;
 
@@ -125,20 +127,33 @@ zrange_wide_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ of
 
     const int64_t nsrc = sp.tgt0 - sp.src0;
     const int64_t end = min(npts, base + ZW_PTS_PER_CTA);
-    // the next pair of points is loaded one iteration ahead (the loop is otherwise bound by the load latency)
-    auto load2 = [&](int64_t i0, float& ax, float& ay, float& az, float& bx, float& by, float& bz) {
-        const int64_t i1 = i0 + ZW_THREADS < end ? i0 + ZW_THREADS : i0;    // odd tail: the same point twice
-        const float* p = xyz + (size_t)(sp.src0 + i0) * 3;
-        const float* q = xyz + (size_t)(sp.src0 + i1) * 3;
-        ax = __ldg(p); ay = __ldg(p + 1); az = __ldg(p + 2);
-        bx = __ldg(q); by = __ldg(q + 1); bz = __ldg(q + 2);
+    // The points come through shared memory with cp.async, ZW_STAGES - 1 iterations ahead (the loop is otherwise bound
+    // by the load latency).  A thread only reads back what it copied itself: no block barrier, wait_prior is enough.
+    __shared__ float s_stage[ZW_STAGES][6][ZW_THREADS];
+    auto issue = [&](int64_t i0, int st) {
+        if (i0 < end) {
+            const int64_t i1 = i0 + ZW_THREADS < end ? i0 + ZW_THREADS : i0;    // odd tail: the same point twice
+            const float* p = xyz + (size_t)(sp.src0 + i0) * 3;
+            const float* q = xyz + (size_t)(sp.src0 + i1) * 3;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                __pipeline_memcpy_async(&s_stage[st][k][threadIdx.x], p + k, 4);
+                __pipeline_memcpy_async(&s_stage[st][3 + k][threadIdx.x], q + k, 4);
+            }
+        }
+        __pipeline_commit();
     };
-    float nax = 0.f, nay = 0.f, naz = 0.f, nbx = 0.f, nby = 0.f, nbz = 0.f;
-    if (base + threadIdx.x < end) load2(base + threadIdx.x, nax, nay, naz, nbx, nby, nbz);
+    const int64_t first = base + threadIdx.x;
+#pragma unroll
+    for (int st = 0; st < ZW_STAGES - 1; ++st) issue(first + (int64_t)st * 2 * ZW_THREADS, st);
+    int st = 0;
 #pragma unroll 1
-    for (int64_t i0 = base + threadIdx.x; i0 < end; i0 += 2 * ZW_THREADS) {
-        float ax = nax, ay = nay, az = naz, bx = nbx, by = nby, bz = nbz;
-        if (i0 + 2 * ZW_THREADS < end) load2(i0 + 2 * ZW_THREADS, nax, nay, naz, nbx, nby, nbz);
+    for (int64_t i0 = first; i0 < end; i0 += 2 * ZW_THREADS) {
+        issue(i0 + (int64_t)(ZW_STAGES - 1) * 2 * ZW_THREADS, st == 0 ? ZW_STAGES - 1 : st - 1);
+        __pipeline_wait_prior(ZW_STAGES - 1);
+        float ax = s_stage[st][0][threadIdx.x], ay = s_stage[st][1][threadIdx.x], az = s_stage[st][2][threadIdx.x];
+        float bx = s_stage[st][3][threadIdx.x], by = s_stage[st][4][threadIdx.x], bz = s_stage[st][5][threadIdx.x];
+        st = st == ZW_STAGES - 1 ? 0 : st + 1;
         if (pose) {
             const int64_t i1 = i0 + ZW_THREADS < end ? i0 + ZW_THREADS : i0;
             if (i0 < nsrc) apply_pose(s_pose, ax, ay, az);
