@@ -39,6 +39,8 @@ struct StreamParams {
     float* lpv;                                          // [B][V][2][4096]  pv a point of the cell needs at least (S2 -> S2b voxel masks)
     float* uimg;                                         // [B][V][2][4096]  U(q) (S2 -> the exact far test of the second round)
     float* lpv9;                                         // [B][V][2][192][192]  the same threshold per third of a cell (S2 -> S3 step 1)
+    unsigned long long* seed2;                           // [B][V][2][4096]  second round: per rim cell the survivor that does best at the cell's AIM (~score bits, index)
+    float2* aim;                                         // [B][V][2][4096]  a point FS_AIM cells outwards of a cell that borders empty space (NaN: none)
     float4* win;                                         // [B][V][2][4096][8] per cell, one 128-byte line: U of the 5 x 5 pixels around it (row-major,
                                                          //   -inf outside the image), then T_far at its 4 corners, 3 pads (S2 -> S3 step 2)
     int* surv; unsigned* surv_cnt; int surv_cap;         // [B][V][2][surv_cap], [B][V][2]   survivors of the first round
@@ -55,6 +57,7 @@ constexpr int FS_VPC = 2;                                // views per CTA task o
 constexpr int FS_VPC_FILTER = 64;                        // ... of S3: one 64-bit voxel mask word covers them
 constexpr int FV_G = 64;                                 // voxels per axis of a cloud's bounding box (S2b): g^3 mask words per group of 64 views
 constexpr int FS_TC = (FC_G + 1) * (FC_G + 1);           // cell corners per image
+constexpr float FS_AIM = 6.0f;                            // how far (cells) outside a rim cell its aim lies
 constexpr int FS_SUB = 3;                                // S3 step 1 thresholds per cell and axis (odd: the pixel centre in the middle sub-cell)
 constexpr float FS_PV_ABS = 4e-7f;                       // |1 - (z-zmin)*rcp(range) - pv_exact| (two roundings + rcp) stays below this
 
@@ -209,6 +212,48 @@ stream_bound_kernel(StreamParams P)
     }
     __syncthreads();
 
+    // Rim cells (occupied, empty cells within 3): their AIM, a point FS_AIM cells out into the empty side.  The second round
+    // keeps, per rim cell, the survivor that does best THERE as an extra seed: for the far pixels of the empty side the
+    // cell's own seed (best at the cell's pixel) is a poor bound -- the outermost point wins them, by ~D h in score.
+    for (int cell = tid; cell < FC_CELLS; cell += 1024) {
+        const int i = cell >> 6, j = cell & 63;
+        float2 a = make_float2(NAN, NAN);
+        if (s_seedpt[cell].z < INFINITY) {
+            int sx = 0, sy = 0;
+            for (int di = -3; di <= 3; ++di)
+                for (int dj = -3; dj <= 3; ++dj) {
+                    const int qi = i + di, qj = j + dj;
+                    if (qi >= 0 && qi < FC_G && qj >= 0 && qj < FC_G && !(s_seedpt[qi * FC_G + qj].z < INFINITY)) { sx += dj; sy += di; }
+                }
+            if (sx != 0 || sy != 0) {
+                const float n = FS_AIM * h * rsqrtf((float)(sx * sx + sy * sy));
+                a = make_float2(((float)j + 0.5f) * h - 1.0f + (float)sx * n, ((float)i + 0.5f) * h - 1.0f + (float)sy * n);
+            }
+        }
+        P.aim[img * FC_CELLS + cell] = a;
+    }
+    // extra seeds of the second round, exactly placed, as a compact list (in s_A, which is free until the row pass)
+    __shared__ int s_nextra;
+    float4* s_extra = reinterpret_cast<float4*>(s_A);
+    constexpr int FS_EXTRA_MAX = (FC_G + 1) * FC_G / 4;
+    if (tid == 0) s_nextra = 0;
+    __syncthreads();
+    for (int cell = tid; cell < FC_CELLS; cell += 1024) {
+        const unsigned long long key = P.seed2[img * FC_CELLS + cell];
+        if (key == 0ull) continue;
+        const float* q = P.xyz + (size_t)(lo + (int64_t)(unsigned)(key & 0xFFFFFFFFull)) * 3;
+        float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+        if (posed) apply_pose(s_pose, x, y, z);
+        const float pv_lo = __fmaf_rn(-(rot_row(s_R + 6, x, y, z) - zmin), rcp_range, 1.0f) - FS_PV_ABS;
+        if (!(pv_lo > 0.0f)) continue;
+        const int slot = atomicAdd(&s_nextra, 1);
+        if (slot < FS_EXTRA_MAX)
+            s_extra[slot] = make_float4(rot_row(s_R, x, y, z), rot_row(s_R + 3, x, y, z),
+                                        fmaxf(-logf(pv_lo) * inv_k, 0.0f) * (1.0f + 1e-5f) + 1e-12f, 0.f);
+    }
+    __syncthreads();
+    const int nextra = min(s_nextra, FS_EXTRA_MAX);
+
     // U(q): rings of cells around the pixel's own cell, until no farther seed can beat the best so far
     for (int q = tid; q < FC_CELLS; q += 1024) {
         const int i = q >> 6, j = q & 63;
@@ -240,6 +285,11 @@ stream_bound_kernel(StreamParams P)
                     best = fminf(best, __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, sd.z)));
                 }
             }
+        }
+        for (int e = 0; e < nextra; ++e) {                                   // any real point bounds the minimum
+            const float4 sd = s_extra[e];
+            const float dx = sd.x - qx, dy = sd.y - qy;
+            best = fminf(best, __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, sd.z)));
         }
         // Denormal range (k U > 80): values are multiples of 2^-149, so scores up to -ln(1 - u)/k <= 1.5 u/k apart
         // (u = 8 * 2^-149 * e^(k U)) may tie or swap; from u >= 1/2 on every non-zero value may.  Same rule as the
@@ -705,6 +755,7 @@ stream_filter_kernel(StreamParams P)
 // again from them gives the true per-cell best, and the same exact test then leaves little more than the winners.
 // Both kernels walk one image's list: grid (chunks of FS_R2_CHUNK list entries, V * 2, B).
 constexpr int FS_R2_CHUNK = 32768;
+constexpr size_t FS_RESEED_SMEM = (size_t)2 * FC_CELLS * sizeof(unsigned long long);
 constexpr unsigned FS_R2_OVERFLOW = 0xFFFFFFFFu;         // surv2_cnt of an image whose first list overflowed
 
 struct Round2Ctx { size_t img; int64_t lo; unsigned n1; bool posed; };
@@ -722,7 +773,8 @@ __device__ __forceinline__ Round2Ctx round2_ctx(const StreamParams& P) {
 __global__ void __launch_bounds__(FS_THREADS)
 stream_reseed_kernel(StreamParams P)
 {
-    __shared__ unsigned long long s_tile[FC_CELLS];
+    extern __shared__ unsigned long long s_tile[];       // [2][4096]: best at the cell's own pixel / best at the cell's aim
+    unsigned long long* s_tile2 = s_tile + FC_CELLS;
     __shared__ StreamView s_view;
     __shared__ float s_pose[12];
     const Round2Ctx C = round2_ctx(P);
@@ -730,8 +782,10 @@ stream_reseed_kernel(StreamParams P)
     const int tid = threadIdx.x, b = blockIdx.z, v = blockIdx.y >> 1;
     stream_load_views(P, b, v, 1, &s_view);
     if (C.posed && tid < 12) s_pose[tid] = P.pose[(size_t)b * 12 + tid];
-    for (int t = tid; t < FC_CELLS; t += FS_THREADS) s_tile[t] = 0ull;
+    for (int t = tid; t < 2 * FC_CELLS; t += FS_THREADS) s_tile[t] = 0ull;
     __syncthreads();
+    const float inv_k = -1.0f / P.negk;
+    const float2* aim = P.aim + C.img * FC_CELLS;
     const float negkc = P.negk / (FC_CELLS_PER_NDC * FC_CELLS_PER_NDC);
     const int* list = P.surv + C.img * (size_t)P.surv_cap;
     const unsigned stop = min(C.n1, (blockIdx.x + 1u) * FS_R2_CHUNK);
@@ -748,12 +802,24 @@ stream_reseed_kernel(StreamParams P)
         unsigned long long* slot = &s_tile[pt.cell];
         if (val > 0.0f && bits > (unsigned)(*reinterpret_cast<volatile unsigned long long*>(slot) >> 32))
             atomicMax(slot, ((unsigned long long)bits << 32) | li);
+        // rim cells: the smallest score at the cell's aim (scores are positive floats: their bits order like uints)
+        const float2 a = __ldg(aim + pt.cell);
+        if (a.x == a.x) {
+            const float dx = rot_row(s_view.R, x, y, z) - a.x, dy = rot_row(s_view.R + 3, x, y, z) - a.y;
+            const float sc = __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, -logf(pv_lo) * inv_k));
+            const unsigned nb = ~__float_as_uint(fmaxf(sc, 0.0f));
+            unsigned long long* slot2 = &s_tile2[pt.cell];
+            if (nb > (unsigned)(*reinterpret_cast<volatile unsigned long long*>(slot2) >> 32))
+                atomicMax(slot2, ((unsigned long long)nb << 32) | li);
+        }
     }
     __syncthreads();
     unsigned long long* out = P.seed + C.img * FC_CELLS;
+    unsigned long long* out2 = P.seed2 + C.img * FC_CELLS;
     for (int t = tid; t < FC_CELLS; t += FS_THREADS) {
-        const unsigned long long key = s_tile[t];
+        const unsigned long long key = s_tile[t], key2 = s_tile2[t];
         if (key != 0ull && key > out[t]) atomicMax(&out[t], key);
+        if (key2 != 0ull && key2 > out2[t]) atomicMax(&out2[t], key2);
     }
 }
 

@@ -54,9 +54,9 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
     L.surv_cap = (int)std::min<int64_t>(std::max<int64_t>(FS_SURV_MIN, total_pts / 16), 1 << 26);
     if (L.stream) {
         const size_t imgs = (size_t)B * V * 2;
-        L.seed_off = take(imgs * FC_CELLS * sizeof(unsigned long long));    // (value bits, point) seed keys
+        L.seed_off = take(imgs * FC_CELLS * 2 * sizeof(unsigned long long));    // (value bits, point) seed keys, then the second round's aim seeds
         L.cnt_off = take(imgs * 2 * sizeof(unsigned) + 64 + (size_t)B * 12 * sizeof(unsigned)); // round-1 and round-2 counters, 3 diagnostic u64, bounding-box keys; directly after seed: one memset clears all
-        L.thr_off = take(imgs * (size_t)FC_CELLS * (34 + FS_SUB * FS_SUB) * sizeof(float));     // per cell: one 128-byte line of the per-point test, then lpv, U, sub-cell lpv
+        L.thr_off = take(imgs * (size_t)FC_CELLS * (36 + FS_SUB * FS_SUB) * sizeof(float));     // per cell: one 128-byte line of the per-point test, then lpv, U, sub-cell lpv
         L.surv_off = take(imgs * (size_t)L.surv_cap * sizeof(int));
         L.surv2_off = take(imgs * (size_t)L.surv2_cap * sizeof(int));
         L.vox_off = take((size_t)B * ((V + FS_VPC_FILTER - 1) / FS_VPC_FILTER) * 2 * (size_t)L.vox_g * L.vox_g * L.vox_g * sizeof(unsigned long long));
@@ -147,6 +147,8 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         S.lpv = reinterpret_cast<float*>(S.win + (size_t)B * V * 2 * FC_CELLS * 8);
         S.uimg = S.lpv + (size_t)B * V * 2 * FC_CELLS;
         S.lpv9 = S.uimg + (size_t)B * V * 2 * FC_CELLS;
+        S.aim = reinterpret_cast<float2*>(S.lpv9 + (size_t)B * V * 2 * FC_CELLS * FS_SUB * FS_SUB);
+        S.seed2 = S.seed + (size_t)B * V * 2 * FC_CELLS;
         S.surv_cnt = reinterpret_cast<unsigned*>((char*)ws + L.cnt_off);
         S.surv = reinterpret_cast<int*>((char*)ws + L.surv_off); S.surv_cap = L.surv_cap;
         S.surv2_cnt = S.surv_cnt + (size_t)B * V * 2;
@@ -175,6 +177,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
                 CUDA_TRY(cudaFuncSetAttribute(stream_bound_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_BOUND_SMEM));
                 CUDA_TRY(cudaFuncSetAttribute(stream_seed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_SEED_SMEM));
                 CUDA_TRY(cudaFuncSetAttribute(stream_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_FILTER_SMEM));
+                CUDA_TRY(cudaFuncSetAttribute(stream_reseed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FS_RESEED_SMEM));
                 bound_attr_dev = dev;
             }
         }
@@ -191,7 +194,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
             const unsigned r2chunks = (unsigned)((std::min<int64_t>(mi, L.surv_cap) + FS_R2_CHUNK - 1) / FS_R2_CHUNK);
             CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.cnt_off - L.seed_off, st));
             const dim3 g2(r2chunks, (unsigned)(V * 2), (unsigned)B);
-            stream_reseed_kernel<<<g2, FS_THREADS, 0, st>>>(S);
+            stream_reseed_kernel<<<g2, FS_THREADS, FS_RESEED_SMEM, st>>>(S);
             stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM, st>>>(S);
             stream_refilter_kernel<<<g2, FS_THREADS, 0, st>>>(S);
         }

@@ -14,7 +14,7 @@ imgs=torch.empty((1,V,2,64,64),device=dev); win=torch.empty((1,V,2,64,64),dtype=
 rc=lib.scream_render_forward(xyz.data_ptr(),offs.data_ptr(),n,n,None,views.data_ptr(),1,V,64,24.0,1,imgs.data_ptr(),win.data_ptr(),zr.data_ptr(),ws.data_ptr(),nws,torch.cuda.current_stream().cuda_stream)
 torch.cuda.synchronize(); assert rc==0
 al=lambda x:(x+255)//256*256
-cnt_off=al(V*2*4)+al(V*2*4096*8)
+cnt_off=al(V*2*4)+al(V*2*4096*16)
 cnt=ws[cnt_off:cnt_off+V*2*4].view(torch.int32).cpu().numpy()
 cnt2=ws[cnt_off+V*2*4:cnt_off+V*2*8].view(torch.int32).cpu().numpy()
 print("n",n,"round-1 survivors per image: mean",cnt.mean(),"max",cnt.max(),"frac of cloud",cnt.mean()/(n/2))
@@ -26,7 +26,7 @@ print("   round-2 survivors per image: mean",cnt2.mean(),"max",cnt2.max())
 w=win[0].cpu().numpy(); print("distinct winners per image (mean)", np.mean([len(np.unique(w[v,c])) for v in range(V) for c in range(2)]))
 # where (in the image plane) the round-2 survivors of image (view 0, source cloud) lie, against the winners
 S1=(n//16 if n//16>49152 else 49152); S1=min(S1,1<<26); S2=1<<18
-thr_off=cnt_off+al(V*2*8+64+48); surv_off=thr_off+al(V*2*4096*43*4); surv2_off=surv_off+al(V*2*S1*4)
+thr_off=cnt_off+al(V*2*8+64+48); surv_off=thr_off+al(V*2*4096*45*4); surv2_off=surv_off+al(V*2*S1*4)
 ids=ws[surv2_off:surv2_off+int(cnt2[0])*4].view(torch.int32).long()
 R=views[0]; src=xyz[:n//2]
 def radii(idx):
