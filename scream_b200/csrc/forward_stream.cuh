@@ -527,7 +527,8 @@ stream_voxmask_kernel(StreamParams P)
 // bit-identical to rendering the cloud.  No block barrier in the loop (queues are per warp, fill levels in registers).
 constexpr int FS_WQ = 64;                                // step-2 queue entries per warp: view << 21 | cloud << 20 | point of the chunk
 constexpr int FS_Q1 = 2048;                              // pair queue per warp, a ring (u16: slot << 11 | view << 5 | lane): < 32 left over + 32 * 32 per half round
-constexpr size_t FS_FILTER_SMEM = (size_t)(FS_FILTER_THREADS / 32) * (FS_WQ * sizeof(unsigned) + FS_Q1 * sizeof(unsigned short) + 2 * 96 * sizeof(float));
+constexpr size_t FS_FILTER_SMEM = (size_t)(FS_FILTER_THREADS / 32) * (FS_WQ * sizeof(unsigned) + FS_Q1 * sizeof(unsigned short) + 2 * 96 * sizeof(float))
+                                + (size_t)3 * FS_VPC_FILTER * 8 * sizeof(float4);
 static_assert(FS_WQ >= 64 && FS_FILTER_CHUNK_MAX <= (1 << 20) && FS_VPC_FILTER == 64 && 32 * 32 + 32 <= FS_Q1, "queue layout, one mask word per view group");
 
 struct StreamViewPacked { float4 rx, ry, rz; };          // (R0..2, zmin), (R3..5, rcp_range), (R6..8, -)
@@ -592,6 +593,9 @@ stream_filter_kernel(StreamParams P)
     extern __shared__ __align__(16) unsigned s_q[];      // step-2 queues, pair queues, point rings
     unsigned short* s_q1 = reinterpret_cast<unsigned short*>(s_q + (FS_FILTER_THREADS / 32) * FS_WQ);
     float* s_ring = reinterpret_cast<float*>(s_q1 + (FS_FILTER_THREADS / 32) * FS_Q1);
+    // the cell test reads a random view per lane: 8 copies of the constants, copy (lane & 7) at 16-byte unit 8 * view + copy,
+    // so the 8 lanes of a quarter warp always hit 8 different bank groups
+    float4* s_vrep = reinterpret_cast<float4*>(s_ring + (FS_FILTER_THREADS / 32) * 2 * 96);       // [3][64][8]
     __shared__ StreamViewPacked s_view[FS_VPC_FILTER];
     __shared__ float s_pose[12];
     __shared__ float s_grid[6];                          // voxel grid of this cloud: lo x,y,z, voxels per unit length x,y,z (S2b)
@@ -617,6 +621,11 @@ stream_filter_kernel(StreamParams P)
         const VoxelGrid G = voxel_grid(P.bbox + ((size_t)b * 2 + c) * 6, P.vox_g, nullptr);
         for (int a = 0; a < 3; ++a) { s_grid[a] = G.lo[a]; s_grid[3 + a] = G.inv[a]; }
         s_grid_ok = G.ok;
+    }
+    __syncthreads();
+    for (int t = tid; t < 3 * FS_VPC_FILTER * 8; t += FS_FILTER_THREADS) {
+        const int k = t / (FS_VPC_FILTER * 8), vv = (t >> 3) % FS_VPC_FILTER;
+        s_vrep[t] = vv < nv ? (k == 0 ? s_view[vv].rx : k == 1 ? s_view[vv].ry : s_view[vv].rz) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     __syncthreads();
     const size_t img0 = ((size_t)b * P.V + v0) * 2;
@@ -677,7 +686,7 @@ stream_filter_kernel(StreamParams P)
         const int slot = (int)(e >> 11), vv = (int)(e >> 5) & 63, sl = (int)(e & 31u);
         const float* pt = ring + slot * 96 + sl;
         const float px = pt[0], py = pt[32], pz = pt[64];
-        const float4 rx = s_view[vv].rx, ry = s_view[vv].ry, rz = s_view[vv].rz;
+        const float4 rx = s_vrep[vv * 8 + (lane & 7)], ry = s_vrep[(FS_VPC_FILTER + vv) * 8 + (lane & 7)], rz = s_vrep[(2 * FS_VPC_FILTER + vv) * 8 + (lane & 7)];
         // the transform of filter_point() / stream_point(); sub-cell by integer floor of 3 x the cell coordinate
         const float ux = __fmaf_rn(__fmaf_rn(rx.z, pz, __fmaf_rn(rx.y, py, __fmul_rn(rx.x, px))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
         const float uy = __fmaf_rn(__fmaf_rn(ry.z, pz, __fmaf_rn(ry.y, py, __fmul_rn(ry.x, px))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
