@@ -25,7 +25,8 @@ constexpr int FS_THREADS = 1024;                        // S1: one CTA per SM (1
 constexpr int FS_FILTER_THREADS = 1024;
 constexpr int FS_FILTER_CHUNK_MAX = 131072;              // points per CTA task of S3 (amortises staging the thresholds)
 constexpr int FS_FILTER_CHUNK_MIN = 2048;
-constexpr int FS_CHUNK = 32768;                          // points per CTA task
+constexpr int FS_CHUNK = 32768;                          // points per sampled chunk of S1
+constexpr int FS_SEED_CPB = 4;                           // sampled chunks per CTA of S1
 constexpr int FS_SURV_MIN = 4 * FC_CAP;                  // survivors kept per image: at least 49152, else total_pts / 16
 constexpr int64_t FS_MIN_AVG_PTS = 4 * FC_CAP;           // stream path when total_pts / B reaches this
 constexpr float FS_DOWN = 1.0f - 1e-4f;                  // covers ex2.approx + argument rounding at |arg| <= 108
@@ -114,30 +115,44 @@ stream_seed_kernel(StreamParams P)
     __shared__ float s_pose[12];
     const int v0 = blockIdx.y * FS_VPC, nv = min(FS_VPC, P.V - v0), b = blockIdx.z;
     const ItemSpan sp = item_span(P.offs, b);
-    const int64_t base = sp.src0 + (int64_t)blockIdx.x * P.seed_stride * FS_CHUNK;
-    if (base >= sp.end) return;
+    // the CTA takes FS_SEED_CPB sampled chunks (one flush of its tiles for all of them)
+    if (sp.src0 + (int64_t)blockIdx.x * FS_SEED_CPB * P.seed_stride * FS_CHUNK >= sp.end) return;
     const int tid = threadIdx.x;
     stream_load_views(P, b, v0, nv, s_view);
     if (P.pose && tid < 12) s_pose[tid] = P.pose[(size_t)b * 12 + tid];
     for (int t = tid; t < nv * 2 * FC_CELLS; t += FS_THREADS) s_tile[t] = 0ull;
     __syncthreads();
     const float negkc = P.negk / (FC_CELLS_PER_NDC * FC_CELLS_PER_NDC);
-    const int64_t stop = min(sp.end, base + FS_CHUNK);
-    for (int64_t gi = base + tid; gi < stop; gi += FS_THREADS) {
-        const int c = gi >= sp.tgt0;
-        const unsigned li = (unsigned)(gi - (c ? sp.tgt0 : sp.src0));
-        const float* q = P.xyz + (size_t)gi * 3;
-        float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
-        if (P.pose != nullptr && c == 0) apply_pose(s_pose, x, y, z);
-        for (int vv = 0; vv < nv; ++vv) {
-            const StreamPoint pt = stream_point(x, y, z, s_view[vv]);
-            const float pv_lo = pt.pv - FS_PV_ABS;
-            if (!(pv_lo > 0.0f) || !pt.inside) continue;     // clamped points may be anywhere outside: they cannot seed
-            const float val = pv_lo * home_weight(pt, negkc);
-            const unsigned bits = __float_as_uint(val);
-            unsigned long long* slot = &s_tile[(vv * 2 + c) * FC_CELLS + pt.cell];
-            if (val > 0.0f && bits > (unsigned)(*reinterpret_cast<volatile unsigned long long*>(slot) >> 32))
-                atomicMax(slot, ((unsigned long long)bits << 32) | li);
+    for (int kk = 0; kk < FS_SEED_CPB; ++kk) {
+        const int64_t base = sp.src0 + ((int64_t)blockIdx.x * FS_SEED_CPB + kk) * P.seed_stride * FS_CHUNK;
+        if (base >= sp.end) break;
+        const int64_t stop = min(sp.end, base + FS_CHUNK);
+        for (int64_t g0 = base + tid; g0 < stop; g0 += 4 * FS_THREADS) {     // four points in flight per thread
+            float x[4], y[4], z[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t gi = g0 + (int64_t)u * FS_THREADS;
+                x[u] = y[u] = z[u] = 0.0f;
+                if (gi < stop) { const float* q = P.xyz + (size_t)gi * 3; x[u] = __ldg(q); y[u] = __ldg(q + 1); z[u] = __ldg(q + 2); }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t gi = g0 + (int64_t)u * FS_THREADS;
+                if (gi >= stop) break;
+                const int c = gi >= sp.tgt0;
+                const unsigned li = (unsigned)(gi - (c ? sp.tgt0 : sp.src0));
+                if (P.pose != nullptr && c == 0) apply_pose(s_pose, x[u], y[u], z[u]);
+                for (int vv = 0; vv < nv; ++vv) {
+                    const StreamPoint pt = stream_point(x[u], y[u], z[u], s_view[vv]);
+                    const float pv_lo = pt.pv - FS_PV_ABS;
+                    if (!(pv_lo > 0.0f) || !pt.inside) continue;     // clamped points may be anywhere outside: they cannot seed
+                    const float val = pv_lo * home_weight(pt, negkc);
+                    const unsigned bits = __float_as_uint(val);
+                    unsigned long long* slot = &s_tile[(vv * 2 + c) * FC_CELLS + pt.cell];
+                    if (val > 0.0f && bits > (unsigned)(*reinterpret_cast<volatile unsigned long long*>(slot) >> 32))
+                        atomicMax(slot, ((unsigned long long)bits << 32) | li);
+                }
+            }
         }
     }
     __syncthreads();
