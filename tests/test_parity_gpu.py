@@ -284,6 +284,8 @@ GIANT_CASES = [
     (150000, 150000, 24, "shell", 2),           # surfaces + large empty margins (far pixels, unknown-zone thresholds)
     (200000, 100000, 48, "slab", 2),            # KITTI-like
     (120000, 90000, 24, "ballx", 2),            # points outside [-1,1]^2 (clamped cells must not seed)
+    (150000, 110000, 24, "far", 3),             # depth offset of 40 units, in-plane rotations: voxel boxes at large coordinates
+    (130000, 130000, 24, "plane", 2),           # z constant: a voxel grid of zero extent along one axis
 ]
 
 
@@ -296,15 +298,25 @@ def test_giant_cloud_stream_filter_is_exact(case):
         src, tgt = synth.unit_ball(n, 21), synth.unit_ball(m, 22)
     elif kind == "ballx":
         src, tgt = synth.unit_ball(n, 23) * np.float32(1.4), synth.unit_ball(m, 24) * np.float32(1.2)
+    elif kind == "far":
+        src, tgt = synth.unit_ball(n, 31) * np.float32(0.8), synth.unit_ball(m, 32) * np.float32(0.7)
+        src[:, 2] += np.float32(40.0); tgt[:, 2] += np.float32(40.25)
+    elif kind == "plane":
+        src, tgt = synth.unit_ball(n, 33), synth.unit_ball(m, 34)
+        src[:, 2] = np.float32(0.125); tgt[:, 2] = np.float32(-0.25)
     elif kind == "shell":
         src, tgt = synth.room_shell(n, 25), synth.room_shell(m, 26)
     else:
         src, tgt = synth.kitti_slab(n, 27), synth.kitti_slab(m, 28)
     views = torch.from_numpy(np.concatenate([np.eye(3, dtype=np.float32)[None], synth.random_views(V - 1, 7)], 0)).to(DEV)
+    if kind == "far":                                  # rotations about the depth axis keep the cloud in the image
+        ang = np.array([0.0, 0.7, 2.1][:V])
+        rz = np.stack([np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]], np.float32) for a in ang])
+        views = torch.from_numpy(rz).to(DEV)
     xyz = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV)
     offs = make_offsets([(n, m)]).to(DEV)
     pose = torch.from_numpy(synth.random_pose(3))[None].contiguous().to(DEV)
-    for p in (None, pose):
+    for p in ((None,) if kind == "far" else (None, pose)):
         a = render_batch(xyz, offs, views, rho, 64, pose=p, raw=True, need_winner=True, no_stream=True)
         b = render_batch(xyz, offs, views, rho, 64, pose=p, raw=True, need_winner=True)
         assert torch.equal(a[2], b[2])
