@@ -9,9 +9,14 @@
 //              flushed to the global seed image: per cell, one real point that does well at the cell's own pixel.
 //   S2 bound   per image, in the score domain (s = d^2 + c, c = -ln(pv)/k): U(q) = best seed score at every pixel, its
 //              squared-distance transform T at the cell corners, and a per-cell pv threshold (details at the kernel).
-//   S3 filter  every point: it survives iff it may reach U at some pixel -- a per-cell pv threshold first, then the
-//              per-point test with the corner values of its cell.  Survivors (cloud-local indices) are appended to a
-//              per-image list.  Every point that attains a pixel's maximum survives, including all points that tie.
+//   S2b masks  a voxel grid over each cloud's bounding box; per voxel one bit per view: "a point in here could pass that
+//              view's cell test".  Conservative; lets S3 skip ~90 % of the (point, view) pairs on one 8-byte load.
+//   S3 filter  every point, read once for all views: it survives iff it may reach U at some pixel -- voxel bit, then a pv
+//              threshold per third of a cell, then the per-point test with the window line of its cell.  Survivors
+//              (cloud-local indices) are appended to a per-image list.  Every point that attains a pixel's maximum
+//              survives, including all points that tie.
+//   round 2    (large clouds) seeds again from the survivors, plus per rim cell the survivor that does best at a point
+//              out in the empty side; bounds again; the survivor lists filtered again, far candidates settled exactly.
 //   S4 render  forward_culled_kernel on the survivor lists (FwdParams::surv*); an image whose list
 //              overflowed is rendered from the full cloud in batches (correct, slow).
 #pragma once

@@ -286,6 +286,7 @@ GIANT_CASES = [
     (120000, 90000, 24, "ballx", 2),            # points outside [-1,1]^2 (clamped cells must not seed)
     (150000, 110000, 24, "far", 3),             # depth offset of 40 units, in-plane rotations: voxel boxes at large coordinates
     (130000, 130000, 24, "plane", 2),           # z constant: a voxel grid of zero extent along one axis
+    (60000, 50000, 24, "ball", 66),             # more than 64 views: two mask words per voxel, the second group partial
 ]
 
 
@@ -365,3 +366,23 @@ def test_depth_range_signed_zero_same_in_both_kernels():
             out.append(zr[0, 0].cpu().numpy().view(np.uint32).copy())
         want = 0x80000000 if sign > 0 else 0x00000000
         assert out[0][0 if sign > 0 else 1] == want and out[1][0 if sign > 0 else 1] == want, (sign, out)
+
+
+def test_giant_batch_of_unequal_items():
+    """Two giant items of different sizes in one call (per-item bounding boxes, chunk grids sized by the largest item),
+    one of them posed: same bits as rendering every batch of each cloud."""
+    sizes = [(90000, 70000), (150000, 30000)]
+    parts = []
+    for i, (n, m) in enumerate(sizes):
+        parts += [synth.unit_ball(n, 500 + i) * np.float32(0.9 + 0.3 * i), synth.room_shell(m, 600 + i)]
+    xyz = torch.from_numpy(np.concatenate(parts, 0)).to(DEV)
+    offs = make_offsets(sizes).to(DEV)
+    views = torch.from_numpy(synth.random_views(3, 12)).to(DEV)
+    pose = torch.from_numpy(np.stack([synth.random_pose(70 + i) for i in range(2)])).contiguous().to(DEV)
+    for p in (None, pose):
+        for thin in (False, True):
+            a = render_batch(xyz, offs, views, 24, 64, pose=p, raw=True, need_winner=True, no_stream=True)
+            b = render_batch(xyz, offs, views, 24, 64, pose=p, raw=True, need_winner=True, thin_seed=thin)
+            assert torch.equal(a[2], b[2])
+            assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
+            assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
