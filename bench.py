@@ -170,6 +170,49 @@ def run_reference(args, rank: int):
     print(json.dumps(line), flush=True)
 
 
+def streaming_leg_sharded(dev, peak_gbs: float, rank: int, world: int, n: int = 100_000_000, n_views: int = 64, steps: int = 5):
+    """The same cfg5 cloud with its POINTS sharded over the ranks: every rank holds n / world points, the
+    z ranges are combined with all_reduce(MIN/MAX), every rank renders its shard through the giant-cloud path and one
+    all_reduce(MAX) over packed (value, index) keys merges the images -- bit-identical to the single-GPU render
+    (tests/test_shard_cpu.py, test_point_sharded_merge_equals_unsharded).  Strong scaling: total work fixed."""
+    import torch.distributed as dist
+    from scream_b200 import synth
+    from scream_b200.render import render_cloud_point_sharded
+    from scream_b200.shard import balanced_slice
+    ns, nt = n // 2, n - n // 2
+    (s0, s1), (t0, t1) = balanced_slice(ns, rank, world), balanced_slice(nt, rank, world)
+
+    def ball(count, seed):
+        g = torch.Generator(device=dev).manual_seed(seed)
+        d = torch.randn((count, 3), generator=g, device=dev)
+        d /= d.norm(dim=1, keepdim=True)
+        return (d * torch.rand((count, 1), generator=g, device=dev) ** (1.0 / 3.0)).contiguous()
+    src, tgt = ball(s1 - s0, 9000 + rank), ball(t1 - t0, 9500 + rank)
+    views = torch.from_numpy(synth.random_views(n_views, 5)).to(dev)
+    run = lambda: render_cloud_point_sharded(src, tgt, s0, t0, views, RHO, W_IMG)
+    for _ in range(3):
+        run()
+    dist.barrier(); torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out = run()
+    e1.record()
+    dist.barrier(); torch.cuda.synchronize(dev)
+    t = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    alg = n_views * 12 * n + n_views * 2 * W_IMG * W_IMG * 8
+    return {"workload": f"cfg5: one pair, 100 M points x 64 views, fwd + winner maps, points sharded over {world} GPUs "
+                        "(all_reduce of the z ranges, all_reduce(MAX) of the packed key images)",
+            "n_points": n, "views": n_views, "ms_per_step": ms, "steps": steps, "scaling": "strong",
+            "gpoint_views_per_sec": n_views * n / ms / 1e6, "images_per_sec": 2 * n_views / ms * 1e3,
+            "roofline": {"bound": "hbm", "achieved": alg / ms / 1e6, "peak": peak_gbs * world, "unit": "GB/s",
+                         "frac": alg / ms / 1e6 / (peak_gbs * world), "algorithmic_bytes_per_step": alg,
+                         "note": "per-view accounting (SURVEY 8d), peak = measured single-GPU copy bandwidth x GPUs"},
+            "checksum": float(out[0].sum())}
+
+
 def streaming_leg(dev, peak_gbs: float, n: int = 100_000_000, n_views: int = 64, steps: int = 5):
     """BASELINE.json configs[4] on one GPU (the regime where HBM is the roofline the metric names): one pair of n/2 +
     n/2 unit-ball points, 64 random views, w = 64, rho = 24, forward with winner maps, inputs resident in HBM
@@ -311,6 +354,11 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         if t.get("pairs_per_gpu") == B and t.get("cloud") == CLOUD and not dense:
             traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     ach = (b_fake + b_real) / ((t_fake + t_real) / 1e3) / 1e9
+    streaming = None
+    if world > 1 and not args.no_stream_leg:           # every rank takes part in the collectives
+        del pipe
+        torch.cuda.empty_cache()
+        streaming = streaming_leg_sharded(dev, peak, rank, world)
     if rank != 0:
         return
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -332,6 +380,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             "clocks": clocks}
     if world == 1 and not args.no_stream_leg:
         line["streaming"] = streaming_leg(dev, peak)
+    elif streaming is not None:
+        line["streaming"] = streaming
     if world == 1 and not args.no_cpu:
         t0 = time.perf_counter()
         cpu_reference_step(0)                      # warm-up
@@ -356,7 +406,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dense", action="store_true", help="force the dense exact kernel")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-stream-leg", action="store_true", help="skip the cfg5 streaming-regime leg (N=1 only)")
+    ap.add_argument("--no-stream-leg", action="store_true", help="skip the cfg5 streaming-regime leg (one GPU: the whole cloud; N > 1: its points sharded over the ranks)")
     ap.add_argument("--chunk", type=int, default=37, help="pairs per chunk of the host-buffer pipeline (e2e leg)")
     ap.add_argument("--streams", type=int, default=6, help="CUDA streams of the host-buffer pipeline (e2e leg)")
     ap.add_argument("--cloud", default="ball", choices=["ball", "shell"], help="synthetic cloud family (cfg2 default: ball)")
