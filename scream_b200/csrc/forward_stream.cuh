@@ -197,8 +197,8 @@ stream_bound_kernel(StreamParams P)
 {
     extern __shared__ float4 s_seedpt[];                 // [4096] (x', y', c_up, -) of the cell's seed; c = +inf: none
     float* s_U = reinterpret_cast<float*>(s_seedpt + FC_CELLS);          // [4096]
-    float* s_A = s_U + FC_CELLS;                                         // [65][64] row pass
-    float* s_E = s_A + (FC_G + 1) * FC_G;                                // [65][64] row pass without the 4 columns around X
+    float* s_A = s_U + FC_CELLS;                                         // [64][65] row pass: [pixel row][corner column]
+    float* s_E = s_A + (FC_G + 1) * FC_G;                                // [64][65] row pass without the 4 columns around X
     float* s_T = s_E + (FC_G + 1) * FC_G;                                // [65][65]
     __shared__ float s_R[9], s_pose[12];
     const int vc = blockIdx.x, v = vc >> 1, c = vc & 1, b = blockIdx.y, tid = threadIdx.x;
@@ -327,7 +327,7 @@ stream_bound_kernel(StreamParams P)
     // T_far at the corners: pixels outside the 4 x 4 block around corner (Y, X) -- every pixel that is NOT in the 5 x 5
     // neighbourhood of a cell touching the corner.  Row pass over all / over the far columns, then the column pass.
     for (int t = tid; t < (FC_G + 1) * FC_G; t += 1024) {
-        const int X = t / FC_G, qy = t % FC_G;
+        const int qy = t / (FC_G + 1), X = t % (FC_G + 1);                   // lanes along X: U is read as a broadcast
         float a = INFINITY, e = INFINITY;
         for (int qx = 0; qx < FC_G; ++qx) {
             const float dx = ((float)(X - qx) - 0.5f) * h;
@@ -335,7 +335,7 @@ stream_bound_kernel(StreamParams P)
             a = fminf(a, val);
             if (qx < X - 2 || qx > X + 1) e = fminf(e, val);
         }
-        s_A[X * FC_G + qy] = a; s_E[X * FC_G + qy] = e;
+        s_A[qy * (FC_G + 1) + X] = a; s_E[qy * (FC_G + 1) + X] = e;      // [qy][X]: both passes free of bank conflicts
     }
     __syncthreads();
     for (int t = tid; t < FS_TC; t += 1024) {
@@ -344,7 +344,7 @@ stream_bound_kernel(StreamParams P)
         for (int qy = 0; qy < FC_G; ++qy) {
             const float dy = ((float)(Y - qy) - 0.5f) * h;
             const bool far_row = qy < Y - 2 || qy > Y + 1;
-            m = fminf(m, __fmaf_rn(dy, dy, far_row ? s_A[X * FC_G + qy] : s_E[X * FC_G + qy]));
+            m = fminf(m, __fmaf_rn(dy, dy, far_row ? s_A[qy * (FC_G + 1) + X] : s_E[qy * (FC_G + 1) + X]));
         }
         s_T[t] = m;
     }
@@ -371,6 +371,18 @@ stream_bound_kernel(StreamParams P)
         // pv >= exp(-k cmax); cmax < 0: nothing can pass (pv <= 1)
         P.lpv[img * FC_CELLS + cell] = expf(fmaxf(P.negk * cmax, -120.0f)) * (1.0f - 1e-4f);
     }
+    // largest U over the 5 x 5 window of every cell (in s_A, free again): where it is small, the outer rings of the window
+    // cannot carry the maximum below -- the own pixel's term is >= -(0.236 h)^2, a ring-1 term <= Umax - (0.5 h)^2, a ring-2
+    // term <= Umax - (1.5 h)^2 -- and are skipped
+    __syncthreads();
+    for (int cell = tid; cell < FC_CELLS; cell += 1024) {
+        const int i = cell >> 6, j = cell & 63;
+        float um = 0.0f;
+        for (int qi = max(i - 2, 0); qi <= min(i + 2, FC_G - 1); ++qi)
+            for (int qj = max(j - 2, 0); qj <= min(j + 2, FC_G - 1); ++qj) um = fmaxf(um, s_U[qi * FC_G + qj]);
+        s_A[cell] = um;
+    }
+    __syncthreads();
     // the same threshold per THIRD of a cell (3 x 3 sub-cells; the pixel centre lies in the middle one): in a dense cloud
     // the winner of a pixel sits within a fraction of a pixel of its centre, and the other eight sub-cells refuse outright
     for (int t = tid; t < FS_SUB * FC_G * FS_SUB * FC_G; t += 1024) {
@@ -382,11 +394,13 @@ stream_bound_kernel(StreamParams P)
         // the sub-cell's box relative to the cell's pixel centre, in cells, widened by the rounding of the classification
         const float x0 = (float)sa / FS_SUB - 0.5f - 1e-4f, x1 = (float)(sa + 1) / FS_SUB - 0.5f + 1e-4f;
         const float y0 = (float)sb / FS_SUB - 0.5f - 1e-4f, y1 = (float)(sb + 1) / FS_SUB - 0.5f + 1e-4f;
-        for (int di = -2; di <= 2; ++di) {
+        const float um = s_A[i * FC_G + j];
+        const int rad = um <= 0.18f * h * h ? 0 : (um <= 2.0f * h * h ? 1 : 2);
+        for (int di = -rad; di <= rad; ++di) {
             const int qi = i + di;
             if (qi < 0 || qi >= FC_G) continue;
             const float ay = fmaxf(fmaxf((float)di - y1, y0 - (float)di), 0.0f) * h;
-            for (int dj = -2; dj <= 2; ++dj) {
+            for (int dj = -rad; dj <= rad; ++dj) {
                 const int qj = j + dj;
                 if (qj < 0 || qj >= FC_G) continue;
                 const float ax = fmaxf(fmaxf((float)dj - x1, x0 - (float)dj), 0.0f) * h;
