@@ -493,23 +493,25 @@ __device__ __forceinline__ VoxelGrid voxel_grid(const unsigned* __restrict__ bb,
 
 // grid (ceil(g^3 / 256), view groups * 2 clouds, B): one thread per voxel, the FS_VPC_FILTER views of the group.
 constexpr int FV_FOOT_MAX = 8;                            // projections wider than this many cells: keep
+constexpr int FV_VIEWS_PER_THREAD = 16;                   // a quarter of a mask word per thread
 
 __global__ void __launch_bounds__(256)
 stream_voxmask_kernel(StreamParams P)
 {
-    __shared__ StreamView s_view[FS_VPC_FILTER];
+    __shared__ StreamView s_view[FV_VIEWS_PER_THREAD];
     const int g = P.vox_g, nvox = g * g * g;
-    const int grp = blockIdx.y >> 1, c = blockIdx.y & 1, b = blockIdx.z;
-    const int v0 = grp * FS_VPC_FILTER, nv = min(FS_VPC_FILTER, P.V - v0);
+    // blockIdx.y = ((view group * 2 + cloud) * 4 + quarter): a thread does 16 of the 64 views of its voxel's word
+    const int quarter = blockIdx.y & 3, c = (blockIdx.y >> 2) & 1, grp = blockIdx.y >> 3, b = blockIdx.z;
+    const int v0 = grp * FS_VPC_FILTER + quarter * FV_VIEWS_PER_THREAD, nv = max(0, min(FV_VIEWS_PER_THREAD, P.V - v0));
     stream_load_views(P, b, v0, nv, s_view);
     __syncthreads();
     const int vox = blockIdx.x * 256 + threadIdx.x;
     if (vox >= nvox) return;
     const int groups = (P.V + FS_VPC_FILTER - 1) / FS_VPC_FILTER;
-    unsigned long long* out = P.vox + (((size_t)b * groups + grp) * 2 + c) * (size_t)nvox + vox;
+    unsigned short* out = reinterpret_cast<unsigned short*>(P.vox + (((size_t)b * groups + grp) * 2 + c) * (size_t)nvox + vox) + quarter;
     float ext[3];
     const VoxelGrid G = voxel_grid(P.bbox + ((size_t)b * 2 + c) * 6, g, ext);
-    if (!G.ok) { *out = ~0ull; return; }
+    if (!G.ok) { *out = 0xFFFFu; return; }
     const int iv[3] = { vox % g, (vox / g) % g, vox / (g * g) };
     float cp[3], hs[3], M = 0.0f;
 #pragma unroll
@@ -521,7 +523,7 @@ stream_voxmask_kernel(StreamParams P)
         cp[a] = G.lo[a] + ((float)iv[a] + 0.5f) * s;
         hs[a] = 0.5f * s * (1.0f + 1e-3f) + rnd;          // index rounding (<= 2e-5 voxels) and the centre's own rounding
     }
-    unsigned long long mask = 0ull;
+    unsigned mask = 0u;
     for (int vv = 0; vv < nv; ++vv) {
         const StreamView& W = s_view[vv];
         const float uxc = __fmaf_rn(rot_row(W.R, cp[0], cp[1], cp[2]), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
@@ -541,9 +543,9 @@ stream_voxmask_kernel(StreamParams P)
                 for (int j = (int)fj0; j <= (int)fj1; ++j) lim = fminf(lim, __ldg(L + i * FC_G + j));
             keep = pv_max >= lim;
         }
-        if (keep) mask |= 1ull << vv;
+        if (keep) mask |= 1u << vv;
     }
-    *out = mask;
+    *out = (unsigned short)mask;
 }
 
 // ---- S3: filter --------------------------------------------------------------------------------

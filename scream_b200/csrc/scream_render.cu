@@ -185,7 +185,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         stream_seed_kernel<<<dim3((unsigned)((chunks + FS_SEED_CPB - 1) / FS_SEED_CPB), (unsigned)((V + FS_VPC - 1) / FS_VPC), (unsigned)B), FS_THREADS, FS_SEED_SMEM, st>>>(S);
         stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM, st>>>(S);
         stream_bbox_kernel<<<dim3((unsigned)((mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS), (unsigned)B), FV_BBOX_THREADS, 0, st>>>(S);
-        stream_voxmask_kernel<<<dim3((unsigned)((L.vox_g * L.vox_g * L.vox_g + 255) / 256), (unsigned)(vgroups * 2), (unsigned)B), 256, 0, st>>>(S);
+        stream_voxmask_kernel<<<dim3((unsigned)((L.vox_g * L.vox_g * L.vox_g + 255) / 256), (unsigned)(vgroups * 2 * 4), (unsigned)B), 256, 0, st>>>(S);
         stream_filter_kernel<<<dim3((unsigned)vgroups, (unsigned)(fchunks * 2), (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
         // second round: seeds from the survivors (the true per-cell best), bounds again, survivor lists filtered again.
         // Pays once the first round's seeds are a thin sample of the cloud (its survivors grow with the stride).
