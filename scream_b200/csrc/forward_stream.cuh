@@ -452,9 +452,19 @@ stream_bbox_kernel(StreamParams P)
 #pragma unroll
     for (int k = 0; k < 6; ++k) { lo[k / 3][k % 3] = INFINITY; hi[k / 3][k % 3] = -INFINITY; }
     const int64_t stop = min(sp.end, base + FV_BBOX_PTS);
-    for (int64_t gi = base + tid; gi < stop; gi += FV_BBOX_THREADS) {
-        const float* q = P.xyz + (size_t)gi * 3;
-        float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+    for (int64_t g0 = base + tid; g0 < stop; g0 += 4 * FV_BBOX_THREADS) {      // four points in flight per thread
+      float px[4], py[4], pz[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int64_t gi = g0 + (int64_t)u * FV_BBOX_THREADS;
+        px[u] = py[u] = pz[u] = 0.0f;
+        if (gi < stop) { const float* q = P.xyz + (size_t)gi * 3; px[u] = __ldg(q); py[u] = __ldg(q + 1); pz[u] = __ldg(q + 2); }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int64_t gi = g0 + (int64_t)u * FV_BBOX_THREADS;
+        if (gi >= stop) break;
+        float x = px[u], y = py[u], z = pz[u];
         if (gi < sp.tgt0) {
             if (P.pose) apply_pose(s_pose, x, y, z);
             lo[0][0] = fminf(lo[0][0], x); lo[0][1] = fminf(lo[0][1], y); lo[0][2] = fminf(lo[0][2], z);
@@ -463,6 +473,7 @@ stream_bbox_kernel(StreamParams P)
             lo[1][0] = fminf(lo[1][0], x); lo[1][1] = fminf(lo[1][1], y); lo[1][2] = fminf(lo[1][2], z);
             hi[1][0] = fmaxf(hi[1][0], x); hi[1][1] = fmaxf(hi[1][1], y); hi[1][2] = fmaxf(hi[1][2], z);
         }
+      }
     }
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
@@ -916,7 +927,16 @@ stream_refilter_kernel(StreamParams P)
             if (C.posed) apply_pose(s_pose, x, y, z);
             const FilterPoint f = filter_point(x, y, z, s_view);
             ux = f.ux; uy = f.uy;
-            if (f.pv_hi > 0.0f) code = f.inside ? point_may_win(f, P.win + C.img * (size_t)FC_CELLS * 8, inv_k, &thr) : 2;
+            if (f.pv_hi > 0.0f) {
+                if (!f.inside) code = 2;
+                else {
+                    // the sub-cell threshold of THIS round's bounds first (4 bytes): most of the list fails it
+                    const int j3 = __float2int_rd(f.ux * (float)FS_SUB), i3 = __float2int_rd(f.uy * (float)FS_SUB);
+                    const bool in3 = (unsigned)j3 < (unsigned)(FS_SUB * FC_G) && (unsigned)i3 < (unsigned)(FS_SUB * FC_G);
+                    const float lim = in3 ? __ldg(P.lpv9 + C.img * (size_t)(FS_SUB * FC_G * FS_SUB * FC_G) + i3 * (FS_SUB * FC_G) + j3) : 0.0f;
+                    if (f.pv_hi >= lim) code = point_may_win(f, P.win + C.img * (size_t)FC_CELLS * 8, inv_k, &thr);
+                }
+            }
         }
         // the far candidates, one at a time, all lanes on it
         unsigned todo = __ballot_sync(0xFFFFFFFFu, code == 1);
