@@ -158,8 +158,8 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         S.vox = reinterpret_cast<unsigned long long*>((char*)ws + L.vox_off); S.vox_g = L.vox_g;
         CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
         const int64_t mi = (max_item_pts <= 0 || max_item_pts > total_pts) ? total_pts : max_item_pts;
-        // S1 seeds from a subset of the cloud (about 4 M points per item: ~1000 per pixel): any subset gives valid bounds
-        S.seed_stride = (int)std::min<int64_t>(std::max<int64_t>(mi / (4 << 20), 1), 64);
+        // S1 seeds from a subset of the cloud (at most 4 M points per item: ~1000 per pixel): any subset gives valid bounds
+        S.seed_stride = (int)std::min<int64_t>(std::max<int64_t>((mi + (4 << 20) - 1) / (4 << 20), 1), 64);
         if (flags & SCREAM_F_THINSEED) S.seed_stride = std::max(S.seed_stride, 4);
         const int64_t chunks = ((mi + FS_CHUNK - 1) / FS_CHUNK + S.seed_stride - 1) / S.seed_stride;
         // S3: chunks small enough to fill the GPU (>= ~4 CTAs per SM over all view groups), large enough to amortise staging
