@@ -89,7 +89,7 @@ zrange_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ offs,
 constexpr int ZW_THREADS = 256;
 constexpr int ZW_VPG = 16;
 constexpr int ZW_PTS_PER_THREAD = 64;
-constexpr int ZW_STAGES = 4;                // cp.async stages per thread (2 points each)
+constexpr int ZW_STAGES = 3;                // cp.async stages per thread (4 points each)
 constexpr int ZW_PTS_PER_CTA = ZW_THREADS * ZW_PTS_PER_THREAD;
 constexpr int64_t ZW_MIN_PTS = 1 << 18;
 
@@ -125,45 +125,50 @@ zrange_wide_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ of
     }
     __syncthreads();
 
-    const int64_t nsrc = sp.tgt0 - sp.src0;
-    const int64_t end = min(npts, base + ZW_PTS_PER_CTA);
     // The points come through shared memory with cp.async, ZW_STAGES - 1 iterations ahead (the loop is otherwise bound
-    // by the load latency).  A thread only reads back what it copied itself: no block barrier, wait_prior is enough.
-    __shared__ float s_stage[ZW_STAGES][6][ZW_THREADS];
-    auto issue = [&](int64_t i0, int st) {
-        if (i0 < end) {
-            const int64_t i1 = i0 + ZW_THREADS < end ? i0 + ZW_THREADS : i0;    // odd tail: the same point twice
-            const float* p = xyz + (size_t)(sp.src0 + i0) * 3;
-            const float* q = xyz + (size_t)(sp.src0 + i1) * 3;
+    // by the load latency), four per thread and iteration.  A thread only reads back what it copied itself: no block
+    // barrier, wait_prior is enough.  Indices are local to the CTA's chunk (32-bit).
+    __shared__ float s_stage[ZW_STAGES][12][ZW_THREADS];
+    const float* pbase = xyz + (size_t)(sp.src0 + base) * 3;
+    const int nloc = (int)min((int64_t)ZW_PTS_PER_CTA, npts - base);                 // points of this chunk
+    const int nsrc = (int)max((int64_t)0, min((int64_t)nloc, sp.tgt0 - sp.src0 - base)); // ... of which source points (posed)
+    const int tid = threadIdx.x;
+    auto issue = [&](int i0, int st) {
+        if (i0 < nloc) {
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                __pipeline_memcpy_async(&s_stage[st][k][threadIdx.x], p + k, 4);
-                __pipeline_memcpy_async(&s_stage[st][3 + k][threadIdx.x], q + k, 4);
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * ZW_THREADS < nloc ? i0 + u * ZW_THREADS : i0;     // tail: the first point again
+                const float* p = pbase + i * 3;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) __pipeline_memcpy_async(&s_stage[st][3 * u + k][tid], p + k, 4);
             }
         }
         __pipeline_commit();
     };
-    const int64_t first = base + threadIdx.x;
 #pragma unroll
-    for (int st = 0; st < ZW_STAGES - 1; ++st) issue(first + (int64_t)st * 2 * ZW_THREADS, st);
+    for (int st = 0; st < ZW_STAGES - 1; ++st) issue(tid + st * 4 * ZW_THREADS, st);
     int st = 0;
 #pragma unroll 1
-    for (int64_t i0 = first; i0 < end; i0 += 2 * ZW_THREADS) {
-        issue(i0 + (int64_t)(ZW_STAGES - 1) * 2 * ZW_THREADS, st == 0 ? ZW_STAGES - 1 : st - 1);
+    for (int i0 = tid; i0 < nloc; i0 += 4 * ZW_THREADS) {
+        issue(i0 + (ZW_STAGES - 1) * 4 * ZW_THREADS, st == 0 ? ZW_STAGES - 1 : st - 1);
         __pipeline_wait_prior(ZW_STAGES - 1);
-        float ax = s_stage[st][0][threadIdx.x], ay = s_stage[st][1][threadIdx.x], az = s_stage[st][2][threadIdx.x];
-        float bx = s_stage[st][3][threadIdx.x], by = s_stage[st][4][threadIdx.x], bz = s_stage[st][5][threadIdx.x];
+        float px[4], py[4], pz[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { px[u] = s_stage[st][3 * u][tid]; py[u] = s_stage[st][3 * u + 1][tid]; pz[u] = s_stage[st][3 * u + 2][tid]; }
         st = st == ZW_STAGES - 1 ? 0 : st + 1;
-        if (pose) {
-            const int64_t i1 = i0 + ZW_THREADS < end ? i0 + ZW_THREADS : i0;
-            if (i0 < nsrc) apply_pose(s_pose, ax, ay, az);
-            if (i1 < nsrc) apply_pose(s_pose, bx, by, bz);
+        if (pose && i0 < nsrc) {                          // warp-uniform up to the one warp that straddles the clouds
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * ZW_THREADS < nloc ? i0 + u * ZW_THREADS : i0;
+                if (i < nsrc) apply_pose(s_pose, px[u], py[u], pz[u]);
+            }
         }
 #pragma unroll
         for (int v = 0; v < ZW_VPG; ++v) {
-            const float za = rot_row(r[v], ax, ay, az), zb = rot_row(r[v], bx, by, bz);
-            lo[v] = fmin3(lo[v], za, zb);
-            hi[v] = fmax3(hi[v], za, zb);
+            const float za = rot_row(r[v], px[0], py[0], pz[0]), zb = rot_row(r[v], px[1], py[1], pz[1]);
+            const float zc = rot_row(r[v], px[2], py[2], pz[2]), zd = rot_row(r[v], px[3], py[3], pz[3]);
+            lo[v] = fmin3(fmin3(lo[v], za, zb), zc, zd);
+            hi[v] = fmax3(fmax3(hi[v], za, zb), zc, zd);
         }
     }
 #pragma unroll
