@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define SCREAM_ABI_VERSION 4
+#define SCREAM_ABI_VERSION 5
 
 /* error codes */
 #define SCREAM_OK            0
@@ -66,6 +66,12 @@ extern "C" {
 
 #define SCREAM_F_THINSEED  16u   /* giant clouds: seed the pre-filter from every 4th chunk only and always run its second
                                     round, as clouds of >= 16 M points do by themselves (testing; same bits) */
+#define SCREAM_F_DUAL      32u   /* one launch renders every item twice (train_3d_match.py:186-201 renders the
+                                   "fake" pair and the "real" pair, which share the target cloud): once with the clouds as
+                                   given and once with the source posed.  pose must not be NULL; imgs / winner / zrange get
+                                   a leading dimension of 2 ([2][B][V]...: 0 = as given, 1 = posed); the workspace query
+                                   is unchanged.  The target cloud is sorted once and searched twice.  Not combined
+                                   with SCREAM_F_DENSE or SCREAM_F_ZRANGE_IN, nor with giant clouds (SCREAM_E_UNSUPPORTED). */
 
 /* opaque CUDA stream handle (cudaStream_t / CUstream) */
 typedef void *scream_stream_t;

@@ -11,13 +11,14 @@ import threading
 
 from .csrc import build as _build
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 F_RAW = 1
 F_DENSE = 2
 F_ZRANGE_IN = 4
 F_NOSTREAM = 8
 F_THINSEED = 16
+F_DUAL = 32
 
 _lock = threading.Lock()
 _lib = None

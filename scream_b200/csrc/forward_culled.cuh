@@ -207,6 +207,8 @@ __device__ __forceinline__ void disc_scan(const FcShared& S, const ExactCtx& E, 
     }
 }
 
+constexpr unsigned FC_FLAG_DUAL = 32u;                   // SCREAM_F_DUAL
+
 __global__ void __launch_bounds__(FC_THREADS, 1)
 forward_culled_kernel(FwdParams P)
 {
@@ -226,14 +228,24 @@ forward_culled_kernel(FwdParams P)
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int w = P.w, npix = w * w, half = w / 2;
-    int bid = blockIdx.x;
-    const int c = bid % 2; bid /= 2;
+    // Work of this CTA.  Plain call: image (b, v, c).  SCREAM_F_DUAL (the "fake" and the "real" render of a
+    // training step in one launch): outputs carry a leading pose dimension [2][B]... -- 0 = clouds as given, 1 = source
+    // posed -- and the CTAs of (b, v) are: source as given, source posed, and ONE for the target, which sorts the target
+    // once and searches it twice: its two images differ only through the depth range (render.py:30-31 takes it over
+    // source + target), i.e. through the score offsets c.
+    const bool dual = (P.flags & FC_FLAG_DUAL) != 0u;
+    int bid = blockIdx.x, c, pass0 = 0, pass1 = 1;
+    if (!dual) { c = bid % 2; bid /= 2; }
+    else {
+        const int job = bid % 3; bid /= 3;
+        c = job == 2;
+        pass0 = job == 1; pass1 = job == 0 ? 1 : 2;
+    }
     const int v = bid % P.V;
     const int b = bid / P.V;
 
     if (tid < 9) s_R[tid] = P.views[(size_t)v * 9 + tid];
-    const bool posed = P.pose != nullptr && c == 0;
-    if (posed && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    if (P.pose != nullptr && c == 0 && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
 
     const ItemSpan sp = item_span(P.offs, b);
     const int64_t lo = c ? sp.tgt0 : sp.src0, hi = c ? sp.end : sp.tgt0;
@@ -250,10 +262,6 @@ forward_culled_kernel(FwdParams P)
             if (n1 <= (unsigned)P.surv1_cap) { surv = P.surv1 + img * (size_t)P.surv1_cap; npts = (int64_t)n1; }
         }
     }
-    const float zmin = dec_f32(P.zenc[((size_t)b * P.V + v) * 2]);
-    const float zmax = dec_f32(P.zenc[((size_t)b * P.V + v) * 2 + 1]);
-    const float range = z_range(zmin, zmax);
-    const size_t img_off = (((size_t)b * P.V + v) * 2 + c) * npix;
     const bool raw = P.flags & 1u;
     const float inv_k = -P.inv_negk;                      // 1/k, k = rho^2/2
     const float s_zero = __fmul_rn(FC_EXP_ZERO, inv_k);   // scores beyond: value exactly 0
@@ -261,17 +269,27 @@ forward_culled_kernel(FwdParams P)
     // normalised output and no winner map, already when val <= 2^-26 ((val-0.5)/0.5 rounds to -1).
     const bool minus1_ok = !raw && P.winner == nullptr;
     const float r2cap_all = minus1_ok ? fminf(s_zero, __fmul_rn(FC_EXP_MINUS1, inv_k)) : s_zero;
-
-    if (P.zrange && c == 0 && tid == 0) {
-        P.zrange[((size_t)b * P.V + v) * 2] = zmin;
-        P.zrange[((size_t)b * P.V + v) * 2 + 1] = zmax;
-    }
     __syncthreads();
 
     FcShared S; S.xy = s_xy; S.c = s_c; S.idx = s_idx; S.start = s_start;
     S.rowmask = s_rowmask; S.blockmask = s_blockmask;
+
+  for (int pass = pass0; pass < pass1; ++pass) {
+    // outputs and depth range of this pass (dual: item pass * B + b of the pose-major outputs)
+    const size_t ob = dual ? (size_t)pass * P.B + b : (size_t)b;
+    const bool posed = (dual ? pass == 1 : P.pose != nullptr) && c == 0;
+    const float zmin = dec_f32(P.zenc[(ob * P.V + v) * 2]);
+    const float zmax = dec_f32(P.zenc[(ob * P.V + v) * 2 + 1]);
+    const float range = z_range(zmin, zmax);
+    const size_t img_off = ((ob * P.V + v) * 2 + c) * npix;
+    if (P.zrange && c == 0 && tid == 0) {
+        P.zrange[(ob * P.V + v) * 2] = zmin;
+        P.zrange[(ob * P.V + v) * 2 + 1] = zmax;
+    }
     ExactCtx E; E.xyz = P.xyz; E.lo = lo; E.R = s_R; E.pose = s_pose; E.posed = posed;
     E.zmin = zmin; E.range = range; E.negk = P.negk;
+    // the target's second pass keeps the sorted records of the first (one batch only) and renews the score offsets
+    const bool resort = !(pass > pass0 && npts <= (int64_t)FC_CAP);
 
     int batch = 0;
     int64_t c0 = 0;                                      // position in the point list of this image
@@ -280,6 +298,7 @@ forward_culled_kernel(FwdParams P)
         const bool last = c0 + cnt >= npts;
         E.lo = lo;                                        // record indices are cloud-local
 
+        if (resort) {
         // ---------------- P1: transform + histogram -------------------------------------------
         for (int t = tid; t < FC_CELLS + 4; t += FC_THREADS) s_hist[t] = 0u;
         __syncthreads();
@@ -391,6 +410,16 @@ forward_culled_kernel(FwdParams P)
                     if (i + d < FC_G) best = min(best, max(d, (int)s_h[cell + d * FC_G]));
                 }
                 s_ring[cell] = (unsigned char)best;
+            }
+            __syncthreads();
+        }
+
+        } else {
+            // same positions, same cell order, same occupancy: only c = -ln(pv)/k follows the new depth range
+            for (int pos = tid; pos < cnt; pos += FC_THREADS) {
+                const float* q = P.xyz + (size_t)(lo + s_idx[pos]) * 3;
+                const float zr = rot_row(s_R + 6, __ldg(q), __ldg(q + 1), __ldg(q + 2));
+                s_c[pos] = __fmul_rn(logf(depth_weight(zr, zmin, range)), P.inv_negk);
             }
             __syncthreads();
         }
@@ -523,6 +552,8 @@ forward_culled_kernel(FwdParams P)
     if (hi <= lo && P.winner) {
         for (int p = tid; p < npix; p += FC_THREADS) P.winner[img_off + p] = -1;
     }
+    __syncthreads();
+  }
 }
 
 }  // namespace scream

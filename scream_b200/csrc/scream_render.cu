@@ -45,7 +45,7 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
     WsLayout L;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
-    L.zenc_off = take((size_t)B * V * 2 * sizeof(unsigned));
+    L.zenc_off = take((size_t)B * V * 2 * 2 * sizeof(unsigned));        // two sets: SCREAM_F_DUAL keeps the range of both renders
     L.stream = stream_eligible(B, w, total_pts);
     L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = L.vox_off = 0;
     L.vox_g = total_pts / B >= (4 << 20) ? FV_G : FV_G / 2;   // ~100+ points per voxel; the mask kernel costs g^3 x V
@@ -122,11 +122,20 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
     if (!imgs) return fail(SCREAM_E_ARG, "imgs is NULL");
     const WsLayout L = ws_layout(B, V, w, total_pts);
     if (!ws || ws_bytes < L.total) return fail(SCREAM_E_WORKSPACE, "workspace needs %zu bytes, got %zu", L.total, ws_bytes);
+    if (flags & SCREAM_F_DUAL) {
+        if (!pose) return fail(SCREAM_E_ARG, "SCREAM_F_DUAL needs a pose");
+        if (flags & (SCREAM_F_DENSE | SCREAM_F_ZRANGE_IN)) return fail(SCREAM_E_UNSUPPORTED, "SCREAM_F_DUAL with SCREAM_F_DENSE / SCREAM_F_ZRANGE_IN");
+        if (L.stream && !(flags & SCREAM_F_NOSTREAM)) return fail(SCREAM_E_UNSUPPORTED, "SCREAM_F_DUAL with giant clouds: render the two poses separately");
+        if ((long long)B * V * 3 > 2147483647LL) return fail(SCREAM_E_UNSUPPORTED, "B*V too large for one launch");
+    }
     cudaStream_t st = (cudaStream_t)stream;
     unsigned* zenc = reinterpret_cast<unsigned*>((char*)ws + L.zenc_off);
     if (flags & SCREAM_F_ZRANGE_IN) {
         if (!zrange) return fail(SCREAM_E_ARG, "SCREAM_F_ZRANGE_IN needs a zrange buffer");
         zrange_encode_kernel<<<(B * V * 2 + 255) / 256, 256, 0, st>>>(zrange, zenc, B * V * 2);
+    } else if (flags & SCREAM_F_DUAL) {
+        if (int rc = launch_zrange(xyz, offs, total_pts, max_item_pts, nullptr, views, B, V, zenc, st)) return rc;
+        if (int rc = launch_zrange(xyz, offs, total_pts, max_item_pts, pose, views, B, V, zenc + (size_t)B * V * 2, st)) return rc;
     } else if (int rc = launch_zrange(xyz, offs, total_pts, max_item_pts, pose, views, B, V, zenc, st)) return rc;
 
     FwdParams P;
@@ -217,7 +226,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
             CUDA_TRY(cudaFuncSetAttribute(forward_culled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FC_SMEM));
             attr_dev = dev;
         }
-        forward_culled_kernel<<<(unsigned)((long long)B * V * 2), FC_THREADS, FC_SMEM, st>>>(P);
+        forward_culled_kernel<<<(unsigned)((long long)B * V * ((flags & SCREAM_F_DUAL) ? 3 : 2)), FC_THREADS, FC_SMEM, st>>>(P);
     }
     CUDA_TRY(cudaGetLastError());
     return 0;

@@ -160,6 +160,62 @@ def render_batch(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho
                                        bool(need_winner), int(max_item_pts), zrange_in)
 
 
+class _DualRender(torch.autograd.Function):
+    """One launch for the two renders of a training step (train_3d_match.py:186-201): the pair as given
+    ("fake", differentiable) and the pair with the source posed ("real", a constant for autograd, as the caller-side
+    transform of the reference is applied to data, not to a prediction).  C ABI: SCREAM_F_DUAL."""
+
+    @staticmethod
+    def forward(ctx, xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts):
+        _require_cuda(xyz, offs, pose, views)
+        lib = _lib.load()
+        assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.dim() == 2 and xyz.shape[1] == 3
+        assert offs.dtype == torch.int64 and offs.is_contiguous() and offs.numel() % 2 == 1
+        assert views.dtype == torch.float32 and views.is_contiguous() and views.shape[1:] == (3, 3)
+        B, V, total = (offs.numel() - 1) // 2, views.shape[0], xyz.shape[0]
+        assert pose is not None and pose.dtype == torch.float32 and pose.is_contiguous() and pose.shape == (B, 3, 4)
+        dev = xyz.device
+        with torch.cuda.device(dev):
+            imgs = torch.empty((2, B, V, 2, w, w), dtype=torch.float32, device=dev)
+            winner = torch.empty((2, B, V, 2, w, w) if want_winner else (0,), dtype=torch.int32, device=dev)
+            zrange = torch.empty((2, B, V, 2), dtype=torch.float32, device=dev)
+            nws = _lib.workspace_bytes(B, V, w, total)
+            ws = torch.empty((nws,), dtype=torch.uint8, device=dev)
+            rc = lib.scream_render_forward(_ptr(xyz), _ptr(offs), total, max_item_pts, _ptr(pose), _ptr(views),
+                                           B, V, w, float(rho), flags | _lib.F_DUAL, _ptr(imgs),
+                                           _ptr(winner) if want_winner else None, _ptr(zrange),
+                                           _ptr(ws), nws, _stream_ptr(dev))
+        _lib.check(rc, "scream_render_forward (dual)")
+        fake, real = imgs[0], imgs[1]
+        ctx.save_for_backward(xyz, offs, views, winner, zrange)
+        ctx.cfg = (w, rho, flags, max_item_pts, want_winner)
+        ctx.mark_non_differentiable(real, winner, zrange)
+        return fake, real, winner, zrange
+
+    @staticmethod
+    def backward(ctx, g_fake, g_real, g_winner, g_zrange):
+        xyz, offs, views, winner, zrange = ctx.saved_tensors
+        w, rho, flags, max_item_pts, want_winner = ctx.cfg
+        if not want_winner:
+            raise RuntimeError("render_pair was run without a winner map (need_winner=False)")
+        g = torch.ops.scream.render_bwd(xyz, offs, None, views, w, rho, flags, g_fake, winner[0], zrange[0], max_item_pts)
+        return g, None, None, None, None, None, None, None, None
+
+
+def render_pair(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho, w: int, pose: torch.Tensor,
+                raw: bool = False, need_winner: Optional[bool] = None, max_item_pts: int = 0):
+    """The two renders of a training step in ONE launch: (fake [B,V,2,w,w] = the pairs as given, differentiable w.r.t.
+    xyz; real [B,V,2,w,w] = source clouds posed by pose [B,3,4], no gradient; winner int32 [2,B,V,2,w,w] or empty;
+    zrange [2,B,V,2]).  Bit-identical to render_batch(...) and render_batch(..., pose=pose); the target clouds are
+    sorted once.  Not for giant clouds (the C ABI answers SCREAM_E_UNSUPPORTED)."""
+    if w < 64 or w % 64:
+        raise ValueError("w must be a positive multiple of 64 (render.py:33-34,55)")
+    if need_winner is None:
+        need_winner = torch.is_grad_enabled() and xyz.requires_grad
+    return _DualRender.apply(xyz, offs, pose, views, int(w), float(rho), int(_lib.F_RAW if raw else 0),
+                             bool(need_winner), int(max_item_pts))
+
+
 def depth_range(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, pose: Optional[torch.Tensor] = None,
                 max_item_pts: int = 0) -> torch.Tensor:
     """[B,V,2] (zmin, zmax) of the rotated depth over both clouds of every item (render.py:30-31), on the

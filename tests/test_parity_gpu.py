@@ -7,7 +7,7 @@ import torch
 from conftest import golden_names, load_golden
 from oracle_utils import c_backward, c_forward, c_transform, check_images
 from scream_b200 import _lib, synth
-from scream_b200.render import RegistrationRender, depth_range, make_offsets, render_batch, view_matrices
+from scream_b200.render import RegistrationRender, depth_range, make_offsets, render_batch, render_pair, view_matrices
 
 pytestmark = pytest.mark.gpu
 NAMES = golden_names()
@@ -386,3 +386,40 @@ def test_giant_batch_of_unequal_items():
             assert torch.equal(a[2], b[2])
             assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
             assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
+
+
+def test_dual_render_equals_two_calls():
+    """SCREAM_F_DUAL: the fake and the real render of a training step in one launch, the target sorted
+    once -- same bits as the two separate calls, values, winner maps, depth ranges and the gradient of the fake render;
+    items of unequal sizes, one of them larger than one batch of the culled kernel."""
+    sizes = [(9000, 10000), (300, 12000), (14000, 13500), (10000, 0)]
+    parts = []
+    for i, (n, m) in enumerate(sizes):
+        parts += [synth.unit_ball(n, 800 + i), synth.room_shell(m, 900 + i) if m else np.zeros((0, 3), np.float32)]
+    views = view_matrices(RegistrationRender(24, 64, device="cpu").eulers).to(DEV)
+    offs = make_offsets(sizes).to(DEV)
+    pose = torch.from_numpy(np.stack([synth.random_pose(40 + i) for i in range(len(sizes))])).contiguous().to(DEV)
+    grad = torch.from_numpy(np.random.default_rng(9).standard_normal((len(sizes), 6, 2, 64, 64)).astype(np.float32)).to(DEV)
+    for raw in (False, True):
+        x1 = torch.from_numpy(np.concatenate(parts, 0)).to(DEV).requires_grad_(True)
+        x2 = x1.detach().clone().requires_grad_(True)
+        fake, win, zr = render_batch(x1, offs, views, 24, 64, raw=raw, need_winner=True)
+        real, winr, zrr = render_batch(x1.detach(), offs, views, 24, 64, pose=pose, raw=raw, need_winner=True)
+        fake.backward(grad)
+        dfake, dreal, dwin, dzr = render_pair(x2, offs, views, 24, 64, pose, raw=raw, need_winner=True)
+        dfake.backward(grad)
+        assert torch.equal(dzr[0], zr) and torch.equal(dzr[1], zrr)
+        assert torch.equal(dfake, fake) and torch.equal(dreal, real)
+        assert torch.equal(dwin[0], win) and torch.equal(dwin[1], winr)
+        assert torch.equal(x2.grad, x1.grad) or np.abs((x2.grad - x1.grad).cpu().numpy()).max() <= 1e-5 * float(x1.grad.abs().max())
+        assert not dreal.requires_grad
+
+
+def test_dual_render_refuses_giant_clouds():
+    n = 60000
+    xyz = torch.from_numpy(synth.unit_ball(2 * n, 5)).to(DEV)
+    offs = make_offsets([(n, n)]).to(DEV)
+    views = torch.eye(3, device=DEV)[None].contiguous()
+    pose = torch.from_numpy(synth.random_pose(1))[None].contiguous().to(DEV)
+    with pytest.raises(_lib.ScreamError):
+        render_pair(xyz, offs, views, 24, 64, pose)
