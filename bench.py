@@ -262,7 +262,7 @@ def config_dict(B: int):
 # --------------------------------------------------------------------------------------------
 def run_ours(args, rank: int, local_rank: int, world: int):
     import torch.distributed as dist
-    from scream_b200.render import render_batch, view_matrices, RegistrationRender
+    from scream_b200.render import render_batch, render_pair, view_matrices, RegistrationRender
     from scream_b200 import _lib
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
@@ -275,6 +275,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     xyz, offs, pose, grad = [t.to(dev) for t in (h_xyz, h_offs, h_pose, h_grad)]
     max_item = 2 * N_PTS
     dense = args.dense
+    dual = args.dual and not dense
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
     def step_device(rec=None):
@@ -282,6 +283,14 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         x = xyz.detach().requires_grad_(True)
         if rec is not None:
             e = [ev() for _ in range(6)]; e[0].record()
+        if dual:                       # SCREAM_F_DUAL: both renders in one launch, the target cloud sorted once
+            fake, real, _, _ = render_pair(x, offs, views, RHO, W_IMG, pose, need_winner=True, max_item_pts=max_item)
+            if rec is not None:
+                e[1].record(); e[2].record()
+            fake.backward(grad)
+            if rec is not None:
+                e[3].record(); e[4].record(); e[5].record(); rec.append(e)
+            return fake, real, x.grad
         fake, _, _ = render_batch(x, offs, views, RHO, W_IMG, dense=dense, need_winner=True, max_item_pts=max_item)
         if rec is not None:
             e[1].record(); e[2].record()
@@ -300,7 +309,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     h_gxyz = torch.empty_like(h_xyz).pin_memory()
 
     from scream_b200.pipeline import StepPipeline
-    pipe = StepPipeline([(N_PTS, N_PTS)] * B, views, RHO, W_IMG, dev, chunk_pairs=args.chunk, n_streams=args.streams, dense=dense)
+    pipe = StepPipeline([(N_PTS, N_PTS)] * B, views, RHO, W_IMG, dev, chunk_pairs=args.chunk, n_streams=args.streams, dense=dense,
+                        dual=dual)
 
     def step_e2e():
         """Same step through the public host-buffer API (scream_b200.pipeline.StepPipeline): every step copies its
@@ -346,12 +356,14 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     t_bwd = float(np.mean([e[2].elapsed_time(e[3]) for e in rec]))
     t_real = float(np.mean([e[4].elapsed_time(e[5]) for e in rec]))
     b_fake, b_real, b_bwd = algorithmic_bytes(B)
+    if dual:        # one launch: the clouds are read once per view, both image sets and both winner maps are written
+        b_fake, b_real = b_fake + B * 2 * V * 2 * W_IMG * W_IMG * 4, 0
     peak, peak_src = peaks()
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         t = json.load(open(tpath)).get("forward_culled_kernel", {})
-        if t.get("pairs_per_gpu") == B and t.get("cloud") == CLOUD and not dense:
+        if t.get("pairs_per_gpu") == B and t.get("cloud") == CLOUD and not dense and not dual:
             traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     ach = (b_fake + b_real) / ((t_fake + t_real) / 1e3) / 1e9
     streaming = None
@@ -369,9 +381,9 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": int(h_xyz.numel() * 4 + h_pose.numel() * 4 + h_grad.numel() * 4),
                     "d2h_bytes_per_step": int(h_fake.numel() * 4 * 2 + h_gxyz.numel() * 4),
-                    "api": f"scream_b200.pipeline.StepPipeline(chunk_pairs={args.chunk}, n_streams={args.streams})"},
-            "gpu_launches": args.steps * 7,
-            "kernel": "dense" if dense else "culled",
+                    "api": f"scream_b200.pipeline.StepPipeline(chunk_pairs={args.chunk}, n_streams={args.streams}{", dual=True" if dual else ""})"},
+            "gpu_launches": args.steps * (4 if dual else 7),
+            "kernel": "dense" if dense else ("culled, dual launch (SCREAM_F_DUAL)" if dual else "culled"),
             "roofline": {"bound": "hbm", "kernel": "forward_culled_kernel (timed as one forward call: z-range kernels + it; fake and real calls averaged)",
                          "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
                          "peak_source": peak_src,
@@ -405,6 +417,7 @@ def main():
     ap.add_argument("--batch", type=int, default=512, help="pairs per GPU per step")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dense", action="store_true", help="force the dense exact kernel")
+    ap.add_argument("--dual", action="store_true", help="fake + real render in one launch (SCREAM_F_DUAL, SURVEY 8 f1)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-stream-leg", action="store_true", help="skip the cfg5 streaming-regime leg (one GPU: the whole cloud; N > 1: its points sharded over the ranks)")
     ap.add_argument("--chunk", type=int, default=37, help="pairs per chunk of the host-buffer pipeline (e2e leg)")

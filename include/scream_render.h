@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define SCREAM_ABI_VERSION 5
+#define SCREAM_ABI_VERSION 6
 
 /* error codes */
 #define SCREAM_OK            0
@@ -72,6 +72,12 @@ extern "C" {
                                    a leading dimension of 2 ([2][B][V]...: 0 = as given, 1 = posed); the workspace query
                                    is unchanged.  The target cloud is sorted once and searched twice.  Not combined
                                    with SCREAM_F_DENSE or SCREAM_F_ZRANGE_IN, nor with giant clouds (SCREAM_E_UNSUPPORTED). */
+
+#define SCREAM_F_HALF      64u   /* fp16 (autocast) input mode, SURVEY 8 f2 (train_kitti.py:154-169: under torch.cuda.amp.autocast()
+                                   render.py:68's matmul and render.py:31 run in fp16): xyz holds clouds already rotated and
+                                   rounded by scream_half_rotate, views is the identity, and the depth weight follows the
+                                   fp16 chain h(1 - h(h(z - zmin) / range)).  No pose, no SCREAM_F_DUAL; giant clouds take
+                                   the plain culled kernel.  Pass the same flag to scream_render_backward. */
 
 /* opaque CUDA stream handle (cudaStream_t / CUstream) */
 typedef void *scream_stream_t;
@@ -109,6 +115,19 @@ int scream_render_backward(const float *xyz, const int64_t *offs, int64_t total_
                            const float *grad_imgs, const int32_t *winner, const float *zrange,
                            float *grad_xyz,
                            void *ws, size_t ws_bytes, scream_stream_t stream);
+
+/* fp16 (autocast) input mode, stage 1 (replaces the fp16 torch.matmul of render.py:68 under
+ * train_kitti.py:154's autocast): every item's clouds rotated by every view with fp16 operands, fp32 accumulation and an
+ * fp16 result, stored as fp32 words.  xr [V*total_pts,3]: item b, view v at rows V*offs[2b] + v*(n_b+m_b) ...;
+ * offs_out [2*B*V+1]: CSR offsets presenting xr as B*V items (index b*V+v) for scream_render_forward(..., B*V items,
+ * one identity view, flags | SCREAM_F_HALF), whose [B*V,1,2,w,w] outputs are the [B,V,2,w,w] outputs. */
+int scream_half_rotate(const float *xyz, const int64_t *offs, int64_t total_pts, int64_t max_item_pts,
+                       const float *views, int B, int V, float *xr, int64_t *offs_out, scream_stream_t stream);
+
+/* ... and its gradient: grad_xyz[i] = sum_v fp16(R_v)^T grad_xr[v][i] (fp32; the casts pass gradients straight through,
+ * as autograd does for .half()).  grad_xr in xr's layout = scream_render_backward's grad_xyz of the B*V-item call. */
+int scream_half_rotate_backward(const float *grad_xr, const int64_t *offs, int64_t total_pts, int64_t max_item_pts,
+                                const float *views, int B, int V, float *grad_xyz, scream_stream_t stream);
 
 /* Transform stage only (testing / parity of the "index path"): rotated coordinates [B? no: total_pts
  * per view] rotated [V,total_pts,3], pv [V,total_pts] (render.py:31), zrange [B,V,2].  Any output may

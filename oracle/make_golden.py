@@ -86,6 +86,44 @@ def freeze(name, src, tgt, rho, w, eulers, pose=None, grad=False, view="muti"):
           f"max={v.max():.4f} zero_px={(v == 0).mean():.3f}")
 
 
+def freeze_half(name, src, tgt, rho, w, eulers):
+    """the reference under autocast (train_kitti.py:154-169 uses torch.cuda.amp.autocast(); this container
+    has no GPU, so the reference runs under torch.autocast("cpu", dtype=torch.float16): same autocast op lists, the
+    matmul of render.py:68 in fp16, render.py:31 in fp16, fp32 from render.py:42 on).  Forward: the explicit-rounding
+    restatement must equal it bit for bit.  Backward: the reference's own autograd under autocast (it rounds the
+    gradient intermediates to fp16 too) is frozen; the product's straight-through fp32 gradient is compared with it
+    to a tolerance in the tests."""
+    src_t, tgt_t = torch.from_numpy(src), torch.from_numpy(tgt)
+    ref = make_reference(rho, w)
+    ref.eulers = [np.asarray(e, dtype=np.float64) for e in eulers]
+    with torch.no_grad(), torch.autocast("cpu", dtype=torch.float16):
+        want = ref(src_t, tgt_t)
+    assert want.dtype == torch.float32
+    views = orc.view_matrices(ref.eulers)
+    ins = orc.forward_instrumented(src_t, tgt_t, rho, w, views, half=True)
+    assert torch.equal(want, ins["imgs"]), f"{name}: fp16-mode restatement differs from the reference under autocast"
+    with torch.no_grad():
+        plain = ref(src_t, tgt_t)
+    g = torch.from_numpy(np.random.default_rng(7).standard_normal(want.shape).astype(np.float32))
+    s = src_t.clone().requires_grad_(True)
+    t = tgt_t.clone().requires_grad_(True)
+    with torch.autocast("cpu", dtype=torch.float16):
+        out = ref(s, t)
+    out.backward(g)
+    rec = dict(src=src, tgt=tgt, rho=np.float64(rho), w=np.int64(w), eulers=np.stack(ref.eulers).astype(np.float64),
+               views=views.numpy(), imgs=want.numpy(), val=ins["val"].numpy(), idx=ins["idx"].numpy(),
+               second=ins["second"].numpy(), zrange=ins["zrange"].numpy(),
+               grad_out=g.numpy(), grad_src=s.grad.numpy(), grad_tgt=t.grad.numpy())
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **rec)
+    print(f"wrote {name}: restatement == reference under autocast(fp16); differs from the fp32 render at "
+          f"{(plain != want).float().mean().item():.3f} of the pixels (max {(plain - want).abs().max().item():.2e})")
+
+
+def freeze_half_all():
+    freeze_half("half_kitti_bev", synth.kitti_slab(1800, 61), synth.kitti_slab(1700, 62), 48, 64, [np.array([0, np.pi, 0])])
+    freeze_half("half_ball_six", synth.unit_ball(900, 63), synth.room_shell(800, 64), 24, 64, orc.canonical_eulers("muti"))
+
+
 def reference_function(path, name, namespace):
     """Execute ONE unmodified top-level function of a reference file whose module cannot be imported here
     (utils.py imports open3d): its source segment is compiled as is, in a namespace holding its globals."""
@@ -120,6 +158,9 @@ def main():
     if "--only-colorize" in sys.argv:
         freeze_colorize()
         return
+    if "--only-half" in sys.argv:
+        freeze_half_all()
+        return
     torch.manual_seed(0)
     six = orc.canonical_eulers("muti")
     one = orc.canonical_eulers("single")
@@ -139,6 +180,7 @@ def main():
     # sparse cloud: most pixels are far from every point (exact zeros, denormals)
     freeze("sparse_far_pixels", synth.unit_ball(40, 51) * np.float32(0.2), synth.unit_ball(16, 52), 48, 64, six)
     freeze_colorize()
+    freeze_half_all()
 
 
 if __name__ == "__main__":

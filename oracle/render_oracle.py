@@ -87,6 +87,36 @@ def depth_weights(x: torch.Tensor) -> Tuple[torch.Tensor, float, float]:
     return pv, zmin, zmax
 
 
+# --------------------------------------------------------------------------------------
+# f2  fp16 (autocast) input mode: what render.py:29-31,68 compute when the caller wraps the generator in
+# torch.cuda.amp.autocast() (train_kitti.py:154-169).  Written with EXPLICIT roundings, not with autocast, so it is an
+# independent restatement; oracle/make_golden.py checks it bit for bit against the reference executed under
+# torch.autocast("cpu", dtype=torch.float16) (the only autocast this container can run).
+# --------------------------------------------------------------------------------------
+def _h(x: torch.Tensor) -> torch.Tensor:
+    """round to fp16, keep as fp32"""
+    return x.half().float()
+
+
+def rotate_half(view: torch.Tensor, pts: torch.Tensor) -> torch.Tensor:
+    """render.py:68 under autocast: fp16 operands, fp32 accumulation in k order, fp16 result ([N,3], as fp32)."""
+    r, p = _h(view), _h(pts)
+    acc = r[:, 0][None] * p[:, 0:1]                       # products of fp16 values are exact in fp32
+    acc = acc + r[:, 1][None] * p[:, 1:2]
+    acc = acc + r[:, 2][None] * p[:, 2:3]
+    return _h(acc)
+
+
+def depth_weights_half(x: torch.Tensor) -> Tuple[torch.Tensor, float, float]:
+    """render.py:29-31 on fp16 depths: every tensor (op) Python-scalar kernel computes in fp32 and rounds to fp16."""
+    z = x[:, 2]
+    zmin = torch.min(z, dim=0)[0].item()
+    zmax = torch.max(z, dim=0)[0].item()
+    rng = torch.tensor(zmax - zmin, dtype=torch.float64).float()      # the double difference, cast to the fp32 opmath type
+    pv = _h(1 - _h(_h(z - zmin) / rng))
+    return pv, zmin, zmax
+
+
 def _splat_block(xy: torch.Tensor, pv: torch.Tensor, centres: torch.Tensor, rho) -> torch.Tensor:
     """[P, npix] values pv_i * exp(-|xy_i - c_p|^2 / 2 * rho^2), render.py:42-43,46."""
     npix = centres.shape[0]
@@ -131,11 +161,11 @@ def forward_dense(src: torch.Tensor, tgt: torch.Tensor, rho, w: int,
 # Same per-element arithmetic as render_dense; the max over points is merged across
 # chunks (first index wins ties, like torch.max(dim=0)).  Bit-identical values.
 # --------------------------------------------------------------------------------------
-def render_instrumented(x: torch.Tensor, src_n: int, rho, w: int, chunk: int = 2048):
+def render_instrumented(x: torch.Tensor, src_n: int, rho, w: int, chunk: int = 2048, half: bool = False):
     """Returns dict(val[2,w,w] f32, idx[2,w,w] i64 cloud-local, second[2,w,w] f32, zmin, zmax)."""
     centres = pixel_centres(w)
     npix = w * w
-    pv, zmin, zmax = depth_weights(x)
+    pv, zmin, zmax = depth_weights_half(x) if half else depth_weights(x)
     best = torch.full((2, npix), -math.inf)
     second = torch.full((2, npix), -math.inf)
     arg = torch.zeros((2, npix), dtype=torch.int64)
@@ -167,8 +197,9 @@ def render_instrumented(x: torch.Tensor, src_n: int, rho, w: int, chunk: int = 2
 
 
 def forward_instrumented(src: torch.Tensor, tgt: torch.Tensor, rho, w: int, views: torch.Tensor,
-                         pose: Optional[torch.Tensor] = None, chunk: int = 2048):
+                         pose: Optional[torch.Tensor] = None, chunk: int = 2048, half: bool = False):
     """Full forward with explicit fp32 view matrices [V,3,3] and optional pose [3,4] on src.
+    half=True: the fp16 (autocast) input mode above.
 
     Returns dict(imgs[V,2,w,w] normalised, val, idx (int32), second, zrange[V,2]).
     """
@@ -177,7 +208,8 @@ def forward_instrumented(src: torch.Tensor, tgt: torch.Tensor, rho, w: int, view
     pts = torch.cat([src, tgt], dim=0)
     vals, idxs, seconds, zr = [], [], [], []
     for v in range(views.shape[0]):
-        r = render_instrumented(rotate(views[v], pts), src.shape[0], rho, w, chunk)
+        x = rotate_half(views[v], pts) if half else rotate(views[v], pts)
+        r = render_instrumented(x, src.shape[0], rho, w, chunk, half=half)
         vals.append(r["val"]); idxs.append(r["idx"]); seconds.append(r["second"])
         zr.append([r["zmin"], r["zmax"]])
     val = torch.stack(vals, dim=0)

@@ -11,7 +11,7 @@ import threading
 
 from .csrc import build as _build
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 F_RAW = 1
 F_DENSE = 2
@@ -19,6 +19,7 @@ F_ZRANGE_IN = 4
 F_NOSTREAM = 8
 F_THINSEED = 16
 F_DUAL = 32
+F_HALF = 64
 
 _lock = threading.Lock()
 _lib = None
@@ -34,6 +35,8 @@ _SIGNATURES = {
                                          C.c_double, C.c_uint, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "scream_render_transform": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, C.c_int, C.c_int,
                                           _P, _P, _P, _P, C.c_size_t, _P]),
+    "scream_half_rotate": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, C.c_int, C.c_int, _P, _P, _P]),
+    "scream_half_rotate_backward": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, C.c_int, C.c_int, _P, _P]),
     "scream_depth_to_rgb8": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
     "scream_render_forward_host": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_double, C.c_uint,
                                              _P, _P, _P, C.c_int]),

@@ -54,7 +54,7 @@ backward_scatter_kernel(BwdParams P)
     const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z), zr = rot_row(s_R + 6, x, y, z);
     const float zmin = P.zrange[((size_t)b * P.V + v) * 2], zmax = P.zrange[((size_t)b * P.V + v) * 2 + 1];
     const float range = z_range(zmin, zmax);
-    const float pv = depth_weight(zr, zmin, range);
+    const float pv = depth_weight_m(zr, zmin, range, (P.flags & 64u) != 0);   // 64u: SCREAM_F_HALF
     const float dx = __fsub_rn(xr, pixel_centre(p % w, half)), dy = __fsub_rn(yr, pixel_centre(p / w, half));
     const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
     const float wgt = expf(__fmul_rn(d2, P.negk));

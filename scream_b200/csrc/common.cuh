@@ -6,6 +6,7 @@
 // rotation is the FMA chain of MKL sgemm, fmaf(r2, z, fmaf(r1, y, r0 * x)).
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <math.h>
 
@@ -41,6 +42,23 @@ __device__ __forceinline__ float z_range(float zmin, float zmax) {
 // render.py:31  pv = 1 - (z - zmin) / range      (true fp32 division on the CPU reference)
 __device__ __forceinline__ float depth_weight(float z, float zmin, float range) {
     return __fsub_rn(1.0f, __fdiv_rn(__fsub_rn(z, zmin), range));
+}
+
+// ---- fp16 (autocast) input mode, SURVEY 8 f2: train_kitti.py:154-169 wraps the generator in torch.cuda.amp.autocast(), so
+// render.py:68's matmul runs in fp16 (rotated coordinates rounded to fp16) and render.py:31 is a chain of fp16 tensor (op)
+// Python-scalar kernels, each computed in fp32 and rounded to fp16; from render.py:42 on the fp32 pix_xy promotes everything
+// back to fp32.  Pinned against the reference executed under torch.autocast("cpu", dtype=float16) (oracle/make_golden.py).
+__device__ __forceinline__ float round_f16(float v) { return __half2float(__float2half_rn(v)); }
+__device__ __forceinline__ float depth_weight_f16(float z, float zmin, float range) {
+    return round_f16(__fsub_rn(1.0f, round_f16(__fdiv_rn(round_f16(__fsub_rn(z, zmin)), range))));
+}
+__device__ __forceinline__ float depth_weight_m(float z, float zmin, float range, bool f16) {
+    return f16 ? depth_weight_f16(z, zmin, range) : depth_weight(z, zmin, range);
+}
+// rotated coordinate of the fp16 matmul: fp16 operands, fp32 accumulation (the products are exact in fp32), fp16 result
+__device__ __forceinline__ float rot_row_f16(const float* __restrict__ r, float x, float y, float z) {
+    return round_f16(__fmaf_rn(round_f16(r[2]), round_f16(z), __fmaf_rn(round_f16(r[1]), round_f16(y),
+                     __fmul_rn(round_f16(r[0]), round_f16(x)))));
 }
 
 // render.py:14-16  pixel centre ((j - w//2) + 0.5) / (w//2)  -- exact in fp32 (w/2 is a power of two

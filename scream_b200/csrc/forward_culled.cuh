@@ -92,14 +92,14 @@ __device__ __forceinline__ unsigned long long col_mask(int j0, int j1) {
 // exact value of record s at pixel g: the reference expression, pv recomputed from the point itself
 struct ExactCtx {
     const float* xyz; int64_t lo; const float* R; const float* pose; bool posed;
-    float zmin, range, negk;
+    float zmin, range, negk; bool f16;
 };
 __device__ __forceinline__ float exact_value(const FcShared& S, const ExactCtx& E, int s, const PixelGeom& g, int& id) {
     id = S.idx[s];
     const float* q = E.xyz + (size_t)(E.lo + id) * 3;
     float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
     if (E.posed) apply_pose(E.pose, x, y, z);
-    const float pv = depth_weight(rot_row(E.R + 6, x, y, z), E.zmin, E.range);
+    const float pv = depth_weight_m(rot_row(E.R + 6, x, y, z), E.zmin, E.range, E.f16);
     const float2 r = S.xy[s];
     return pair_value(pair_d2(r.x, r.y, g.cx, g.cy), pv, E.negk);
 }
@@ -208,6 +208,7 @@ __device__ __forceinline__ void disc_scan(const FcShared& S, const ExactCtx& E, 
 }
 
 constexpr unsigned FC_FLAG_DUAL = 32u;                   // SCREAM_F_DUAL
+constexpr unsigned FC_FLAG_HALF = 64u;                   // SCREAM_F_HALF: fp16 depth-weight chain (common.cuh)
 
 __global__ void __launch_bounds__(FC_THREADS, 1)
 forward_culled_kernel(FwdParams P)
@@ -287,7 +288,7 @@ forward_culled_kernel(FwdParams P)
         P.zrange[(ob * P.V + v) * 2 + 1] = zmax;
     }
     ExactCtx E; E.xyz = P.xyz; E.lo = lo; E.R = s_R; E.pose = s_pose; E.posed = posed;
-    E.zmin = zmin; E.range = range; E.negk = P.negk;
+    E.zmin = zmin; E.range = range; E.negk = P.negk; E.f16 = (P.flags & FC_FLAG_HALF) != 0;
     // the target's second pass keeps the sorted records of the first (one batch only) and renews the score offsets
     const bool resort = !(pass > pass0 && npts <= (int64_t)FC_CAP);
 
@@ -379,7 +380,7 @@ forward_culled_kernel(FwdParams P)
                 const unsigned pos = (unsigned)s_start[packed[k] >> 16] + (packed[k] & 0xFFFFu);
                 s_xy[pos] = make_float2(xr, yr);
                 // c = -ln(pv)/k >= 0; pv == 0 -> +inf (never wins); pv < 0 (rounding corner) -> NaN (never wins)
-                s_c[pos] = __fmul_rn(logf(depth_weight(zr, zmin, range)), P.inv_negk);
+                s_c[pos] = __fmul_rn(logf(depth_weight_m(zr, zmin, range, (P.flags & FC_FLAG_HALF) != 0)), P.inv_negk);
                 s_idx[pos] = (int)pi;
             }
         }
@@ -419,7 +420,7 @@ forward_culled_kernel(FwdParams P)
             for (int pos = tid; pos < cnt; pos += FC_THREADS) {
                 const float* q = P.xyz + (size_t)(lo + s_idx[pos]) * 3;
                 const float zr = rot_row(s_R + 6, __ldg(q), __ldg(q + 1), __ldg(q + 2));
-                s_c[pos] = __fmul_rn(logf(depth_weight(zr, zmin, range)), P.inv_negk);
+                s_c[pos] = __fmul_rn(logf(depth_weight_m(zr, zmin, range, (P.flags & FC_FLAG_HALF) != 0)), P.inv_negk);
             }
             __syncthreads();
         }

@@ -76,7 +76,7 @@ forward_dense_kernel(FwdParams P)
             float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
             if (posed) apply_pose(s_pose, x, y, z);
             float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z), zr = rot_row(s_R + 6, x, y, z);
-            s_pts[j] = make_float4(xr, yr, depth_weight(zr, zmin, range), 0.f);
+            s_pts[j] = make_float4(xr, yr, depth_weight_m(zr, zmin, range, (P.flags & 64u) != 0), 0.f);   // 64u: SCREAM_F_HALF
         }
         __syncthreads();
         const int ibase = (int)(c0 - lo);

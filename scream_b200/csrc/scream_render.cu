@@ -8,6 +8,7 @@
 #include "forward_stream.cuh"
 #include "backward.cuh"
 #include "colorize.cuh"
+#include "half_rotate.cuh"
 
 #include <algorithm>
 #include <cstdarg>
@@ -127,6 +128,10 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         if (flags & (SCREAM_F_DENSE | SCREAM_F_ZRANGE_IN)) return fail(SCREAM_E_UNSUPPORTED, "SCREAM_F_DUAL with SCREAM_F_DENSE / SCREAM_F_ZRANGE_IN");
         if (L.stream && !(flags & SCREAM_F_NOSTREAM)) return fail(SCREAM_E_UNSUPPORTED, "SCREAM_F_DUAL with giant clouds: render the two poses separately");
         if ((long long)B * V * 3 > 2147483647LL) return fail(SCREAM_E_UNSUPPORTED, "B*V too large for one launch");
+    }
+    if (flags & SCREAM_F_HALF) {
+        if (pose || (flags & SCREAM_F_DUAL)) return fail(SCREAM_E_UNSUPPORTED, "SCREAM_F_HALF takes pre-rotated clouds: no pose, no SCREAM_F_DUAL");
+        flags |= SCREAM_F_NOSTREAM;           // the giant-cloud pre-filter bounds the fp32 depth weight
     }
     cudaStream_t st = (cudaStream_t)stream;
     unsigned* zenc = reinterpret_cast<unsigned*>((char*)ws + L.zenc_off);
@@ -249,6 +254,38 @@ int scream_render_backward(const float* xyz, const int64_t* offs, int64_t total_
     P.flags = flags; P.grad_imgs = grad_imgs; P.winner = winner; P.zrange = zrange; P.grad_xyz = grad_xyz;
     const long long grid = (long long)B * V * 2 * (w * w / BW_THREADS);
     backward_scatter_kernel<<<(unsigned)grid, BW_THREADS, 0, st>>>(P);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+static int half_rotate_grid(int64_t total_pts, int64_t max_item_pts, int B, dim3* grid) {
+    if (B > 65535) return fail(SCREAM_E_UNSUPPORTED, "batch too large for the rotate grid");
+    if (max_item_pts <= 0 || max_item_pts > total_pts) max_item_pts = total_pts;
+    const int64_t chunks = std::min<int64_t>((max_item_pts + HR_THREADS - 1) / HR_THREADS, 1 << 20);
+    *grid = dim3((unsigned)std::max<int64_t>(chunks, 1), (unsigned)B);
+    return 0;
+}
+
+int scream_half_rotate(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
+                       const float* views, int B, int V, float* xr, int64_t* offs_out, scream_stream_t stream)
+{
+    if (!xyz || !offs || !views || !xr || !offs_out) return fail(SCREAM_E_ARG, "xyz/offs/views/xr/offs_out must not be NULL");
+    if (B <= 0 || V <= 0 || total_pts <= 0) return fail(SCREAM_E_ARG, "B, V and total_pts must be positive");
+    dim3 grid;
+    if (int rc = half_rotate_grid(total_pts, max_item_pts, B, &grid)) return rc;
+    half_rotate_kernel<<<grid, HR_THREADS, 0, (cudaStream_t)stream>>>(xyz, offs, views, B, V, xr, offs_out);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_half_rotate_backward(const float* grad_xr, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
+                                const float* views, int B, int V, float* grad_xyz, scream_stream_t stream)
+{
+    if (!grad_xr || !offs || !views || !grad_xyz) return fail(SCREAM_E_ARG, "grad_xr/offs/views/grad_xyz must not be NULL");
+    if (B <= 0 || V <= 0 || total_pts <= 0) return fail(SCREAM_E_ARG, "B, V and total_pts must be positive");
+    dim3 grid;
+    if (int rc = half_rotate_grid(total_pts, max_item_pts, B, &grid)) return rc;
+    half_rotate_backward_kernel<<<grid, HR_THREADS, 0, (cudaStream_t)stream>>>(grad_xr, offs, views, V, grad_xyz);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

@@ -19,12 +19,12 @@ import numpy as np
 import torch
 
 from . import _lib
-from .render import make_offsets
+from .render import make_offsets, render_pair
 
 
 class StepPipeline:
     def __init__(self, sizes: Sequence[Tuple[int, int]], views: torch.Tensor, rho, w: int, device,
-                 chunk_pairs: int = 37, n_streams: int = 6, dense: bool = False):
+                 chunk_pairs: int = 37, n_streams: int = 6, dense: bool = False, dual: bool = False):
         if not torch.cuda.is_available():
             raise RuntimeError("scream_b200 renders on CUDA only (no CPU fallback)")
         _lib.load()
@@ -32,6 +32,9 @@ class StepPipeline:
         self.views = views.to(self.dev).contiguous()
         self.rho, self.w = float(rho), int(w)
         self.flags = _lib.F_DENSE if dense else 0
+        if dual and dense:
+            raise ValueError("dual=True (SCREAM_F_DUAL) is a mode of the culled kernel, not of the dense referee")
+        self.dual = bool(dual)                                # fake + real render in one launch
         self.B = len(sizes)
         sizes = [(int(a), int(b)) for a, b in sizes]
         self.chunks: List[Tuple[int, int, int, int, torch.Tensor, int]] = []   # (b0, b1, p0, p1, offs_dev, max_item)
@@ -41,7 +44,8 @@ class StepPipeline:
             offs = make_offsets(sizes[b0:b1]).to(self.dev)
             self.chunks.append((b0, b1, int(pts[b0]), int(pts[b1]), offs, max(a + b for a, b in sizes[b0:b1])))
         self.streams = [torch.cuda.Stream(self.dev) for _ in range(max(1, n_streams))]
-        self.launches_per_run = 7 * len(self.chunks)          # zrange_init, zrange, forward (x2) + backward scatter
+        # zrange_init, zrange, forward (x2, or once for a dual launch) + backward scatter
+        self.launches_per_run = (4 if self.dual else 7) * len(self.chunks)
 
     def run(self, h_xyz: torch.Tensor, h_pose: Optional[torch.Tensor], h_grad: torch.Tensor,
             out_fake: torch.Tensor, out_real: torch.Tensor, out_gxyz: torch.Tensor) -> None:
@@ -57,6 +61,15 @@ class StepPipeline:
                 x = h_xyz[p0:p1].to(self.dev, non_blocking=True)
                 g = h_grad[b0:b1].to(self.dev, non_blocking=True)
                 p = h_pose[b0:b1].to(self.dev, non_blocking=True) if h_pose is not None else None
+                if self.dual:
+                    with torch.no_grad():
+                        fake, real, win, zr = render_pair(x, offs, self.views, self.rho, self.w, p, need_winner=True,
+                                                          max_item_pts=max_item)
+                    out_fake[b0:b1].copy_(fake, non_blocking=True)
+                    out_real[b0:b1].copy_(real, non_blocking=True)
+                    gx = ops.render_bwd(x, offs, None, self.views, self.w, self.rho, self.flags, g, win[0], zr[0], max_item)
+                    out_gxyz[p0:p1].copy_(gx, non_blocking=True)
+                    continue
                 fake, win, zr = ops.render_fwd(x, offs, None, self.views, self.w, self.rho, self.flags, True, max_item, None)
                 out_fake[b0:b1].copy_(fake, non_blocking=True)
                 gx = ops.render_bwd(x, offs, None, self.views, self.w, self.rho, self.flags, g, win, zr, max_item)

@@ -146,14 +146,23 @@ def make_offsets(sizes: Sequence[Tuple[int, int]]) -> torch.Tensor:
 def render_batch(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho, w: int,
                  pose: Optional[torch.Tensor] = None, raw: bool = False, dense: bool = False,
                  need_winner: Optional[bool] = None, max_item_pts: int = 0,
-                 zrange_in: Optional[torch.Tensor] = None, no_stream: bool = False, thin_seed: bool = False):
+                 zrange_in: Optional[torch.Tensor] = None, no_stream: bool = False, thin_seed: bool = False,
+                 half: bool = False):
     """Render B pairs at once.  xyz [total,3] fp32 cuda, offs [2B+1] int64 cuda, views [V,3,3] fp32 cuda,
     pose [B,3,4] or None; zrange_in [B,V,2]: use this depth range instead of reducing it (point-sharded
-    clouds, scream_b200/shard.py).  Returns (imgs [B,V,2,w,w], winner int32 or empty, zrange [B,V,2])."""
+    clouds, scream_b200/shard.py).  half=True: the reference's arithmetic under torch.cuda.amp.autocast()
+    (train_kitti.py:154-169: fp16 rotation and depth weight); no pose / zrange_in there.
+    Returns (imgs [B,V,2,w,w], winner int32 or empty, zrange [B,V,2])."""
     if w < 64 or w % 64:
         raise ValueError("w must be a positive multiple of 64 (render.py:33-34,55)")
     if need_winner is None:
         need_winner = torch.is_grad_enabled() and xyz.requires_grad
+    if half:
+        if pose is not None or zrange_in is not None:
+            raise ValueError("half=True (autocast mode) takes neither a pose nor a zrange_in (train_kitti.py:193-194 renders "
+                             "the posed pair outside autocast)")
+        flags = (_lib.F_RAW if raw else 0) | (_lib.F_DENSE if dense else 0)
+        return _HalfRender.apply(xyz, offs, views, int(w), float(rho), int(flags), bool(need_winner), int(max_item_pts))
     flags = (_lib.F_RAW if raw else 0) | (_lib.F_DENSE if dense else 0) | (_lib.F_NOSTREAM if no_stream else 0) \
         | (_lib.F_THINSEED if thin_seed else 0)
     return torch.ops.scream.render_fwd(xyz, offs, pose, views, int(w), float(rho), int(flags),
@@ -214,6 +223,55 @@ def render_pair(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho,
         need_winner = torch.is_grad_enabled() and xyz.requires_grad
     return _DualRender.apply(xyz, offs, pose, views, int(w), float(rho), int(_lib.F_RAW if raw else 0),
                              bool(need_winner), int(max_item_pts))
+
+
+class _HalfRender(torch.autograd.Function):
+    """fp16 (autocast) input mode, SURVEY 8 f2 (train_kitti.py:154-169): what the reference computes when its generator
+    runs under torch.cuda.amp.autocast() -- render.py:68's matmul in fp16 (fp16 operands and result), render.py:31 as a
+    chain of fp16 kernels, fp32 from render.py:42 on.  C ABI: scream_half_rotate, then the forward call on B*V
+    pre-rotated items with SCREAM_F_HALF; backward = scream_render_backward + scream_half_rotate_backward (the casts
+    pass gradients straight through, in fp32: the reference rounds its gradient intermediates to fp16 as well)."""
+
+    @staticmethod
+    def forward(ctx, xyz, offs, views, w, rho, flags, want_winner, max_item_pts):
+        _require_cuda(xyz, offs, views)
+        lib = _lib.load()
+        assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.dim() == 2 and xyz.shape[1] == 3
+        assert offs.dtype == torch.int64 and offs.is_contiguous() and offs.numel() % 2 == 1
+        assert views.dtype == torch.float32 and views.is_contiguous() and views.shape[1:] == (3, 3)
+        B, V, total = (offs.numel() - 1) // 2, views.shape[0], xyz.shape[0]
+        dev = xyz.device
+        with torch.cuda.device(dev):
+            xr = torch.empty((V * total, 3), dtype=torch.float32, device=dev)
+            offs_bv = torch.empty((2 * B * V + 1,), dtype=torch.int64, device=dev)
+            rc = lib.scream_half_rotate(_ptr(xyz), _ptr(offs), total, max_item_pts, _ptr(views), B, V,
+                                        _ptr(xr), _ptr(offs_bv), _stream_ptr(dev))
+            _lib.check(rc, "scream_half_rotate")
+            eye = torch.eye(3, dtype=torch.float32, device=dev).unsqueeze(0).contiguous()
+        flags |= _lib.F_HALF
+        imgs, winner, zrange = torch.ops.scream.render_fwd(xr, offs_bv, None, eye, w, rho, flags, want_winner,
+                                                           max_item_pts, None)
+        ctx.save_for_backward(xr, offs_bv, eye, offs, views, winner, zrange)
+        ctx.cfg = (w, rho, flags, max_item_pts, want_winner, B, V, total)
+        winner = winner.view(B, V, 2, w, w) if want_winner else winner
+        ctx.mark_non_differentiable(winner, zrange)
+        return imgs.view(B, V, 2, w, w), winner, zrange.view(B, V, 2)
+
+    @staticmethod
+    def backward(ctx, g_imgs, g_winner, g_zrange):
+        xr, offs_bv, eye, offs, views, winner, zrange = ctx.saved_tensors
+        w, rho, flags, max_item_pts, want_winner, B, V, total = ctx.cfg
+        if not want_winner:
+            raise RuntimeError("the fp16-mode render was run without a winner map (need_winner=False)")
+        g_xr = torch.ops.scream.render_bwd(xr, offs_bv, None, eye, w, rho, flags,
+                                           g_imgs.contiguous().view(B * V, 1, 2, w, w), winner, zrange, max_item_pts)
+        dev = xr.device
+        with torch.cuda.device(dev):
+            g = torch.empty((total, 3), dtype=torch.float32, device=dev)
+            rc = _lib.load().scream_half_rotate_backward(_ptr(g_xr), _ptr(offs), total, max_item_pts, _ptr(views), B, V,
+                                                         _ptr(g), _stream_ptr(dev))
+        _lib.check(rc, "scream_half_rotate_backward")
+        return g, None, None, None, None, None, None, None
 
 
 def depth_range(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, pose: Optional[torch.Tensor] = None,
@@ -307,15 +365,21 @@ class RegistrationRender(nn.Module):
             self._cache[key] = hit
         return hit
 
-    def _call(self, src, tgt, views, raw):
+    def _call(self, src, tgt, views, raw, half=False, prerotated_half=False):
         if src.dim() != 2 or tgt.dim() != 2 or src.shape[1] != 3 or tgt.shape[1] != 3:
             raise ValueError("expected [n,3] and [m,3] point tensors")
         if src.shape[0] == 0 or tgt.shape[0] == 0:
             raise RuntimeError("max(): cannot reduce over an empty cloud (render.py:46,49)")
         xyz = torch.cat([src.float(), tgt.float()], dim=0)         # render.py:63
         n, m = src.shape[0], tgt.shape[0]
+        if prerotated_half:        # render() of fp16 coordinates: only the depth-weight chain of render.py:31 is fp16
+            need = torch.is_grad_enabled() and xyz.requires_grad
+            imgs, _, _ = torch.ops.scream.render_fwd(xyz.contiguous(), self._offsets(n, m, xyz.device), None, views,
+                                                     int(self.w), float(self.rho), int(_lib.F_RAW | _lib.F_HALF),
+                                                     bool(need), n + m, None)
+            return imgs[0]
         imgs, _, _ = render_batch(xyz, self._offsets(n, m, xyz.device), views, self.rho, self.w,
-                                  raw=raw, max_item_pts=n + m)
+                                  raw=raw, max_item_pts=n + m, half=half)
         return imgs[0]
 
     def render(self, x, src_n):
@@ -325,12 +389,19 @@ class RegistrationRender(nn.Module):
         if eye is None:
             eye = torch.eye(3, dtype=torch.float32, device=x.device).unsqueeze(0).contiguous()
             self._cache[("eye", str(x.device))] = eye
-        return self._call(x[:src_n], x[src_n:], eye, raw=True)[0]
+        if x.dtype == torch.bfloat16:
+            raise NotImplementedError("bf16 coordinates: the reference's KITTI scripts autocast to fp16 (train_kitti.py:154)")
+        return self._call(x[:src_n], x[src_n:], eye, raw=True, prerotated_half=x.dtype == torch.float16)[0]
 
     def forward(self, src_pred, tgt_pcd):
         """[V,2,w,w] fp32 in [-1,1) (render.py:61-73)."""
         _require_cuda(src_pred, tgt_pcd)
-        return self._call(src_pred, tgt_pcd, self._views(src_pred.device), raw=False)
+        half = False
+        if torch.is_autocast_enabled("cuda"):       # train_kitti.py:154-169: render.py:68 runs as an fp16 matmul
+            if torch.get_autocast_dtype("cuda") != torch.float16:
+                raise NotImplementedError("autocast to bf16: the reference's KITTI scripts autocast to fp16 (train_kitti.py:154)")
+            half = True
+        return self._call(src_pred, tgt_pcd, self._views(src_pred.device), raw=False, half=half)
 
     # no parameters / buffers: keep checkpoints of the enclosing model loadable (SURVEY section 5)
     def __getstate__(self):

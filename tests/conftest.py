@@ -19,9 +19,14 @@ def pytest_configure(config):
 
 
 def golden_names():
-    """Renderer fixtures (the colouriser's fixture has its own tests)."""
+    """Renderer fixtures of the fp32 path (the colouriser's fixture and the fp16-mode fixtures have their own tests)."""
     names = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-    return [n for n in names if not n.startswith("colorize")]
+    return [n for n in names if not n.startswith(("colorize", "half_"))]
+
+
+def half_golden_names():
+    """Fixtures of the fp16 (autocast) input mode, SURVEY 8 f2: the reference executed under torch.autocast (CPU, fp16)."""
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "half_*.npz")))
 
 
 def load_golden(name):

@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import golden_names, load_golden
+from conftest import golden_names, half_golden_names, load_golden
 from oracle import render_oracle as orc
 from oracle_utils import c_backward, c_forward, c_transform
 
@@ -129,3 +129,19 @@ def test_views_are_independent_and_w128_is_row_blocks():
     for v in (0, 3):
         one = orc.forward_dense(src, tgt, 36, 128, [six[v]])
         assert torch.equal(full[v], one[0])
+
+
+@pytest.mark.parametrize("name", half_golden_names())
+def test_half_mode_oracle_matches_reference_under_autocast(name):
+    """the explicit-rounding restatement of the fp16 (autocast) input mode reproduces the fixtures that
+    oracle/make_golden.py froze from the reference executed under torch.autocast("cpu", dtype=float16)."""
+    g = load_golden(name)
+    r = orc.forward_instrumented(torch.from_numpy(g["src"]), torch.from_numpy(g["tgt"]), float(g["rho"]), int(g["w"]),
+                                 torch.from_numpy(g["views"]), half=True)
+    assert np.array_equal(r["imgs"].numpy(), g["imgs"]) and np.array_equal(r["idx"].numpy(), g["idx"])
+    assert np.array_equal(r["zrange"].numpy(), g["zrange"])
+    # every rotated coordinate and depth weight is an fp16 value
+    x = orc.rotate_half(torch.from_numpy(g["views"][0]), torch.from_numpy(np.concatenate([g["src"], g["tgt"]], 0)))
+    pv, _, _ = orc.depth_weights_half(x)
+    assert torch.equal(x, x.half().float()) and torch.equal(pv, pv.half().float())
+    assert pv.min() == 0 and pv.max() == 1
