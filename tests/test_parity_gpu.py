@@ -251,8 +251,10 @@ def test_point_sharded_merge_equals_unsharded():
     assert torch.equal(i2, win.long())
 
 
-def test_host_pipeline_equals_render_batch():
-    """scream_b200.pipeline.StepPipeline (chunks over CUDA streams, pinned host buffers) == one render_batch call."""
+@pytest.mark.parametrize("dual", [False, True])
+def test_host_pipeline_equals_render_batch(dual):
+    """scream_b200.pipeline.StepPipeline (chunks over CUDA streams, pinned host buffers) == one render_batch call;
+    dual=True: the fake and the real render of every chunk in one launch (SCREAM_F_DUAL)."""
     from scream_b200.pipeline import StepPipeline
     sizes = [(700, 650), (512, 300), (40, 900), (1000, 1000), (333, 77)]
     V, w, rho = 6, 64, 24
@@ -265,7 +267,7 @@ def test_host_pipeline_equals_render_batch():
     h_grad = torch.from_numpy(np.random.default_rng(3).standard_normal((len(sizes), V, 2, w, w)).astype(np.float32)).pin_memory()
     o_fake, o_real = torch.empty_like(h_grad).pin_memory(), torch.empty_like(h_grad).pin_memory()
     o_g = torch.empty_like(h_xyz).pin_memory()
-    pipe = StepPipeline(sizes, views, rho, w, DEV, chunk_pairs=2, n_streams=3)
+    pipe = StepPipeline(sizes, views, rho, w, DEV, chunk_pairs=2, n_streams=3, dual=dual)
     pipe.run(h_xyz, h_pose, h_grad, o_fake, o_real, o_g)
     pipe.synchronize()
     x = h_xyz.to(DEV).requires_grad_(True)
