@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define SCREAM_ABI_VERSION 6
+#define SCREAM_ABI_VERSION 7
 
 /* error codes */
 #define SCREAM_OK            0
@@ -128,6 +128,22 @@ int scream_half_rotate(const float *xyz, const int64_t *offs, int64_t total_pts,
  * as autograd does for .half()).  grad_xr in xr's layout = scream_render_backward's grad_xyz of the B*V-item call. */
 int scream_half_rotate_backward(const float *grad_xr, const int64_t *offs, int64_t total_pts, int64_t max_item_pts,
                                 const float *views, int B, int V, float *grad_xyz, scream_stream_t stream);
+
+/* Nearest target of every (predicted) source point: replaces square_distance(src_ / s, tgt / s)[0].min(dim=1),
+ * pointnet.py:71 + utils.py:72-78 (the reference materialises the n x m matrix).  src [n,3], tgt [m,3] device fp32,
+ * s the scale both clouds are divided by; dist [n] fp32 and ind [n] int64 (either may be NULL), bit-identical to the
+ * reference (first index on ties).  ws: n * 8 bytes. */
+int scream_nearest_target(const float *src, int64_t n, const float *tgt, int64_t m, float s,
+                          float *dist, int64_t *ind, void *ws, size_t ws_bytes, scream_stream_t stream);
+
+/* Weighted Kabsch fit: replaces rigid_transform_3d, utils.py:138-178, including its CPU SVD (utils.py:169) -- no host
+ * round trip.  A [bs,k,3]; correspondence i of item b pairs A[b,i] with B[b, b_index ? b_index[b,i] : i], B [bs,b_rows,3];
+ * weights [bs,k] or NULL (ones); weights below weight_threshold count 0 (utils.py:151); valid_dist [bs,k] or NULL:
+ * correspondences with !(valid_dist < valid_thr) count 0 (the boolean mask of pointnet.py:72-74 as a weight, which
+ * spares the mask's device->host sync).  T [bs,4,4] row-major homogeneous transforms.  ws: bs * 128 bytes. */
+int scream_rigid_transform(const float *A, const float *B, const int64_t *b_index, const float *weights,
+                           const float *valid_dist, float valid_thr, float weight_threshold,
+                           int bs, int64_t k, int64_t b_rows, float *T, void *ws, size_t ws_bytes, scream_stream_t stream);
 
 /* Transform stage only (testing / parity of the "index path"): rotated coordinates [B? no: total_pts
  * per view] rotated [V,total_pts,3], pv [V,total_pts] (render.py:31), zrange [B,V,2].  Any output may

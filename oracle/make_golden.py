@@ -153,8 +153,44 @@ def freeze_colorize():
     print(f"wrote colorize_strip: imgs {imgs.shape} -> strip {want.shape}, restatement == reference")
 
 
+def freeze_registration():
+    """tests/golden/registration_*.npz: the reference's square_distance / rigid_transform_3d executed verbatim
+    on the call pattern of pointnet.py:71-74."""
+    from oracle import registration_oracle as reg
+    ns = {"torch": torch, "np": np}
+    for fn in ("integrate_trans", "square_distance", "rigid_transform_3d"):
+        reference_function("/root/reference/utils.py", fn, ns)
+    ref_sq, ref_fit = ns["square_distance"], ns["rigid_transform_3d"]
+    cases = [("registration_ball", synth.unit_ball(1500, 71), synth.random_pose(72), 0.02, 1.0, 0.075, 1300),
+             ("registration_kitti", synth.kitti_slab(2000, 73), synth.random_pose(74), 0.05, 1.7, 0.9, 1800)]
+    for name, src, pose, noise, s, thr, m in cases:
+        rng = np.random.default_rng(len(name))
+        moved = (src @ pose[:, :3].T + pose[:, 3]).astype(np.float32)
+        tgt = (moved[rng.permutation(len(src))[:m]] + rng.normal(0, 0.003, (m, 3))).astype(np.float32)
+        pred = (moved + rng.normal(0, noise, moved.shape)).astype(np.float32)       # the generator's src_pred
+        pred[:7] += np.float32(3.0)                                                   # a few predictions far from every target
+        src_t, pred_t, tgt_t = torch.from_numpy(src), torch.from_numpy(pred), torch.from_numpy(tgt)
+        dist, ind = ref_sq(pred_t[None] / s, tgt_t[None] / s)[0].min(dim=1)           # pointnet.py:71, reference code
+        valid = dist < thr
+        T = ref_fit(src_t[None][:, valid], tgt_t[None][:, ind[valid]])[0]            # pointnet.py:72-74, reference code
+        T2, d2, i2 = reg.estimate_transform(src_t, pred_t, tgt_t, s, thr)
+        assert torch.equal(dist, d2) and torch.equal(ind, i2) and torch.equal(T, T2), f"{name}: restatement differs"
+        w = torch.from_numpy(rng.uniform(0, 1, (2, 400)).astype(np.float32))
+        A2 = torch.from_numpy(np.stack([src[:400], src[400:800]]))
+        B2 = torch.from_numpy(np.stack([moved[:400], -moved[400:800]]))             # item 1: a reflection (det < 0 branch)
+        Tw = ref_fit(A2, B2, w.clone(), 0.3)
+        assert torch.equal(Tw, reg.rigid_transform_3d(A2, B2, w.clone(), 0.3)), f"{name}: weighted restatement differs"
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), src=src, pred=pred, tgt=tgt, s=np.float64(s), thr=np.float64(thr),
+                            dist=dist.numpy(), ind=ind.numpy(), T=T.numpy(), pose=pose,
+                            wA=A2.numpy(), wB=B2.numpy(), w=w.numpy(), w_thr=np.float64(0.3), Tw=Tw.numpy())
+        print(f"wrote {name}: n={len(src)} m={m} valid={int(valid.sum())} det(Tw[1])={np.linalg.det(Tw[1, :3, :3].numpy()):+.3f}")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--only-registration" in sys.argv:
+        freeze_registration()
+        return
     if "--only-colorize" in sys.argv:
         freeze_colorize()
         return
@@ -181,6 +217,7 @@ def main():
     freeze("sparse_far_pixels", synth.unit_ball(40, 51) * np.float32(0.2), synth.unit_ball(16, 52), 48, 64, six)
     freeze_colorize()
     freeze_half_all()
+    freeze_registration()
 
 
 if __name__ == "__main__":

@@ -11,7 +11,7 @@ import threading
 
 from .csrc import build as _build
 
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 F_RAW = 1
 F_DENSE = 2
@@ -37,6 +37,9 @@ _SIGNATURES = {
                                           _P, _P, _P, _P, C.c_size_t, _P]),
     "scream_half_rotate": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, C.c_int, C.c_int, _P, _P, _P]),
     "scream_half_rotate_backward": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, C.c_int, C.c_int, _P, _P]),
+    "scream_nearest_target": (C.c_int, [_P, C.c_int64, _P, C.c_int64, C.c_float, _P, _P, _P, C.c_size_t, _P]),
+    "scream_rigid_transform": (C.c_int, [_P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_int, C.c_int64, C.c_int64,
+                                         _P, _P, C.c_size_t, _P]),
     "scream_depth_to_rgb8": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
     "scream_render_forward_host": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_double, C.c_uint,
                                              _P, _P, _P, C.c_int]),

@@ -9,6 +9,7 @@
 #include "backward.cuh"
 #include "colorize.cuh"
 #include "half_rotate.cuh"
+#include "registration.cuh"
 
 #include <algorithm>
 #include <cstdarg>
@@ -286,6 +287,42 @@ int scream_half_rotate_backward(const float* grad_xr, const int64_t* offs, int64
     dim3 grid;
     if (int rc = half_rotate_grid(total_pts, max_item_pts, B, &grid)) return rc;
     half_rotate_backward_kernel<<<grid, HR_THREADS, 0, (cudaStream_t)stream>>>(grad_xr, offs, views, V, grad_xyz);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_nearest_target(const float* src, int64_t n, const float* tgt, int64_t m, float s,
+                          float* dist, int64_t* ind, void* ws, size_t ws_bytes, scream_stream_t stream)
+{
+    if (!src || !tgt || !ws) return fail(SCREAM_E_ARG, "src/tgt/ws must not be NULL");
+    if (n <= 0 || m <= 0) return fail(SCREAM_E_ARG, "min(): cannot reduce over an empty cloud (n=%lld m=%lld)", (long long)n, (long long)m);
+    if (m > 0xFFFFFFFFLL) return fail(SCREAM_E_UNSUPPORTED, "more than 2^32 targets");
+    if (ws_bytes < (size_t)n * 8) return fail(SCREAM_E_WORKSPACE, "workspace needs %zu bytes, got %zu", (size_t)n * 8, ws_bytes);
+    const int64_t gx = (n + NN_THREADS - 1) / NN_THREADS, gy = (m + NN_TILE - 1) / NN_TILE;
+    if (gx > 2147483647LL || gy > 65535) return fail(SCREAM_E_UNSUPPORTED, "clouds too large for the search grid");
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned long long* best = reinterpret_cast<unsigned long long*>(ws);
+    nn_init_kernel<<<(unsigned)gx, NN_THREADS, 0, st>>>(best, n);
+    nn_search_kernel<<<dim3((unsigned)gx, (unsigned)gy), NN_THREADS, 0, st>>>(src, n, tgt, m, s, best);
+    nn_finish_kernel<<<(unsigned)gx, NN_THREADS, 0, st>>>(best, n, dist, ind);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_rigid_transform(const float* A, const float* Bp, const int64_t* b_index, const float* weights,
+                           const float* valid_dist, float valid_thr, float weight_threshold,
+                           int bs, int64_t k, int64_t b_rows, float* T, void* ws, size_t ws_bytes, scream_stream_t stream)
+{
+    if (!A || !Bp || !T || !ws) return fail(SCREAM_E_ARG, "A/B/T/ws must not be NULL");
+    if (bs <= 0 || bs > 65535 || k <= 0 || b_rows <= 0) return fail(SCREAM_E_ARG, "bad sizes (bs=%d k=%lld)", bs, (long long)k);
+    if (ws_bytes < (size_t)bs * 16 * sizeof(double)) return fail(SCREAM_E_WORKSPACE, "workspace needs %zu bytes, got %zu", (size_t)bs * 16 * sizeof(double), ws_bytes);
+    cudaStream_t st = (cudaStream_t)stream;
+    double* acc = reinterpret_cast<double*>(ws);
+    CUDA_TRY(cudaMemsetAsync(acc, 0, (size_t)bs * 16 * sizeof(double), st));
+    const int64_t gx = std::min<int64_t>((k + KB_THREADS - 1) / KB_THREADS, 592);
+    kabsch_accum_kernel<<<dim3((unsigned)gx, (unsigned)bs), KB_THREADS, 0, st>>>(A, Bp, b_index, weights, valid_dist, valid_thr,
+                                                                                  weight_threshold, k, b_rows, acc);
+    kabsch_solve_kernel<<<(bs + 63) / 64, 64, 0, st>>>(acc, bs, T);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

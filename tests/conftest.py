@@ -21,7 +21,7 @@ def pytest_configure(config):
 def golden_names():
     """Renderer fixtures of the fp32 path (the colouriser's fixture and the fp16-mode fixtures have their own tests)."""
     names = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-    return [n for n in names if not n.startswith(("colorize", "half_"))]
+    return [n for n in names if not n.startswith(("colorize", "half_", "registration_"))]
 
 
 def half_golden_names():
