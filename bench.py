@@ -275,7 +275,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     xyz, offs, pose, grad = [t.to(dev) for t in (h_xyz, h_offs, h_pose, h_grad)]
     max_item = 2 * N_PTS
     dense = args.dense
-    dual = args.dual and not dense
+    dual = args.dual and not dense                       # device-resident leg: one dual launch instead of two forwards
+    e2e_dual = not dense and not args.no_e2e_dual        # host-buffer leg (StepPipeline): dual launches per chunk by default
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
     def step_device(rec=None):
@@ -310,7 +311,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
 
     from scream_b200.pipeline import StepPipeline
     pipe = StepPipeline([(N_PTS, N_PTS)] * B, views, RHO, W_IMG, dev, chunk_pairs=args.chunk, n_streams=args.streams, dense=dense,
-                        dual=dual)
+                        dual=e2e_dual)
 
     def step_e2e():
         """Same step through the public host-buffer API (scream_b200.pipeline.StepPipeline): every step copies its
@@ -362,8 +363,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
-        t = json.load(open(tpath)).get("forward_culled_kernel", {})
-        if t.get("pairs_per_gpu") == B and t.get("cloud") == CLOUD and not dense and not dual:
+        t = json.load(open(tpath)).get("forward_culled_kernel_dual" if dual else "forward_culled_kernel", {})
+        if t.get("pairs_per_gpu") == B and t.get("cloud") == CLOUD and not dense:
             traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     ach = (b_fake + b_real) / ((t_fake + t_real) / 1e3) / 1e9
     streaming = None
@@ -381,7 +382,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": int(h_xyz.numel() * 4 + h_pose.numel() * 4 + h_grad.numel() * 4),
                     "d2h_bytes_per_step": int(h_fake.numel() * 4 * 2 + h_gxyz.numel() * 4),
-                    "api": f"scream_b200.pipeline.StepPipeline(chunk_pairs={args.chunk}, n_streams={args.streams}{", dual=True" if dual else ""})"},
+                    "api": f"scream_b200.pipeline.StepPipeline(chunk_pairs={args.chunk}, n_streams={args.streams}{", dual=True" if e2e_dual else ""})"},
             "gpu_launches": args.steps * (4 if dual else 7),
             "kernel": "dense" if dense else ("culled, dual launch (SCREAM_F_DUAL)" if dual else "culled"),
             "roofline": {"bound": "hbm", "kernel": "forward_culled_kernel (timed as one forward call: z-range kernels + it; fake and real calls averaged)",
@@ -417,7 +418,8 @@ def main():
     ap.add_argument("--batch", type=int, default=512, help="pairs per GPU per step")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dense", action="store_true", help="force the dense exact kernel")
-    ap.add_argument("--dual", action="store_true", help="fake + real render in one launch (SCREAM_F_DUAL, SURVEY 8 f1)")
+    ap.add_argument("--dual", action="store_true", help="device-resident leg: fake + real render in one launch (SCREAM_F_DUAL, SURVEY 8 f1)")
+    ap.add_argument("--no-e2e-dual", action="store_true", help="host-buffer leg: two forward calls per chunk instead of one dual launch")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-stream-leg", action="store_true", help="skip the cfg5 streaming-regime leg (one GPU: the whole cloud; N > 1: its points sharded over the ranks)")
     ap.add_argument("--chunk", type=int, default=37, help="pairs per chunk of the host-buffer pipeline (e2e leg)")

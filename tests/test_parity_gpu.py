@@ -288,7 +288,7 @@ GIANT_CASES = [
     (120000, 90000, 24, "ballx", 2),            # points outside [-1,1]^2 (clamped cells must not seed)
     (150000, 110000, 24, "far", 3),             # depth offset of 40 units, in-plane rotations: voxel boxes at large coordinates
     (130000, 130000, 24, "plane", 2),           # z constant: a voxel grid of zero extent along one axis
-    (60000, 50000, 24, "ball", 66),             # more than 64 views: two mask words per voxel, the second group partial
+    (85000, 70000, 24, "ball", 66),             # more than 64 views: two mask words per voxel, the second group partial
 ]
 
 
@@ -418,7 +418,7 @@ def test_dual_render_equals_two_calls():
 
 
 def test_dual_render_refuses_giant_clouds():
-    n = 60000
+    n = 80000
     xyz = torch.from_numpy(synth.unit_ball(2 * n, 5)).to(DEV)
     offs = make_offsets([(n, n)]).to(DEV)
     views = torch.eye(3, device=DEV)[None].contiguous()
