@@ -14,7 +14,17 @@ bad = 0
 for it in range(int(os.environ.get("ITERS", "300"))):
     if it % 3 == 0:
         imgs = r(s, t); imgs.backward(torch.randn_like(imgs)); del imgs
-        junk = torch.full((int(np.random.randint(1, 2000000)),), float("nan"), device=DEV); del junk
+        junk = []
+        for k in range(24):                      # freed blocks of many size classes, filled with NaN / ones / random bits / zeros
+            nby = int(2 ** np.random.uniform(9, 24))
+            j = torch.empty((nby // 4,), dtype=torch.int32, device=DEV)
+            mode = (it // 3 + k) % 4
+            if mode == 0: j.fill_(0x7fc00000)
+            elif mode == 1: j.fill_(-1)
+            elif mode == 2: j.random_(-2**31, 2**31 - 1)
+            else: j.zero_()
+            junk.append(j)
+        del junk
     with torch.autocast("cuda", dtype=torch.float16), torch.no_grad():
         h = r(s.detach(), t.detach())
     e = (h.cpu() - want["imgs"]).abs()
