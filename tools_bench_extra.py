@@ -53,6 +53,50 @@ def kitti_leg(B=64, n=30000):
     return out
 
 
+def opengg_leg(B=64, side=128, coarse=32):
+    """BASELINE config 4: OpenGG DSM-DEM patches (regular grids: dense per-pixel contention, exact ties), one orthographic
+    view, at growing image sides; rho grows with w so that a splat stays a few pixels wide (pointnet.py:35: rho 36 at w 128)."""
+    parts, sizes = [], []
+    for i in range(B):
+        dsm, dem = synth.opengg_patch(side, 100 + i, coarse)
+        parts += [dsm, dem]; sizes.append((len(dsm), len(dem)))
+    xyz = torch.from_numpy(np.concatenate(parts, 0)).to(DEV)
+    offs = make_offsets(sizes).to(DEV)
+    views = torch.eye(3, device=DEV)[None].contiguous()
+    out = {"workload": f"cfg4: {B} OpenGG-shaped patches, DSM {side}x{side} + DEM {coarse}x{coarse} grid points, 1 orthographic view, "
+                       "forward(+winner) + backward"}
+    for w, rho in ((64, 24), (128, 36), (256, 72), (512, 144)):
+        grad = torch.randn((B, 1, 2, w, w), device=DEV)
+
+        def step():
+            x = xyz.detach().requires_grad_(True)
+            imgs, _, _ = render_batch(x, offs, views, rho, w, need_winner=True, max_item_pts=side * side + coarse * coarse)
+            imgs.backward(grad)
+        ms = timed(step)
+        out[f"w{w}_rho{rho}"] = {"ms_per_step": ms, "images_per_sec": 2 * B / (ms / 1e3), "gpixels_per_sec": 2 * B * w * w / (ms / 1e3) / 1e9}
+    return out
+
+
+def single_pair_leg(n=10000):
+    """BASELINE config 1 through the drop-in module: ONE 3DMatch-sized pair per call (the reference asserts batch 1,
+    pointnet.py:39-40) -- per-call latency, forward alone and forward + backward, single view and the six views."""
+    from scream_b200.render import RegistrationRender
+    src = torch.from_numpy(synth.unit_ball(n, 1)).to(DEV)
+    tgt = torch.from_numpy(synth.unit_ball(n, 2)).to(DEV)
+    out = {"workload": f"cfg1: one pair, n = m = {n}, w 64, rho 24, RegistrationRender.forward per call"}
+    for view in ("single", "muti"):
+        r = RegistrationRender(24, 64, view=view, device=DEV)
+        grad = torch.randn((len(r.eulers), 2, 64, 64), device=DEV)
+        with torch.no_grad():
+            f = timed(lambda: r(src, tgt), steps=50)
+
+        def step():
+            s = src.detach().requires_grad_(True)
+            r(s, tgt).backward(grad)
+        out[view] = {"views": len(r.eulers), "forward_ms": f, "forward_backward_ms": timed(step, steps=50)}
+    return out
+
+
 def registration_leg(n):
     rng = np.random.default_rng(n)
     src = synth.unit_ball(n, 1)
@@ -77,5 +121,7 @@ def registration_leg(n):
 
 if __name__ == "__main__":
     print(json.dumps(kitti_leg()), flush=True)
+    print(json.dumps(opengg_leg()), flush=True)
+    print(json.dumps(single_pair_leg()), flush=True)
     for n in (10000, 30000):
         print(json.dumps(registration_leg(n)), flush=True)
