@@ -5,7 +5,7 @@ renders it twice per iteration (`train_3d_match.py:186-201`: "fake" with gradien
 pose).  `StepPipeline` does the same work for a whole batch of pairs, cut into chunks that travel through
 `n_streams` CUDA streams, so the host->device copy of chunk i+1, the kernels of chunk i and the
 device->host copy of chunk i-1 overlap (two copy engines + compute).  It calls the same C-ABI entry
-points as `render_batch` (through the torch custom ops) -- there is no other compute path.
+points as `render_batch` (the same host functions the torch custom ops wrap) -- there is no other compute path.
 
     pipe = StepPipeline(sizes, views, rho, w, device)          # sizes: [(n_src, n_tgt)] * B
     pipe.run(h_xyz, h_pose, h_grad, out_fake, out_real, out_gxyz)   # all pinned host tensors
@@ -19,7 +19,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .render import make_offsets, render_pair
+from .render import _bwd_impl, _fwd_impl, make_offsets, render_pair
 
 
 class StepPipeline:
@@ -52,7 +52,6 @@ class StepPipeline:
         """Enqueue one step.  h_* are pinned host tensors: xyz [total,3], pose [B,3,4] (GT [R|t] of the
         "real" render), grad [B,V,2,w,w] (upstream gradient of the fake images).  Results land in the
         pinned out_* tensors (fake/real images [B,V,2,w,w], grad_xyz [total,3]) after synchronize()."""
-        ops = torch.ops.scream
         cur = torch.cuda.current_stream(self.dev)
         for i, (b0, b1, p0, p1, offs, max_item) in enumerate(self.chunks):
             st = self.streams[i % len(self.streams)]
@@ -67,14 +66,14 @@ class StepPipeline:
                                                           max_item_pts=max_item)
                     out_fake[b0:b1].copy_(fake, non_blocking=True)
                     out_real[b0:b1].copy_(real, non_blocking=True)
-                    gx = ops.render_bwd(x, offs, None, self.views, self.w, self.rho, self.flags, g, win[0], zr[0], max_item)
+                    gx = _bwd_impl(x, offs, None, self.views, self.w, self.rho, self.flags, g, win[0], zr[0], max_item)
                     out_gxyz[p0:p1].copy_(gx, non_blocking=True)
                     continue
-                fake, win, zr = ops.render_fwd(x, offs, None, self.views, self.w, self.rho, self.flags, True, max_item, None)
+                fake, win, zr = _fwd_impl(x, offs, None, self.views, self.w, self.rho, self.flags, True, max_item, None)
                 out_fake[b0:b1].copy_(fake, non_blocking=True)
-                gx = ops.render_bwd(x, offs, None, self.views, self.w, self.rho, self.flags, g, win, zr, max_item)
+                gx = _bwd_impl(x, offs, None, self.views, self.w, self.rho, self.flags, g, win, zr, max_item)
                 out_gxyz[p0:p1].copy_(gx, non_blocking=True)
-                real, _, _ = ops.render_fwd(x, offs, p, self.views, self.w, self.rho, self.flags, False, max_item, None)
+                real, _, _ = _fwd_impl(x, offs, p, self.views, self.w, self.rho, self.flags, False, max_item, None)
                 out_real[b0:b1].copy_(real, non_blocking=True)
 
     def join(self) -> None:

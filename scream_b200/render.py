@@ -39,11 +39,7 @@ def _stream_ptr(dev: torch.device) -> int:
 # ----------------------------------------------------------------------------------------------
 # custom ops
 # ----------------------------------------------------------------------------------------------
-@torch.library.custom_op("scream::render_fwd", mutates_args=())
-def render_fwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tensor], views: torch.Tensor,
-               w: int, rho: float, flags: int, want_winner: bool, max_item_pts: int,
-               zrange_in: Optional[torch.Tensor] = None
-               ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+def _fwd_impl(xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts, zrange_in=None):
     _require_cuda(xyz, offs, pose, views, zrange_in)
     lib = _lib.load()
     assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.dim() == 2 and xyz.shape[1] == 3
@@ -72,6 +68,14 @@ def render_fwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tenso
     return imgs, winner, zrange
 
 
+@torch.library.custom_op("scream::render_fwd", mutates_args=())
+def render_fwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tensor], views: torch.Tensor,
+               w: int, rho: float, flags: int, want_winner: bool, max_item_pts: int,
+               zrange_in: Optional[torch.Tensor] = None
+               ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    return _fwd_impl(xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts, zrange_in)
+
+
 @render_fwd.register_fake
 def _(xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts, zrange_in=None):
     B, V = (offs.numel() - 1) // 2, views.shape[0]
@@ -80,10 +84,7 @@ def _(xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts, zrange_i
             xyz.new_empty((B, V, 2)))
 
 
-@torch.library.custom_op("scream::render_bwd", mutates_args=())
-def render_bwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tensor], views: torch.Tensor,
-               w: int, rho: float, flags: int, grad_imgs: torch.Tensor, winner: torch.Tensor,
-               zrange: torch.Tensor, max_item_pts: int) -> torch.Tensor:
+def _bwd_impl(xyz, offs, pose, views, w, rho, flags, grad_imgs, winner, zrange, max_item_pts):
     _require_cuda(xyz, offs, pose, views, grad_imgs, winner, zrange)
     lib = _lib.load()
     B, V, total = (offs.numel() - 1) // 2, views.shape[0], xyz.shape[0]
@@ -97,6 +98,13 @@ def render_bwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tenso
                                         _ptr(zrange), _ptr(grad_xyz), None, 0, _stream_ptr(dev))
     _lib.check(rc, "scream_render_backward")
     return grad_xyz
+
+
+@torch.library.custom_op("scream::render_bwd", mutates_args=())
+def render_bwd(xyz: torch.Tensor, offs: torch.Tensor, pose: Optional[torch.Tensor], views: torch.Tensor,
+               w: int, rho: float, flags: int, grad_imgs: torch.Tensor, winner: torch.Tensor,
+               zrange: torch.Tensor, max_item_pts: int) -> torch.Tensor:
+    return _bwd_impl(xyz, offs, pose, views, w, rho, flags, grad_imgs, winner, zrange, max_item_pts)
 
 
 @render_bwd.register_fake
@@ -127,6 +135,27 @@ def _backward(ctx, g_imgs, g_winner, g_zrange):
 
 
 render_fwd.register_autograd(_backward, setup_context=_setup_ctx)
+
+
+class _EagerRender(torch.autograd.Function):
+    """The same two C-ABI calls as scream::render_fwd / scream::render_bwd without the custom-op dispatcher: in eager mode
+    one pair per call (the reference's batch 1, pointnet.py:39-40) is bound by host overhead, not by the kernels.
+    render_batch uses this unless torch.compile is tracing (then the registered ops, which have fake kernels)."""
+
+    @staticmethod
+    def forward(ctx, xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts, zrange_in):
+        imgs, winner, zrange = _fwd_impl(xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts, zrange_in)
+        ctx.save_for_backward(xyz, offs, views, winner, zrange, *(() if pose is None else (pose,)))
+        ctx.cfg = (w, rho, flags, max_item_pts)
+        ctx.mark_non_differentiable(winner, zrange)
+        return imgs, winner, zrange
+
+    @staticmethod
+    def backward(ctx, g_imgs, g_winner, g_zrange):
+        xyz, offs, views, winner, zrange, *rest = ctx.saved_tensors
+        w, rho, flags, max_item_pts = ctx.cfg
+        g = _bwd_impl(xyz, offs, rest[0] if rest else None, views, w, rho, flags, g_imgs, winner, zrange, max_item_pts)
+        return g, None, None, None, None, None, None, None, None, None
 
 
 # ----------------------------------------------------------------------------------------------
@@ -165,8 +194,11 @@ def render_batch(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho
         return _HalfRender.apply(xyz, offs, views, int(w), float(rho), int(flags), bool(need_winner), int(max_item_pts))
     flags = (_lib.F_RAW if raw else 0) | (_lib.F_DENSE if dense else 0) | (_lib.F_NOSTREAM if no_stream else 0) \
         | (_lib.F_THINSEED if thin_seed else 0)
-    return torch.ops.scream.render_fwd(xyz, offs, pose, views, int(w), float(rho), int(flags),
-                                       bool(need_winner), int(max_item_pts), zrange_in)
+    if torch.compiler.is_compiling():
+        return torch.ops.scream.render_fwd(xyz, offs, pose, views, int(w), float(rho), int(flags),
+                                           bool(need_winner), int(max_item_pts), zrange_in)
+    return _EagerRender.apply(xyz, offs, pose, views, int(w), float(rho), int(flags), bool(need_winner), int(max_item_pts),
+                              zrange_in)
 
 
 class _DualRender(torch.autograd.Function):
@@ -207,7 +239,7 @@ class _DualRender(torch.autograd.Function):
         w, rho, flags, max_item_pts, want_winner = ctx.cfg
         if not want_winner:
             raise RuntimeError("render_pair was run without a winner map (need_winner=False)")
-        g = torch.ops.scream.render_bwd(xyz, offs, None, views, w, rho, flags, g_fake, winner[0], zrange[0], max_item_pts)
+        g = _bwd_impl(xyz, offs, None, views, w, rho, flags, g_fake, winner[0], zrange[0], max_item_pts)
         return g, None, None, None, None, None, None, None, None
 
 
@@ -249,8 +281,7 @@ class _HalfRender(torch.autograd.Function):
             _lib.check(rc, "scream_half_rotate")
             eye = torch.eye(3, dtype=torch.float32, device=dev).unsqueeze(0).contiguous()
         flags |= _lib.F_HALF
-        imgs, winner, zrange = torch.ops.scream.render_fwd(xr, offs_bv, None, eye, w, rho, flags, want_winner,
-                                                           max_item_pts, None)
+        imgs, winner, zrange = _fwd_impl(xr, offs_bv, None, eye, w, rho, flags, want_winner, max_item_pts, None)
         ctx.save_for_backward(xr, offs_bv, eye, offs, views, winner, zrange)
         ctx.cfg = (w, rho, flags, max_item_pts, want_winner, B, V, total)
         winner = winner.view(B, V, 2, w, w) if want_winner else winner
@@ -263,8 +294,8 @@ class _HalfRender(torch.autograd.Function):
         w, rho, flags, max_item_pts, want_winner, B, V, total = ctx.cfg
         if not want_winner:
             raise RuntimeError("the fp16-mode render was run without a winner map (need_winner=False)")
-        g_xr = torch.ops.scream.render_bwd(xr, offs_bv, None, eye, w, rho, flags,
-                                           g_imgs.contiguous().view(B * V, 1, 2, w, w), winner, zrange, max_item_pts)
+        g_xr = _bwd_impl(xr, offs_bv, None, eye, w, rho, flags, g_imgs.contiguous().view(B * V, 1, 2, w, w), winner, zrange,
+                         max_item_pts)
         dev = xr.device
         with torch.cuda.device(dev):
             g = torch.empty((total, 3), dtype=torch.float32, device=dev)
