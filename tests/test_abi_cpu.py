@@ -67,3 +67,19 @@ def test_view_matrices_are_the_reference_conversion():
 
 def test_make_offsets():
     assert make_offsets([(3, 4), (5, 6)]).tolist() == [0, 3, 7, 12, 18]
+
+
+def test_custom_ops_have_fake_kernels():
+    """scream::render_fwd / render_bwd stay registered for torch.compile (eager calls go through a plain
+    autograd.Function around the same host functions): their fake kernels give the shapes and dtypes of the real ones."""
+    import torch
+    import scream_b200.render  # noqa: F401  (registers the ops)
+    xyz = torch.empty(100, 3, device="meta")
+    offs = torch.empty(5, dtype=torch.int64, device="meta")
+    views = torch.empty(6, 3, 3, device="meta")
+    imgs, win, zr = torch.ops.scream.render_fwd(xyz, offs, None, views, 64, 24.0, 0, True, 0, None)
+    assert imgs.shape == (2, 6, 2, 64, 64) and win.shape == imgs.shape and win.dtype == torch.int32 and zr.shape == (2, 6, 2)
+    _, no_win, _ = torch.ops.scream.render_fwd(xyz, offs, None, views, 64, 24.0, 0, False, 0, None)
+    assert no_win.numel() == 0
+    g = torch.ops.scream.render_bwd(xyz, offs, None, views, 64, 24.0, 0, imgs, win, zr, 0)
+    assert g.shape == xyz.shape

@@ -425,3 +425,24 @@ def test_dual_render_refuses_giant_clouds():
     pose = torch.from_numpy(synth.random_pose(1))[None].contiguous().to(DEV)
     with pytest.raises(_lib.ScreamError):
         render_pair(xyz, offs, views, 24, 64, pose)
+
+
+def test_registered_custom_ops_equal_eager_path():
+    """torch.ops.scream.render_fwd / render_bwd (the torch.compile-able ops, with their registered autograd) give the bits of
+    render_batch's eager autograd.Function -- both wrap the same two C-ABI calls."""
+    sizes = [(800, 700), (50, 1200)]
+    parts = []
+    for i, (n, m) in enumerate(sizes):
+        parts += [synth.unit_ball(n, 700 + i), synth.room_shell(m, 710 + i)]
+    views = view_matrices(RegistrationRender(24, 64, device="cpu").eulers).to(DEV)
+    offs = make_offsets(sizes).to(DEV)
+    pose = torch.from_numpy(np.stack([synth.random_pose(720 + i) for i in range(2)])).contiguous().to(DEV)
+    grad = torch.from_numpy(np.random.default_rng(11).standard_normal((2, 6, 2, 64, 64)).astype(np.float32)).to(DEV)
+    for p in (None, pose):
+        x1 = torch.from_numpy(np.concatenate(parts, 0)).to(DEV).requires_grad_(True)
+        x2 = x1.detach().clone().requires_grad_(True)
+        a, wa, za = render_batch(x1, offs, views, 24, 64, pose=p, need_winner=True)
+        b, wb, zb = torch.ops.scream.render_fwd(x2, offs, p, views, 64, 24.0, 0, True, 0, None)
+        assert torch.equal(a, b) and torch.equal(wa, wb) and torch.equal(za, zb)
+        a.backward(grad); b.backward(grad)
+        assert np.abs((x1.grad - x2.grad).cpu().numpy()).max() <= 1e-5 * float(x1.grad.abs().max())      # atomics order
