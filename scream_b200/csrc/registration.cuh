@@ -15,14 +15,17 @@
 namespace scream {
 
 constexpr int NN_THREADS = 256;
-constexpr int NN_TILE = 2048;          // targets per CTA (32 KB of float4 in shared memory)
+constexpr int NN_TILE = 1024;          // targets per CTA (16 KB of float4 in shared memory)
+constexpr int NN_PPT = 2;              // source points per thread
 
 __global__ void nn_init_kernel(unsigned long long* __restrict__ best, int64_t n) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) best[i] = ~0ull;
 }
 
-// grid (ceil(n / 256), ceil(m / NN_TILE)); one source point per thread, the CTA's tile of targets broadcast from shared memory
+// grid (ceil(n / (256 * NN_PPT)), ceil(m / NN_TILE)); NN_PPT source points per thread (one shared-memory read serves NN_PPT
+// pairs), the CTA's tile of targets broadcast from shared memory.  Per pair: 1/NN_PPT LDS.128 + FMUL + 3 FFMA + FADD + FSETP +
+// 2 SEL.  fl(fl(-2 * dot) + |a|^2) == fmaf(-2, dot, |a|^2): the product by -2 is exact, so the sum is rounded once either way.
 __global__ void __launch_bounds__(NN_THREADS)
 nn_search_kernel(const float* __restrict__ src, int64_t n, const float* __restrict__ tgt, int64_t m, float s,
                  unsigned long long* __restrict__ best)
@@ -36,23 +39,34 @@ nn_search_kernel(const float* __restrict__ src, int64_t n, const float* __restri
         s_b[j] = make_float4(x, y, z, __fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z)));
     }
     __syncthreads();
-    const int64_t i = (int64_t)blockIdx.x * NN_THREADS + threadIdx.x;
-    if (i >= n) return;
-    const float* p = src + (size_t)i * 3;
-    const float ax = __fdiv_rn(__ldg(p), s), ay = __fdiv_rn(__ldg(p + 1), s), az = __fdiv_rn(__ldg(p + 2), s);
-    const float na = __fadd_rn(__fadd_rn(__fmul_rn(ax, ax), __fmul_rn(ay, ay)), __fmul_rn(az, az));
-    float bd = INFINITY; int bj = -1;
+    float ax[NN_PPT], ay[NN_PPT], az[NN_PPT], na[NN_PPT], bd[NN_PPT];
+    int bj[NN_PPT];
+    int64_t ip[NN_PPT];
+#pragma unroll
+    for (int u = 0; u < NN_PPT; ++u) {
+        ip[u] = ((int64_t)blockIdx.x * NN_PPT + u) * NN_THREADS + threadIdx.x;
+        const float* p = src + (size_t)min(ip[u], n - 1) * 3;             // past the end: the last point again (not stored)
+        ax[u] = __fdiv_rn(__ldg(p), s); ay[u] = __fdiv_rn(__ldg(p + 1), s); az[u] = __fdiv_rn(__ldg(p + 2), s);
+        na[u] = __fadd_rn(__fadd_rn(__fmul_rn(ax[u], ax[u]), __fmul_rn(ay[u], ay[u])), __fmul_rn(az[u], az[u]));
+        bd[u] = INFINITY; bj[u] = -1;
+    }
 #pragma unroll 4
     for (int j = 0; j < cnt; ++j) {
         const float4 b = s_b[j];
-        const float dot = __fmaf_rn(az, b.z, __fmaf_rn(ay, b.y, __fmul_rn(ax, b.x)));
-        const float d = __fadd_rn(__fadd_rn(__fmul_rn(-2.0f, dot), na), b.w);
-        if (d < bd || bj < 0) { if (d == d) { bd = d; bj = j; } }
+#pragma unroll
+        for (int u = 0; u < NN_PPT; ++u) {
+            const float dot = __fmaf_rn(az[u], b.z, __fmaf_rn(ay[u], b.y, __fmul_rn(ax[u], b.x)));
+            const float d = __fadd_rn(__fmaf_rn(-2.0f, dot, na[u]), b.w);
+            if (d < bd[u]) { bd[u] = d; bj[u] = j; }                      // strict: the first index keeps ties; NaN never wins
+        }
     }
-    if (bj >= 0) {
+#pragma unroll
+    for (int u = 0; u < NN_PPT; ++u) {
+        if (ip[u] >= n) continue;
+        // nothing below +inf in this tile (overflowing or NaN coordinates): +inf at the tile's first index, as torch.min would
         // (-0) + (+0) = +0: torch.min sees the two zeros as equal (first index wins), the integer order below does not
-        const unsigned long long key = ((unsigned long long)enc_f32(__fadd_rn(bd, 0.0f)) << 32) | (unsigned)(j0 + bj);
-        atomicMin(best + i, key);
+        const unsigned long long key = ((unsigned long long)enc_f32(__fadd_rn(bd[u], 0.0f)) << 32) | (unsigned)(j0 + max(bj[u], 0));
+        atomicMin(best + ip[u], key);
     }
 }
 
@@ -62,9 +76,8 @@ __global__ void nn_finish_kernel(const unsigned long long* __restrict__ best, in
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const unsigned long long k = best[i];
-    const bool none = k == ~0ull;                 // every distance was NaN
-    if (dist) dist[i] = none ? __int_as_float(0x7fc00000) : dec_f32((unsigned)(k >> 32));
-    if (ind) ind[i] = none ? 0 : (int64_t)(k & 0xFFFFFFFFull);
+    if (dist) dist[i] = dec_f32((unsigned)(k >> 32));
+    if (ind) ind[i] = (int64_t)(k & 0xFFFFFFFFull);
 }
 
 // ---- weighted Kabsch, utils.py:138-178 ---------------------------------------------------------------------------------

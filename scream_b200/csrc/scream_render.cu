@@ -299,11 +299,12 @@ int scream_nearest_target(const float* src, int64_t n, const float* tgt, int64_t
     if (m > 0xFFFFFFFFLL) return fail(SCREAM_E_UNSUPPORTED, "more than 2^32 targets");
     if (ws_bytes < (size_t)n * 8) return fail(SCREAM_E_WORKSPACE, "workspace needs %zu bytes, got %zu", (size_t)n * 8, ws_bytes);
     const int64_t gx = (n + NN_THREADS - 1) / NN_THREADS, gy = (m + NN_TILE - 1) / NN_TILE;
+    const int64_t gs = (n + NN_THREADS * NN_PPT - 1) / (NN_THREADS * NN_PPT);
     if (gx > 2147483647LL || gy > 65535) return fail(SCREAM_E_UNSUPPORTED, "clouds too large for the search grid");
     cudaStream_t st = (cudaStream_t)stream;
     unsigned long long* best = reinterpret_cast<unsigned long long*>(ws);
     nn_init_kernel<<<(unsigned)gx, NN_THREADS, 0, st>>>(best, n);
-    nn_search_kernel<<<dim3((unsigned)gx, (unsigned)gy), NN_THREADS, 0, st>>>(src, n, tgt, m, s, best);
+    nn_search_kernel<<<dim3((unsigned)gs, (unsigned)gy), NN_THREADS, 0, st>>>(src, n, tgt, m, s, best);
     nn_finish_kernel<<<(unsigned)gx, NN_THREADS, 0, st>>>(best, n, dist, ind);
     CUDA_TRY(cudaGetLastError());
     return 0;

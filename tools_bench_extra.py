@@ -120,8 +120,13 @@ def registration_leg(n):
 
 
 if __name__ == "__main__":
-    print(json.dumps(kitti_leg()), flush=True)
-    print(json.dumps(opengg_leg()), flush=True)
-    print(json.dumps(single_pair_leg()), flush=True)
-    for n in (10000, 30000):
-        print(json.dumps(registration_leg(n)), flush=True)
+    only = sys.argv[sys.argv.index("--only") + 1] if "--only" in sys.argv else None      # kitti | opengg | single | reg
+    if only in (None, "kitti"):
+        print(json.dumps(kitti_leg()), flush=True)
+    if only in (None, "opengg"):
+        print(json.dumps(opengg_leg()), flush=True)
+    if only in (None, "single"):
+        print(json.dumps(single_pair_leg()), flush=True)
+    if only in (None, "reg"):
+        for n in (10000, 30000):
+            print(json.dumps(registration_leg(n)), flush=True)
