@@ -162,7 +162,8 @@ int scream_depth_to_rgb8(const float *imgs, int B, int V, int w, unsigned char *
 
 /* Host-buffer convenience entry point (end-to-end path: H2D copies, forward, D2H copies, one stream
  * synchronise).  All pointers are HOST pointers; device staging is allocated per call and freed.
- * device < 0 uses the current device. */
+ * device < 0 uses the current device.  flags: SCREAM_F_RAW, _DENSE, _NOSTREAM, _THINSEED; the others
+ * (_DUAL, _ZRANGE_IN, _HALF change the buffer layout or make zrange an input) answer SCREAM_E_UNSUPPORTED. */
 int scream_render_forward_host(const float *xyz_host, const int64_t *offs_host,
                                const float *pose_host, const float *views_host,
                                int B, int V, int w, double rho, unsigned flags,

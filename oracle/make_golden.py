@@ -42,12 +42,26 @@ def make_reference(rho, w, view="muti"):
     return r
 
 
-def freeze(name, src, tgt, rho, w, eulers, pose=None, grad=False, view="muti"):
+def cloud_hash(src, tgt):
+    import hashlib
+    return hashlib.sha1(np.ascontiguousarray(src).tobytes() + np.ascontiguousarray(tgt).tobytes()).hexdigest()
+
+
+def freeze(name, src, tgt, rho, w, eulers, pose=None, grad=False, view="muti", full=None, pose44=None):
     src_t, tgt_t = torch.from_numpy(src), torch.from_numpy(tgt)
     ref = make_reference(rho, w, view)
     ref.eulers = [np.asarray(e, dtype=np.float64) for e in eulers]
     # the caller-side rigid transform of the "real" render (train_3d_match.py:198-199)
-    if pose is not None:
+    if pose44 is not None:
+        # the pose as a lie.torch SE3 and ITS transform (lie/torch/se3.py:142-147), executed from the reference
+        from lie.torch import SE3
+        T = SE3(torch.from_numpy(pose44)[None])                    # liegroupbase.py:18-23: data [1,4,4]
+        src_in = T.transform(src_t[None])[0]
+        pose = np.ascontiguousarray(pose44[:3, :])
+        p = torch.from_numpy(pose)
+        assert torch.equal(src_in, (torch.matmul(p[:, :3], src_t.t()) + p[:, 3:4]).t()), \
+            f"{name}: SE3.transform differs from the caller-side matmul + trans"
+    elif pose is not None:
         p = torch.from_numpy(pose)
         src_in = (torch.matmul(p[:, :3], src_t.t()) + p[:, 3:4]).t()
     else:
@@ -58,15 +72,32 @@ def freeze(name, src, tgt, rho, w, eulers, pose=None, grad=False, view="muti"):
     assert torch.equal(want, got), f"{name}: dense restatement differs from the reference"
     views = orc.view_matrices(ref.eulers)
     ins = orc.forward_instrumented(src_t, tgt_t, rho, w, views,
-                                   pose=None if pose is None else torch.from_numpy(pose))
+                                   pose=None if pose is None else torch.from_numpy(pose), runners=True)
     assert torch.equal(want, ins["imgs"]), f"{name}: chunked restatement differs from the reference"
+    if full is not None:
+        # BASELINE-size fixture: outputs only (the inputs are re-generated from `full`, a seeded recipe, and checked by hash)
+        n_max = max(len(src), len(tgt))
+        rec = dict(recipe=np.array(full), xyz_sha1=np.array(cloud_hash(src, tgt)), rho=np.float64(rho), w=np.int64(w),
+                   eulers=np.stack(ref.eulers).astype(np.float64), views=views.numpy(),
+                   val=ins["val"].numpy(), idx=ins["idx"].numpy().astype(np.int16 if n_max < 32768 else np.int32),
+                   tie=(ins["second"] == ins["val"]).numpy(), zrange=ins["zrange"].numpy(),
+                   near_pix=ins["near_pix"].numpy().astype(np.int32), near_idx=ins["near_idx"].numpy().astype(np.int32))
+        if pose is not None:
+            rec["pose"] = pose
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), **rec)
+        print(f"wrote {name} (outputs only): V={len(ref.eulers)} n={len(src)} m={len(tgt)} w={w} rho={rho} "
+              f"exact-tie px={int(rec['tie'].sum())} near-tie px={len(rec['near_pix'])}")
+        return
     # winner indices must reproduce the value they claim
     rec = dict(src=src, tgt=tgt, rho=np.float64(rho), w=np.int64(w),
                eulers=np.stack(ref.eulers).astype(np.float64), views=views.numpy(),
                imgs=want.numpy(), val=ins["val"].numpy(), idx=ins["idx"].numpy(),
-               second=ins["second"].numpy(), zrange=ins["zrange"].numpy())
+               second=ins["second"].numpy(), zrange=ins["zrange"].numpy(),
+               near_pix=ins["near_pix"].numpy().astype(np.int32), near_idx=ins["near_idx"].numpy().astype(np.int32))
     if pose is not None:
         rec["pose"] = pose
+    if pose44 is not None:
+        rec["pose44"] = pose44
     if grad:
         g = torch.from_numpy(np.random.default_rng(7).standard_normal(want.shape).astype(np.float32))
         s = src_in.clone().requires_grad_(True)
@@ -86,6 +117,44 @@ def freeze(name, src, tgt, rho, w, eulers, pose=None, grad=False, view="muti"):
           f"max={v.max():.4f} zero_px={(v == 0).mean():.3f}")
 
 
+FULL_RECIPES = {
+    # name: (recipe string understood by scream_b200/synth.py:cloud_from_recipe, rho, w, eulers key, posed)
+    "full_cfg2_ball": ("ball:10000:2101|ball:10000:2102", 24, 64, "six", False),
+    "full_cfg2_shell_real": ("shell:10000:2103|shell:10000:2104", 24, 64, "six", True),
+    "full_cfg3_kitti": ("slab:15000:2105|slab:15000:2106", 48, 64, "bev", False),
+    "full_cfg4_w64": ("grid:100:2107", 24, 64, "one", False),
+    "full_cfg4_w128": ("grid:100:2107", 36, 128, "one", False),
+    "full_cfg4_w256": ("grid:100:2107", 72, 256, "one", False),
+}
+
+
+def freeze_full():
+    """BASELINE-size fixtures: the reference executed at cfg2 / cfg3 / cfg4 sizes, outputs only."""
+    eul = {"six": orc.canonical_eulers("muti"), "one": orc.canonical_eulers("single"), "bev": [np.array([0, np.pi, 0])]}
+    for name, (recipe, rho, w, ek, posed) in FULL_RECIPES.items():
+        src, tgt = synth.cloud_from_recipe(recipe)
+        freeze(name, src, tgt, rho, w, eul[ek], pose=synth.random_pose(2199) if posed else None,
+               view="single" if ek == "one" else "muti", full=recipe)
+
+
+def freeze_extra():
+    """a8: pose given as a lie.torch SE3; NaN semantics (render.py:30-31,46: a NaN coordinate poisons every image)."""
+    p44 = np.concatenate([synth.random_pose(81), np.array([[0, 0, 0, 1]], np.float32)], 0)
+    freeze("cfg2_se3_pose", synth.room_shell(900, 82), synth.unit_ball(800, 83), 24, 64, orc.canonical_eulers("muti"),
+           pose44=np.ascontiguousarray(p44))
+    src, tgt = synth.unit_ball(300, 84), synth.unit_ball(280, 85)
+    tgt[17, 1] = np.float32(np.nan)
+    ref = make_reference(24, 64)
+    with torch.no_grad():
+        want = ref(torch.from_numpy(src), torch.from_numpy(tgt))
+    col = torch.full((5, 3), float("nan"))
+    assert torch.isnan(want).all() and (torch.max(col, dim=0)[1] == 0).all()     # all-NaN column: NaN at index 0
+    np.savez_compressed(os.path.join(OUT, "nan_point.npz"), src=src, tgt=tgt, rho=np.float64(24), w=np.int64(64),
+                        eulers=np.stack(ref.eulers).astype(np.float64), views=orc.view_matrices(ref.eulers).numpy(),
+                        imgs=want.numpy())
+    print("wrote nan_point: every pixel of every view and cloud is NaN in the reference")
+
+
 def freeze_half(name, src, tgt, rho, w, eulers):
     """the reference under autocast (train_kitti.py:154-169 uses torch.cuda.amp.autocast(); this container
     has no GPU, so the reference runs under torch.autocast("cpu", dtype=torch.float16): same autocast op lists, the
@@ -100,7 +169,7 @@ def freeze_half(name, src, tgt, rho, w, eulers):
         want = ref(src_t, tgt_t)
     assert want.dtype == torch.float32
     views = orc.view_matrices(ref.eulers)
-    ins = orc.forward_instrumented(src_t, tgt_t, rho, w, views, half=True)
+    ins = orc.forward_instrumented(src_t, tgt_t, rho, w, views, half=True, runners=True)
     assert torch.equal(want, ins["imgs"]), f"{name}: fp16-mode restatement differs from the reference under autocast"
     with torch.no_grad():
         plain = ref(src_t, tgt_t)
@@ -113,6 +182,7 @@ def freeze_half(name, src, tgt, rho, w, eulers):
     rec = dict(src=src, tgt=tgt, rho=np.float64(rho), w=np.int64(w), eulers=np.stack(ref.eulers).astype(np.float64),
                views=views.numpy(), imgs=want.numpy(), val=ins["val"].numpy(), idx=ins["idx"].numpy(),
                second=ins["second"].numpy(), zrange=ins["zrange"].numpy(),
+               near_pix=ins["near_pix"].numpy().astype(np.int32), near_idx=ins["near_idx"].numpy().astype(np.int32),
                grad_out=g.numpy(), grad_src=s.grad.numpy(), grad_tgt=t.grad.numpy())
     np.savez_compressed(os.path.join(OUT, name + ".npz"), **rec)
     print(f"wrote {name}: restatement == reference under autocast(fp16); differs from the fp32 render at "
@@ -197,6 +267,12 @@ def main():
     if "--only-half" in sys.argv:
         freeze_half_all()
         return
+    if "--only-full" in sys.argv:
+        freeze_full()
+        return
+    if "--only-extra" in sys.argv:
+        freeze_extra()
+        return
     torch.manual_seed(0)
     six = orc.canonical_eulers("muti")
     one = orc.canonical_eulers("single")
@@ -215,9 +291,11 @@ def main():
     freeze("cfg4_opengg_w128", dsm, dem, 36, 128, one, view="single")
     # sparse cloud: most pixels are far from every point (exact zeros, denormals)
     freeze("sparse_far_pixels", synth.unit_ball(40, 51) * np.float32(0.2), synth.unit_ball(16, 52), 48, 64, six)
+    freeze_extra()
     freeze_colorize()
     freeze_half_all()
     freeze_registration()
+    freeze_full()
 
 
 if __name__ == "__main__":

@@ -161,8 +161,10 @@ def forward_dense(src: torch.Tensor, tgt: torch.Tensor, rho, w: int,
 # Same per-element arithmetic as render_dense; the max over points is merged across
 # chunks (first index wins ties, like torch.max(dim=0)).  Bit-identical values.
 # --------------------------------------------------------------------------------------
-def render_instrumented(x: torch.Tensor, src_n: int, rho, w: int, chunk: int = 2048, half: bool = False):
-    """Returns dict(val[2,w,w] f32, idx[2,w,w] i64 cloud-local, second[2,w,w] f32, zmin, zmax)."""
+def render_instrumented(x: torch.Tensor, src_n: int, rho, w: int, chunk: int = 2048, half: bool = False,
+                        runners: bool = False):
+    """Returns dict(val[2,w,w] f32, idx[2,w,w] i64 cloud-local, second[2,w,w] f32, zmin, zmax); runners=True adds the
+    near-tie adjudication lists near_pix / near_idx."""
     centres = pixel_centres(w)
     npix = w * w
     pv, zmin, zmax = depth_weights_half(x) if half else depth_weights(x)
@@ -190,14 +192,48 @@ def render_instrumented(x: torch.Tensor, src_n: int, rho, w: int, chunk: int = 2
                     s.copy_(new_second)
                     a.copy_(torch.where(take, ci + (s0 - lo), a))
                     b.copy_(torch.where(take, cb, b))
-    return {
+    out = {
         "val": best.view(2, w, w), "idx": arg.view(2, w, w), "second": second.view(2, w, w),
         "zmin": zmin, "zmax": zmax,
     }
+    if runners:
+        # Near-tie pixels (0 < top-2 gap <= 2 ulp): the points other than the winner whose value reaches the
+        # runner-up value, found by re-evaluating the same blocks with the same ATen kernels (so the bits are the bits of
+        # the pass above).  [K] flat pixel index into [2, w*w] and [K, 4] cloud-local point indices (-1 padded).
+        gap = best - second
+        near = (gap > 0) & (gap <= 2 * _ulp(best))
+        pix, cand = [], []
+        with torch.no_grad():
+            for c, (lo, hi) in enumerate(spans):
+                for p0 in range(0, npix, PIXEL_BLOCK):
+                    cols = near[c, p0:p0 + PIXEL_BLOCK].nonzero().flatten()
+                    if cols.numel() == 0:
+                        continue
+                    found = [[] for _ in range(cols.numel())]
+                    for s0 in range(lo, hi, chunk):
+                        s1 = min(hi, s0 + chunk)
+                        v = _splat_block(x[s0:s1, :2], pv[s0:s1], centres[p0:p0 + PIXEL_BLOCK], rho)[:, cols]
+                        hit = (v >= second[c, p0 + cols].unsqueeze(0)).nonzero()
+                        for r, k in hit.tolist():
+                            found[k].append(r + s0 - lo)
+                    for k, col in enumerate(cols.tolist()):
+                        others = [i for i in found[k] if i != int(arg[c, p0 + col])][:4]
+                        pix.append(c * npix + p0 + col)
+                        cand.append(others + [-1] * (4 - len(others)))
+        out["near_pix"] = torch.tensor(pix, dtype=torch.int64)
+        out["near_idx"] = torch.tensor(cand, dtype=torch.int64).view(-1, 4)
+    return out
+
+
+def _ulp(v: torch.Tensor) -> torch.Tensor:
+    """spacing of fp32 values (distance to the next larger magnitude)"""
+    a = v.abs()
+    return torch.nextafter(a, torch.full_like(a, math.inf)) - a
 
 
 def forward_instrumented(src: torch.Tensor, tgt: torch.Tensor, rho, w: int, views: torch.Tensor,
-                         pose: Optional[torch.Tensor] = None, chunk: int = 2048, half: bool = False):
+                         pose: Optional[torch.Tensor] = None, chunk: int = 2048, half: bool = False,
+                         runners: bool = False):
     """Full forward with explicit fp32 view matrices [V,3,3] and optional pose [3,4] on src.
     half=True: the fp16 (autocast) input mode above.
 
@@ -206,14 +242,18 @@ def forward_instrumented(src: torch.Tensor, tgt: torch.Tensor, rho, w: int, view
     if pose is not None:
         src = apply_pose(pose[:, :3].contiguous(), pose[:, 3:4].contiguous(), src)
     pts = torch.cat([src, tgt], dim=0)
-    vals, idxs, seconds, zr = [], [], [], []
+    vals, idxs, seconds, zr, npx, nid = [], [], [], [], [], []
     for v in range(views.shape[0]):
         x = rotate_half(views[v], pts) if half else rotate(views[v], pts)
-        r = render_instrumented(x, src.shape[0], rho, w, chunk, half=half)
+        r = render_instrumented(x, src.shape[0], rho, w, chunk, half=half, runners=runners)
         vals.append(r["val"]); idxs.append(r["idx"]); seconds.append(r["second"])
         zr.append([r["zmin"], r["zmax"]])
+        if runners:
+            npx.append(r["near_pix"] + v * 2 * w * w); nid.append(r["near_idx"])
     val = torch.stack(vals, dim=0)
+    extra = {"near_pix": torch.cat(npx), "near_idx": torch.cat(nid)} if runners else {}
     return {
+        **extra,
         "imgs": ((val - 0.5) / 0.5).contiguous(),
         "val": val,
         "idx": torch.stack(idxs, dim=0).to(torch.int32),

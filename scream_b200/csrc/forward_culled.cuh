@@ -287,6 +287,15 @@ forward_culled_kernel(FwdParams P)
         P.zrange[(ob * P.V + v) * 2] = zmin;
         P.zrange[(ob * P.V + v) * 2 + 1] = zmax;
     }
+    if (zmin != zmin || zmax != zmax) {
+        // a NaN coordinate anywhere in the pair: torch.min / torch.max propagate it (render.py:30), every pv of render.py:31
+        // is NaN, and torch.max(dim=0) of an all-NaN column is NaN at index 0 (render.py:46,49) -- both clouds, every pixel
+        for (int p = tid; p < npix; p += FC_THREADS) {
+            P.imgs[img_off + p] = __int_as_float(0x7FC00000);
+            if (P.winner) P.winner[img_off + p] = hi > lo ? 0 : -1;
+        }
+        continue;                                         // uniform over the CTA
+    }
     ExactCtx E; E.xyz = P.xyz; E.lo = lo; E.R = s_R; E.pose = s_pose; E.posed = posed;
     E.zmin = zmin; E.range = range; E.negk = P.negk; E.f16 = (P.flags & FC_FLAG_HALF) != 0;
     // the target's second pass keeps the sorted records of the first (one batch only) and renews the score offsets

@@ -106,6 +106,7 @@ forward_dense_kernel(FwdParams P)
 #pragma unroll
     for (int u = 0; u < FD_PX; ++u) {
         float r = (hi > lo) ? best[u] : 0.0f;
+        if (zmin != zmin || zmax != zmax) { r = __int_as_float(0x7FC00000); arg[u] = 0; }   // NaN depth: see forward_culled.cuh
         out[u] = raw ? r : __fmul_rn(__fsub_rn(r, 0.5f), 2.0f);     // (img - 0.5) / 0.5, render.py:69
     }
     *reinterpret_cast<float4*>(P.imgs + o) = make_float4(out[0], out[1], out[2], out[3]);

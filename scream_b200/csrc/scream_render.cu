@@ -370,6 +370,10 @@ int scream_render_forward_host(const float* xyz_host, const int64_t* offs_host,
 {
     if (!xyz_host || !offs_host || !views_host || !imgs_host) return fail(SCREAM_E_ARG, "NULL host pointer");
     if (B <= 0 || V <= 0) return fail(SCREAM_E_ARG, "B and V must be positive");
+    // the staging slab below is sized for the plain [B,V,2,w,w] layout and zrange is an output only
+    if (flags & (SCREAM_F_DUAL | SCREAM_F_ZRANGE_IN | SCREAM_F_HALF))
+        return fail(SCREAM_E_UNSUPPORTED, "scream_render_forward_host takes SCREAM_F_RAW / DENSE / NOSTREAM / THINSEED only "
+                                           "(DUAL, ZRANGE_IN and HALF need the device entry points)");
     if (device >= 0) CUDA_TRY(cudaSetDevice(device));
     const int64_t total = offs_host[2 * B];
     int64_t max_item = 0;

@@ -84,7 +84,7 @@ zrange_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ offs,
 // ---- large clouds (>= ZW_MIN_PTS points in an item): views in registers, points streamed ---------------------
 // grid (chunks, view groups, B).  A thread keeps the z rows and the running min / max of ZW_VPG views in
 // registers and walks ZW_PTS_PER_THREAD points two at a time: per (point, view) 3 FMA-pipe instructions and one
-// three-input FMNMX3 (sm_100), against ~10 in the kernel above.  The cloud is read V / ZW_VPG times (from L2
+// three-input FMNMX3 (sm_100, .NaN: a NaN depth poisons the range like torch.min / torch.max do), against ~10 in the kernel above.  The cloud is read V / ZW_VPG times (from L2
 // when it fits).  Float min / max order -0 < +0 like the integer keys do, so both kernels give the same bits.
 constexpr int ZW_THREADS = 256;
 constexpr int ZW_VPG = 16;
@@ -94,10 +94,10 @@ constexpr int ZW_PTS_PER_CTA = ZW_THREADS * ZW_PTS_PER_THREAD;
 constexpr int64_t ZW_MIN_PTS = 1 << 18;
 
 __device__ __forceinline__ float fmin3(float a, float b, float c) {
-    float r; asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r;
+    float r; asm("min.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r;
 }
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
-    float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r;
+    float r; asm("max.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r;
 }
 
 __global__ void __launch_bounds__(ZW_THREADS)

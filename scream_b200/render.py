@@ -12,6 +12,7 @@ sequence for a whole training batch, which the reference cannot do (pointnet.py:
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -36,6 +37,38 @@ def _stream_ptr(dev: torch.device) -> int:
     return torch.cuda.current_stream(dev).cuda_stream
 
 
+_POISON = os.environ.get("SCREAM_POISON", "") not in ("", "0")
+
+
+def _empty(shape, dtype, dev) -> torch.Tensor:
+    """torch.empty for every buffer the path allocates.  SCREAM_POISON=1 (diagnostics): the block is filled with 0xFF bytes
+    first (NaN as fp32, -1 as int32), so a kernel that reads a word it never wrote cannot pass the parity tests by luck."""
+    t = torch.empty(shape, dtype=dtype, device=dev)
+    if _POISON and t.numel():
+        t.view(torch.uint8).fill_(0xFF)
+    return t
+
+
+def as_pose(pose, B: int, dev) -> Optional[torch.Tensor]:
+    """[B,3,4] fp32 contiguous [R|t] rows on `dev` from what a SCREAM caller has at hand: a [B,3,4] / [B,4,4] (or, for one
+    item, [3,4] / [4,4]) tensor, or a lie.torch SE3 -- anything whose `.data` is a [...,4,4] tensor
+    (lie/torch/liegroupbase.py:18-23; SE3.transform, lie/torch/se3.py:142-147, reads exactly data[..., :3, :3] and
+    data[..., :3, 3:4]).  None stays None."""
+    if pose is None:
+        return None
+    if not isinstance(pose, torch.Tensor):
+        data = getattr(pose, "data", None)
+        if not isinstance(data, torch.Tensor):
+            raise TypeError("pose must be a tensor or an SE3-like object with a .data tensor of shape [...,4,4]")
+        pose = data
+    if pose.dim() == 2:
+        pose = pose.unsqueeze(0)
+    if pose.dim() != 3 or pose.shape[0] != B or pose.shape[2] != 4 or pose.shape[1] not in (3, 4):
+        raise ValueError(f"pose must be [B,3,4] or [B,4,4] with B={B}, got {tuple(pose.shape)}")
+    _require_cuda(pose)
+    return pose[:, :3, :].to(device=dev, dtype=torch.float32).contiguous()
+
+
 # ----------------------------------------------------------------------------------------------
 # custom ops
 # ----------------------------------------------------------------------------------------------
@@ -50,16 +83,16 @@ def _fwd_impl(xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts, 
         assert pose.dtype == torch.float32 and pose.is_contiguous() and pose.shape == (B, 3, 4)
     dev = xyz.device
     with torch.cuda.device(dev):
-        imgs = torch.empty((B, V, 2, w, w), dtype=torch.float32, device=dev)
-        winner = torch.empty((B, V, 2, w, w) if want_winner else (0,), dtype=torch.int32, device=dev)
+        imgs = _empty((B, V, 2, w, w), torch.float32, dev)
+        winner = _empty((B, V, 2, w, w) if want_winner else (0,), torch.int32, dev)
         if zrange_in is not None:                 # point-sharded clouds: the range of the WHOLE cloud (shard.py)
             assert zrange_in.shape == (B, V, 2) and zrange_in.dtype == torch.float32
-            zrange = zrange_in.contiguous().clone()
+            zrange = zrange_in.contiguous()       # an input with SCREAM_F_ZRANGE_IN: read, never written
             flags |= _lib.F_ZRANGE_IN
         else:
-            zrange = torch.empty((B, V, 2), dtype=torch.float32, device=dev)
+            zrange = _empty((B, V, 2), torch.float32, dev)
         nws = _lib.workspace_bytes(B, V, w, total)
-        ws = torch.empty((nws,), dtype=torch.uint8, device=dev)
+        ws = _empty((nws,), torch.uint8, dev)
         rc = lib.scream_render_forward(_ptr(xyz), _ptr(offs), total, max_item_pts, _ptr(pose), _ptr(views),
                                        B, V, w, float(rho), flags, _ptr(imgs),
                                        _ptr(winner) if want_winner else None, _ptr(zrange),
@@ -92,7 +125,7 @@ def _bwd_impl(xyz, offs, pose, views, w, rho, flags, grad_imgs, winner, zrange, 
     grad_imgs = grad_imgs.contiguous().float()
     dev = xyz.device
     with torch.cuda.device(dev):
-        grad_xyz = torch.empty_like(xyz)
+        grad_xyz = _empty(tuple(xyz.shape), torch.float32, dev)
         rc = lib.scream_render_backward(_ptr(xyz), _ptr(offs), total, max_item_pts, _ptr(pose), _ptr(views),
                                         B, V, w, float(rho), flags, _ptr(grad_imgs), _ptr(winner),
                                         _ptr(zrange), _ptr(grad_xyz), None, 0, _stream_ptr(dev))
@@ -178,7 +211,7 @@ def render_batch(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho
                  zrange_in: Optional[torch.Tensor] = None, no_stream: bool = False, thin_seed: bool = False,
                  half: bool = False):
     """Render B pairs at once.  xyz [total,3] fp32 cuda, offs [2B+1] int64 cuda, views [V,3,3] fp32 cuda,
-    pose [B,3,4] or None; zrange_in [B,V,2]: use this depth range instead of reducing it (point-sharded
+    pose [B,3,4] / [B,4,4] / a lie.torch SE3 (as_pose) or None; zrange_in [B,V,2]: use this depth range instead of reducing it (point-sharded
     clouds, scream_b200/shard.py).  half=True: the reference's arithmetic under torch.cuda.amp.autocast()
     (train_kitti.py:154-169: fp16 rotation and depth weight); no pose / zrange_in there.
     Returns (imgs [B,V,2,w,w], winner int32 or empty, zrange [B,V,2])."""
@@ -186,6 +219,7 @@ def render_batch(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho
         raise ValueError("w must be a positive multiple of 64 (render.py:33-34,55)")
     if need_winner is None:
         need_winner = torch.is_grad_enabled() and xyz.requires_grad
+    pose = as_pose(pose, (offs.numel() - 1) // 2, xyz.device)
     if half:
         if pose is not None or zrange_in is not None:
             raise ValueError("half=True (autocast mode) takes neither a pose nor a zrange_in (train_kitti.py:193-194 renders "
@@ -217,11 +251,11 @@ class _DualRender(torch.autograd.Function):
         assert pose is not None and pose.dtype == torch.float32 and pose.is_contiguous() and pose.shape == (B, 3, 4)
         dev = xyz.device
         with torch.cuda.device(dev):
-            imgs = torch.empty((2, B, V, 2, w, w), dtype=torch.float32, device=dev)
-            winner = torch.empty((2, B, V, 2, w, w) if want_winner else (0,), dtype=torch.int32, device=dev)
-            zrange = torch.empty((2, B, V, 2), dtype=torch.float32, device=dev)
+            imgs = _empty((2, B, V, 2, w, w), torch.float32, dev)
+            winner = _empty((2, B, V, 2, w, w) if want_winner else (0,), torch.int32, dev)
+            zrange = _empty((2, B, V, 2), torch.float32, dev)
             nws = _lib.workspace_bytes(B, V, w, total)
-            ws = torch.empty((nws,), dtype=torch.uint8, device=dev)
+            ws = _empty((nws,), torch.uint8, dev)
             rc = lib.scream_render_forward(_ptr(xyz), _ptr(offs), total, max_item_pts, _ptr(pose), _ptr(views),
                                            B, V, w, float(rho), flags | _lib.F_DUAL, _ptr(imgs),
                                            _ptr(winner) if want_winner else None, _ptr(zrange),
@@ -253,6 +287,7 @@ def render_pair(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho,
         raise ValueError("w must be a positive multiple of 64 (render.py:33-34,55)")
     if need_winner is None:
         need_winner = torch.is_grad_enabled() and xyz.requires_grad
+    pose = as_pose(pose, (offs.numel() - 1) // 2, xyz.device)
     return _DualRender.apply(xyz, offs, pose, views, int(w), float(rho), int(_lib.F_RAW if raw else 0),
                              bool(need_winner), int(max_item_pts))
 
@@ -274,8 +309,8 @@ class _HalfRender(torch.autograd.Function):
         B, V, total = (offs.numel() - 1) // 2, views.shape[0], xyz.shape[0]
         dev = xyz.device
         with torch.cuda.device(dev):
-            xr = torch.empty((V * total, 3), dtype=torch.float32, device=dev)
-            offs_bv = torch.empty((2 * B * V + 1,), dtype=torch.int64, device=dev)
+            xr = _empty((V * total, 3), torch.float32, dev)
+            offs_bv = _empty((2 * B * V + 1,), torch.int64, dev)
             rc = lib.scream_half_rotate(_ptr(xyz), _ptr(offs), total, max_item_pts, _ptr(views), B, V,
                                         _ptr(xr), _ptr(offs_bv), _stream_ptr(dev))
             _lib.check(rc, "scream_half_rotate")
@@ -298,7 +333,7 @@ class _HalfRender(torch.autograd.Function):
                          max_item_pts)
         dev = xr.device
         with torch.cuda.device(dev):
-            g = torch.empty((total, 3), dtype=torch.float32, device=dev)
+            g = _empty((total, 3), torch.float32, dev)
             rc = _lib.load().scream_half_rotate_backward(_ptr(g_xr), _ptr(offs), total, max_item_pts, _ptr(views), B, V,
                                                          _ptr(g), _stream_ptr(dev))
         _lib.check(rc, "scream_half_rotate_backward")
@@ -314,9 +349,9 @@ def depth_range(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, pose
     B, V, total = (offs.numel() - 1) // 2, views.shape[0], xyz.shape[0]
     dev = xyz.device
     with torch.cuda.device(dev):
-        zr = torch.empty((B, V, 2), dtype=torch.float32, device=dev)
-        nws = _lib.workspace_bytes(B, V, 64, total)
-        ws = torch.empty((nws,), dtype=torch.uint8, device=dev)
+        zr = _empty((B, V, 2), torch.float32, dev)
+        nws = (B * V * 2 * 4 + 255) // 256 * 256          # the transform stage only keeps the encoded z range there
+        ws = _empty((nws,), torch.uint8, dev)
         rc = lib.scream_render_transform(_ptr(xyz), _ptr(offs), total, int(max_item_pts), _ptr(pose), _ptr(views),
                                          B, V, None, None, _ptr(zr), _ptr(ws), nws, _stream_ptr(dev))
     _lib.check(rc, "scream_render_transform")
@@ -365,9 +400,11 @@ class RegistrationRender(nn.Module):
         dev = torch.device(device)           # the reference hard-codes cuda:0 (render.py:12)
         i, j = np.arange(w * w) // w, np.arange(w * w) % w
         pix_xy = torch.from_numpy(np.concatenate([j.reshape(-1, 1), i.reshape(-1, 1)], axis=1)).float()
-        # kept for API compatibility (render.py:15-16); the kernels recompute the centres exactly
+        # kept for API compatibility (render.py:15-16); the kernels recompute the centres exactly (common.cuh,
+        # pixel_centre), so a caller who REPLACES or edits pix_xy is refused at call time instead of silently ignored
         self.pix_xy = ((pix_xy - w // 2 + 0.5) / (w // 2)).to(dev) if dev.type == "cuda" and torch.cuda.is_available() \
             else (pix_xy - w // 2 + 0.5) / (w // 2)
+        self._pix_ok = (id(self.pix_xy), self.pix_xy._version, w)
         if view == "muti":
             self.eulers = [np.array([0, 0, 0]), np.array([0, np.pi / 2, 0]), np.array([0, np.pi, 0]),
                            np.array([0, np.pi * 3 / 2, 0]),
@@ -396,7 +433,24 @@ class RegistrationRender(nn.Module):
             self._cache[key] = hit
         return hit
 
+    def _check_pix_xy(self):
+        """render.py:42 reads self.pix_xy on every call; here the grid is implied by w.  A pix_xy that is no longer the
+        constructor's tensor (or was written in place, or belongs to another w) must equal the canonical grid of the
+        CURRENT w -- anything else has no kernel and raises."""
+        key = (id(self.pix_xy), getattr(self.pix_xy, "_version", None), self.w)
+        if key == self._pix_ok:
+            return
+        w = int(self.w)
+        p = np.arange(w * w)
+        want = (torch.from_numpy(np.stack([p % w, p // w], axis=1)).float() - w // 2 + 0.5) / (w // 2)
+        got = self.pix_xy
+        if not isinstance(got, torch.Tensor) or tuple(got.shape) != (w * w, 2) or not torch.equal(got.detach().float().cpu(), want):
+            raise NotImplementedError("pix_xy was changed to something other than the pixel-centre grid of w=%d "
+                                      "(render.py:14-16): the B200 kernels render on that grid only" % w)
+        self._pix_ok = key
+
     def _call(self, src, tgt, views, raw, half=False, prerotated_half=False):
+        self._check_pix_xy()
         if src.dim() != 2 or tgt.dim() != 2 or src.shape[1] != 3 or tgt.shape[1] != 3:
             raise ValueError("expected [n,3] and [m,3] point tensors")
         if src.shape[0] == 0 or tgt.shape[0] == 0:
@@ -438,4 +492,5 @@ class RegistrationRender(nn.Module):
     def __getstate__(self):
         st = dict(self.__dict__)
         st["_cache"] = {}
+        st["_pix_ok"] = None           # ids do not survive pickling: re-checked on the first call
         return st

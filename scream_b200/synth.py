@@ -76,3 +76,17 @@ def random_pose(seed: int, max_trans: float = 0.15) -> np.ndarray:
 def random_views(v: int, seed: int) -> np.ndarray:
     """[v,3,3] fp32 random view rotations (cfg5: 64 views)."""
     return np.ascontiguousarray(Rotation.random(v, random_state=seed).as_matrix().astype(np.float32))
+
+
+def cloud_from_recipe(recipe: str):
+    """(src, tgt) from a seeded recipe string: "kind:n:seed|kind:m:seed" with kind in ball / shell / slab, or
+    "grid:side:seed" (OpenGG patch: DSM grid + coarse DEM).  The BASELINE-size golden fixtures (tests/golden/full_*.npz)
+    store their outputs and this string instead of the clouds."""
+    def one(tok):
+        kind, n, seed = tok.split(":")
+        return {"ball": unit_ball, "shell": room_shell, "slab": kitti_slab}[kind](int(n), int(seed))
+    if recipe.startswith("grid:"):
+        _, side, seed = recipe.split(":")
+        return opengg_patch(int(side), int(seed))
+    a, b = recipe.split("|")
+    return one(a), one(b)

@@ -19,9 +19,32 @@ def pytest_configure(config):
 
 
 def golden_names():
-    """Renderer fixtures of the fp32 path (the colouriser's fixture and the fp16-mode fixtures have their own tests)."""
+    """Renderer fixtures of the fp32 path (the colouriser's fixture, the fp16-mode fixtures, the NaN case and the
+    BASELINE-size "full_*" fixtures have their own tests)."""
     names = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-    return [n for n in names if not n.startswith(("colorize", "half_", "registration_"))]
+    return [n for n in names if not n.startswith(("colorize", "half_", "registration_", "full_", "nan_"))]
+
+
+def full_golden_names():
+    """BASELINE-size fixtures: the executed reference's outputs only; the clouds come back from the seeded recipe."""
+    return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "full_*.npz")))
+
+
+def load_full_golden(name):
+    import hashlib
+    from scream_b200 import synth
+    g = load_golden(name)
+    src, tgt = synth.cloud_from_recipe(str(g["recipe"]))
+    sha = hashlib.sha1(np.ascontiguousarray(src).tobytes() + np.ascontiguousarray(tgt).tobytes()).hexdigest()
+    assert sha == str(g["xyz_sha1"]), f"{name}: the seeded recipe no longer reproduces the fixture's clouds"
+    g["src"], g["tgt"] = src, tgt
+    return g
+
+
+# winner-map budget per fixture: how many near-tie pixels (oracle top-2 gap within 2 ulp) may take the runner-up.
+# 0 = the winner map must be bit-exact (regular grids: exact ties only; sparse clouds: no near-ties at all).
+NEAR_TIE_BUDGET = {"cfg4_opengg_w64": 0, "cfg4_opengg_w128": 0, "sparse_far_pixels": 0,
+                   "full_cfg4_w64": 0, "full_cfg4_w128": 0}
 
 
 def half_golden_names():

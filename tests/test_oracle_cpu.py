@@ -145,3 +145,60 @@ def test_half_mode_oracle_matches_reference_under_autocast(name):
     pv, _, _ = orc.depth_weights_half(x)
     assert torch.equal(x, x.half().float()) and torch.equal(pv, pv.half().float())
     assert pv.min() == 0 and pv.max() == 1
+
+
+# ---- round 2: BASELINE-size fixtures, the tightened winner rule, the SE3 pose source -------------------------------
+def test_full_size_golden_present():
+    from conftest import full_golden_names
+    assert len(full_golden_names()) >= 6
+
+
+@pytest.mark.parametrize("name", ["full_cfg3_kitti", "full_cfg4_w64"])
+def test_c_oracle_matches_full_size_golden(name, c_oracle):
+    """The scalar C restatement against the reference executed at BASELINE size (recipe -> clouds, hash-checked)."""
+    from conftest import NEAR_TIE_BUDGET, load_full_golden
+    from oracle_utils import check_images
+    g = load_full_golden(name)
+    r = c_forward(c_oracle, g["src"], g["tgt"], g["views"], float(g["rho"]), int(g["w"]), g.get("pose"))
+    assert np.array_equal(r["zrange"], g["zrange"])
+    check_images(r["val"], r["idx"], g, budget=NEAR_TIE_BUDGET.get(name), label=name + " (C oracle)")
+
+
+def test_check_images_rejects_a_wrong_tie_break_and_a_far_winner():
+    """tests/oracle_utils.py:check_images is the gate of every GPU parity test: a higher index on an EXACT tie, a winner
+    change at a pixel whose top-2 gap exceeds 2 ulp, and a near-tie choice that is not the runner-up must all fail."""
+    from oracle_utils import check_images
+    val = np.array([[0.5, 0.25, 0.125]], np.float32)
+    idx = np.array([[3, 7, 9]], np.int64)
+    near = np.nextafter(np.float32(0.125), np.float32(0))
+    want = dict(val=val, idx=idx, second=np.array([[0.5, 0.2, near]], np.float32),
+                near_pix=np.array([2], np.int32), near_idx=np.array([[11, -1, -1, -1]], np.int32))
+    assert check_images(val, idx, want) == 0
+    assert check_images(val, np.array([[3, 7, 11]]), want) == 1                 # the listed runner-up of a near-tie: allowed
+    with pytest.raises(AssertionError, match="exact ties"):
+        check_images(val, np.array([[4, 7, 9]]), want)                           # exact tie, higher index
+    with pytest.raises(AssertionError, match="exceeds 2 ulp"):
+        check_images(val, np.array([[3, 8, 9]]), want)
+    with pytest.raises(AssertionError, match="runner-ups"):
+        check_images(val, np.array([[3, 7, 12]]), want)
+    with pytest.raises(AssertionError, match="budget"):
+        check_images(val, np.array([[3, 7, 11]]), want, budget=0)
+    with pytest.raises(AssertionError, match="value mismatch"):
+        check_images(val * np.float32(1.00001), idx, want)
+
+
+@pytest.mark.skipif(not __import__("os").path.isdir("/root/reference/lie"), reason="the reference tree is not mounted here")
+def test_se3_transform_of_the_reference_equals_the_pose_stage():
+    """lie/torch/se3.py:142-147 executed from the reference == the oracle's caller-side pose stage == the C
+    oracle's (the arithmetic the CUDA kernels restate), bit for bit; and as_pose() reads SE3.data the way transform does."""
+    import sys
+    sys.path.insert(0, "/root/reference")
+    from lie.torch import SE3
+    from scream_b200 import synth
+    g = load_golden("cfg2_se3_pose")
+    T = SE3(torch.from_numpy(g["pose44"])[None])
+    src = torch.from_numpy(g["src"])
+    moved = T.transform(src[None])[0]
+    p = torch.from_numpy(g["pose44"][:3])
+    assert torch.equal(moved, orc.apply_pose(p[:, :3].contiguous(), p[:, 3:4].contiguous(), src))
+    assert np.array_equal(T.data[0, :3, :].numpy(), g["pose"])

@@ -4,13 +4,14 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import golden_names, load_golden
+from conftest import NEAR_TIE_BUDGET, full_golden_names, golden_names, load_full_golden, load_golden
 from oracle_utils import c_backward, c_forward, c_transform, check_images
 from scream_b200 import _lib, synth
 from scream_b200.render import RegistrationRender, depth_range, make_offsets, render_batch, render_pair, view_matrices
 
 pytestmark = pytest.mark.gpu
 NAMES = golden_names()
+FULL_NAMES = full_golden_names()
 DEV = "cuda:0"
 
 
@@ -51,9 +52,22 @@ def test_forward_matches_golden(name, dense, c_oracle):
     w, rho = int(g["w"]), float(g["rho"])
     r = gpu_forward(g["src"], g["tgt"], g["views"], rho, w, g.get("pose"), dense=dense)
     assert np.array_equal(r["zrange"], g["zrange"])                       # bit-exact z range
-    pvf = oracle_pair_value(c_oracle, g["src"], g["tgt"], g["views"], rho, w, g.get("pose"), r["idx"])
-    check_images(r["val"], r["idx"], g["val"], g["idx"], g["second"], pvf)
+    check_images(r["val"], r["idx"], g, budget=NEAR_TIE_BUDGET.get(name), label=f"{name} dense={dense}")
     assert np.abs(r["imgs"] - g["imgs"]).max() <= 2e-6                    # normalised output, abs
+
+
+@pytest.mark.parametrize("dense", [True, False])
+@pytest.mark.parametrize("name", FULL_NAMES)
+def test_forward_matches_full_size_golden(name, dense):
+    """BASELINE-size fixtures (cfg2 10 k + 10 k x 6 views, cfg3 15 k + 15 k, cfg4 100 x 100 grid at w 64 / 128 / 256): the
+    outputs of the reference itself executed at those sizes (oracle/make_golden.py --only-full)."""
+    g = load_full_golden(name)
+    w, rho = int(g["w"]), float(g["rho"])
+    r = gpu_forward(g["src"], g["tgt"], g["views"], rho, w, g.get("pose"), dense=dense)
+    assert np.array_equal(r["zrange"], g["zrange"])
+    check_images(r["val"], r["idx"], g, budget=NEAR_TIE_BUDGET.get(name), label=f"{name} dense={dense}")
+    want_imgs = ((torch.from_numpy(g["val"]) - 0.5) / 0.5).numpy()         # render.py:69 on the oracle's values
+    assert np.abs(r["imgs"] - want_imgs).max() <= 2e-6
 
 
 @pytest.mark.parametrize("name", ["cfg2_shell_real", "cfg3_kitti_bev", "cfg4_opengg_w64"])
@@ -146,7 +160,8 @@ def test_fresh_inputs_against_c_oracle(cfg, c_oracle):
         r = gpu_forward(src, tgt, views, rho, w, dense=dense)
         assert np.array_equal(r["zrange"], want["zrange"])
         pvf = oracle_pair_value(c_oracle, src, tgt, views, rho, w, None, r["idx"])
-        check_images(r["val"], r["idx"], want["val"], want["idx"], want["second"], pvf, rtol=2e-6)
+        check_images(r["val"], r["idx"], want, pvf, rtol=2e-6, budget=0 if kind == "grid" else None,
+                     label=f"fresh {kind} dense={dense}")
 
 
 def test_culled_equals_dense_bitwise_at_full_size():
@@ -177,7 +192,16 @@ def test_host_entry_point(c_oracle):
     _lib.check(rc, "forward_host")
     assert np.abs(imgs[0] - g["imgs"]).max() <= 2e-6
     assert np.array_equal(zr[0], g["zrange"])
-    assert (win[0] != g["idx"]).mean() < 1e-3
+    rc = lib.scream_render_forward_host(xyz.ctypes.data, offs.ctypes.data, None, views.ctypes.data, 1, V, w,
+                                        float(g["rho"]), _lib.F_RAW, imgs.ctypes.data, win.ctypes.data, zr.ctypes.data, 0)
+    _lib.check(rc, "forward_host raw")
+    check_images(imgs[0], win[0], g, label="forward_host")
+    # the flags that change the buffer layout (or make zrange an input) are refused, not overrun
+    for bad in (_lib.F_DUAL, _lib.F_ZRANGE_IN, _lib.F_HALF):
+        pose = np.ascontiguousarray(synth.random_pose(1)[None])
+        rc = lib.scream_render_forward_host(xyz.ctypes.data, offs.ctypes.data, pose.ctypes.data, views.ctypes.data, 1, V, w,
+                                            float(g["rho"]), bad, imgs.ctypes.data, win.ctypes.data, zr.ctypes.data, 0)
+        assert rc == -4, (bad, rc)
 
 
 CULL_CASES = [
@@ -446,3 +470,152 @@ def test_registered_custom_ops_equal_eager_path():
         assert torch.equal(a, b) and torch.equal(wa, wb) and torch.equal(za, zb)
         a.backward(grad); b.backward(grad)
         assert np.abs((x1.grad - x2.grad).cpu().numpy()).max() <= 1e-5 * float(x1.grad.abs().max())      # atomics order
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# round 2: the holes VERDICT r1 named -- pose as an SE3, NaN semantics, pix_xy, BASELINE cfg5 sizes
+# ------------------------------------------------------------------------------------------------------------------
+class _SE3Like:
+    """Stand-in for lie.torch.SE3 (lie/torch/liegroupbase.py:18-23): an object whose .data is [...,4,4]."""
+    def __init__(self, data):
+        self.data = data
+
+
+def test_pose_given_as_lie_torch_se3():
+    """the fixture's source cloud was moved by the reference's own SE3.transform (lie/torch/se3.py:142-147,
+    executed by oracle/make_golden.py); here the same [4,4] matrix is handed over as an SE3-like object, as a [B,4,4]
+    tensor and as the [B,3,4] rows -- all three must give the bits of the fixture's winner map."""
+    g = load_golden("cfg2_se3_pose")
+    w, rho = int(g["w"]), float(g["rho"])
+    xyz = torch.from_numpy(np.concatenate([g["src"], g["tgt"]], 0)).to(DEV)
+    offs = make_offsets([(len(g["src"]), len(g["tgt"]))]).to(DEV)
+    views = torch.from_numpy(g["views"]).to(DEV)
+    T = torch.from_numpy(g["pose44"]).to(DEV)
+    outs = []
+    for pose in (_SE3Like(T[None]), T[None], T[None, :3, :].contiguous(), T):
+        val, idx, zr = render_batch(xyz, offs, views, rho, w, pose=pose, raw=True, need_winner=True)
+        outs.append((val, idx, zr))
+        assert np.array_equal(zr[0].cpu().numpy(), g["zrange"])
+        check_images(val[0].cpu().numpy(), idx[0].cpu().numpy(), g, label="cfg2_se3_pose")
+    for o in outs[1:]:
+        assert all(torch.equal(a, b) for a, b in zip(o, outs[0]))
+    fake, real, _, _ = render_pair(xyz, offs, views, rho, w, _SE3Like(T[None]), raw=True, need_winner=True)
+    assert torch.equal(real, outs[0][0])
+    with pytest.raises(ValueError):
+        render_batch(xyz, offs, views, rho, w, pose=T[None, :2], raw=True)
+
+
+@pytest.mark.parametrize("dense", [False, True])
+def test_nan_coordinate_poisons_every_image_like_the_reference(dense):
+    """render.py:30-31: torch.min / torch.max propagate a NaN depth, every pv is NaN, every pixel of BOTH clouds in EVERY
+    view is NaN and torch.max(dim=0) names index 0 -- the fixture is the executed reference's output."""
+    g = load_golden("nan_point")
+    assert np.isnan(g["imgs"]).all()
+    r = gpu_forward(g["src"], g["tgt"], g["views"], float(g["rho"]), int(g["w"]), dense=dense)
+    assert np.isnan(r["imgs"]).all() and np.isnan(r["val"]).all()
+    assert (r["idx"] == 0).all()
+    # a batch neighbour without NaN is untouched
+    clean = np.nan_to_num(g["tgt"], nan=0.25)
+    xyz = torch.from_numpy(np.concatenate([g["src"], g["tgt"], g["src"], clean], 0)).to(DEV)
+    offs = make_offsets([(len(g["src"]), len(g["tgt"]))] * 2).to(DEV)
+    views = torch.from_numpy(g["views"]).to(DEV)
+    both, _, _ = render_batch(xyz, offs, views, 24, 64, dense=dense, need_winner=False)
+    one = gpu_forward(g["src"], clean, g["views"], 24, 64, dense=dense)
+    assert torch.isnan(both[0]).all() and np.array_equal(both[1].cpu().numpy(), one["imgs"])
+
+
+def test_nan_depth_in_a_large_cloud_reaches_the_range():
+    """Items of >= 2^18 points take zrange_wide_kernel (three-input float min / max): a NaN must survive it too."""
+    n = (1 << 17) + 77
+    pts = synth.unit_ball(2 * n, 5)
+    pts[n + 12345, 0] = np.float32(np.nan)
+    xyz = torch.from_numpy(pts).to(DEV)
+    zr = depth_range(xyz, make_offsets([(n, n)]).to(DEV), torch.from_numpy(synth.random_views(17, 3)).to(DEV))
+    assert torch.isnan(zr).any(dim=-1).all()
+
+
+def test_mutated_pix_xy_is_checked_not_ignored():
+    g = load_golden("cfg1_ball_single")
+    s, t = torch.from_numpy(g["src"]).to(DEV), torch.from_numpy(g["tgt"]).to(DEV)
+    r = RegistrationRender(24, 64, view="single", device=DEV)
+    base = r(s, t)
+    r.pix_xy = r.pix_xy.clone()                       # replaced by an equal grid: accepted
+    assert torch.equal(r(s, t), base)
+    r.pix_xy[5, 0] += 0.01                            # edited in place: the kernels have no such grid
+    with pytest.raises(NotImplementedError):
+        r(s, t)
+    r2 = RegistrationRender(24, 64, view="single", device=DEV)
+    r2.pix_xy = r2.pix_xy * 0.5                       # replaced by another grid
+    with pytest.raises(NotImplementedError):
+        r2(s, t)
+
+
+def _oracle_crop(src, tgt, view, rho, w, pix):
+    """torch-CPU oracle (the restatement pinned to the executed reference) on a handful of pixels of one view: rotation
+    and depth range over the WHOLE pair (render.py:29-31,68), then the max over point chunks at the pixels `pix`.
+    -> val [2,K], idx [2,K], second [2,K]"""
+    from oracle import render_oracle as orc
+    pts = torch.from_numpy(np.concatenate([src, tgt], 0))
+    x = orc.rotate(torch.from_numpy(view), pts)
+    pv, zmin, zmax = orc.depth_weights(x)
+    cen = orc.pixel_centres(w)[torch.from_numpy(pix)]
+    K, n = len(pix), len(src)
+    val = torch.full((2, K), -np.inf); sec = torch.full((2, K), -np.inf); idx = torch.zeros((2, K), dtype=torch.int64)
+    for c, (lo, hi) in enumerate([(0, n), (n, len(pts))]):
+        for s0 in range(lo, hi, 65536):
+            s1 = min(hi, s0 + 65536)
+            v = orc._splat_block(x[s0:s1, :2], pv[s0:s1], cen, rho)
+            top, _ = torch.topk(v, 2, dim=0)
+            cb, ci = torch.max(v, dim=0)
+            take = cb > val[c]
+            sec[c] = torch.where(take, torch.maximum(val[c], top[1]), torch.maximum(sec[c], cb))
+            idx[c] = torch.where(take, ci + (s0 - lo), idx[c])
+            val[c] = torch.where(take, cb, val[c])
+    return val.numpy(), idx.numpy(), sec.numpy(), (zmin, zmax)
+
+
+def test_million_point_cloud_against_the_torch_oracle_on_a_pixel_crop():
+    """BASELINE config 5 at 10^6 points: the giant-cloud path (default flags) against the oracle itself -- not against
+    another CUDA kernel -- on 256 pixels (a 16 x 16 block off-centre, so rim and interior are both in it)."""
+    n = 500_000
+    src, tgt = synth.unit_ball(n, 61), synth.room_shell(n, 62)
+    views = synth.random_views(2, 15)
+    w, rho = 64, 24
+    rows, cols = np.meshgrid(np.arange(4, 20), np.arange(40, 56), indexing="ij")
+    pix = (rows * w + cols).reshape(-1).astype(np.int64)
+    xyz = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV)
+    offs = make_offsets([(n, n)]).to(DEV)
+    val, idx, zr = render_batch(xyz, offs, torch.from_numpy(views).to(DEV), rho, w, raw=True, need_winner=True, max_item_pts=2 * n)
+    val, idx, zr = val[0].cpu().numpy(), idx[0].cpu().numpy(), zr[0].cpu().numpy()
+    for v in range(len(views)):
+        wv, wi, ws, (zmin, zmax) = _oracle_crop(src, tgt, views[v], rho, w, pix)
+        assert np.float32(zmin) == zr[v, 0] and np.float32(zmax) == zr[v, 1]
+        gv, gi = val[v].reshape(2, -1)[:, pix], idx[v].reshape(2, -1)[:, pix]
+
+        def pair_value(sel, v=v, gi=gi):
+            from oracle import render_oracle as orc
+            pts = torch.from_numpy(np.concatenate([src, tgt], 0))
+            x = orc.rotate(torch.from_numpy(views[v]), pts)
+            pv, _, _ = orc.depth_weights(x)
+            cc, kk = np.nonzero(sel)
+            k = torch.from_numpy(gi[cc, kk].astype(np.int64) + np.where(cc == 1, n, 0))
+            return orc.pair_values(x, pv, k, torch.from_numpy(pix[kk]), rho, w).numpy()
+        check_images(gv, gi, dict(val=wv, idx=wi, second=ws), pair_value, label=f"1M crop view {v}")
+
+
+def test_sixteen_million_points_default_path_equals_rendering_every_batch():
+    """>= 16 M points: seed stride 4, the automatic second filter round and the 64^3 voxel grid (the path bench.py's cfg5
+    leg times at 10^8) -- never reached by the smaller giant-cloud cases, which emulate it with SCREAM_F_THINSEED."""
+    n = 8_400_000
+    g = torch.Generator(device=DEV).manual_seed(77)
+    d = torch.randn((2 * n, 3), generator=g, device=DEV)
+    d /= d.norm(dim=1, keepdim=True)
+    xyz = (d * torch.rand((2 * n, 1), generator=g, device=DEV) ** (1.0 / 3.0)).contiguous()
+    del d
+    offs = make_offsets([(n, n)]).to(DEV)
+    views = torch.from_numpy(synth.random_views(2, 21)).to(DEV)
+    a = render_batch(xyz, offs, views, 24, 64, raw=True, need_winner=True, max_item_pts=2 * n)
+    b = render_batch(xyz, offs, views, 24, 64, raw=True, need_winner=True, max_item_pts=2 * n, no_stream=True)
+    assert torch.equal(a[2], b[2])
+    assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
+    assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"

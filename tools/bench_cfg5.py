@@ -6,7 +6,7 @@ Prints one JSON line: Gpoint-views/s, depth images/s, % of the HBM roofline by S
 (V*12*N + V*2*w^2*8 bytes)."""
 import argparse, json, os, sys
 import numpy as np, torch
-ROOT = os.path.dirname(os.path.abspath(__file__)); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
 from scream_b200 import synth
 from scream_b200.render import render_batch, make_offsets
 

@@ -11,7 +11,7 @@ import time
 import numpy as np
 import torch
 
-ROOT = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from scream_b200 import synth                                           # noqa: E402
 from scream_b200.registration import estimate_transform, nearest_target  # noqa: E402

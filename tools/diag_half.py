@@ -1,6 +1,6 @@
 """Determinism stress of the fp16 (autocast) mode: the module under autocast against the oracle, with allocator churn (NaN-filled\nblocks freed between calls).  ITERS=2 under compute-sanitizer (initcheck / racecheck)."""
 import sys, os, numpy as np, torch
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import render_oracle as orc
 from scream_b200 import synth, _lib
 from scream_b200.render import RegistrationRender, make_offsets, render_batch, view_matrices

@@ -3,7 +3,7 @@
 stream path vs SCREAM_F_NOSTREAM, CUDA events.  usage: tools_sweep_stream.py"""
 import json, os, sys
 import numpy as np, torch
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from scream_b200 import synth
 from scream_b200.render import RegistrationRender, make_offsets, render_batch, view_matrices
 DEV = torch.device("cuda", 0)
