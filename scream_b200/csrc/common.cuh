@@ -13,9 +13,13 @@
 namespace scream {
 
 // ---- order-preserving float <-> uint encoding (for integer min/max atomics / redux.sync) -------
+// NaN encodes to the top of the order (explicitly: ptxas turns b | 0x80000000 into FADD -|x|, which re-canonicalises a NaN
+// to 0x7FFFFFFF, the middle of the order), so the maximum of a range that saw a NaN depth decodes to NaN -- torch.min /
+// torch.max propagate NaN (render.py:30) and the forward kernels poison the images from it.
 __device__ __forceinline__ unsigned enc_f32(float f) {
     unsigned b = __float_as_uint(f);
-    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+    const unsigned e = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+    return (f != f) ? 0xFFFFFFFFu : e;
 }
 __device__ __forceinline__ float dec_f32(unsigned e) {
     unsigned b = (e & 0x80000000u) ? (e & 0x7fffffffu) : ~e;
