@@ -46,17 +46,51 @@ constexpr float FC_EXP_DENORM = 80.0f;                   // k*s beyond this: tre
 constexpr float FC_EXP_MINUS1 = 18.1f;                   // k*s beyond this: (val-0.5)/0.5 == -1 exactly
 
 // shared-memory carve-up (bytes)
-constexpr size_t FC_OFF_XY = 0;
-constexpr size_t FC_OFF_C = FC_OFF_XY + (size_t)FC_CAP * 8;
-constexpr size_t FC_OFF_IDX = FC_OFF_C + (size_t)FC_CAP * 4;
+constexpr size_t FC_OFF_REC = 0;                                             // record PAIRS (see FcShared): xy2 | c2 | idx
+constexpr size_t FC_OFF_C2 = FC_OFF_REC + (size_t)FC_CAP * 8;
+constexpr size_t FC_OFF_IDX = FC_OFF_C2 + (size_t)FC_CAP * 4;
 constexpr size_t FC_OFF_START = FC_OFF_IDX + (size_t)FC_CAP * 4;             // u16 [CELLS + 8]
 constexpr size_t FC_OFF_SCRATCH = FC_OFF_START + (size_t)(FC_CELLS + 8) * 2; // u32 hist[CELLS+4] | u16 cand[TPIX], queue[TPIX]
 constexpr size_t FC_SMEM = FC_OFF_SCRATCH + (size_t)(FC_CELLS + 4) * 4;
 
+// Records live in shared memory as PAIRS: xy2[p] = {x0, x1, y0, y1} (16 B), c2[p] = {c0, c1} (8 B), idx[2p], idx[2p+1],
+// for records 2p and 2p+1: one LDS.128 + one LDS.64 feed the packed fp32x2 pipe (FADD2 / FFMA2, sm_100), two scores for
+// four FMA-pipe instructions.  A run of records [rb, re) is walked as the pairs [rb >> 1, (re + 1) >> 1): the extra record
+// at either end is a real point of a neighbouring cell (or the +inf pad behind the last record), and a real point is
+// always a valid candidate.  The search loops address the arrays through 32-bit shared-window addresses (no generic ->
+// shared conversion in the loops) and load the next pair before they work on the current one.
 struct FcShared {
-    const float2* xy; const float* c; const int* idx; const unsigned short* start;
+    unsigned xy2, c2;                                    // shared-window addresses of the pair arrays
+    unsigned char* rec;                                  // generic pointer to the same block (scalar accessors)
+    const unsigned short* start;
     const unsigned long long* rowmask; const unsigned long long* blockmask;   // cell occupancy: per grid row, per 4 rows
 };
+__device__ __forceinline__ float* rec_x(unsigned char* rec, int s) { return reinterpret_cast<float*>(rec) + ((s >> 1) << 2) + (s & 1); }
+__device__ __forceinline__ float* rec_c(unsigned char* rec, int s) { return reinterpret_cast<float*>(rec + FC_OFF_C2 - FC_OFF_REC) + s; }
+__device__ __forceinline__ int* rec_idx(unsigned char* rec, int s) { return reinterpret_cast<int*>(rec + FC_OFF_IDX - FC_OFF_REC) + s; }
+__device__ __forceinline__ float4 lds128(unsigned a) {
+    float4 v; asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a)); return v;
+}
+__device__ __forceinline__ float2 lds64(unsigned a) {
+    float2 v; asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a)); return v;
+}
+
+__device__ __forceinline__ float2 sub2(float2 a, float b) {
+    float2 d;
+    asm("{ .reg .b64 ra, rb, rd;\n  mov.b64 ra, {%2, %3};\n  mov.b64 rb, {%4, %4};\n  sub.rn.f32x2 rd, ra, rb;\n  mov.b64 {%0, %1}, rd; }"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b));
+    return d;
+}
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+    float2 d;
+    asm("{ .reg .b64 ra, rb, rc, rd;\n  mov.b64 ra, {%2, %3};\n  mov.b64 rb, {%4, %5};\n  mov.b64 rc, {%6, %7};\n"
+        "  fma.rn.f32x2 rd, ra, rb, rc;\n  mov.b64 {%0, %1}, rd; }"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return d;
+}
+__device__ __forceinline__ float fmin3f(float a, float b, float c) {     // NaN operands are ignored, like fminf
+    float r; asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r;
+}
 
 __device__ __forceinline__ int cell_of(float x) {
     // fl(fl(x + 1) * G/2), clamped; NaN -> 0
@@ -78,10 +112,52 @@ __device__ __forceinline__ float score_margin(float s, float inv_k) {
 
 struct PixelGeom { float cx, cy, ux, uy; };              // centre in NDC and in cell coordinates
 
+// scores of records 2p and 2p+1 at pixel g: fl(dx*dx + fl(dy*dy + c)) each, the same bits wherever it is evaluated
+__device__ __forceinline__ float2 pair_scores(float4 q, float2 c, const PixelGeom& g) {
+    const float2 dx = sub2(make_float2(q.x, q.y), g.cx), dy = sub2(make_float2(q.z, q.w), g.cy);
+    return fma2(dx, dx, fma2(dy, dy, c));
+}
+__device__ __forceinline__ float2 score_pair(const FcShared& S, int p, const PixelGeom& g) {
+    return pair_scores(lds128(S.xy2 + 16u * (unsigned)p), lds64(S.c2 + 8u * (unsigned)p), g);
+}
 __device__ __forceinline__ float score_of(const FcShared& S, int s, const PixelGeom& g) {
-    const float2 q = S.xy[s];
-    const float dx = __fsub_rn(q.x, g.cx), dy = __fsub_rn(q.y, g.cy);
-    return __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, S.c[s]));
+    const float2 sc = score_pair(S, s >> 1, g);
+    return (s & 1) ? sc.y : sc.x;
+}
+__device__ __forceinline__ float2 record_xy(const FcShared& S, int s) {
+    const float* f = rec_x(S.rec, s);
+    return make_float2(f[0], f[2]);
+}
+// one step of the (best, runner-up, best pair) search over a pair of scores
+__device__ __forceinline__ void top2_step(float2 sc, int p, float& s1, float& s2, int& a1, bool& improved) {
+    const float lo = fminf(sc.x, sc.y), hi = fmaxf(sc.x, sc.y);
+    s2 = fmin3f(s2, fmaxf(lo, s1), hi);
+    if (lo < s1) { s1 = lo; a1 = p; improved = true; }
+}
+// (best, runner-up, best pair) over the records [rb, re), software-pipelined: the loads of pair p + 1 are in flight while
+// pair p is scored (the load past the end stays inside the CTA's shared memory and is never used)
+__device__ __forceinline__ void scan_run(const FcShared& S, int rb, int re, const PixelGeom& g,
+                                         float& s1, float& s2, int& a1, bool& improved) {
+    int p = rb >> 1;
+    const int pe = (re + 1) >> 1;
+    if (p >= pe) return;
+    unsigned axy = S.xy2 + 16u * (unsigned)p, ac = S.c2 + 8u * (unsigned)p;
+    float4 q = lds128(axy); float2 c = lds64(ac);
+#pragma unroll 1
+    for (; p + 1 < pe; p += 2) {                          // two pairs per trip, registers ping-pong (no moves)
+        const float4 qn = lds128(axy + 16u); const float2 cn = lds64(ac + 8u);
+        top2_step(pair_scores(q, c, g), p, s1, s2, a1, improved);
+        axy += 32u; ac += 16u;
+        q = lds128(axy); c = lds64(ac);
+        top2_step(pair_scores(qn, cn, g), p + 1, s1, s2, a1, improved);
+    }
+    if (p < pe) top2_step(pair_scores(q, c, g), p, s1, s2, a1, improved);
+}
+// pair index -> record index of the better of the two (ties inside the pair leave s2 == s1: the pixel is not resolved)
+__device__ __forceinline__ int best_of_pair(const FcShared& S, int p, const PixelGeom& g) {
+    if (p < 0) return -1;
+    const float2 sc = score_pair(S, p, g);
+    return 2 * p + (sc.y < sc.x ? 1 : 0);
 }
 
 // bits j0..j1 (inclusive) of a 64-column occupancy word
@@ -95,12 +171,12 @@ struct ExactCtx {
     float zmin, range, negk; bool f16;
 };
 __device__ __forceinline__ float exact_value(const FcShared& S, const ExactCtx& E, int s, const PixelGeom& g, int& id) {
-    id = S.idx[s];
+    id = *rec_idx(S.rec, s);
     const float* q = E.xyz + (size_t)(E.lo + id) * 3;
     float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
     if (E.posed) apply_pose(E.pose, x, y, z);
     const float pv = depth_weight_m(rot_row(E.R + 6, x, y, z), E.zmin, E.range, E.f16);
-    const float2 r = S.xy[s];
+    const float2 r = record_xy(S, s);
     return pair_value(pair_d2(r.x, r.y, g.cx, g.cy), pv, E.negk);
 }
 
@@ -146,11 +222,17 @@ __device__ __forceinline__ void disc_scan(const FcShared& S, const ExactCtx& E, 
                 const int rb = S.start[i * FC_G + j0], re = S.start[i * FC_G + j1 + 1];
                 if (EXACT) {
 #pragma unroll 1
-                    for (int s = rb; s < re; ++s) {
-                        if (score_of(S, s, g) <= s_thr) {
-                            int id;
-                            const float val = exact_value(S, E, s, g, id);
-                            if (val > best || (val == best && id < arg)) { best = val; arg = id; }
+                    for (int p = rb >> 1; p < (re + 1) >> 1; ++p) {
+                        const float2 sc = score_pair(S, p, g);
+                        if (fminf(sc.x, sc.y) <= s_thr) {
+#pragma unroll
+                            for (int h = 0; h < 2; ++h) {
+                                if ((h ? sc.y : sc.x) <= s_thr) {
+                                    int id;
+                                    const float val = exact_value(S, E, 2 * p + h, g, id);
+                                    if (val > best || (val == best && id < arg)) { best = val; arg = id; }
+                                }
+                            }
                         }
                     }
                 } else {
@@ -168,9 +250,9 @@ __device__ __forceinline__ void disc_scan(const FcShared& S, const ExactCtx& E, 
                         if (jn >= 0) {
                             const int nb = S.start[i * FC_G + jn], ne = S.start[i * FC_G + jn + 1];
 #pragma unroll 1
-                            for (int s = nb; s < ne; ++s) {
-                                const float sc = score_of(S, s, g);
-                                if (sc < s1) { s1 = sc; }
+                            for (int p = nb >> 1; p < (ne + 1) >> 1; ++p) {
+                                const float2 sc = score_pair(S, p, g);
+                                s1 = fmin3f(s1, sc.x, sc.y);
                             }
                             // radius from this bound; the full span below re-visits the cell (s1/s2/a1 stay consistent)
                             const float r2n = fminf(r2, s1 + score_margin(s1, inv_k));
@@ -181,21 +263,11 @@ __device__ __forceinline__ void disc_scan(const FcShared& S, const ExactCtx& E, 
                             rb2 = S.start[i * FC_G + j0n];
                             const int re2 = S.start[i * FC_G + j1n + 1];
                             s1 = INFINITY;
-#pragma unroll 1
-                            for (int s = rb2; s < re2; ++s) {
-                                const float sc = score_of(S, s, g);
-                                s2 = fminf(s2, fmaxf(sc, s1));
-                                if (sc < s1) { s1 = sc; a1 = s; improved = true; }
-                            }
+                            scan_run(S, rb2, re2, g, s1, s2, a1, improved);
                             rb2 = re;                     // span done
                         }
                     }
-#pragma unroll 1
-                    for (int s = rb2; s < re; ++s) {
-                        const float sc = score_of(S, s, g);
-                        s2 = fminf(s2, fmaxf(sc, s1));
-                        if (sc < s1) { s1 = sc; a1 = s; improved = true; }
-                    }
+                    scan_run(S, rb2, re, g, s1, s2, a1, improved);
                     if (improved) {
                         r2 = fminf(r2, s1 + score_margin(s1, inv_k));
                         rc = radius_cells(r2);
@@ -205,6 +277,25 @@ __device__ __forceinline__ void disc_scan(const FcShared& S, const ExactCtx& E, 
         }
         if (!live) break;
     }
+    if (!EXACT) a1 = best_of_pair(S, a1, g);             // the search tracked the best PAIR
+}
+
+// a pixel whose nearest occupied cell is `ring` cells away (Chebyshev) has no point nearer than (ring - 1 + edge) cells:
+// beyond the radius that can change the output it is background
+__device__ __forceinline__ bool blank_pixel(int ring, float edge, float r2cap_all) {
+    const float dlb = __fmul_rn((float)(ring - 1) + edge, 1.0f / FC_CELLS_PER_NDC);
+    return ring >= 2 && __fmul_rn(__fmul_rn(dlb, dlb), 0.99999f) > r2cap_all;
+}
+// ring / blank of pixel (row, col): the expressions of phase A
+__device__ __forceinline__ void pixel_class(int row, int col, int half, float r2cap_all, const unsigned char* s_ring,
+                                            int& ring, bool& blank) {
+    const float ux = __fmul_rn(__fadd_rn(pixel_centre(col, half), 1.0f), FC_CELLS_PER_NDC);
+    const float uy = __fmul_rn(__fadd_rn(pixel_centre(row, half), 1.0f), FC_CELLS_PER_NDC);
+    const int ci = (int)uy, cj = (int)ux;
+    const float fx = ux - (float)cj, fy = uy - (float)ci;
+    const float edge = fminf(fminf(fx, 1.0f - fx), fminf(fy, 1.0f - fy));
+    ring = s_ring[ci * FC_G + cj];
+    blank = blank_pixel(ring, edge, r2cap_all);
 }
 
 constexpr unsigned FC_FLAG_DUAL = 32u;                   // SCREAM_F_DUAL
@@ -214,16 +305,14 @@ __global__ void __launch_bounds__(FC_THREADS, 1)
 forward_culled_kernel(FwdParams P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float2* s_xy = reinterpret_cast<float2*>(smem_raw + FC_OFF_XY);
-    float* s_c = reinterpret_cast<float*>(smem_raw + FC_OFF_C);
-    int* s_idx = reinterpret_cast<int*>(smem_raw + FC_OFF_IDX);
+    unsigned char* s_rec = smem_raw + FC_OFF_REC;
     unsigned short* s_start = reinterpret_cast<unsigned short*>(smem_raw + FC_OFF_START);
     unsigned* s_hist = reinterpret_cast<unsigned*>(smem_raw + FC_OFF_SCRATCH);
     unsigned short* s_cand = reinterpret_cast<unsigned short*>(smem_raw + FC_OFF_SCRATCH);
     unsigned short* s_queue = s_cand + FC_TPIX;
     __shared__ float s_R[9], s_pose[12];
     __shared__ unsigned s_warp_tot[FC_THREADS / 32];
-    __shared__ unsigned s_qfar, s_qnear, s_qhead;
+    __shared__ unsigned s_qfar, s_qnear, s_qhead, s_work;
     __shared__ unsigned long long s_rowmask[FC_G], s_blockmask[FC_G / 4];
     __shared__ unsigned char s_ring[FC_CELLS];            // Chebyshev distance (cells) to the nearest occupied cell
 
@@ -272,7 +361,8 @@ forward_culled_kernel(FwdParams P)
     const float r2cap_all = minus1_ok ? fminf(s_zero, __fmul_rn(FC_EXP_MINUS1, inv_k)) : s_zero;
     __syncthreads();
 
-    FcShared S; S.xy = s_xy; S.c = s_c; S.idx = s_idx; S.start = s_start;
+    FcShared S; S.rec = s_rec; S.start = s_start;
+    S.xy2 = (unsigned)__cvta_generic_to_shared(s_rec); S.c2 = S.xy2 + (unsigned)(FC_OFF_C2 - FC_OFF_REC);
     S.rowmask = s_rowmask; S.blockmask = s_blockmask;
 
   for (int pass = pass0; pass < pass1; ++pass) {
@@ -312,20 +402,32 @@ forward_culled_kernel(FwdParams P)
         // ---------------- P1: transform + histogram -------------------------------------------
         for (int t = tid; t < FC_CELLS + 4; t += FC_THREADS) s_hist[t] = 0u;
         __syncthreads();
-        unsigned packed[FC_PPT];
-#pragma unroll
-        for (int k = 0; k < FC_PPT; ++k) {
+        unsigned packed[FC_PPT];                          // (cell << 16) | rank inside the cell
+        // the loads of point k + 1 are in flight while point k is binned (a thread that walks its points strictly one by
+        // one exposes 12 serial L2 round trips here and 12 more in P3)
+        auto fetch = [&](int k, float& x, float& y, float& z, int& id) {
             const int j = k * FC_THREADS + tid;
-            packed[k] = 0xFFFFFFFFu;
             if (j < cnt) {
                 const int64_t pi = surv ? (int64_t)__ldg(surv + c0 + j) : c0 + j;
                 const float* q = P.xyz + (size_t)(lo + pi) * 3;
-                float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
-                if (posed) apply_pose(s_pose, x, y, z);
-                const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z);
-                const int cell = cell_of(yr) * FC_G + cell_of(xr);
-                const unsigned rank = atomicAdd(&s_hist[cell], 1u);
-                packed[k] = ((unsigned)cell << 16) | (rank & 0xFFFFu);       // cnt <= 12288 < 65536
+                x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2); id = (int)pi;
+            }
+        };
+        {
+            float nx = 0.f, ny = 0.f, nz = 0.f; int nid = 0;
+            fetch(0, nx, ny, nz, nid);
+#pragma unroll
+            for (int k = 0; k < FC_PPT; ++k) {
+                float x = nx, y = ny, z = nz;
+                if (k + 1 < FC_PPT) fetch(k + 1, nx, ny, nz, nid);
+                packed[k] = 0xFFFFFFFFu;
+                if (k * FC_THREADS + tid < cnt) {
+                    if (posed) apply_pose(s_pose, x, y, z);
+                    const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z);
+                    const int cell = cell_of(yr) * FC_G + cell_of(xr);
+                    const unsigned rank = atomicAdd(&s_hist[cell], 1u);
+                    packed[k] = ((unsigned)cell << 16) | (rank & 0xFFFFu);       // cnt <= 12288 < 65536
+                }
             }
         }
         __syncthreads();
@@ -377,21 +479,28 @@ forward_culled_kernel(FwdParams P)
             }
             if (lane == 0) s_blockmask[wq] = bm;
         }
+        {
+            float nx = 0.f, ny = 0.f, nz = 0.f; int nid = 0;
+            fetch(0, nx, ny, nz, nid);
 #pragma unroll
-        for (int k = 0; k < FC_PPT; ++k) {
-            if (packed[k] != 0xFFFFFFFFu) {
-                const int j = k * FC_THREADS + tid;
-                const int64_t pi = surv ? (int64_t)__ldg(surv + c0 + j) : c0 + j;
-                const float* q = P.xyz + (size_t)(lo + pi) * 3;
-                float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
-                if (posed) apply_pose(s_pose, x, y, z);
-                const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z), zr = rot_row(s_R + 6, x, y, z);
-                const unsigned pos = (unsigned)s_start[packed[k] >> 16] + (packed[k] & 0xFFFFu);
-                s_xy[pos] = make_float2(xr, yr);
-                // c = -ln(pv)/k >= 0; pv == 0 -> +inf (never wins); pv < 0 (rounding corner) -> NaN (never wins)
-                s_c[pos] = __fmul_rn(logf(depth_weight_m(zr, zmin, range, (P.flags & FC_FLAG_HALF) != 0)), P.inv_negk);
-                s_idx[pos] = (int)pi;
+            for (int k = 0; k < FC_PPT; ++k) {
+                float x = nx, y = ny, z = nz; const int id = nid;
+                if (k + 1 < FC_PPT) fetch(k + 1, nx, ny, nz, nid);
+                if (packed[k] != 0xFFFFFFFFu) {
+                    if (posed) apply_pose(s_pose, x, y, z);
+                    const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z), zr = rot_row(s_R + 6, x, y, z);
+                    const unsigned pos = (unsigned)s_start[packed[k] >> 16] + (packed[k] & 0xFFFFu);
+                    float* rx = rec_x(s_rec, (int)pos);
+                    rx[0] = xr; rx[2] = yr;
+                    // c = -ln(pv)/k >= 0; pv == 0 -> +inf (never wins); pv < 0 (rounding corner) -> NaN (never wins)
+                    *rec_c(s_rec, (int)pos) = __fmul_rn(logf(depth_weight_m(zr, zmin, range, (P.flags & FC_FLAG_HALF) != 0)), P.inv_negk);
+                    *rec_idx(s_rec, (int)pos) = id;
+                }
             }
+        }
+        if (tid == 0 && (cnt & 1)) {                      // pad behind an odd count: a record that can never win
+            float* rx = rec_x(s_rec, cnt);
+            rx[0] = 0.0f; rx[2] = 0.0f; *rec_c(s_rec, cnt) = INFINITY; *rec_idx(s_rec, cnt) = 0;
         }
         __syncthreads();
 
@@ -427,9 +536,9 @@ forward_culled_kernel(FwdParams P)
         } else {
             // same positions, same cell order, same occupancy: only c = -ln(pv)/k follows the new depth range
             for (int pos = tid; pos < cnt; pos += FC_THREADS) {
-                const float* q = P.xyz + (size_t)(lo + s_idx[pos]) * 3;
+                const float* q = P.xyz + (size_t)(lo + *rec_idx(s_rec, pos)) * 3;
                 const float zr = rot_row(s_R + 6, __ldg(q), __ldg(q + 1), __ldg(q + 2));
-                s_c[pos] = __fmul_rn(logf(depth_weight_m(zr, zmin, range, (P.flags & FC_FLAG_HALF) != 0)), P.inv_negk);
+                *rec_c(s_rec, pos) = __fmul_rn(logf(depth_weight_m(zr, zmin, range, (P.flags & FC_FLAG_HALF) != 0)), P.inv_negk);
             }
             __syncthreads();
         }
@@ -438,96 +547,55 @@ forward_culled_kernel(FwdParams P)
         const int tiles_side = w / FC_TILE;
         for (int tile = 0; tile < tiles_side * tiles_side; ++tile) {
             const int trow0 = (tile / tiles_side) * FC_TILE, tcol0 = (tile % tiles_side) * FC_TILE;
-            if (tid == 0) { s_qfar = 0u; s_qnear = 0u; s_qhead = 0u; }
+            if (tid == 0) { s_qfar = 0u; s_qnear = 0u; s_qhead = 0u; s_work = 0u; }
             __syncthreads();
 
-            // ---- phase A: 3 x 3 cells, lane per pixel ----
-            for (int pl = tid; pl < FC_TPIX; pl += FC_THREADS) {
-                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+            // write one pixel: merge with what the earlier batches of a large cloud found, (value, lowest index)
+            auto put = [&](int row, int col, float val, int id) {
+                const size_t o = img_off + (size_t)row * w + col;
+                if (batch > 0) {
+                    const float pb = P.imgs[o];
+                    const int pid = P.winner ? P.winner[o] : 0;
+                    if (!(val > pb || (val == pb && id < pid))) { val = pb; id = pid; }
+                }
+                P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
+                if (P.winner) P.winner[o] = id;
+            };
+            auto geom = [&](int row, int col) {
                 PixelGeom g;
                 g.cx = pixel_centre(col, half); g.cy = pixel_centre(row, half);
                 g.ux = __fmul_rn(__fadd_rn(g.cx, 1.0f), FC_CELLS_PER_NDC);
                 g.uy = __fmul_rn(__fadd_rn(g.cy, 1.0f), FC_CELLS_PER_NDC);
-                const int ci = (int)g.uy, cj = (int)g.ux;
-                const float fx = g.ux - (float)cj, fy = g.uy - (float)ci;
-                const float edge = fminf(fminf(fx, 1.0f - fx), fminf(fy, 1.0f - fy));
-                const float cov = __fmul_rn(1.0f + edge, 1.0f / FC_CELLS_PER_NDC);
-                const float cov2 = __fmul_rn(__fmul_rn(cov, cov), 0.99999f);
-                const int j0 = max(cj - 1, 0), j1 = min(cj + 1, FC_G - 1);
-                float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
-                const int ring = s_ring[ci * FC_G + cj];
-                // nothing nearer than (ring - 1 + edge) cells: beyond the radius that can change the output?
-                const float dlb = __fmul_rn((float)(ring - 1) + edge, 1.0f / FC_CELLS_PER_NDC);
-                const bool blank = ring >= 2 && __fmul_rn(__fmul_rn(dlb, dlb), 0.99999f) > r2cap_all;
-                for (int i = max(ci - 1, 0); ring < 2 && i <= min(ci + 1, FC_G - 1); ++i) {
-                    const int rb = s_start[i * FC_G + j0], re = s_start[i * FC_G + j1 + 1];
-#pragma unroll 1
-                    for (int s = rb; s < re; ++s) {
-                        const float sc = score_of(S, s, g);
-                        s2 = fminf(s2, fmaxf(sc, s1));
-                        if (sc < s1) { s1 = sc; a1 = s; }
-                    }
-                }
-                const float m = score_margin(s1, inv_k);
-                const bool resolved = (s1 + m < cov2) && (s2 > s1 + m) && (__fmul_rn(s1, -P.negk) < FC_EXP_DENORM);
-                s_cand[pl] = (unsigned short)(a1 < 0 ? 0xFFFF : a1);
-                if (blank) {                              // background: value 0 (index 0), or what earlier batches found
-                    const size_t o = img_off + (size_t)row * w + col;
-                    float val = 0.0f; int id = 0;
-                    if (batch > 0) { val = P.imgs[o]; id = P.winner ? P.winner[o] : 0; }
-                    P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
-                    if (P.winner) P.winner[o] = id;
-                }
-                if (resolved) {
-                    int id;
-                    float val = exact_value(S, E, a1, g, id);
-                    const size_t o = img_off + (size_t)row * w + col;
-                    if (batch > 0) {                      // merge with the earlier batches: (value, lowest index)
-                        const float pb = P.imgs[o];
-                        const int pid = P.winner ? P.winner[o] : 0;
-                        if (!(val > pb || (val == pb && id < pid))) { val = pb; id = pid; }
-                    }
-                    P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
-                    if (P.winner) P.winner[o] = id;
-                }
-                // unresolved pixels: "far" ones (nothing within the window: the expensive scans) are queued
-                // from the front, the rest from the back; phase C drains front to back.
-                const bool far = !resolved && !blank && a1 < 0, near = !resolved && a1 >= 0;
-                const unsigned fm = __ballot_sync(0xFFFFFFFFu, far), nm = __ballot_sync(0xFFFFFFFFu, near);
-                if (fm | nm) {
-                    unsigned fb = 0, nb = 0;
-                    if (lane == 0) {
-                        if (fm) fb = atomicAdd(&s_qfar, (unsigned)__popc(fm));
-                        if (nm) nb = atomicAdd(&s_qnear, (unsigned)__popc(nm));
-                    }
-                    fb = __shfl_sync(0xFFFFFFFFu, fb, 0); nb = __shfl_sync(0xFFFFFFFFu, nb, 0);
-                    const unsigned lt = (1u << lane) - 1u;
-                    if (far) s_queue[fb + __popc(fm & lt)] = (unsigned short)pl;
-                    if (near) s_queue[FC_TPIX - 1 - (nb + __popc(nm & lt))] = (unsigned short)pl;
+                return g;
+            };
+
+            // ---- classification: background pixels are written, "far" pixels (no occupied cell within the 3 x 3 window:
+            // the long disc scans) are queued.  Rows are visited from the tile's top and bottom edges towards its middle,
+            // so the pixels farthest from a centred cloud enter the queue first: longest tasks first.
+            for (int vl = tid; vl < FC_TPIX; vl += FC_THREADS) {
+                const int vis = vl / FC_TILE;
+                const int rl = vis < 16 ? vis : (vis < 32 ? 79 - vis : (vis < 48 ? vis - 16 : 95 - vis));
+                const int row = trow0 + rl, col = tcol0 + vl % FC_TILE;
+                int ring; bool blank;
+                pixel_class(row, col, half, r2cap_all, s_ring, ring, blank);
+                if (blank) put(row, col, 0.0f, 0);        // background: value 0 (index 0), or what earlier batches found
+                const bool far = ring >= 2 && !blank;
+                const unsigned fm = __ballot_sync(0xFFFFFFFFu, far);
+                if (fm) {
+                    unsigned fb = 0;
+                    if (lane == 0) fb = atomicAdd(&s_qfar, (unsigned)__popc(fm));
+                    fb = __shfl_sync(0xFFFFFFFFu, fb, 0);
+                    if (far) s_queue[fb + __popc(fm & ((1u << lane) - 1u))] = (unsigned short)(rl * FC_TILE + vl % FC_TILE);
                 }
             }
             __syncthreads();
 
-            // ---- phase C: disc scan for the unresolved pixels ----
-            const int nfar = (int)s_qfar, qn = nfar + (int)s_qnear;
-            for (;;) {
-                int qi = 0;
-                if (lane == 0) qi = (int)atomicAdd(&s_qhead, 32u);
-                qi = __shfl_sync(0xFFFFFFFFu, qi, 0) + lane;
-                if (qi - lane >= qn) break;
-                if (qi >= qn) continue;
-                const int pl = qi < nfar ? s_queue[qi] : s_queue[FC_TPIX - 1 - (qi - nfar)];
+            // ---- disc scan of one queued pixel (far: no candidate; near: the best record of its 3 x 3 window) ----
+            auto scan_pixel = [&](int pl, int cand) {
                 const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
-                PixelGeom g;
-                g.cx = pixel_centre(col, half); g.cy = pixel_centre(row, half);
-                g.ux = __fmul_rn(__fadd_rn(g.cx, 1.0f), FC_CELLS_PER_NDC);
-                g.uy = __fmul_rn(__fadd_rn(g.cy, 1.0f), FC_CELLS_PER_NDC);
-                const size_t o = img_off + (size_t)row * w + col;
-                float prev = 0.0f; int prev_id = 0;
-                if (batch > 0) { prev = P.imgs[o]; prev_id = P.winner ? P.winner[o] : 0; }
+                const PixelGeom g = geom(row, col);
                 // nothing beyond r2cap can change the output of this pixel
                 const float r2cap = r2cap_all;
-                const int cand = s_cand[pl];
                 float s1 = cand == 0xFFFF ? INFINITY : score_of(S, cand, g), s2; int a1;
                 float val = 0.0f; int id = 0;
                 disc_scan<false>(S, E, g, fminf(r2cap, s1 + score_margin(s1, inv_k)), inv_k, s1, s2, a1, val, id);
@@ -549,9 +617,94 @@ forward_culled_kernel(FwdParams P)
                     }
                     if (val == 0.0f) id = 0;              // all-zero pixel: torch.max returns index 0
                 }
-                if (batch > 0 && !(val > prev || (val == prev && id < prev_id))) { val = prev; id = prev_id; }
-                P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
-                if (P.winner) P.winner[o] = id;
+                put(row, col, val, id);
+            };
+
+            // ---- one dynamic work list: the far batches first (long), then the 3 x 3 chunks (short, uniform) fill the
+            // gaps -- the heavy scans do not start after a barrier behind the 3 x 3 phase.
+            const int nfar = (int)s_qfar, far_batches = (nfar + 31) >> 5;
+            for (;;) {
+                int t = 0;
+                if (lane == 0) t = (int)atomicAdd(&s_work, 1u);
+                t = __shfl_sync(0xFFFFFFFFu, t, 0);
+                if (t >= far_batches + FC_TPIX / 32) break;
+                if (t < far_batches) {
+                    const int qi = t * 32 + lane;
+                    if (qi < nfar) scan_pixel(s_queue[qi], 0xFFFF);
+                    continue;
+                }
+                // ---- 3 x 3 cells, lane per pixel ----
+                const int pl = (t - far_batches) * 32 + lane;
+                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                const PixelGeom g = geom(row, col);
+                const int ci = (int)g.uy, cj = (int)g.ux;
+                const float fx = g.ux - (float)cj, fy = g.uy - (float)ci;
+                const float edge = fminf(fminf(fx, 1.0f - fx), fminf(fy, 1.0f - fy));
+                const float cov = __fmul_rn(1.0f + edge, 1.0f / FC_CELLS_PER_NDC);
+                const float cov2 = __fmul_rn(__fmul_rn(cov, cov), 0.99999f);
+                const int j0 = max(cj - 1, 0), j1 = min(cj + 1, FC_G - 1);
+                float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
+                const int ring = s_ring[ci * FC_G + cj];
+                bool found = false;
+                for (int i = max(ci - 1, 0); ring < 2 && i <= min(ci + 1, FC_G - 1); ++i) {
+                    const int rb = s_start[i * FC_G + j0], re = s_start[i * FC_G + j1 + 1];
+                    scan_run(S, rb, re, g, s1, s2, a1, found);
+                }
+                a1 = best_of_pair(S, a1, g);
+                const float m = score_margin(s1, inv_k);
+                const bool resolved = (s1 + m < cov2) && (s2 > s1 + m) && (__fmul_rn(s1, -P.negk) < FC_EXP_DENORM);
+                if (resolved) {
+                    int id;
+                    const float val = exact_value(S, E, a1, g, id);
+                    put(row, col, val, id);
+                }
+                // something in the 3 x 3 window, but not settled by it: the near queue
+                const bool near = !resolved && ring < 2;
+                const unsigned nm = __ballot_sync(0xFFFFFFFFu, near);
+                if (nm) {
+                    unsigned nb = 0;
+                    if (lane == 0) nb = atomicAdd(&s_qnear, (unsigned)__popc(nm));
+                    nb = __shfl_sync(0xFFFFFFFFu, nb, 0);
+                    if (near) s_queue[FC_TPIX - 1 - (nb + __popc(nm & ((1u << lane) - 1u)))] = (unsigned short)pl;
+                }
+            }
+            __syncthreads();
+
+            // ---- the near queue, 32 pixels at a time with all lanes busy: the 5 x 5 window, five row runs in lockstep.
+            // Typical case: the winner is a deep point (score offset c > 2.25 cells^2, i.e. pv < 0.53), so the 3 x 3 radius
+            // test can never pass although the winner is a cell away; 17 % of the pixels of a unit-ball view, none of them
+            // with a best score beyond the 5 x 5 reach of 6.25 cells^2.  What stays open takes the general disc scan.
+            const int nnear = (int)s_qnear;
+            for (;;) {
+                int qi = 0;
+                if (lane == 0) qi = (int)atomicAdd(&s_qhead, 32u);
+                qi = __shfl_sync(0xFFFFFFFFu, qi, 0) + lane;
+                if (qi - lane >= nnear) break;
+                if (qi >= nnear) continue;
+                const int pl = s_queue[FC_TPIX - 1 - qi];
+                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                const PixelGeom g = geom(row, col);
+                const int ci = (int)g.uy, cj = (int)g.ux;
+                const float fx = g.ux - (float)cj, fy = g.uy - (float)ci;
+                const float edge = fminf(fminf(fx, 1.0f - fx), fminf(fy, 1.0f - fy));
+                float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
+                bool found = false;
+                {
+                    const int j0 = max(cj - 2, 0), j1 = min(cj + 2, FC_G - 1);
+                    for (int i = max(ci - 2, 0); i <= min(ci + 2, FC_G - 1); ++i)
+                        scan_run(S, s_start[i * FC_G + j0], s_start[i * FC_G + j1 + 1], g, s1, s2, a1, found);
+                }
+                a1 = best_of_pair(S, a1, g);
+                const float cov = __fmul_rn(2.0f + edge, 1.0f / FC_CELLS_PER_NDC);
+                const float cov2 = __fmul_rn(__fmul_rn(cov, cov), 0.99999f);
+                const float m = score_margin(s1, inv_k);
+                if ((s1 + m < cov2) && (s2 > s1 + m) && (__fmul_rn(s1, -P.negk) < FC_EXP_DENORM)) {
+                    int id;
+                    const float val = exact_value(S, E, a1, g, id);
+                    put(row, col, val, id);
+                } else {
+                    scan_pixel(pl, a1 < 0 ? 0xFFFF : a1);
+                }
             }
             __syncthreads();
         }

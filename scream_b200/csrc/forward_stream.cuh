@@ -32,8 +32,8 @@ constexpr int FS_FILTER_CHUNK_MAX = 131072;              // points per CTA task 
 constexpr int FS_FILTER_CHUNK_MIN = 2048;
 constexpr int FS_CHUNK = 32768;                          // points per sampled chunk of S1
 constexpr int FS_SEED_CPB = 4;                           // sampled chunks per CTA of S1
-constexpr int FS_SURV_MIN = 4 * FC_CAP;                  // survivors kept per image: at least 49152, else total_pts / 16
-constexpr int64_t FS_MIN_AVG_PTS = 12 * FC_CAP;          // stream path when total_pts / B reaches this (147,456): measured crossover on
+constexpr int FS_SURV_MIN = 49152;                       // survivors kept per image: at least 49152, else total_pts / 16
+constexpr int64_t FS_MIN_AVG_PTS = 147456;          // stream path when total_pts / B reaches this (147,456): measured crossover on
                                                          // B200 between 120 k and 240 k points per item (profiles/r01q_sweep_stream.jsonl)
 constexpr float FS_DOWN = 1.0f - 1e-4f;                  // covers ex2.approx + argument rounding at |arg| <= 108
 constexpr float FS_UP = 1.0f + 1e-4f;
