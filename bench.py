@@ -163,31 +163,62 @@ def run_reference(args, rank: int):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": done, "warmup": args.warmup, "ms_per_step": 1e3 * total / done, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_dict(args.batch), "gpu_launches": 0,
+            "config": dict(config_dict(args.batch), sampled="1 pair x 1 of the 6 views per step (cost is linear in pairs and views): "
+                           "the reference asserts batch 1 (pointnet.py:39-40) and needs N x 4096 temporaries per view"),
+            "gpu_launches": 0,
             "gpoints_per_sec": val * N_PTS / 1e9,
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
+def counter_ball(lo: int, hi: int, seed: int, dev, chunk: int = 8_000_000):
+    """Points lo..hi-1 of a unit-ball cloud defined by a COUNTER-based generator (splitmix64 of the global point index, then
+    Box-Muller + cube-root radius, all elementwise fp32): point i has the same bits whichever slice it is generated in, so a
+    rank's shard IS a slice of the cloud every other world size renders."""
+    out = torch.empty((hi - lo, 3), dtype=torch.float32, device=dev)
+
+    def u01(idx, salt):
+        z = idx + ((seed * 0x632BE59BD9B4E019 + salt * 0x9E3779B97F4A7C15) & 0x7FFFFFFFFFFFFFFF)
+        z = (z ^ (z >> 30)) * -0x40A7B892E31B1A47          # 0xBF58476D1CE4E5B9 as int64
+        z = (z ^ (z >> 27)) * -0x6B2FB644ECCEEE15          # 0x94D049BB133111EB as int64
+        z = z ^ (z >> 31)
+        return (((z >> 20) & 0xFFFFFF).to(torch.float32) + 0.5) * (1.0 / 16777216.0)
+    for c0 in range(lo, hi, chunk):
+        c1 = min(hi, c0 + chunk)
+        idx = torch.arange(c0, c1, dtype=torch.int64, device=dev)
+        r1, r2 = torch.sqrt(-2.0 * torch.log(u01(idx, 1))), torch.sqrt(-2.0 * torch.log(u01(idx, 3)))
+        a1, a2 = 6.2831853 * u01(idx, 2), 6.2831853 * u01(idx, 4)
+        d = torch.stack([r1 * torch.cos(a1), r1 * torch.sin(a1), r2 * torch.cos(a2)], dim=1)
+        d = d / d.norm(dim=1, keepdim=True)
+        out[c0 - lo:c1 - lo] = d * u01(idx, 5).unsqueeze(1) ** (1.0 / 3.0)
+    return out
+
+
+def image_hash(val: torch.Tensor, winner: torch.Tensor) -> str:
+    """64-bit order-sensitive hash of a raw value image and its winner map (bit patterns, wrapping int64 arithmetic)."""
+    v = val.contiguous().view(torch.int32).to(torch.int64).reshape(-1)
+    w = winner.to(torch.int64).reshape(-1)
+    k = torch.arange(1, v.numel() + 1, dtype=torch.int64, device=v.device)
+    h = ((v * 1000003 + w) * (2 * k + 1)).sum() + (w * k).sum() * 7919
+    return f"{int(h.item()) & 0xFFFFFFFFFFFFFFFF:016x}"
+
+
+CFG5_SEED_SRC, CFG5_SEED_TGT = 9000, 9500
+
+
 def streaming_leg_sharded(dev, peak_gbs: float, rank: int, world: int, n: int = 100_000_000, n_views: int = 64, steps: int = 5):
-    """The same cfg5 cloud with its POINTS sharded over the ranks: every rank holds n / world points, the
-    z ranges are combined with all_reduce(MIN/MAX), every rank renders its shard through the giant-cloud path and one
-    all_reduce(MAX) over packed (value, index) keys merges the images -- bit-identical to the single-GPU render
-    (tests/test_shard_cpu.py, test_point_sharded_merge_equals_unsharded).  Strong scaling: total work fixed."""
+    """The cfg5 cloud of streaming_leg() with its POINTS sharded over the ranks: every rank holds a SLICE of the same
+    cloud (counter_ball), the z ranges are combined with all_reduce(MIN/MAX), every rank renders its shard through the
+    giant-cloud path and one all_reduce(MAX) over packed (value, index) keys merges the images.  Strong scaling: total work
+    fixed.  After the timed region rank 0 renders the WHOLE cloud on its own GPU and compares bit for bit."""
     import torch.distributed as dist
     from scream_b200 import synth
-    from scream_b200.render import render_cloud_point_sharded
+    from scream_b200.render import make_offsets, render_batch, render_cloud_point_sharded
     from scream_b200.shard import balanced_slice
     ns, nt = n // 2, n - n // 2
     (s0, s1), (t0, t1) = balanced_slice(ns, rank, world), balanced_slice(nt, rank, world)
-
-    def ball(count, seed):
-        g = torch.Generator(device=dev).manual_seed(seed)
-        d = torch.randn((count, 3), generator=g, device=dev)
-        d /= d.norm(dim=1, keepdim=True)
-        return (d * torch.rand((count, 1), generator=g, device=dev) ** (1.0 / 3.0)).contiguous()
-    src, tgt = ball(s1 - s0, 9000 + rank), ball(t1 - t0, 9500 + rank)
+    src, tgt = counter_ball(s0, s1, CFG5_SEED_SRC, dev), counter_ball(t0, t1, CFG5_SEED_TGT, dev)
     views = torch.from_numpy(synth.random_views(n_views, 5)).to(dev)
     run = lambda: render_cloud_point_sharded(src, tgt, s0, t0, views, RHO, W_IMG)
     for _ in range(3):
@@ -203,30 +234,43 @@ def streaming_leg_sharded(dev, peak_gbs: float, rank: int, world: int, n: int = 
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     alg = n_views * 12 * n + n_views * 2 * W_IMG * W_IMG * 8
+    h = image_hash(out[1], out[2])
+    identical = None
+    if rank == 0:                                   # the single-GPU render of the same cloud, outside the timed region
+        del src, tgt
+        torch.cuda.empty_cache()
+        xyz = torch.cat([counter_ball(0, ns, CFG5_SEED_SRC, dev), counter_ball(0, nt, CFG5_SEED_TGT, dev)], 0)
+        val1, win1, _ = render_batch(xyz, make_offsets([(ns, nt)]).to(dev), views, RHO, W_IMG, raw=True, need_winner=True, max_item_pts=n)
+        identical = bool(torch.equal(val1[0], out[1]) and torch.equal(win1[0].to(torch.int64), out[2]))
+        h1 = image_hash(val1[0], win1[0])
+        del xyz
+        torch.cuda.empty_cache()
     return {"workload": f"cfg5: one pair, 100 M points x 64 views, fwd + winner maps, points sharded over {world} GPUs "
                         "(all_reduce of the z ranges, all_reduce(MAX) of the packed key images)",
             "n_points": n, "views": n_views, "ms_per_step": ms, "steps": steps, "scaling": "strong",
             "gpoint_views_per_sec": n_views * n / ms / 1e6, "images_per_sec": 2 * n_views / ms * 1e3,
             "roofline": {"bound": "hbm", "achieved": alg / ms / 1e6, "peak": peak_gbs * world, "unit": "GB/s",
                          "frac": alg / ms / 1e6 / (peak_gbs * world), "algorithmic_bytes_per_step": alg,
-                         "note": "per-view accounting (SURVEY 8d), peak = measured single-GPU copy bandwidth x GPUs"},
-            "checksum": float(out[0].sum())}
+                         "note": "ALGORITHMIC throughput, per-view accounting of SURVEY 8d (a kernel that reads a point once for all 64 "
+                                 "views moves fewer bytes); peak = measured single-GPU copy bandwidth x GPUs",
+                         "frac_of_compulsory_traffic": STREAM_PASSES * 12 * n / ms / 1e6 / (peak_gbs * world)},
+            "hash": h, "identical_to_single_gpu": identical, "single_gpu_hash": h1 if rank == 0 else None}
+
+
+STREAM_PASSES = 8    # times the giant-cloud path reads the cloud from HBM (z-range 4 view groups, seed, box, filter, ...: DESIGN 5.2)
 
 
 def streaming_leg(dev, peak_gbs: float, n: int = 100_000_000, n_views: int = 64, steps: int = 5):
     """BASELINE.json configs[4] on one GPU (the regime where HBM is the roofline the metric names): one pair of n/2 +
-    n/2 unit-ball points, 64 random views, w = 64, rho = 24, forward with winner maps, inputs resident in HBM
-    (1.2 GB: ten times the L2).  Reported beside the cfg2 headline; SURVEY 8d's per-view accounting V*12*N + V*2*w^2*8."""
+    n/2 unit-ball points (counter_ball: the cloud the N > 1 runs shard), 64 random views, w = 64, rho = 24, forward with
+    winner maps, inputs resident in HBM (1.2 GB: ten times the L2).  SURVEY 8d's per-view accounting V*12*N + V*2*w^2*8."""
     from scream_b200 import synth
     from scream_b200.render import render_batch, make_offsets
-    g = torch.Generator(device=dev).manual_seed(1234 + 5)
-    d = torch.randn((n, 3), generator=g, device=dev)
-    d /= d.norm(dim=1, keepdim=True)
-    xyz = (d * torch.rand((n, 1), generator=g, device=dev) ** (1.0 / 3.0)).contiguous()
-    del d
-    offs = make_offsets([(n // 2, n - n // 2)]).to(dev)
+    ns, nt = n // 2, n - n // 2
+    xyz = torch.cat([counter_ball(0, ns, CFG5_SEED_SRC, dev), counter_ball(0, nt, CFG5_SEED_TGT, dev)], 0)
+    offs = make_offsets([(ns, nt)]).to(dev)
     views = torch.from_numpy(synth.random_views(n_views, 5)).to(dev)
-    run = lambda: render_batch(xyz, offs, views, RHO, W_IMG, need_winner=True, max_item_pts=n)
+    run = lambda: render_batch(xyz, offs, views, RHO, W_IMG, raw=True, need_winner=True, max_item_pts=n)
     for _ in range(3):
         run()
     torch.cuda.synchronize(dev)
@@ -243,18 +287,224 @@ def streaming_leg(dev, peak_gbs: float, n: int = 100_000_000, n_views: int = 64,
            "gpoint_views_per_sec": n_views * n / ms / 1e6, "images_per_sec": 2 * n_views / ms * 1e3,
            "roofline": {"bound": "hbm", "achieved": alg / ms / 1e6, "peak": peak_gbs, "unit": "GB/s",
                         "frac": alg / ms / 1e6 / peak_gbs, "algorithmic_bytes_per_step": alg,
-                        "note": "per-view accounting (SURVEY 8d); the strict compulsory traffic is 12*N per pass over the cloud"},
-           "checksum": float(out[0].sum())}
+                        "note": "ALGORITHMIC throughput, per-view accounting of SURVEY 8d (a kernel that reads a point once for all 64 "
+                                "views moves fewer bytes, so this is not physical HBM utilisation)",
+                        "frac_of_compulsory_traffic": STREAM_PASSES * 12 * n / ms / 1e6 / peak_gbs},
+           "hash": image_hash(out[0][0], out[1][0])}
     del xyz, out
     torch.cuda.empty_cache()
     return res
 
 
-def config_dict(B: int):
+def _timed(fn, steps, dev, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    return e0.elapsed_time(e1) / steps, (time.perf_counter() - t0) * 1e3 / steps
+
+
+def _alg_bytes(B, n, m, V, w, winner=True, bwd=True):
+    """forward V*12*(n+m) + V*2*w^2*4 (+ the same again for the winner map); backward V*2*w^2*8 + 12*(n+m)."""
+    img = V * 2 * w * w * 4
+    return B * (V * 12 * (n + m) + img * (2 if winner else 1)), (B * (2 * img + 12 * (n + m)) if bwd else 0)
+
+
+def _cpu_sample(src, tgt, rho, w, eulers, backward, block_frac=1.0):
+    """One reference render on the host cores (oracle/render_oracle.py, bit-identical to render.py): seconds."""
+    from oracle import render_oracle as orc
+    s, t = torch.from_numpy(src), torch.from_numpy(tgt)
+    t0 = time.perf_counter()
+    if backward:
+        sg = s.clone().requires_grad_(True)
+        out = orc.forward_dense(sg, t, rho, w, eulers)
+        out.backward(torch.ones_like(out))
+    else:
+        with torch.no_grad():
+            orc.forward_dense(s, t, rho, w, eulers)
+    return time.perf_counter() - t0
+
+
+def leg_cfg1(dev, peak, cpu: bool):
+    """BASELINE configs[0] -- the reference's own call pattern: ONE pair per call through the drop-in module
+    (RegistrationRender.forward, pointnet.py:39-40 asserts batch 1), n = m = 10,000 unit-ball points, rho 24, w 64, one
+    view ("single depth image") and the six stock views.  Launch-bound, not bandwidth-bound: device and wall time per call."""
+    from scream_b200 import synth
+    from scream_b200.render import RegistrationRender
+    src_h, tgt_h = synth.unit_ball(N_PTS, 4101), synth.unit_ball(N_PTS, 4102)
+    src, tgt = torch.from_numpy(src_h).to(dev), torch.from_numpy(tgt_h).to(dev)
+    out = {"workload": "cfg1: one 3DMatch-sized pair per call (n = m = 10000), RegistrationRender.forward, w 64, rho 24"}
+    for view, V in (("single", 1), ("muti", 6)):
+        r = RegistrationRender(RHO, W_IMG, view=view, device=dev)
+        g = torch.randn((V, 2, W_IMG, W_IMG), device=dev)
+
+        def fwd():
+            with torch.no_grad():
+                return r(src, tgt)
+
+        def fwd_bwd():
+            s = src.detach().requires_grad_(True)
+            r(s, tgt).backward(g)
+        f_dev, f_wall = _timed(fwd, 200, dev, warm=20)
+        b_dev, b_wall = _timed(fwd_bwd, 200, dev, warm=20)
+        fb, bb = _alg_bytes(1, N_PTS, N_PTS, V, W_IMG, winner=False)
+        out[f"views_{V}"] = {"fwd_us_device": 1e3 * f_dev, "fwd_us_wall": 1e3 * f_wall, "fwd_bwd_us_device": 1e3 * b_dev,
+                             "fwd_bwd_us_wall": 1e3 * b_wall, "images_per_sec_fwd": 2 * V / (f_dev / 1e3),
+                             "roofline": {"bound": "hbm", "achieved": fb / (f_dev / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
+                                          "frac": fb / (f_dev / 1e3) / 1e9 / peak, "algorithmic_bytes": fb,
+                                          "note": "one call = 0.27 MB (V=1): 42 ns at the HBM peak; a call is launch-latency bound"}}
+    if cpu:
+        from oracle import render_oracle as orc
+        _cpu_sample(src_h[:2000], tgt_h[:2000], RHO, W_IMG, orc.canonical_eulers("single"), False)
+        dt = _cpu_sample(src_h, tgt_h, RHO, W_IMG, orc.canonical_eulers("single"), False)
+        out["cpu_baseline"] = {"value": 2 / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": "1 pair, 1 view, forward (the reference's CPU-runnable case)", "ms_per_call": 1e3 * dt}
+    return out
+
+
+def leg_cfg3(dev, peak, cpu: bool, rank: int, world: int, B: int = 64):
+    """BASELINE configs[2]: KITTI-scale pairs (n = m = 15,000 bird's-eye slab points), ONE view eulers [0, pi, 0], rho 48
+    (train_kitti.py:47-48), batched, B pairs per GPU (items sharded over the ranks, no data-path collective): fake forward
+    (+ winner map) + backward + real (posed) forward -> 4 B depth images per step."""
+    from scream_b200 import synth
+    from scream_b200.render import make_offsets, render_batch, view_matrices
+    n = 15_000
+    parts = []
+    for i in range(B):
+        parts += [synth.kitti_slab(n, 5000 + 2 * (rank * B + i)), synth.kitti_slab(n, 5001 + 2 * (rank * B + i))]
+    xyz = torch.from_numpy(np.concatenate(parts, 0)).to(dev)
+    offs = make_offsets([(n, n)] * B).to(dev)
+    pose = torch.from_numpy(np.stack([synth.random_pose(6000 + i) for i in range(B)])).to(dev)
+    views = view_matrices([np.array([0, np.pi, 0])]).to(dev)
+    grad = torch.randn((B, 1, 2, W_IMG, W_IMG), device=dev)
+
+    def step():
+        x = xyz.detach().requires_grad_(True)
+        fake, _, _ = render_batch(x, offs, views, 48, W_IMG, need_winner=True, max_item_pts=2 * n)
+        fake.backward(grad)
+        with torch.no_grad():
+            render_batch(xyz, offs, views, 48, W_IMG, pose=pose, need_winner=False, max_item_pts=2 * n)
+    ms, _ = _timed(step, 10, dev)
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    f1, b1 = _alg_bytes(B, n, n, 1, W_IMG, winner=True)
+    f2, _ = _alg_bytes(B, n, n, 1, W_IMG, winner=False, bwd=False)
+    alg = f1 + b1 + f2
+    out = {"workload": f"cfg3: KITTI-scale, {B} pairs per GPU x (n = m = 15000 BEV slab), 1 view [0,pi,0], rho 48, w 64: "
+                       "fake fwd(+winner) + bwd + real(posed) fwd; items sharded over the GPUs",
+           "pairs_per_gpu": B, "n_gpus": world, "ms_per_step": ms, "images_per_sec": 4 * B * world / (ms / 1e3),
+           "gpoint_views_per_sec": 2 * 2 * n * B * world / (ms / 1e3) / 1e9,
+           "roofline": {"bound": "hbm", "achieved": alg / (ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
+                        "frac": alg / (ms / 1e3) / 1e9 / peak, "algorithmic_bytes_per_step_per_gpu": alg}}
+    if cpu:
+        from oracle import render_oracle as orc
+        dt = _cpu_sample(parts[0], parts[1], 48, W_IMG, [np.array([0, np.pi, 0])], True)
+        out["cpu_baseline"] = {"value": 2 / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": "1 pair (15000 + 15000), 1 view, forward + backward", "ms_per_call": 1e3 * dt}
+    return out
+
+
+def leg_cfg4(dev, peak, cpu: bool, B: int = 64):
+    """BASELINE configs[3]: OpenGG DSM-DEM patches (DSM = 100 x 100 regular grid: exact ties, dense per-pixel contention;
+    DEM = 6 x 6 coarse points), view="single" (pointnet.py:133), at w 64 / 128 / 256 with rho 24 / 36 / 72 (pointnet.py:35:
+    rho grows with w); B patches per launch, forward (+ winner map) + backward."""
+    from scream_b200 import synth
+    from scream_b200.render import make_offsets, render_batch
+    parts, sizes = [], []
+    for i in range(B):
+        dsm, dem = synth.opengg_patch(100, 7000 + i)
+        parts += [dsm, dem]; sizes.append((len(dsm), len(dem)))
+    xyz = torch.from_numpy(np.concatenate(parts, 0)).to(dev)
+    offs = make_offsets(sizes).to(dev)
+    views = torch.eye(3, device=dev)[None].contiguous()
+    n, m = sizes[0]
+    out = {"workload": f"cfg4: {B} OpenGG patches per launch (DSM 100 x 100 grid + DEM 6 x 6), 1 orthographic view, fwd(+winner) + bwd"}
+    for w, rho in ((64, 24), (128, 36), (256, 72)):
+        grad = torch.randn((B, 1, 2, w, w), device=dev)
+
+        def step():
+            x = xyz.detach().requires_grad_(True)
+            imgs, _, _ = render_batch(x, offs, views, rho, w, need_winner=True, max_item_pts=n + m)
+            imgs.backward(grad)
+        ms, _ = _timed(step, 10, dev)
+        f, b = _alg_bytes(B, n, m, 1, w, winner=True)
+        out[f"w{w}_rho{rho}"] = {"ms_per_step": ms, "images_per_sec": 2 * B / (ms / 1e3), "gpixels_per_sec": 2 * B * w * w / (ms / 1e3) / 1e9,
+                                 "roofline": {"bound": "hbm", "achieved": (f + b) / (ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
+                                              "frac": (f + b) / (ms / 1e3) / 1e9 / peak, "algorithmic_bytes_per_step": f + b}}
+    if cpu:
+        from oracle import render_oracle as orc
+        dt = _cpu_sample(parts[0], parts[1], 36, 128, orc.canonical_eulers("single"), False)
+        out["cpu_baseline"] = {"value": 2 / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": "1 patch, w 128, rho 36, forward", "ms_per_call": 1e3 * dt}
+    return out
+
+
+def gpu_eager_baseline(dev):
+    """SURVEY 8d's secondary comparator: the reference's own op sequence (oracle/render_oracle.forward_dense = render.py:61-73
+    restated op for op) run by stock PyTorch eager ON THE GPU -- what a SCREAM user gets today.  One pair x 6 views, forward."""
+    from oracle import render_oracle as orc
+    from scream_b200 import synth
+    src = torch.from_numpy(synth.unit_ball(N_PTS, 4101)).to(dev)
+    tgt = torch.from_numpy(synth.unit_ball(N_PTS, 4102)).to(dev)
+    eul = orc.canonical_eulers("muti")
+
+    def fwd():
+        with torch.no_grad():
+            return orc.forward_dense(src, tgt, RHO, W_IMG, eul)
+    try:
+        ms, wall = _timed(fwd, 3, dev, warm=1)
+    except Exception as e:                                  # noqa: BLE001  (a comparator must not take the bench down)
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+    torch.cuda.empty_cache()
+    return {"workload": "stock PyTorch eager on the B200, the reference's op sequence: 1 pair (10000 + 10000) x 6 views, forward",
+            "ms_per_call_device": ms, "ms_per_call_wall": wall, "images_per_sec": 12 / (wall / 1e3)}
+
+
+def copy_probe(dev, h2d_bytes: int, d2h_bytes: int, chunks: int, streams: int, world: int):
+    """The e2e leg's own bound: the same bytes through pinned host memory with NO kernels in between -- one
+    cudaMemcpyAsync per chunk buffer, H2D and D2H on `streams` CUDA streams, as the pipeline issues them."""
+    h_in = torch.empty(h2d_bytes // chunks, dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(d2h_bytes // chunks, dtype=torch.uint8).pin_memory()
+    d_in = [torch.empty_like(h_in, device=dev) for _ in range(streams)]
+    d_out = [torch.empty(d2h_bytes // chunks, dtype=torch.uint8, device=dev) for _ in range(streams)]
+    sts = [torch.cuda.Stream(dev) for _ in range(streams)]
+
+    def step():
+        cur = torch.cuda.current_stream(dev)
+        for i in range(chunks):
+            st = sts[i % streams]
+            st.wait_stream(cur)
+            with torch.cuda.stream(st):
+                d_in[i % streams].copy_(h_in, non_blocking=True)
+                h_out.copy_(d_out[i % streams], non_blocking=True)
+        for st in sts:
+            cur.wait_stream(st)
+    ms, _ = _timed(step, 10, dev)
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def config_dict(B: int, world: int = 1, gather: bool = False):
+    par = "one GPU" if world == 1 else ("items sharded over the GPUs; every step ends with the all_gather of the depth images and the "
+                                        "all_reduce of the statistics (NCCL, overlapped with the next step)" if gather else
+                                        "items sharded over the GPUs, no collective in the timed step (--no-gather)")
     return {"workload": "cfg2: 3DMatch training-batch render, fake fwd(+winner)+bwd and real(posed) fwd",
             "pairs_per_gpu": B, "cloud": CLOUD, "n_src": N_PTS, "n_tgt": N_PTS, "views": V, "w": W_IMG, "rho": RHO,
             "images_per_step_per_gpu": 24 * B, "cache": "inputs+outputs per step exceed the 126 MB L2 (B>=512)",
-            "parallelism": "items sharded over GPUs, no data-path collective"}
+            "parallelism": par}
 
 
 # --------------------------------------------------------------------------------------------
@@ -279,8 +529,34 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     e2e_dual = not dense and not args.no_e2e_dual        # host-buffer leg (StepPipeline): dual launches per chunk by default
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
+    # N > 1: the step ends with the gather north_star names -- every rank receives every rank's depth images (fake and
+    # real, [world*B,V,2,w,w] each) and the summed validation statistics.  The collectives are launched asynchronously
+    # (NCCL's own stream) and overlap the next step's kernels; all of them are waited for inside the timed region.
+    gather = {"on": world > 1 and not args.no_gather, "pending": [], "bufs": None}
+    if gather["on"]:
+        gather["bufs"] = [[torch.empty((world * B, V, 2, W_IMG, W_IMG), device=dev) for _ in range(2)] for _ in range(2)]
+
+    def gather_step(i, fake, real):
+        for h in gather["pending"]:                # at most one step's collectives in flight behind the current one
+            h.wait()
+        out = gather["bufs"][i % 2]
+        stats = torch.stack([fake.detach().sum(dtype=torch.float64), real.sum(dtype=torch.float64)])
+        gather["pending"] = [dist.all_gather_into_tensor(out[0], fake.detach(), async_op=True),
+                             dist.all_gather_into_tensor(out[1], real, async_op=True),
+                             dist.all_reduce(stats, async_op=True)]
+        gather["keep"] = (fake, real, stats)
+
+    step_no = [0]
+
     def step_device(rec=None):
-        """fake fwd(+winner) -> bwd -> real fwd, inputs resident in HBM."""
+        """fake fwd(+winner) -> bwd -> real fwd, inputs resident in HBM (-> gather of the images at N > 1)."""
+        out = step_render(rec)
+        if gather["on"]:
+            gather_step(step_no[0], out[0], out[1])
+            step_no[0] += 1
+        return out
+
+    def step_render(rec=None):
         x = xyz.detach().requires_grad_(True)
         if rec is not None:
             e = [ev() for _ in range(6)]; e[0].record()
@@ -330,6 +606,9 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         e0.record()
         for _ in range(steps):
             fn(rec) if rec is not None else fn()
+        for h in gather["pending"]:                # the last step's gather belongs to the timed region
+            h.wait()
+        gather["pending"] = []
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -345,9 +624,27 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     rec = []
     ms = timed(step_device, args.steps, rec)
     clocks = sampler.stop() if rank == 0 else None
+    ms_nogather, gather_ms = ms, 0.0
+    if gather["on"]:                                # the same step without the collectives, and the collectives alone
+        gather["on"] = False
+        ms_nogather = timed(step_device, args.steps)
+        fake, real, _ = step_render()
+        bufs = gather["bufs"][0]
+
+        def only_gather():
+            dist.all_gather_into_tensor(bufs[0], fake.detach())
+            dist.all_gather_into_tensor(bufs[1], real)
+        gather_ms = timed(only_gather, args.steps) / args.steps
+        gather["on"] = True
+    gather["bufs"] = None
+    torch.cuda.empty_cache()
     for _ in range(2):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
+    h2d = int(h_xyz.numel() * 4 + h_pose.numel() * 4 + h_grad.numel() * 4)
+    d2h = int(h_fake.numel() * 4 * 2 + h_gxyz.numel() * 4)
+    n_chunks = (B + args.chunk - 1) // args.chunk
+    copy_ms = copy_probe(dev, h2d, d2h, n_chunks, args.streams, world)
 
     imgs_step = 24 * B * world
     value = imgs_step * args.steps / (ms / 1e3)
@@ -367,21 +664,28 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         if t.get("pairs_per_gpu") == B and t.get("cloud") == CLOUD and not dense:
             traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     ach = (b_fake + b_real) / ((t_fake + t_real) / 1e3) / 1e9
+    del pipe
+    torch.cuda.empty_cache()
+    cfg3 = None if args.no_legs else leg_cfg3(dev, peak, world == 1 and not args.no_cpu and rank == 0, rank, world)
     streaming = None
     if world > 1 and not args.no_stream_leg:           # every rank takes part in the collectives
-        del pipe
-        torch.cuda.empty_cache()
         streaming = streaming_leg_sharded(dev, peak, rank, world)
     if rank != 0:
         return
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_dict(B),
+            "config": config_dict(B, world, gather["on"]),
             "gpoints_per_sec": value * N_PTS / 1e9,
+            "gather": None if world == 1 else {
+                "in_timed_step": bool(gather["on"]), "what": "all_gather of the fake and the real images to every rank + all_reduce of the statistics, asynchronous (overlaps the next step)",
+                "bytes_received_per_rank_per_step": int(2 * world * B * V * 2 * W_IMG * W_IMG * 4),
+                "gather_ms": gather_ms, "ms_per_step_without_gather": ms_nogather / args.steps,
+                "value_without_gather": imgs_step * args.steps / (ms_nogather / 1e3)},
             "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                    "h2d_bytes_per_step": int(h_xyz.numel() * 4 + h_pose.numel() * 4 + h_grad.numel() * 4),
-                    "d2h_bytes_per_step": int(h_fake.numel() * 4 * 2 + h_gxyz.numel() * 4),
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "copy_roofline_ms": copy_ms, "frac_of_copy_roofline": copy_ms / (ms_e2e / args.steps),
+                    "copy_roofline": "the same H2D + D2H bytes through pinned memory, one cudaMemcpyAsync per chunk buffer on the same streams, no kernels",
                     "api": f"scream_b200.pipeline.StepPipeline(chunk_pairs={args.chunk}, n_streams={args.streams}{", dual=True" if e2e_dual else ""})"},
             "gpu_launches": args.steps * (4 if dual else 7),
             "kernel": "dense" if dense else ("culled, dual launch (SCREAM_F_DUAL)" if dual else "culled"),
@@ -390,7 +694,17 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": {"fwd_fake": b_fake, "fwd_real": b_real, "bwd": b_bwd},
                          "ms_per_launch": {"fwd_fake": t_fake, "bwd": t_bwd, "fwd_real": t_real}},
+            "roofline_bwd": {"bound": "hbm", "kernel": "backward_scatter_kernel (L2 RED.ADD.F32 through the winner map)",
+                             "achieved": b_bwd / (t_bwd / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
+                             "frac": b_bwd / (t_bwd / 1e3) / 1e9 / peak},
             "clocks": clocks}
+    cpu_legs = world == 1 and not args.no_cpu
+    if not args.no_legs:
+        line["legs"] = {"cfg1": leg_cfg1(dev, peak, cpu_legs), "cfg4": leg_cfg4(dev, peak, cpu_legs)}
+        if world == 1:
+            line["gpu_eager_baseline"] = gpu_eager_baseline(dev)
+    if cfg3 is not None:
+        line.setdefault("legs", {})["cfg3"] = cfg3
     if world == 1 and not args.no_stream_leg:
         line["streaming"] = streaming_leg(dev, peak)
     elif streaming is not None:
@@ -421,6 +735,8 @@ def main():
     ap.add_argument("--dual", action="store_true", help="device-resident leg: fake + real render in one launch (SCREAM_F_DUAL, SURVEY 8 f1)")
     ap.add_argument("--no-e2e-dual", action="store_true", help="host-buffer leg: two forward calls per chunk instead of one dual launch")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-legs", action="store_true", help="skip the cfg1 / cfg3 / cfg4 legs and the GPU-eager comparator")
+    ap.add_argument("--no-gather", action="store_true", help="N > 1: leave the all_gather of the images out of the timed step")
     ap.add_argument("--no-stream-leg", action="store_true", help="skip the cfg5 streaming-regime leg (one GPU: the whole cloud; N > 1: its points sharded over the ranks)")
     ap.add_argument("--chunk", type=int, default=37, help="pairs per chunk of the host-buffer pipeline (e2e leg)")
     ap.add_argument("--streams", type=int, default=6, help="CUDA streams of the host-buffer pipeline (e2e leg)")
@@ -444,6 +760,7 @@ def main():
     finally:
         if world > 1:
             import torch.distributed as dist
+            dist.barrier()                              # rank 0 runs the single-GPU legs after the collective ones
             dist.destroy_process_group()
 
 

@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define SCREAM_ABI_VERSION 7
+#define SCREAM_ABI_VERSION 8
 
 /* error codes */
 #define SCREAM_OK            0
@@ -115,6 +115,23 @@ int scream_render_backward(const float *xyz, const int64_t *offs, int64_t total_
                            const float *grad_imgs, const int32_t *winner, const float *zrange,
                            float *grad_xyz,
                            void *ws, size_t ws_bytes, scream_stream_t stream);
+
+/* One pair per call -- the reference's own call pattern: RegistrationRender.forward(src_pred, tgt_pcd), render.py:61-73, is
+ * handed the two clouds as two tensors and pointnet.py:39-40 asserts batch 1.  src [n,3], tgt [m,3] are separate device
+ * buffers (no torch.cat of render.py:63, no offsets); pose [3,4] or NULL; imgs [V,2,w,w], winner [V,2,w,w] or NULL, zrange
+ * [V,2] or NULL (output).  ONE kernel launch: every CTA reduces the depth range of render.py:30-31 itself, and each image is
+ * shared by up to 8 CTAs (a 6-view pair fills 96 SMs instead of 12).  Same bits as scream_render_forward on the
+ * concatenated pair.  flags: SCREAM_F_RAW, SCREAM_F_HALF.  n + m < 147456 (giant pairs: scream_render_forward). */
+int scream_render_forward_pair(const float *src, int64_t n, const float *tgt, int64_t m,
+                               const float *pose, const float *views, int V, int w, double rho, unsigned flags,
+                               float *imgs, int32_t *winner, float *zrange, scream_stream_t stream);
+
+/* ... and its backward: grad_src [n,3], grad_tgt [m,3] (overwritten), the gradient w.r.t. both inputs as the reference's
+ * autograd returns it (render.py:63's cat routes it to the two tensors). */
+int scream_render_backward_pair(const float *src, int64_t n, const float *tgt, int64_t m,
+                                const float *pose, const float *views, int V, int w, double rho, unsigned flags,
+                                const float *grad_imgs, const int32_t *winner, const float *zrange,
+                                float *grad_src, float *grad_tgt, scream_stream_t stream);
 
 /* fp16 (autocast) input mode, stage 1 (replaces the fp16 torch.matmul of render.py:68 under
  * train_kitti.py:154's autocast): every item's clouds rotated by every view with fp16 operands, fp32 accumulation and an

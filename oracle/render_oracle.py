@@ -147,10 +147,10 @@ def forward_dense(src: torch.Tensor, tgt: torch.Tensor, rho, w: int,
                   eulers: Iterable[Sequence[float]]) -> torch.Tensor:
     """[V,2,w,w] in [-1,1): RegistrationRender.forward, render.py:61-73. Differentiable."""
     pts = torch.cat([src, tgt], dim=0)
-    centres = pixel_centres(w)
+    centres = pixel_centres(w).to(pts.device)              # render.py:15: pix_xy lives on the module's device
     out = []
     for e in eulers:
-        view = torch.Tensor(Rotation.from_euler("zyx", e).as_matrix())
+        view = torch.Tensor(Rotation.from_euler("zyx", e).as_matrix()).to(pts.device)   # render.py:67
         img = render_dense(rotate(view, pts), src.shape[0], rho, w, centres)
         out.append((img - 0.5) / 0.5)
     return torch.stack(out, dim=0).contiguous()

@@ -11,7 +11,7 @@ import threading
 
 from .csrc import build as _build
 
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 F_RAW = 1
 F_DENSE = 2
@@ -33,6 +33,10 @@ _SIGNATURES = {
                                         C.c_double, C.c_uint, _P, _P, _P, _P, C.c_size_t, _P]),
     "scream_render_backward": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, C.c_int, C.c_int, C.c_int,
                                          C.c_double, C.c_uint, _P, _P, _P, _P, _P, C.c_size_t, _P]),
+    "scream_render_forward_pair": (C.c_int, [_P, C.c_int64, _P, C.c_int64, _P, _P, C.c_int, C.c_int, C.c_double, C.c_uint,
+                                             _P, _P, _P, _P]),
+    "scream_render_backward_pair": (C.c_int, [_P, C.c_int64, _P, C.c_int64, _P, _P, C.c_int, C.c_int, C.c_double, C.c_uint,
+                                              _P, _P, _P, _P, _P, _P]),
     "scream_render_transform": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, C.c_int, C.c_int,
                                           _P, _P, _P, _P, C.c_size_t, _P]),
     "scream_half_rotate": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, C.c_int, C.c_int, _P, _P, _P]),

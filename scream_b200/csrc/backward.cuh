@@ -19,6 +19,8 @@ struct BwdParams {
     unsigned flags;
     const float* grad_imgs; const int32_t* winner; const float* zrange;
     float* grad_xyz;
+    // pair mode (offs == nullptr; see FwdParams): virtual bases of the target cloud and of its gradient, sizes by value
+    const float* xyz_t; float* grad_t; int64_t pair_n, pair_m;
 };
 
 constexpr int BW_THREADS = 256;
@@ -47,9 +49,10 @@ backward_scatter_kernel(BwdParams P)
     if (wi < 0 || G == 0.0f) return;
     if (!(P.flags & 1u)) G *= 2.0f;
 
-    const ItemSpan sp = item_span(P.offs, b);
+    const ItemSpan sp = item_span(P.offs, b, P.pair_n, P.pair_m);
     const int64_t gi = (c ? sp.tgt0 : sp.src0) + wi;
-    float x = P.xyz[gi * 3], y = P.xyz[gi * 3 + 1], z = P.xyz[gi * 3 + 2];
+    const float* xyz = (c && P.xyz_t != nullptr) ? P.xyz_t : P.xyz;
+    float x = xyz[gi * 3], y = xyz[gi * 3 + 1], z = xyz[gi * 3 + 2];
     if (posed) apply_pose(s_pose, x, y, z);
     const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z), zr = rot_row(s_R + 6, x, y, z);
     const float zmin = P.zrange[((size_t)b * P.V + v) * 2], zmax = P.zrange[((size_t)b * P.V + v) * 2 + 1];
@@ -72,7 +75,7 @@ backward_scatter_kernel(BwdParams P)
         float h2 = s_pose[2] * g0 + s_pose[6] * g1 + s_pose[10] * g2;
         g0 = h0; g1 = h1; g2 = h2;
     }
-    float* dst = P.grad_xyz + gi * 3;
+    float* dst = ((c && P.grad_t != nullptr) ? P.grad_t : P.grad_xyz) + gi * 3;
     atomicAdd(dst, g0); atomicAdd(dst + 1, g1); atomicAdd(dst + 2, g2);
 }
 

@@ -97,5 +97,10 @@ struct ItemSpan { int64_t src0, tgt0, end; };
 __device__ __forceinline__ ItemSpan item_span(const int64_t* __restrict__ offs, int b) {
     ItemSpan s; s.src0 = offs[2 * b]; s.tgt0 = offs[2 * b + 1]; s.end = offs[2 * b + 2]; return s;
 }
+// pair mode (one item, the two clouds in separate buffers, sizes by value): offs == nullptr
+__device__ __forceinline__ ItemSpan item_span(const int64_t* __restrict__ offs, int b, int64_t pair_n, int64_t pair_m) {
+    if (offs != nullptr) return item_span(offs, b);
+    ItemSpan s; s.src0 = 0; s.tgt0 = pair_n; s.end = pair_n + pair_m; return s;
+}
 
 }  // namespace scream

@@ -36,6 +36,8 @@ namespace scream {
 constexpr int FC_THREADS = 1024;
 constexpr int FC_PPT = 12;                               // points per thread per batch
 constexpr int FC_CAP = FC_THREADS * FC_PPT;              // 12288 points per batch
+constexpr int FC_NEAR_SPREAD = 0;                        // near queue spread over all warps also when the GPU is full (A/B)
+constexpr int FC_AHEAD = 2;                              // points whose global loads are in flight ahead of the one in work (P1, P3)
 constexpr int FC_G = 64;                                 // cell grid side
 constexpr int FC_CELLS = FC_G * FC_G;
 constexpr int FC_TILE = 64;                              // pixel tile side of P4
@@ -280,6 +282,11 @@ __device__ __forceinline__ void disc_scan(const FcShared& S, const ExactCtx& E, 
     if (!EXACT) a1 = best_of_pair(S, a1, g);             // the search tracked the best PAIR
 }
 
+// Visiting order of a tile's 64 pixel rows: from the top and bottom edges towards the middle (the pixels farthest from a
+// centred cloud, i.e. the longest disc scans, first).  lpt_row: visiting index -> row; lpt_vis: its inverse.
+__device__ __forceinline__ int lpt_row(int vis) { return vis < 16 ? vis : (vis < 32 ? 79 - vis : (vis < 48 ? vis - 16 : 95 - vis)); }
+__device__ __forceinline__ int lpt_vis(int row) { return row < 16 ? row : (row < 32 ? row + 16 : (row < 48 ? 95 - row : 79 - row)); }
+
 // a pixel whose nearest occupied cell is `ring` cells away (Chebyshev) has no point nearer than (ring - 1 + edge) cells:
 // beyond the radius that can change the output it is background
 __device__ __forceinline__ bool blank_pixel(int ring, float edge, float r2cap_all) {
@@ -312,7 +319,7 @@ forward_culled_kernel(FwdParams P)
     unsigned short* s_queue = s_cand + FC_TPIX;
     __shared__ float s_R[9], s_pose[12];
     __shared__ unsigned s_warp_tot[FC_THREADS / 32];
-    __shared__ unsigned s_qfar, s_qnear, s_qhead, s_work;
+    __shared__ unsigned s_qfar, s_qnear, s_qhead, s_work, s_zr[2];
     __shared__ unsigned long long s_rowmask[FC_G], s_blockmask[FC_G / 4];
     __shared__ unsigned char s_ring[FC_CELLS];            // Chebyshev distance (cells) to the nearest occupied cell
 
@@ -325,6 +332,10 @@ forward_culled_kernel(FwdParams P)
     // source + target), i.e. through the score offsets c.
     const bool dual = (P.flags & FC_FLAG_DUAL) != 0u;
     int bid = blockIdx.x, c, pass0 = 0, pass1 = 1;
+    // nparts CTAs share an image (small grids: one pair per call is 12 images on 148 SMs): every one of them sorts the whole
+    // cloud, then takes the 32-pixel chunks c with c % nparts == part -- the sort is a fifth of the work, the search scales
+    const int nparts = P.nparts, part = bid % nparts;
+    bid /= nparts;
     if (!dual) { c = bid % 2; bid /= 2; }
     else {
         const int job = bid % 3; bid /= 3;
@@ -335,9 +346,11 @@ forward_culled_kernel(FwdParams P)
     const int b = bid / P.V;
 
     if (tid < 9) s_R[tid] = P.views[(size_t)v * 9 + tid];
-    if (P.pose != nullptr && c == 0 && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    if (P.pose != nullptr && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    if (tid == 64) { s_zr[0] = 0xFFFFFFFFu; s_zr[1] = 0u; }
 
-    const ItemSpan sp = item_span(P.offs, b);
+    const ItemSpan sp = item_span(P.offs, b, P.pair_n, P.pair_m);
+    const float* xyz_c = (c && P.xyz_t != nullptr) ? P.xyz_t : P.xyz;      // base of this CTA's cloud
     const int64_t lo = c ? sp.tgt0 : sp.src0, hi = c ? sp.end : sp.tgt0;
     // giant clouds (forward_stream.cuh): render the survivor list of this image instead of the whole cloud,
     // unless the list overflowed.  npts = number of points to render, pidx(j) = cloud-local index of the j-th.
@@ -369,11 +382,35 @@ forward_culled_kernel(FwdParams P)
     // outputs and depth range of this pass (dual: item pass * B + b of the pose-major outputs)
     const size_t ob = dual ? (size_t)pass * P.B + b : (size_t)b;
     const bool posed = (dual ? pass == 1 : P.pose != nullptr) && c == 0;
-    const float zmin = dec_f32(P.zenc[(ob * P.V + v) * 2]);
-    const float zmax = dec_f32(P.zenc[(ob * P.V + v) * 2 + 1]);
+    if (P.fuse_zrange) {
+        // render.py:30-31 inside this kernel: min / max of the rotated depth over BOTH clouds of the item (order-preserving
+        // integer codes: exact in any order, so every CTA of the item finds the same bits)
+        unsigned zl = 0xFFFFFFFFu, zh = 0u;
+        for (int64_t i0 = sp.src0 + tid; i0 < sp.end; i0 += 4 * FC_THREADS) {      // four points in flight per thread
+            float x[4], y[4], z[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t i = i0 + u * FC_THREADS < sp.end ? i0 + u * FC_THREADS : i0;      // tail: the first point again
+                const float* q = ((i >= sp.tgt0 && P.xyz_t != nullptr) ? P.xyz_t : P.xyz) + (size_t)i * 3;
+                x[u] = __ldg(q); y[u] = __ldg(q + 1); z[u] = __ldg(q + 2);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t i = i0 + u * FC_THREADS < sp.end ? i0 + u * FC_THREADS : i0;
+                if (P.pose != nullptr && i < sp.tgt0) apply_pose(s_pose, x[u], y[u], z[u]);
+                const unsigned e = enc_f32(rot_row(s_R + 6, x[u], y[u], z[u]));
+                zl = min(zl, e); zh = max(zh, e);
+            }
+        }
+        zl = __reduce_min_sync(0xFFFFFFFFu, zl); zh = __reduce_max_sync(0xFFFFFFFFu, zh);
+        if (lane == 0) { atomicMin(&s_zr[0], zl); atomicMax(&s_zr[1], zh); }
+        __syncthreads();
+    }
+    const float zmin = dec_f32(P.fuse_zrange ? s_zr[0] : P.zenc[(ob * P.V + v) * 2]);
+    const float zmax = dec_f32(P.fuse_zrange ? s_zr[1] : P.zenc[(ob * P.V + v) * 2 + 1]);
     const float range = z_range(zmin, zmax);
     const size_t img_off = ((ob * P.V + v) * 2 + c) * npix;
-    if (P.zrange && c == 0 && tid == 0) {
+    if (P.zrange && c == 0 && part == 0 && tid == 0) {
         P.zrange[(ob * P.V + v) * 2] = zmin;
         P.zrange[(ob * P.V + v) * 2 + 1] = zmax;
     }
@@ -386,7 +423,7 @@ forward_culled_kernel(FwdParams P)
         }
         continue;                                         // uniform over the CTA
     }
-    ExactCtx E; E.xyz = P.xyz; E.lo = lo; E.R = s_R; E.pose = s_pose; E.posed = posed;
+    ExactCtx E; E.xyz = xyz_c; E.lo = lo; E.R = s_R; E.pose = s_pose; E.posed = posed;
     E.zmin = zmin; E.range = range; E.negk = P.negk; E.f16 = (P.flags & FC_FLAG_HALF) != 0;
     // the target's second pass keeps the sorted records of the first (one batch only) and renews the score offsets
     const bool resort = !(pass > pass0 && npts <= (int64_t)FC_CAP);
@@ -403,23 +440,24 @@ forward_culled_kernel(FwdParams P)
         for (int t = tid; t < FC_CELLS + 4; t += FC_THREADS) s_hist[t] = 0u;
         __syncthreads();
         unsigned packed[FC_PPT];                          // (cell << 16) | rank inside the cell
-        // the loads of point k + 1 are in flight while point k is binned (a thread that walks its points strictly one by
-        // one exposes 12 serial L2 round trips here and 12 more in P3)
+        // the loads of points k + 1 .. k + FC_AHEAD are in flight while point k is binned (a thread that walks its points
+        // strictly one by one exposes 12 serial L2 round trips here and 12 more in P3)
         auto fetch = [&](int k, float& x, float& y, float& z, int& id) {
             const int j = k * FC_THREADS + tid;
             if (j < cnt) {
                 const int64_t pi = surv ? (int64_t)__ldg(surv + c0 + j) : c0 + j;
-                const float* q = P.xyz + (size_t)(lo + pi) * 3;
+                const float* q = xyz_c + (size_t)(lo + pi) * 3;
                 x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2); id = (int)pi;
             }
         };
         {
-            float nx = 0.f, ny = 0.f, nz = 0.f; int nid = 0;
-            fetch(0, nx, ny, nz, nid);
+            float nx[FC_AHEAD], ny[FC_AHEAD], nz[FC_AHEAD]; int nid[FC_AHEAD];
+#pragma unroll
+            for (int a = 0; a < FC_AHEAD; ++a) { nx[a] = ny[a] = nz[a] = 0.f; nid[a] = 0; fetch(a, nx[a], ny[a], nz[a], nid[a]); }
 #pragma unroll
             for (int k = 0; k < FC_PPT; ++k) {
-                float x = nx, y = ny, z = nz;
-                if (k + 1 < FC_PPT) fetch(k + 1, nx, ny, nz, nid);
+                float x = nx[k % FC_AHEAD], y = ny[k % FC_AHEAD], z = nz[k % FC_AHEAD];
+                if (k + FC_AHEAD < FC_PPT) fetch(k + FC_AHEAD, nx[k % FC_AHEAD], ny[k % FC_AHEAD], nz[k % FC_AHEAD], nid[k % FC_AHEAD]);
                 packed[k] = 0xFFFFFFFFu;
                 if (k * FC_THREADS + tid < cnt) {
                     if (posed) apply_pose(s_pose, x, y, z);
@@ -480,12 +518,13 @@ forward_culled_kernel(FwdParams P)
             if (lane == 0) s_blockmask[wq] = bm;
         }
         {
-            float nx = 0.f, ny = 0.f, nz = 0.f; int nid = 0;
-            fetch(0, nx, ny, nz, nid);
+            float nx[FC_AHEAD], ny[FC_AHEAD], nz[FC_AHEAD]; int nid[FC_AHEAD];
+#pragma unroll
+            for (int a = 0; a < FC_AHEAD; ++a) { nx[a] = ny[a] = nz[a] = 0.f; nid[a] = 0; fetch(a, nx[a], ny[a], nz[a], nid[a]); }
 #pragma unroll
             for (int k = 0; k < FC_PPT; ++k) {
-                float x = nx, y = ny, z = nz; const int id = nid;
-                if (k + 1 < FC_PPT) fetch(k + 1, nx, ny, nz, nid);
+                float x = nx[k % FC_AHEAD], y = ny[k % FC_AHEAD], z = nz[k % FC_AHEAD]; const int id = nid[k % FC_AHEAD];
+                if (k + FC_AHEAD < FC_PPT) fetch(k + FC_AHEAD, nx[k % FC_AHEAD], ny[k % FC_AHEAD], nz[k % FC_AHEAD], nid[k % FC_AHEAD]);
                 if (packed[k] != 0xFFFFFFFFu) {
                     if (posed) apply_pose(s_pose, x, y, z);
                     const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z), zr = rot_row(s_R + 6, x, y, z);
@@ -536,7 +575,7 @@ forward_culled_kernel(FwdParams P)
         } else {
             // same positions, same cell order, same occupancy: only c = -ln(pv)/k follows the new depth range
             for (int pos = tid; pos < cnt; pos += FC_THREADS) {
-                const float* q = P.xyz + (size_t)(lo + *rec_idx(s_rec, pos)) * 3;
+                const float* q = xyz_c + (size_t)(lo + *rec_idx(s_rec, pos)) * 3;
                 const float zr = rot_row(s_R + 6, __ldg(q), __ldg(q + 1), __ldg(q + 2));
                 *rec_c(s_rec, pos) = __fmul_rn(logf(depth_weight_m(zr, zmin, range, (P.flags & FC_FLAG_HALF) != 0)), P.inv_negk);
             }
@@ -572,9 +611,9 @@ forward_culled_kernel(FwdParams P)
             // ---- classification: background pixels are written, "far" pixels (no occupied cell within the 3 x 3 window:
             // the long disc scans) are queued.  Rows are visited from the tile's top and bottom edges towards its middle,
             // so the pixels farthest from a centred cloud enter the queue first: longest tasks first.
-            for (int vl = tid; vl < FC_TPIX; vl += FC_THREADS) {
-                const int vis = vl / FC_TILE;
-                const int rl = vis < 16 ? vis : (vis < 32 ? 79 - vis : (vis < 48 ? vis - 16 : 95 - vis));
+            for (int ol = tid; ol < FC_TPIX / nparts; ol += FC_THREADS) {
+                const int vl = ((ol >> 5) * nparts + part) * 32 + (ol & 31);      // the chunks this CTA owns, in visiting order
+                const int rl = lpt_row(vl / FC_TILE);
                 const int row = trow0 + rl, col = tcol0 + vl % FC_TILE;
                 int ring; bool blank;
                 pixel_class(row, col, half, r2cap_all, s_ring, ring, blank);
@@ -622,19 +661,25 @@ forward_culled_kernel(FwdParams P)
 
             // ---- one dynamic work list: the far batches first (long), then the 3 x 3 chunks (short, uniform) fill the
             // gaps -- the heavy scans do not start after a barrier behind the 3 x 3 phase.
-            const int nfar = (int)s_qfar, far_batches = (nfar + 31) >> 5;
+            // batch = the queue entries a warp takes at once: 32 when the GPU is full (issue-bound: lanes are what counts);
+            // when several CTAs share an image the kernel is latency-bound instead, a warp's time is its slowest lane's
+            // serial chain, and the entries are spread over all 32 warps
+            const int nfar = (int)s_qfar;
+            const int far_take = nparts > 1 ? max(1, min(32, (nfar + 31) >> 5)) : 32;
+            const int far_batches = (nfar + far_take - 1) / far_take;
             for (;;) {
                 int t = 0;
                 if (lane == 0) t = (int)atomicAdd(&s_work, 1u);
                 t = __shfl_sync(0xFFFFFFFFu, t, 0);
-                if (t >= far_batches + FC_TPIX / 32) break;
+                if (t >= far_batches + FC_TPIX / 32 / nparts) break;
                 if (t < far_batches) {
-                    const int qi = t * 32 + lane;
-                    if (qi < nfar) scan_pixel(s_queue[qi], 0xFFFF);
+                    const int qi = t * far_take + lane;
+                    if (lane < far_take && qi < nfar) scan_pixel(s_queue[qi], 0xFFFF);
                     continue;
                 }
                 // ---- 3 x 3 cells, lane per pixel ----
-                const int pl = (t - far_batches) * 32 + lane;
+                const int vl = ((t - far_batches) * nparts + part) * 32 + lane;   // same chunks, same visiting order: a pixel
+                const int pl = lpt_row(vl / FC_TILE) * FC_TILE + vl % FC_TILE;    // belongs to ONE CTA in every batch of a cloud
                 const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
                 const PixelGeom g = geom(row, col);
                 const int ci = (int)g.uy, cj = (int)g.ux;
@@ -675,12 +720,13 @@ forward_culled_kernel(FwdParams P)
             // test can never pass although the winner is a cell away; 17 % of the pixels of a unit-ball view, none of them
             // with a best score beyond the 5 x 5 reach of 6.25 cells^2.  What stays open takes the general disc scan.
             const int nnear = (int)s_qnear;
+            const int near_take = (FC_NEAR_SPREAD || nparts > 1) ? max(1, min(32, (nnear + 31) >> 5)) : 32;
             for (;;) {
                 int qi = 0;
-                if (lane == 0) qi = (int)atomicAdd(&s_qhead, 32u);
+                if (lane == 0) qi = (int)atomicAdd(&s_qhead, (unsigned)near_take);
                 qi = __shfl_sync(0xFFFFFFFFu, qi, 0) + lane;
                 if (qi - lane >= nnear) break;
-                if (qi >= nnear) continue;
+                if (lane >= near_take || qi >= nnear) continue;
                 const int pl = s_queue[FC_TPIX - 1 - qi];
                 const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
                 const PixelGeom g = geom(row, col);
@@ -713,7 +759,10 @@ forward_culled_kernel(FwdParams P)
 
     // empty cloud: the reference would raise; the batched C ABI writes the background and winner -1
     if (hi <= lo && P.winner) {
-        for (int p = tid; p < npix; p += FC_THREADS) P.winner[img_off + p] = -1;
+        for (int p = tid; p < npix; p += FC_THREADS) {
+            const int vl = lpt_vis((p / w) % FC_TILE) * FC_TILE + (p % w) % FC_TILE;
+            if ((vl >> 5) % nparts == part) P.winner[img_off + p] = -1;      // the pixels this CTA owns
+        }
     }
     __syncthreads();
   }

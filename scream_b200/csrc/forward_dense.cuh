@@ -25,6 +25,11 @@ struct FwdParams {
     float* imgs; int32_t* winner; float* zrange;
     const int* surv; const unsigned* surv_cnt; int surv_cap;   // survivor lists of the giant-cloud path (last filter round), or nullptr
     const int* surv1; const unsigned* surv1_cnt; int surv1_cap; // first-round lists: used for an image whose last-round list overflowed
+    // culled kernel only:
+    const float* xyz_t;          // pair mode (offs == nullptr): VIRTUAL base of the target cloud, tgt - 3 * pair_n floats, so that
+    int64_t pair_n, pair_m;      //   xyz_t + 3 * (pair_n + i) is target point i; the source cloud is xyz
+    int nparts;                  // CTAs per image (>= 1): CTA `part` owns the 32-pixel chunks c with c % nparts == part
+    int fuse_zrange;             // the CTA reduces the depth range of its (item, view) itself (small grids: two launches less)
 };
 
 __device__ __forceinline__ float zero_or_cull(float best, float inv_negk) {

@@ -80,6 +80,13 @@ int check_common(const void* xyz, const void* offs, const void* views, int B, in
     return 0;
 }
 
+// CTAs per image of the culled kernel: one wave of the 148 SMs (1 CTA / SM) at most, a power of two up to 8
+int culled_parts(long long images) {
+    int parts = 1;
+    while (parts < 8 && images * parts * 2 <= 148) parts *= 2;
+    return parts;
+}
+
 // stage 1: z range of every (item, view) into ws (encoded)
 int launch_zrange(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts, const float* pose,
                   const float* views, int B, int V, unsigned* zenc, cudaStream_t st) {
@@ -152,6 +159,7 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
     P.flags = flags; P.imgs = imgs; P.winner = winner; P.zrange = (flags & SCREAM_F_ZRANGE_IN) ? nullptr : zrange;
     P.surv = nullptr; P.surv_cnt = nullptr; P.surv_cap = 0;
     P.surv1 = nullptr; P.surv1_cnt = nullptr; P.surv1_cap = 0;
+    P.xyz_t = nullptr; P.pair_n = P.pair_m = 0; P.nparts = 1; P.fuse_zrange = 0;
     // giant clouds: seed z-buffer -> bounds -> filter, then the culled kernel renders the survivors
     const int zero_radius = (int)ceilf(sqrtf(FC_EXP_ZERO / (0.5f * rho2)) * FC_CELLS_PER_NDC) + 1;
     if (L.stream && !(flags & (SCREAM_F_DENSE | SCREAM_F_NOSTREAM)) && zero_radius <= 32) {
@@ -232,7 +240,10 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
             CUDA_TRY(cudaFuncSetAttribute(forward_culled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FC_SMEM));
             attr_dev = dev;
         }
-        forward_culled_kernel<<<(unsigned)((long long)B * V * ((flags & SCREAM_F_DUAL) ? 3 : 2)), FC_THREADS, FC_SMEM, st>>>(P);
+        // small grids: several CTAs per image (forward_culled.cuh: nparts), as many as keep the grid within one wave
+        const long long images = (long long)B * V * ((flags & SCREAM_F_DUAL) ? 3 : 2);
+        if (!(flags & SCREAM_F_DUAL)) P.nparts = culled_parts(images);
+        forward_culled_kernel<<<(unsigned)(images * P.nparts), FC_THREADS, FC_SMEM, st>>>(P);
     }
     CUDA_TRY(cudaGetLastError());
     return 0;
@@ -253,7 +264,72 @@ int scream_render_backward(const float* xyz, const int64_t* offs, int64_t total_
     P.B = B; P.V = V; P.w = w;
     P.negk = -(float)(rho * rho) * 0.5f;
     P.flags = flags; P.grad_imgs = grad_imgs; P.winner = winner; P.zrange = zrange; P.grad_xyz = grad_xyz;
+    P.xyz_t = nullptr; P.grad_t = nullptr; P.pair_n = P.pair_m = 0;
     const long long grid = (long long)B * V * 2 * (w * w / BW_THREADS);
+    backward_scatter_kernel<<<(unsigned)grid, BW_THREADS, 0, st>>>(P);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// ---- one pair per call: the reference's own call pattern (pointnet.py:39-40 asserts batch 1; render.py:61 takes the two
+// clouds as two tensors).  No torch.cat, no offsets tensor, no z-range launches: ONE kernel launch per forward.
+int scream_render_forward_pair(const float* src, int64_t n, const float* tgt, int64_t m,
+                               const float* pose, const float* views, int V, int w, double rho, unsigned flags,
+                               float* imgs, int32_t* winner, float* zrange, scream_stream_t stream)
+{
+    if (!src || !tgt) return fail(SCREAM_E_ARG, "src/tgt must not be NULL");
+    if (n <= 0 || m <= 0) return fail(SCREAM_E_ARG, "max(): cannot reduce over an empty cloud (render.py:46,49)");
+    if (int rc = check_common(src, src, views, 1, V, w, rho, n + m)) return rc;
+    if (!imgs) return fail(SCREAM_E_ARG, "imgs is NULL");
+    if (flags & ~(SCREAM_F_RAW | SCREAM_F_HALF)) return fail(SCREAM_E_UNSUPPORTED, "scream_render_forward_pair takes SCREAM_F_RAW / SCREAM_F_HALF only");
+    if ((flags & SCREAM_F_HALF) && pose) return fail(SCREAM_E_UNSUPPORTED, "SCREAM_F_HALF takes pre-rotated clouds: no pose");
+    if (n + m >= FS_MIN_AVG_PTS) return fail(SCREAM_E_UNSUPPORTED, "giant pair: use scream_render_forward (streaming pre-filter)");
+    cudaStream_t st = (cudaStream_t)stream;
+    FwdParams P;
+    P.xyz = src; P.offs = nullptr; P.pose = pose; P.views = views; P.zenc = nullptr;
+    P.B = 1; P.V = V; P.w = w;
+    const float rho2 = (float)(rho * rho);
+    P.negk = -rho2 * 0.5f; P.inv_negk = 1.0f / P.negk;
+    P.flags = flags; P.imgs = imgs; P.winner = winner; P.zrange = zrange;
+    P.surv = nullptr; P.surv_cnt = nullptr; P.surv_cap = 0;
+    P.surv1 = nullptr; P.surv1_cnt = nullptr; P.surv1_cap = 0;
+    // virtual base: xyz_t + 3 * (n + i) is target point i (never dereferenced below 3 * n)
+    P.xyz_t = reinterpret_cast<const float*>(reinterpret_cast<uintptr_t>(tgt) - (uintptr_t)n * 12u);
+    P.pair_n = n; P.pair_m = m; P.fuse_zrange = 1;
+    P.nparts = culled_parts((long long)V * 2);
+    static thread_local int attr_dev = -1;
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (attr_dev != dev) {
+        CUDA_TRY(cudaFuncSetAttribute(forward_culled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FC_SMEM));
+        attr_dev = dev;
+    }
+    forward_culled_kernel<<<(unsigned)((long long)V * 2 * P.nparts), FC_THREADS, FC_SMEM, st>>>(P);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_render_backward_pair(const float* src, int64_t n, const float* tgt, int64_t m,
+                                const float* pose, const float* views, int V, int w, double rho, unsigned flags,
+                                const float* grad_imgs, const int32_t* winner, const float* zrange,
+                                float* grad_src, float* grad_tgt, scream_stream_t stream)
+{
+    if (!src || !tgt) return fail(SCREAM_E_ARG, "src/tgt must not be NULL");
+    if (n <= 0 || m <= 0) return fail(SCREAM_E_ARG, "empty cloud");
+    if (int rc = check_common(src, src, views, 1, V, w, rho, n + m)) return rc;
+    if (!grad_imgs || !winner || !zrange || !grad_src || !grad_tgt) return fail(SCREAM_E_ARG, "grad_imgs/winner/zrange/grad_src/grad_tgt must not be NULL");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaMemsetAsync(grad_src, 0, (size_t)n * 3 * sizeof(float), st));
+    CUDA_TRY(cudaMemsetAsync(grad_tgt, 0, (size_t)m * 3 * sizeof(float), st));
+    BwdParams P;
+    P.xyz = src; P.offs = nullptr; P.pose = pose; P.views = views;
+    P.B = 1; P.V = V; P.w = w;
+    P.negk = -(float)(rho * rho) * 0.5f;
+    P.flags = flags; P.grad_imgs = grad_imgs; P.winner = winner; P.zrange = zrange; P.grad_xyz = grad_src;
+    P.xyz_t = reinterpret_cast<const float*>(reinterpret_cast<uintptr_t>(tgt) - (uintptr_t)n * 12u);
+    P.grad_t = reinterpret_cast<float*>(reinterpret_cast<uintptr_t>(grad_tgt) - (uintptr_t)n * 12u);
+    P.pair_n = n; P.pair_m = m;
+    const long long grid = (long long)V * 2 * (w * w / BW_THREADS);
     backward_scatter_kernel<<<(unsigned)grid, BW_THREADS, 0, st>>>(P);
     CUDA_TRY(cudaGetLastError());
     return 0;

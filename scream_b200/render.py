@@ -34,7 +34,25 @@ def _require_cuda(*ts: torch.Tensor) -> None:
 
 
 def _stream_ptr(dev: torch.device) -> int:
-    return torch.cuda.current_stream(dev).cuda_stream
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    return torch._C._cuda_getCurrentRawStream(idx)          # what torch.cuda.current_stream(dev).cuda_stream returns, 7 us cheaper
+
+
+class _on_device:
+    """`with torch.cuda.device(dev)` only when dev is not already the current device (the context manager costs ~6 us, a
+    one-pair call has a budget of ~40)."""
+    __slots__ = ("ctx",)
+
+    def __init__(self, dev: torch.device):
+        self.ctx = None if dev.index is None or dev.index == torch.cuda.current_device() else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *a):
+        if self.ctx is not None:
+            self.ctx.__exit__(*a)
 
 
 _POISON = os.environ.get("SCREAM_POISON", "") not in ("", "0")
@@ -292,6 +310,59 @@ def render_pair(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho,
                              bool(need_winner), int(max_item_pts))
 
 
+PAIR_MAX_PTS = 147456          # scream_render_forward_pair's limit (giant pairs take the batched entry point and its pre-filter)
+
+
+class _PairRender(torch.autograd.Function):
+    """RegistrationRender.forward / .render for ONE pair, the reference's call pattern (render.py:61-73, pointnet.py:39-40):
+    the two clouds stay two tensors (no torch.cat, no offsets), one kernel launch forward (scream_render_forward_pair), one
+    backward (scream_render_backward_pair) that writes the two gradients.  Same bits as render_batch on the pair."""
+
+    @staticmethod
+    def run(src, tgt, views, w, rho, flags, want_winner):
+        """-> (imgs [V,2,w,w], winner int32 [V,2,w,w] or None, zrange [V,2] or None); no autograd bookkeeping"""
+        lib = _lib.load()
+        dev = src.device
+        V = views.shape[0]
+        with _on_device(dev):
+            imgs = _empty((V, 2, w, w), torch.float32, dev)
+            winner = zrange = None
+            if want_winner:                           # one block: the winner map, then the V (zmin, zmax) pairs as raw words
+                blk = _empty((V * 2 * w * w + 2 * V,), torch.int32, dev)
+                winner, zrange = blk[:V * 2 * w * w].view(V, 2, w, w), blk[V * 2 * w * w:].view(torch.float32).view(V, 2)
+            rc = lib.scream_render_forward_pair(src.data_ptr(), src.shape[0], tgt.data_ptr(), tgt.shape[0], None, views.data_ptr(),
+                                                V, w, rho, flags, imgs.data_ptr(), _ptr(winner), _ptr(zrange), _stream_ptr(dev))
+        if rc:
+            _lib.check(rc, "scream_render_forward_pair")
+        return imgs, winner, zrange
+
+    @staticmethod
+    def forward(ctx, src, tgt, views, w, rho, flags):
+        imgs, winner, zrange = _PairRender.run(src, tgt, views, w, rho, flags, True)
+        ctx.save_for_backward(src, tgt, views, winner, zrange)
+        ctx.cfg = (w, rho, flags)
+        return imgs
+
+    @staticmethod
+    def backward(ctx, g_imgs):
+        src, tgt, views, winner, zrange = ctx.saved_tensors
+        w, rho, flags = ctx.cfg
+        dev = src.device
+        if g_imgs.dtype != torch.float32 or not g_imgs.is_contiguous():
+            g_imgs = g_imgs.contiguous().float()
+        n, m = src.shape[0], tgt.shape[0]
+        with _on_device(dev):
+            g = _empty((n + m, 3), torch.float32, dev)             # one block, two gradients
+            g_src, g_tgt = g[:n], g[n:]
+            rc = _lib.load().scream_render_backward_pair(src.data_ptr(), n, tgt.data_ptr(), m, None,
+                                                         views.data_ptr(), views.shape[0], w, rho, flags, g_imgs.data_ptr(),
+                                                         winner.data_ptr(), zrange.data_ptr(), g_src.data_ptr(), g_tgt.data_ptr(),
+                                                         _stream_ptr(dev))
+        if rc:
+            _lib.check(rc, "scream_render_backward_pair")
+        return g_src, g_tgt, None, None, None, None
+
+
 class _HalfRender(torch.autograd.Function):
     """fp16 (autocast) input mode, SURVEY 8 f2 (train_kitti.py:154-169): what the reference computes when its generator
     runs under torch.cuda.amp.autocast() -- render.py:68's matmul in fp16 (fp16 operands and result), render.py:31 as a
@@ -415,11 +486,14 @@ class RegistrationRender(nn.Module):
 
     # -- small device-side caches (views by euler content, offsets by sizes) -------------------
     def _views(self, dev) -> torch.Tensor:
-        key = ("v", str(dev), np.asarray(self.eulers, dtype=np.float64).tobytes())
+        try:                 # the eulers are read on EVERY call (train_kitti.py:48 replaces them); content key, cheap to build
+            key = ("v", dev, b"".join([e.tobytes() for e in self.eulers]), self.eulers[0].dtype.num)
+        except AttributeError:
+            key = ("v", dev, np.asarray(self.eulers, dtype=np.float64).tobytes(), -1)
         hit = self._cache.get(key)
         if hit is None:
             hit = view_matrices(self.eulers).to(dev)
-            self._cache = {k: v for k, v in self._cache.items() if k[0] != "v" or k[1] != str(dev)}
+            self._cache = {k: v for k, v in self._cache.items() if k[0] != "v" or k[1] != dev}
             self._cache[key] = hit
         return hit
 
@@ -455,8 +529,16 @@ class RegistrationRender(nn.Module):
             raise ValueError("expected [n,3] and [m,3] point tensors")
         if src.shape[0] == 0 or tgt.shape[0] == 0:
             raise RuntimeError("max(): cannot reduce over an empty cloud (render.py:46,49)")
-        xyz = torch.cat([src.float(), tgt.float()], dim=0)         # render.py:63
         n, m = src.shape[0], tgt.shape[0]
+        if not half and n + m < PAIR_MAX_PTS and not torch.compiler.is_compiling():
+            # one pair, one launch: the clouds stay two tensors (render.py:63's cat is implied by the kernel)
+            s32 = src if src.dtype == torch.float32 and src.is_contiguous() else src.float().contiguous()
+            t32 = tgt if tgt.dtype == torch.float32 and tgt.is_contiguous() else tgt.float().contiguous()
+            flags = (_lib.F_RAW if raw else 0) | (_lib.F_HALF if prerotated_half else 0)
+            if torch.is_grad_enabled() and (s32.requires_grad or t32.requires_grad):
+                return _PairRender.apply(s32, t32, views, int(self.w), float(self.rho), int(flags))
+            return _PairRender.run(s32, t32, views, int(self.w), float(self.rho), int(flags), False)[0]
+        xyz = torch.cat([src.float(), tgt.float()], dim=0)         # render.py:63
         if prerotated_half:        # render() of fp16 coordinates: only the depth-weight chain of render.py:31 is fp16
             need = torch.is_grad_enabled() and xyz.requires_grad
             imgs, _, _ = torch.ops.scream.render_fwd(xyz.contiguous(), self._offsets(n, m, xyz.device), None, views,

@@ -619,3 +619,41 @@ def test_sixteen_million_points_default_path_equals_rendering_every_batch():
     assert torch.equal(a[2], b[2])
     assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
     assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
+
+
+def test_pair_entry_point_equals_batched_render():
+    """scream_render_forward_pair / _backward_pair (one launch per call: the clouds as two buffers, the depth range reduced
+    inside the kernel, up to 8 CTAs per image) give the bits of the batched entry point on the concatenated pair, and the
+    module routes one-pair calls through them."""
+    src, tgt = synth.unit_ball(10000, 31), synth.room_shell(9000, 32)
+    for view, rho, w in (("muti", 24, 64), ("single", 36, 128)):
+        r = RegistrationRender(rho, w, view=view, device=DEV)
+        views = view_matrices(r.eulers).to(DEV)
+        s = torch.from_numpy(src).to(DEV).requires_grad_(True)
+        t = torch.from_numpy(tgt).to(DEV).requires_grad_(True)
+        imgs = r(s, t)                                                       # _PairRender
+        x = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV).requires_grad_(True)
+        offs = make_offsets([(len(src), len(tgt))]).to(DEV)
+        want, win, zr = render_batch(x, offs, views, rho, w, need_winner=True)
+        assert torch.equal(imgs, want[0])
+        g = torch.from_numpy(np.random.default_rng(5).standard_normal(tuple(imgs.shape)).astype(np.float32)).to(DEV)
+        imgs.backward(g)
+        want.backward(g[None])
+        got = torch.cat([s.grad, t.grad], 0)
+        assert np.abs((got - x.grad).cpu().numpy()).max() <= 1e-5 * float(x.grad.abs().max())        # atomics order
+        with torch.no_grad():
+            raw = r.render(torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV), len(src))       # identity view, un-normalised
+        eye = torch.eye(3, device=DEV)[None].contiguous()
+        want_raw, _, _ = render_batch(x.detach(), offs, eye, rho, w, raw=True, need_winner=False)
+        assert torch.equal(raw, want_raw[0, 0])
+
+
+def test_counter_based_cloud_is_slice_invariant():
+    """bench.py's cfg5 cloud: point i has the same bits in whatever slice it is generated (the N-GPU runs shard the cloud the
+    1-GPU run renders)."""
+    import bench
+    a = bench.counter_ball(0, 300_000, 9000, DEV, chunk=100_000)
+    b = bench.counter_ball(123_457, 250_001, 9000, DEV, chunk=33_333)
+    assert torch.equal(a[123_457:250_001], b)
+    r = a.norm(dim=1)
+    assert float(r.max()) <= 1.0 + 1e-6 and abs(float(r.mean()) - 0.75) < 5e-3
