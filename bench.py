@@ -220,7 +220,9 @@ def streaming_leg_sharded(dev, peak_gbs: float, rank: int, world: int, n: int = 
     (s0, s1), (t0, t1) = balanced_slice(ns, rank, world), balanced_slice(nt, rank, world)
     src, tgt = counter_ball(s0, s1, CFG5_SEED_SRC, dev), counter_ball(t0, t1, CFG5_SEED_TGT, dev)
     views = torch.from_numpy(synth.random_views(n_views, 5)).to(dev)
-    run = lambda: render_cloud_point_sharded(src, tgt, s0, t0, views, RHO, W_IMG)
+    xyz_local = torch.cat([src, tgt], 0)          # the shard lives in HBM as one buffer, like the N = 1 cloud
+    src, tgt = xyz_local[:s1 - s0], xyz_local[s1 - s0:]
+    run = lambda: render_cloud_point_sharded(src, tgt, s0, t0, views, RHO, W_IMG, xyz_local=xyz_local, global_counts=(ns, nt))
     for _ in range(3):
         run()
     dist.barrier(); torch.cuda.synchronize(dev)
@@ -237,7 +239,7 @@ def streaming_leg_sharded(dev, peak_gbs: float, rank: int, world: int, n: int = 
     h = image_hash(out[1], out[2])
     identical = None
     if rank == 0:                                   # the single-GPU render of the same cloud, outside the timed region
-        del src, tgt
+        del src, tgt, xyz_local
         torch.cuda.empty_cache()
         xyz = torch.cat([counter_ball(0, ns, CFG5_SEED_SRC, dev), counter_ball(0, nt, CFG5_SEED_TGT, dev)], 0)
         val1, win1, _ = render_batch(xyz, make_offsets([(ns, nt)]).to(dev), views, RHO, W_IMG, raw=True, need_winner=True, max_item_pts=n)

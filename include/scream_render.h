@@ -162,6 +162,35 @@ int scream_rigid_transform(const float *A, const float *B, const int64_t *b_inde
                            const float *valid_dist, float valid_thr, float weight_threshold,
                            int bs, int64_t k, int64_t b_rows, float *T, void *ws, size_t ws_bytes, scream_stream_t stream);
 
+/* Point-sharded giant clouds (BASELINE config 5): the exact cross-rank merge of render.py:46,49's max with first
+ * index on ties.  val [V,2,w,w] un-normalised values and winner [V,2,w,w] cloud-local indices of THIS rank's slice (the
+ * output of scream_render_forward with SCREAM_F_RAW | SCREAM_F_ZRANGE_IN); src_offset / tgt_offset: global index of the
+ * slice's first source / target point.  keys [V,2,w,w] int64 = (value bits << 32) | (0xFFFFFFFF - global index), written
+ * straight into the buffer of the all_reduce(MAX); scream_unpack_keys turns the reduced keys into val, imgs = (val-0.5)/0.5
+ * (NULL to skip) and the global winner map -- bit-identical to the single-GPU render. */
+/* The forward render of ONE RANK's slice of a point-sharded giant cloud, in three stages with a collective between them, so
+ * that the pre-filter of every rank bounds with the best seeds of ALL ranks (a slice's own seeds are only its local best:
+ * its survivor lists, and everything behind them, then do not shrink with the slice).  zrange [B,V,2] is an INPUT (the range
+ * of the whole cloud, SCREAM_F_ZRANGE_IN implied); the same workspace must be passed to the three calls.
+ *   stage 1  depth range -> seed pass over this rank's share of the 4 M-point sample -> seed table.  Returns device pointers
+ *            into the workspace: *seed_keys [n_keys] int64 (value bits << 32 | ~rank)  -> caller: all_reduce(MAX)
+ *   stage 2  table entries that are not their cell's best are cleared; *seed_table [n_table_floats] fp32
+ *                                                                                      -> caller: all_reduce(SUM)
+ *   stage 3  bounds from the pooled seeds, voxel masks, filter, render of the survivors -> imgs / winner of this slice
+ * Needs the giant-cloud path (w == 64, total_pts >= 147456 * B) on EVERY rank; flags: SCREAM_F_RAW. */
+int scream_render_forward_sharded(const float *xyz, const int64_t *offs, int64_t total_pts, int64_t max_item_pts,
+                                  const float *views, int B, int V, int w, double rho, unsigned flags,
+                                  int stage, int rank, int world,
+                                  float *imgs, int32_t *winner, float *zrange,
+                                  void *ws, size_t ws_bytes,
+                                  int64_t **seed_keys, size_t *n_keys, float **seed_table, size_t *n_table_floats,
+                                  scream_stream_t stream);
+
+int scream_pack_keys(const float *val, const int32_t *winner, int64_t src_offset, int64_t tgt_offset, int V, int w,
+                     int64_t *keys, scream_stream_t stream);
+int scream_unpack_keys(const int64_t *keys, int V, int w, float *val, float *imgs, int64_t *winner_global,
+                       scream_stream_t stream);
+
 /* Transform stage only (testing / parity of the "index path"): rotated coordinates [B? no: total_pts
  * per view] rotated [V,total_pts,3], pv [V,total_pts] (render.py:31), zrange [B,V,2].  Any output may
  * be NULL.  Bit-exact against the reference for clouds of >= 16 points (sgemm op order). */

@@ -37,6 +37,11 @@ _SIGNATURES = {
                                              _P, _P, _P, _P]),
     "scream_render_backward_pair": (C.c_int, [_P, C.c_int64, _P, C.c_int64, _P, _P, C.c_int, C.c_int, C.c_double, C.c_uint,
                                               _P, _P, _P, _P, _P, _P]),
+    "scream_render_forward_sharded": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, C.c_int, C.c_int, C.c_int, C.c_double, C.c_uint,
+                                                C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, C.c_size_t,
+                                                C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), _P]),
+    "scream_pack_keys": (C.c_int, [_P, _P, C.c_int64, C.c_int64, C.c_int, C.c_int, _P, _P]),
+    "scream_unpack_keys": (C.c_int, [_P, C.c_int, C.c_int, _P, _P, _P, _P]),
     "scream_render_transform": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, C.c_int, C.c_int,
                                           _P, _P, _P, _P, C.c_size_t, _P]),
     "scream_half_rotate": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, C.c_int, C.c_int, _P, _P, _P]),

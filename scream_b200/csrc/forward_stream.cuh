@@ -58,6 +58,12 @@ struct StreamParams {
     unsigned* bbox;                                      // [B][2][6] per cloud (source posed): max keys of ~enc(min x,y,z), enc(max x,y,z); zero-initialised
     unsigned long long* vox;                             // [B][view groups][2][vox_g^3] bit vv: a point of the voxel may pass view v0 + vv's cell test
     int vox_g;                                           // voxels per axis of the cloud's bounding box
+    // point-sharded clouds: the first round's seeds come from ALL ranks.  seedtab [B][V][2][4096] (x', y', c_up,
+    // value bits) of each cell's seed, exactly placed; built per rank by stream_seedtab_kernel, masked to the rank whose seed
+    // is the best of the cell (all_reduce(MAX) over seed, rewritten as value bits << 32 | ~rank) and summed over the ranks
+    // (all_reduce(SUM): one rank contributes, the others add zeros).  nullptr: seeds are local (P.seed holds point indices).
+    float4* seedtab;
+    int rank;
 };
 
 constexpr int FS_VPC = 2;                                // views per CTA task of S1 (2 views x 2 clouds x 32 KB of 64-bit tiles)
@@ -193,6 +199,57 @@ __device__ __forceinline__ float stream_slack(float inv_k) { return __fmaf_rn(2e
 constexpr size_t FS_BOUND_SMEM = (size_t)FC_CELLS * sizeof(float4) + (size_t)FC_CELLS * sizeof(float)
                                + (size_t)2 * (FC_G + 1) * FC_G * sizeof(float) + (size_t)FS_TC * sizeof(float);
 
+// ---- point-sharded clouds: this rank's seed table, and its mask after the cross-rank MAX --------------------------------
+// grid (V * 2, B) x 1024.  For every cell the seed's (x', y', c_up) exactly as stream_bound_kernel places it, + its value bits;
+// P.seed is rewritten from (value bits << 32 | point index) to (value bits << 32 | ~rank): the collective's payload.
+__global__ void __launch_bounds__(1024)
+stream_seedtab_kernel(StreamParams P)
+{
+    __shared__ float s_R[9], s_pose[12];
+    const int vc = blockIdx.x, v = vc >> 1, c = vc & 1, b = blockIdx.y, tid = threadIdx.x;
+    const size_t img = ((size_t)b * P.V + v) * 2 + c;
+    if (tid < 9) s_R[tid] = P.views[(size_t)v * 9 + tid];
+    const bool posed = P.pose != nullptr && c == 0;
+    if (posed && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    const ItemSpan sp = item_span(P.offs, b);
+    const int64_t lo = c ? sp.tgt0 : sp.src0;
+    const float zmin = dec_f32(P.zenc[((size_t)b * P.V + v) * 2]), zmax = dec_f32(P.zenc[((size_t)b * P.V + v) * 2 + 1]);
+    const float rcp_range = 1.0f / z_range(zmin, zmax);
+    const float inv_k = -1.0f / P.negk;
+    __syncthreads();
+    for (int cell = tid; cell < FC_CELLS; cell += 1024) {
+        const unsigned long long key = P.seed[img * FC_CELLS + cell];
+        float4 sd = make_float4(0.f, 0.f, 0.f, 0.f);
+        unsigned long long out = 0ull;
+        if (key != 0ull) {
+            const float* q = P.xyz + (size_t)(lo + (int64_t)(unsigned)(key & 0xFFFFFFFFull)) * 3;
+            float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+            if (posed) apply_pose(s_pose, x, y, z);
+            const float pv_lo = __fmaf_rn(-(rot_row(s_R + 6, x, y, z) - zmin), rcp_range, 1.0f) - FS_PV_ABS;
+            if (pv_lo > 0.0f) {
+                sd = make_float4(rot_row(s_R, x, y, z), rot_row(s_R + 3, x, y, z),
+                                 fmaxf(-logf(pv_lo) * inv_k, 0.0f) * (1.0f + 1e-5f) + 1e-12f, __uint_as_float((unsigned)(key >> 32)));
+                out = (key & 0xFFFFFFFF00000000ull) | (unsigned long long)(0xFFFFFFFFu - (unsigned)P.rank);
+            }
+        }
+        P.seedtab[img * FC_CELLS + cell] = sd;
+        P.seed[img * FC_CELLS + cell] = out;
+    }
+}
+// after all_reduce(MAX) over P.seed: a rank whose seed is not the cell's best clears its table entry (the SUM over the ranks
+// then holds exactly the best rank's entry)
+__global__ void __launch_bounds__(256)
+stream_seedtab_mask_kernel(StreamParams P, long long total)
+{
+    const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (t >= total) return;
+    const unsigned long long g = P.seed[t];
+    const float4 sd = P.seedtab[t];
+    const bool mine = g != 0ull && (unsigned)(g >> 32) == __float_as_uint(sd.w) && (unsigned)(g & 0xFFFFFFFFull) == 0xFFFFFFFFu - (unsigned)P.rank
+                      && sd.z > 0.0f;             // c_up >= 1e-12 for every placed seed
+    if (!mine) P.seedtab[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
 __global__ void __launch_bounds__(1024)
 stream_bound_kernel(StreamParams P)
 {
@@ -220,7 +277,9 @@ stream_bound_kernel(StreamParams P)
     for (int cell = tid; cell < FC_CELLS; cell += 1024) {
         const unsigned long long key = P.seed[img * FC_CELLS + cell];
         float4 sd = make_float4(0.f, 0.f, INFINITY, 0.f);
-        if (key != 0ull) {
+        if (P.seedtab != nullptr) {                       // the best seed of ANY rank (see StreamParams::seedtab); key 0: none anywhere
+            if (key != 0ull) { sd = P.seedtab[img * FC_CELLS + cell]; sd.w = 0.f; if (!(sd.z > 0.0f)) sd.z = INFINITY; }
+        } else if (key != 0ull) {
             const float* q = P.xyz + (size_t)(lo + (int64_t)(unsigned)(key & 0xFFFFFFFFull)) * 3;
             float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
             if (posed) apply_pose(s_pose, x, y, z);

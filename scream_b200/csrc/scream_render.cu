@@ -10,6 +10,7 @@
 #include "colorize.cuh"
 #include "half_rotate.cuh"
 #include "registration.cuh"
+#include "shard_keys.cuh"
 
 #include <algorithm>
 #include <cstdarg>
@@ -35,7 +36,7 @@ int fail(int code, const char* fmt, ...) {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, surv2_off, vox_off, total; bool stream; int surv_cap, surv2_cap, vox_g; };
+struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, surv2_off, vox_off, tab_off, total; bool stream; int surv_cap, surv2_cap, vox_g; };
 
 // The giant-cloud pre-filter (forward_stream.cuh) is used when the AVERAGE item reaches FS_MIN_AVG_PTS points
 // (decided from B and total_pts alone, so the workspace query and the forward call agree) and w == 64.
@@ -49,7 +50,7 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
     L.zenc_off = take((size_t)B * V * 2 * 2 * sizeof(unsigned));        // two sets: SCREAM_F_DUAL keeps the range of both renders
     L.stream = stream_eligible(B, w, total_pts);
-    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = L.vox_off = 0;
+    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = L.vox_off = L.tab_off = 0;
     L.vox_g = total_pts / B >= (4 << 20) ? FV_G : FV_G / 2;   // ~100+ points per voxel; the mask kernel costs g^3 x V
     L.surv2_cap = 1 << 18;
     // rim cells of a solid cloud pass the cell-level test wholesale (~2-3 % of the points): keep room for 1/16
@@ -62,6 +63,7 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
         L.surv_off = take(imgs * (size_t)L.surv_cap * sizeof(int));
         L.surv2_off = take(imgs * (size_t)L.surv2_cap * sizeof(int));
         L.vox_off = take((size_t)B * ((V + FS_VPC_FILTER - 1) / FS_VPC_FILTER) * 2 * (size_t)L.vox_g * L.vox_g * L.vox_g * sizeof(unsigned long long));
+        L.tab_off = take(imgs * (size_t)FC_CELLS * sizeof(float4));              // point-sharded clouds: the cross-rank seed table
     }
     L.total = off;
     return L;
@@ -121,14 +123,20 @@ int scream_render_workspace_bytes(int B, int V, int w, int64_t total_pts, size_t
     return 0;
 }
 
-int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
-                          const float* pose, const float* views,
-                          int B, int V, int w, double rho, unsigned flags,
-                          float* imgs, int32_t* winner, float* zrange,
-                          void* ws, size_t ws_bytes, scream_stream_t stream)
+}  // extern "C"
+
+namespace {
+// Exchange points of the point-sharded protocol (scream_render_forward_sharded): the whole call, or one of its three stages.
+struct Shard { int stage = 0, rank = 0, world = 1; int64_t** keys = nullptr; size_t* n_keys = nullptr; float** table = nullptr; size_t* n_table = nullptr; };
+
+int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
+                 const float* pose, const float* views,
+                 int B, int V, int w, double rho, unsigned flags,
+                 float* imgs, int32_t* winner, float* zrange,
+                 void* ws, size_t ws_bytes, scream_stream_t stream, const Shard& sh)
 {
     if (int rc = check_common(xyz, offs, views, B, V, w, rho, total_pts)) return rc;
-    if (!imgs) return fail(SCREAM_E_ARG, "imgs is NULL");
+    if (!imgs && sh.stage != 1 && sh.stage != 2) return fail(SCREAM_E_ARG, "imgs is NULL");
     const WsLayout L = ws_layout(B, V, w, total_pts);
     if (!ws || ws_bytes < L.total) return fail(SCREAM_E_WORKSPACE, "workspace needs %zu bytes, got %zu", L.total, ws_bytes);
     if (flags & SCREAM_F_DUAL) {
@@ -143,7 +151,9 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
     }
     cudaStream_t st = (cudaStream_t)stream;
     unsigned* zenc = reinterpret_cast<unsigned*>((char*)ws + L.zenc_off);
-    if (flags & SCREAM_F_ZRANGE_IN) {
+    if (sh.stage >= 2) {
+        // stages 2 and 3 of a sharded call: the encoded range of stage 1 is still in the workspace
+    } else if (flags & SCREAM_F_ZRANGE_IN) {
         if (!zrange) return fail(SCREAM_E_ARG, "SCREAM_F_ZRANGE_IN needs a zrange buffer");
         zrange_encode_kernel<<<(B * V * 2 + 255) / 256, 256, 0, st>>>(zrange, zenc, B * V * 2);
     } else if (flags & SCREAM_F_DUAL) {
@@ -162,8 +172,12 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
     P.xyz_t = nullptr; P.pair_n = P.pair_m = 0; P.nparts = 1; P.fuse_zrange = 0;
     // giant clouds: seed z-buffer -> bounds -> filter, then the culled kernel renders the survivors
     const int zero_radius = (int)ceilf(sqrtf(FC_EXP_ZERO / (0.5f * rho2)) * FC_CELLS_PER_NDC) + 1;
-    if (L.stream && !(flags & (SCREAM_F_DENSE | SCREAM_F_NOSTREAM)) && zero_radius <= 32) {
+    const bool use_stream = L.stream && !(flags & (SCREAM_F_DENSE | SCREAM_F_NOSTREAM)) && zero_radius <= 32;
+    if (sh.stage != 0 && !use_stream) return fail(SCREAM_E_UNSUPPORTED, "the sharded stages need the giant-cloud path (w == 64, >= 147456 points per item, no DENSE / NOSTREAM)");
+    if (use_stream) {
         StreamParams S;
+        S.seedtab = sh.stage != 0 ? reinterpret_cast<float4*>((char*)ws + L.tab_off) : nullptr; S.rank = sh.rank;
+        const size_t n_cells = (size_t)B * V * 2 * FC_CELLS;
         S.xyz = xyz; S.offs = offs; S.pose = pose; S.views = views; S.zenc = zenc; S.B = B; S.V = V; S.negk = P.negk;
         S.seed = reinterpret_cast<unsigned long long*>((char*)ws + L.seed_off);
         S.win = reinterpret_cast<float4*>((char*)ws + L.thr_off);
@@ -179,10 +193,12 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
         S.surv2 = reinterpret_cast<int*>((char*)ws + L.surv2_off); S.surv2_cap = L.surv2_cap;
         S.bbox = reinterpret_cast<unsigned*>(S.stats + 8);
         S.vox = reinterpret_cast<unsigned long long*>((char*)ws + L.vox_off); S.vox_g = L.vox_g;
-        CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
+        if (sh.stage <= 1) CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
         const int64_t mi = (max_item_pts <= 0 || max_item_pts > total_pts) ? total_pts : max_item_pts;
-        // S1 seeds from a subset of the cloud (at most 4 M points per item: ~1000 per pixel): any subset gives valid bounds
-        S.seed_stride = (int)std::min<int64_t>(std::max<int64_t>((mi + (4 << 20) - 1) / (4 << 20), 1), 64);
+        // S1 seeds from a subset of the cloud (at most 4 M points per item: ~1000 per pixel): any subset gives valid bounds.
+        // Sharded: the ranks' samples are pooled (seed table), so each rank draws its share of the 4 M.
+        const int64_t seed_budget = std::max<int64_t>((4 << 20) / std::max(sh.world, 1), 1 << 16);
+        S.seed_stride = (int)std::min<int64_t>(std::max<int64_t>((mi + seed_budget - 1) / seed_budget, 1), 64);
         if (flags & SCREAM_F_THINSEED) S.seed_stride = std::max(S.seed_stride, 4);
         const int64_t chunks = ((mi + FS_CHUNK - 1) / FS_CHUNK + S.seed_stride - 1) / S.seed_stride;
         // S3: chunks small enough to fill the GPU (>= ~4 CTAs per SM over all view groups), large enough to amortise staging
@@ -205,14 +221,29 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
             }
         }
         if (chunks > 2147483647LL || V * 2 > 65535 || (mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS > 2147483647LL) return fail(SCREAM_E_UNSUPPORTED, "cloud too large for the stream grid");
-        stream_seed_kernel<<<dim3((unsigned)((chunks + FS_SEED_CPB - 1) / FS_SEED_CPB), (unsigned)((V + FS_VPC - 1) / FS_VPC), (unsigned)B), FS_THREADS, FS_SEED_SMEM, st>>>(S);
+        if (sh.stage <= 1)
+            stream_seed_kernel<<<dim3((unsigned)((chunks + FS_SEED_CPB - 1) / FS_SEED_CPB), (unsigned)((V + FS_VPC - 1) / FS_VPC), (unsigned)B), FS_THREADS, FS_SEED_SMEM, st>>>(S);
+        if (sh.stage == 1 || sh.stage == 2) {
+            // stage 1: this rank's seed table + keys (value bits << 32 | ~rank) -> caller: all_reduce(MAX) over the keys
+            // stage 2: entries that are not the cell's best are cleared        -> caller: all_reduce(SUM) over the table
+            if (sh.stage == 1) stream_seedtab_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, 0, st>>>(S);
+            else stream_seedtab_mask_kernel<<<(unsigned)((n_cells + 255) / 256), 256, 0, st>>>(S, (long long)n_cells);
+            CUDA_TRY(cudaGetLastError());
+            if (sh.keys) *sh.keys = reinterpret_cast<int64_t*>(S.seed);
+            if (sh.n_keys) *sh.n_keys = n_cells;
+            if (sh.table) *sh.table = reinterpret_cast<float*>(S.seedtab);
+            if (sh.n_table) *sh.n_table = n_cells * 4;
+            return 0;
+        }
         stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM, st>>>(S);
+        S.seedtab = nullptr;                              // a second round seeds from this rank's own survivors again
         stream_bbox_kernel<<<dim3((unsigned)((mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS), (unsigned)B), FV_BBOX_THREADS, 0, st>>>(S);
         stream_voxmask_kernel<<<dim3((unsigned)((L.vox_g * L.vox_g * L.vox_g + 255) / 256), (unsigned)(vgroups * 2 * 4), (unsigned)B), 256, 0, st>>>(S);
         stream_filter_kernel<<<dim3((unsigned)vgroups, (unsigned)(fchunks * 2), (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
         // second round: seeds from the survivors (the true per-cell best), bounds again, survivor lists filtered again.
         // Pays once the first round's seeds are a thin sample of the cloud (its survivors grow with the stride).
-        const bool round2 = S.seed_stride >= 4;
+        // (sharded: the pooled seeds already are the 4 M sample of the whole cloud and a shard's survivor lists are short)
+        const bool round2 = S.seed_stride >= 4 && sh.stage == 0;
         if (round2) {
             const unsigned r2chunks = (unsigned)((std::min<int64_t>(mi, L.surv_cap) + FS_R2_CHUNK - 1) / FS_R2_CHUNK);
             CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.cnt_off - L.seed_off, st));
@@ -247,6 +278,36 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
     }
     CUDA_TRY(cudaGetLastError());
     return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
+                          const float* pose, const float* views,
+                          int B, int V, int w, double rho, unsigned flags,
+                          float* imgs, int32_t* winner, float* zrange,
+                          void* ws, size_t ws_bytes, scream_stream_t stream)
+{
+    return forward_impl(xyz, offs, total_pts, max_item_pts, pose, views, B, V, w, rho, flags, imgs, winner, zrange, ws, ws_bytes,
+                        stream, Shard());
+}
+
+int scream_render_forward_sharded(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
+                                  const float* views, int B, int V, int w, double rho, unsigned flags,
+                                  int stage, int rank, int world,
+                                  float* imgs, int32_t* winner, float* zrange,
+                                  void* ws, size_t ws_bytes,
+                                  int64_t** seed_keys, size_t* n_keys, float** seed_table, size_t* n_table_floats,
+                                  scream_stream_t stream)
+{
+    if (stage < 1 || stage > 3) return fail(SCREAM_E_ARG, "stage must be 1, 2 or 3");
+    if (rank < 0 || world < 1 || rank >= world) return fail(SCREAM_E_ARG, "bad rank / world (%d / %d)", rank, world);
+    if (flags & ~(SCREAM_F_RAW | SCREAM_F_ZRANGE_IN)) return fail(SCREAM_E_UNSUPPORTED, "scream_render_forward_sharded takes SCREAM_F_RAW only (SCREAM_F_ZRANGE_IN is implied)");
+    Shard sh; sh.stage = stage; sh.rank = rank; sh.world = world;
+    sh.keys = seed_keys; sh.n_keys = n_keys; sh.table = seed_table; sh.n_table = n_table_floats;
+    return forward_impl(xyz, offs, total_pts, max_item_pts, nullptr, views, B, V, w, rho, flags | SCREAM_F_ZRANGE_IN, imgs, winner,
+                        zrange, ws, ws_bytes, stream, sh);
 }
 
 int scream_render_backward(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t /*max_item_pts*/,
@@ -435,6 +496,29 @@ int scream_depth_to_rgb8(const float* imgs, int B, int V, int w, unsigned char* 
     const long long grid = (total + CZ_THREADS - 1) / CZ_THREADS;
     if (grid > 2147483647LL) return fail(SCREAM_E_UNSUPPORTED, "B*V*w*w too large for one launch");
     depth_to_rgb8_kernel<<<(unsigned)grid, CZ_THREADS, 0, (cudaStream_t)stream>>>(imgs, B, V, w, rgb);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_pack_keys(const float* val, const int32_t* winner, int64_t src_offset, int64_t tgt_offset, int V, int w,
+                     int64_t* keys, scream_stream_t stream)
+{
+    if (!val || !winner || !keys) return fail(SCREAM_E_ARG, "val/winner/keys must not be NULL");
+    if (V <= 0 || w <= 0) return fail(SCREAM_E_ARG, "V and w must be positive");
+    const long long total = (long long)V * 2 * w * w;
+    pack_keys_kernel<<<(unsigned)((total + SK_THREADS - 1) / SK_THREADS), SK_THREADS, 0, (cudaStream_t)stream>>>(
+        val, winner, (long long)src_offset, (long long)tgt_offset, w * w, total, reinterpret_cast<long long*>(keys));
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_unpack_keys(const int64_t* keys, int V, int w, float* val, float* imgs, int64_t* winner_global, scream_stream_t stream)
+{
+    if (!keys || !val || !winner_global) return fail(SCREAM_E_ARG, "keys/val/winner_global must not be NULL");
+    if (V <= 0 || w <= 0) return fail(SCREAM_E_ARG, "V and w must be positive");
+    const long long total = (long long)V * 2 * w * w;
+    unpack_keys_kernel<<<(unsigned)((total + SK_THREADS - 1) / SK_THREADS), SK_THREADS, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const long long*>(keys), total, val, imgs, reinterpret_cast<long long*>(winner_global));
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

@@ -429,37 +429,113 @@ def depth_range(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, pose
     return zr
 
 
+_OFFS_CACHE = {}
+
+
+def _pair_offsets(n: int, m: int, dev) -> torch.Tensor:
+    key = (n, m, dev)
+    hit = _OFFS_CACHE.get(key)
+    if hit is None:
+        if len(_OFFS_CACHE) > 256:
+            _OFFS_CACHE.clear()
+        hit = _OFFS_CACHE[key] = torch.tensor([0, n, n + m], dtype=torch.int64).to(dev)
+    return hit
+
+
+def _sharded_stages(xyz, offs, views, rho, w, zr, rank, world, group, reduce_fn=None):
+    """scream_render_forward_sharded, stages 1-3 with the two collectives between them (module docstring of shard.py).
+    reduce_fn(tensor, op) replaces torch.distributed.all_reduce (tests emulate the ranks on one GPU).
+    -> (val [V,2,w,w] un-normalised, winner int32 [V,2,w,w]) of this rank's slice."""
+    import ctypes as C
+    import torch.distributed as dist
+    lib = _lib.load()
+    dev = xyz.device
+    V, total = views.shape[0], xyz.shape[0]
+    if reduce_fn is None:
+        reduce_fn = lambda t, op: dist.all_reduce(t, op=op, group=group)
+    with _on_device(dev):
+        val = _empty((V, 2, w, w), torch.float32, dev)
+        win = _empty((V, 2, w, w), torch.int32, dev)
+        nws = _lib.workspace_bytes(1, V, w, total)
+        ws = _empty((nws,), torch.uint8, dev)
+        kp, tp, nk, nt = C.c_void_p(), C.c_void_p(), C.c_size_t(), C.c_size_t()
+        zr1 = zr[None].contiguous()
+
+        def stage(i):
+            rc = lib.scream_render_forward_sharded(xyz.data_ptr(), offs.data_ptr(), total, total, views.data_ptr(), 1, V, w,
+                                                   float(rho), _lib.F_RAW, i, rank, world, val.data_ptr(), win.data_ptr(),
+                                                   zr1.data_ptr(), ws.data_ptr(), nws, C.byref(kp), C.byref(nk), C.byref(tp),
+                                                   C.byref(nt), _stream_ptr(dev))
+            _lib.check(rc, f"scream_render_forward_sharded stage {i}")
+        stage(1)
+        ko = kp.value - ws.data_ptr()
+        reduce_fn(ws[ko:ko + nk.value * 8].view(torch.int64), dist.ReduceOp.MAX)
+        stage(2)
+        to = tp.value - ws.data_ptr()
+        reduce_fn(ws[to:to + nt.value * 4].view(torch.float32), dist.ReduceOp.SUM)
+        stage(3)
+    return val, win
+
+
+SHARD_MIN_PTS = 147456          # a slice this large takes the giant-cloud path (scream_render.cu: FS_MIN_AVG_PTS)
+
+
 def render_cloud_point_sharded(src_local: torch.Tensor, tgt_local: torch.Tensor, src_offset: int, tgt_offset: int,
-                               views: torch.Tensor, rho, w: int, group=None):
-    """One giant pair, points sharded over the ranks of `group` (BASELINE config 5; shard.py has the
-    protocol).  Every rank passes its rows and their global offsets; all ranks get the same
-    (imgs [V,2,w,w], val, winner_global int64, zrange [V,2]), bit-identical to the unsharded render."""
-    from . import shard
+                               views: torch.Tensor, rho, w: int, group=None, xyz_local: Optional[torch.Tensor] = None,
+                               global_counts: Optional[Tuple[int, int]] = None):
+    """One giant pair, points sharded over the ranks of `group` (BASELINE config 5; shard.py has the protocol).  Every rank
+    passes its rows and their global offsets (xyz_local: the two slices already back to back in one [n+m,3] buffer, if the
+    caller keeps them that way -- spares the concatenation); all ranks get the same (imgs [V,2,w,w], val, winner_global
+    int64, zrange [V,2]), bit-identical to the unsharded render.  Two collectives per call: all_reduce(MAX) of the
+    (-zmin, zmax) pairs, all_reduce(MAX) of the packed 64-bit keys, which scream_pack_keys writes straight into the
+    collective's buffer and scream_unpack_keys turns into the images.
+    global_counts = (source points, target points) of the WHOLE cloud, cut with shard.balanced_slice: when every rank's
+    slice is large enough for the giant-cloud path (w == 64), two more collectives pool the ranks' pre-filter seeds
+    (scream_render_forward_sharded), so that the per-rank filter work shrinks with the slice."""
+    import torch.distributed as dist
     dev = src_local.device
-
-    def pair(src, tgt):
-        xyz = torch.cat([src.float(), tgt.float()], 0).contiguous()
-        offs = torch.tensor([0, src.shape[0], src.shape[0] + tgt.shape[0]], dtype=torch.int64, device=dev)
-        return xyz, offs
-
-    def range_fn(src, tgt):
-        xyz, offs = pair(src, tgt)
-        if xyz.shape[0] == 0:
-            z = torch.empty((views.shape[0], 2), dtype=torch.float32, device=dev)
-            z[:, 0], z[:, 1] = float("inf"), float("-inf")
-            return z
-        return depth_range(xyz, offs, views)[0]
-
-    def render_fn(src, tgt, zr):
-        xyz, offs = pair(src, tgt)
-        if xyz.shape[0] == 0:
-            V = views.shape[0]
-            return (torch.zeros((V, 2, w, w), device=dev), torch.full((V, 2, w, w), -1, dtype=torch.int32, device=dev))
-        val, win, _ = render_batch(xyz, offs, views, rho, w, raw=True, need_winner=True, zrange_in=zr[None].contiguous())
-        return val[0], win[0]
-
+    n, m = src_local.shape[0], tgt_local.shape[0]
+    V = views.shape[0]
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+    lib = _lib.load()
     with torch.no_grad():
-        return shard.render_cloud_point_sharded(src_local, tgt_local, src_offset, tgt_offset, range_fn, render_fn, group)
+        if xyz_local is None:
+            xyz_local = torch.cat([src_local.float(), tgt_local.float()], 0).contiguous()
+        offs = _pair_offsets(n, m, dev)
+        if n + m == 0:
+            zr = torch.empty((V, 2), dtype=torch.float32, device=dev)
+            zr[:, 0], zr[:, 1] = float("inf"), float("-inf")
+        else:
+            zr = depth_range(xyz_local, offs, views, max_item_pts=n + m)[0]
+        if world > 1:                               # min and max in ONE collective: max(-zmin), max(zmax); negation is exact
+            zz = torch.stack([-zr[:, 0], zr[:, 1]], dim=-1).contiguous()
+            dist.all_reduce(zz, op=dist.ReduceOp.MAX, group=group)
+            zr = torch.stack([-zz[:, 0], zz[:, 1]], dim=-1).contiguous()
+        with _on_device(dev):
+            keys = _empty((V, 2, w, w), torch.int64, dev)
+            if n + m == 0:
+                keys.zero_()
+            else:
+                pooled = False
+                if global_counts is not None and world > 1 and w == 64:
+                    from .shard import slice_counts
+                    smallest = min(a + b for a, b in zip(slice_counts(global_counts[0], world), slice_counts(global_counts[1], world)))
+                    pooled = smallest >= SHARD_MIN_PTS        # the same answer on every rank
+                if pooled:
+                    val, win = _sharded_stages(xyz_local, offs, views, rho, w, zr, dist.get_rank(group), world, group)
+                else:
+                    val, win, _ = render_batch(xyz_local, offs, views, rho, w, raw=True, need_winner=True, zrange_in=zr[None],
+                                               max_item_pts=n + m)
+                _lib.check(lib.scream_pack_keys(val.data_ptr(), win.data_ptr(), int(src_offset), int(tgt_offset), V, w,
+                                                keys.data_ptr(), _stream_ptr(dev)), "scream_pack_keys")
+            if world > 1:
+                dist.all_reduce(keys, op=dist.ReduceOp.MAX, group=group)
+            val_g = _empty((V, 2, w, w), torch.float32, dev)
+            imgs = _empty((V, 2, w, w), torch.float32, dev)
+            idx_g = _empty((V, 2, w, w), torch.int64, dev)
+            _lib.check(lib.scream_unpack_keys(keys.data_ptr(), V, w, val_g.data_ptr(), imgs.data_ptr(), idx_g.data_ptr(),
+                                              _stream_ptr(dev)), "scream_unpack_keys")
+    return imgs, val_g, idx_g, zr
 
 
 class RegistrationRender(nn.Module):

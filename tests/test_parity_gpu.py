@@ -657,3 +657,86 @@ def test_counter_based_cloud_is_slice_invariant():
     assert torch.equal(a[123_457:250_001], b)
     r = a.norm(dim=1)
     assert float(r.max()) <= 1.0 + 1e-6 and abs(float(r.mean()) - 0.75) < 5e-3
+
+
+def test_key_kernels_and_sharded_entry_point():
+    """scream_pack_keys / scream_unpack_keys == the torch reference of the key arithmetic (scream_b200/shard.py), and the
+    point-sharded entry point at world size 1 == the plain render."""
+    from scream_b200 import shard
+    from scream_b200.render import render_cloud_point_sharded
+    lib = _lib.load()
+    V, w = 3, 64
+    g = torch.Generator(device=DEV).manual_seed(3)
+    val = torch.rand((V, 2, w, w), generator=g, device=DEV)
+    val[0, 0, :4] = 0.0
+    win = torch.randint(0, 50_000_000, (V, 2, w, w), generator=g, device=DEV, dtype=torch.int32)
+    win[1, 1, 5:9] = -1
+    so, to = 3_000_000_000, 1_234_567                                    # global offsets beyond 2^31
+    keys = torch.empty((V, 2, w, w), dtype=torch.int64, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.check(lib.scream_pack_keys(val.data_ptr(), win.data_ptr(), so, to, V, w, keys.data_ptr(), st), "pack")
+    off = torch.tensor([so, to], device=DEV).view(1, 2, 1, 1)
+    gidx = torch.where(win < 0, torch.full_like(win, -1, dtype=torch.int64), win.to(torch.int64) + off)
+    assert torch.equal(keys, shard.pack_keys(val, gidx))
+    v2 = torch.empty_like(val); im = torch.empty_like(val); ig = torch.empty((V, 2, w, w), dtype=torch.int64, device=DEV)
+    _lib.check(lib.scream_unpack_keys(keys.data_ptr(), V, w, v2.data_ptr(), im.data_ptr(), ig.data_ptr(), st), "unpack")
+    wv, wi = shard.unpack_keys(keys)
+    assert torch.equal(v2, wv) and torch.equal(ig, wi) and torch.equal(im, (wv - 0.5) / 0.5)
+
+    src, tgt = synth.unit_ball(90000, 41), synth.room_shell(80000, 42)
+    views = torch.from_numpy(synth.random_views(V, 9)).to(DEV)
+    s, t = torch.from_numpy(src).to(DEV), torch.from_numpy(tgt).to(DEV)
+    imgs, val_g, idx_g, zr = render_cloud_point_sharded(s, t, 0, 0, views, 24, w)
+    xyz = torch.cat([s, t], 0)
+    want, win1, zr1 = render_batch(xyz, make_offsets([(len(src), len(tgt))]).to(DEV), views, 24, w, raw=True, need_winner=True)
+    assert torch.equal(val_g, want[0]) and torch.equal(idx_g, win1[0].long()) and torch.equal(zr, zr1[0])
+    assert torch.equal(imgs, (want[0] - 0.5) / 0.5)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_pooled_seed_stages_equal_unsharded(world):
+    """scream_render_forward_sharded: `world` ranks emulated on one GPU (each slice run through stages 1-3, the two
+    collectives replaced by the same reductions over the emulated ranks' buffers) -> merged keys == the unsharded render."""
+    from scream_b200 import shard
+    from scream_b200.render import _sharded_stages
+    import torch.distributed as dist
+    ns, nt = 700_000, 620_001
+    src, tgt = synth.unit_ball(ns, 51), synth.room_shell(nt, 52)
+    views = torch.from_numpy(synth.random_views(3, 19)).to(DEV)
+    xyz = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV)
+    offs = make_offsets([(ns, nt)]).to(DEV)
+    want_val, want_win, zr = render_batch(xyz, offs, views, 24, 64, raw=True, need_winner=True, max_item_pts=ns + nt)
+    spans = [(shard.balanced_slice(ns, r, world), shard.balanced_slice(nt, r, world)) for r in range(world)]
+    shards = [torch.from_numpy(np.concatenate([src[a:b], tgt[c:d]], 0)).to(DEV) for (a, b), (c, d) in spans]
+    # the emulated collectives need every rank's buffer at the same time: run the ranks as threads that meet at barriers
+    import threading
+    bar = threading.Barrier(world)
+    bufs, out, errs = {}, [None] * world, []
+
+    def reduce_for(rank):
+        def fn(t, op):
+            bufs[rank] = t
+            bar.wait()
+            if rank == 0:
+                st = torch.stack([bufs[r] for r in range(world)])
+                red = st.max(0)[0] if op == dist.ReduceOp.MAX else st.sum(0)
+                for r in range(world):
+                    bufs[r].copy_(red)
+            bar.wait()
+        return fn
+
+    def work(rank):
+        try:
+            (a, b), (c, d) = spans[rank]
+            o = make_offsets([(b - a, d - c)]).to(DEV)
+            v, wn = _sharded_stages(shards[rank], o, views, 24, 64, zr[0], rank, world, None, reduce_fn=reduce_for(rank))
+            off = torch.tensor([a, c], device=DEV).view(1, 2, 1, 1)
+            out[rank] = shard.pack_keys(v, wn.long() + off)
+        except Exception as e:                            # noqa: BLE001
+            errs.append(e); bar.abort()
+    ts = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    [t.start() for t in ts]; [t.join() for t in ts]
+    assert not errs, errs
+    v2, i2 = shard.unpack_keys(torch.stack(out).max(0)[0])
+    assert torch.equal(v2, want_val[0]), f"values differ at {(v2 != want_val[0]).sum().item()} pixels"
+    assert torch.equal(i2, want_win[0].long()), f"winners differ at {(i2 != want_win[0].long()).sum().item()} pixels"
