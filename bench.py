@@ -512,8 +512,27 @@ def config_dict(B: int, world: int = 1, gather: bool = False):
 # --------------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------------
+def bind_to_gpu_numa(index: int):
+    """Pin this process (and so its pinned host buffers, first-touch) to the CPU cores NVML reports as local to GPU `index`:
+    the e2e leg lives on the host link.  Returns a short description for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, wd in enumerate(words) for b in range(64) if (wd >> b) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return f"{len(allowed)} cores local to GPU {index} ({allowed[0]}-{allowed[-1]})"
+        return "NVML affinity empty: not bound"
+    except Exception as e:                                  # noqa: BLE001
+        return f"not bound ({type(e).__name__})"
+
+
 def run_ours(args, rank: int, local_rank: int, world: int):
     import torch.distributed as dist
+    affinity = bind_to_gpu_numa(local_rank) if not args.no_bind else "not bound (--no-bind)"
     from scream_b200.render import render_batch, render_pair, view_matrices, RegistrationRender
     from scream_b200 import _lib
     if not torch.cuda.is_available():
@@ -687,6 +706,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "copy_roofline_ms": copy_ms, "frac_of_copy_roofline": copy_ms / (ms_e2e / args.steps),
+                    "host_affinity": affinity,
                     "copy_roofline": "the same H2D + D2H bytes through pinned memory, one cudaMemcpyAsync per chunk buffer on the same streams, no kernels",
                     "api": f"scream_b200.pipeline.StepPipeline(chunk_pairs={args.chunk}, n_streams={args.streams}{", dual=True" if e2e_dual else ""})"},
             "gpu_launches": args.steps * (4 if dual else 7),
@@ -737,6 +757,7 @@ def main():
     ap.add_argument("--dual", action="store_true", help="device-resident leg: fake + real render in one launch (SCREAM_F_DUAL, SURVEY 8 f1)")
     ap.add_argument("--no-e2e-dual", action="store_true", help="host-buffer leg: two forward calls per chunk instead of one dual launch")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-bind", action="store_true", help="do not pin the process to the GPU's NUMA-local cores")
     ap.add_argument("--no-legs", action="store_true", help="skip the cfg1 / cfg3 / cfg4 legs and the GPU-eager comparator")
     ap.add_argument("--no-gather", action="store_true", help="N > 1: leave the all_gather of the images out of the timed step")
     ap.add_argument("--no-stream-leg", action="store_true", help="skip the cfg5 streaming-regime leg (one GPU: the whole cloud; N > 1: its points sharded over the ranks)")
