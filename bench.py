@@ -450,6 +450,34 @@ def leg_cfg4(dev, peak, cpu: bool, B: int = 64):
     return out
 
 
+def leg_disc_stem(dev, peak, B: int = 512):
+    """SURVEY 8 f4, the consumer's first layer on the renderer's output (gan.py:39: Conv2d(2, 64, 4, 2, 1) + LeakyReLU(0.2)):
+    B x 6 rendered views [B,6,2,64,64] -> [B,6,64,32,32], forward and backward (dx, dW, db).  Bound: the output write (4 * 64
+    bytes per output pixel, 8 x the input)."""
+    from scream_b200.disc_stem import DiscStem
+    torch.manual_seed(0)
+    stem = DiscStem(2, 64).to(dev)
+    imgs = (torch.rand((B, V, 2, W_IMG, W_IMG), device=dev) * 2 - 1).requires_grad_(True)
+    gy = torch.randn((B, V, 64, W_IMG // 2, W_IMG // 2), device=dev)
+
+    def fwd():
+        with torch.no_grad():
+            return stem(imgs)
+
+    def fwd_bwd():
+        imgs.grad = None
+        stem.zero_grad(set_to_none=True)
+        stem(imgs).backward(gy)
+    f_ms, _ = _timed(fwd, 10, dev)
+    fb_ms, _ = _timed(fwd_bwd, 10, dev)
+    n_out = B * V * 64 * (W_IMG // 2) ** 2 * 4
+    n_in = B * V * 2 * W_IMG * W_IMG * 4
+    return {"workload": f"f4: discriminator first layer on {B} x 6 rendered views (2 -> 64 channels, k4 s2 p1, LeakyReLU 0.2)",
+            "fwd_ms": f_ms, "fwd_bwd_ms": fb_ms, "images_per_sec_fwd": B * V * 2 / (f_ms / 1e3),
+            "roofline": {"bound": "hbm", "achieved": (n_in + n_out) / (f_ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": (n_in + n_out) / (f_ms / 1e3) / 1e9 / peak, "algorithmic_bytes": n_in + n_out}}
+
+
 def gpu_eager_baseline(dev):
     """SURVEY 8d's secondary comparator: the reference's own op sequence (oracle/render_oracle.forward_dense = render.py:61-73
     restated op for op) run by stock PyTorch eager ON THE GPU -- what a SCREAM user gets today.  One pair x 6 views, forward."""
@@ -722,7 +750,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             "clocks": clocks}
     cpu_legs = world == 1 and not args.no_cpu
     if not args.no_legs:
-        line["legs"] = {"cfg1": leg_cfg1(dev, peak, cpu_legs), "cfg4": leg_cfg4(dev, peak, cpu_legs)}
+        line["legs"] = {"cfg1": leg_cfg1(dev, peak, cpu_legs), "cfg4": leg_cfg4(dev, peak, cpu_legs),
+                        "f4_disc_stem": leg_disc_stem(dev, peak)}
         if world == 1:
             line["gpu_eager_baseline"] = gpu_eager_baseline(dev)
     if cfg3 is not None:

@@ -206,6 +206,19 @@ int scream_render_transform(const float *xyz, const int64_t *offs, int64_t total
  * The reference shows / writes the strip with cv2 (imshow is unavailable on this box); here it stays a device buffer. */
 int scream_depth_to_rgb8(const float *imgs, int B, int V, int w, unsigned char *rgb, scream_stream_t stream);
 
+/* The consumer's first layer on the renderer's output: replaces the first two modules of NLayerDiscriminator,
+ * models/gan.py:39 -- nn.Conv2d(input_nc, ndf, kernel_size=4, stride=2, padding=1) + nn.LeakyReLU(0.2, True) -- which
+ * loss.py:50-57 applies to the rendered views.  x [N,C,H,W] is the renderer's own [B,V,2,w,w] layout (N = B*V, C = 2; no
+ * permute), weight [F,C,4,4], bias [F] or NULL, y [N,F,H/2,W/2].  C <= 2, F <= 64, H and W even.  fp32; the reference's
+ * cuDNN / oneDNN accumulation order is unspecified, so parity is 1e-5 relative (tests/test_disc_stem.py). */
+int scream_disc_stem_forward(const float *x, const float *weight, const float *bias, int N, int C, int F, int H, int W,
+                             float *y, scream_stream_t stream);
+
+/* ... and its backward (autograd of the two modules; the in-place LeakyReLU differentiates from the saved OUTPUT y):
+ * dx [N,C,H,W], dw [F,C,4,4], db [F]; any of them may be NULL (db only together with dw). */
+int scream_disc_stem_backward(const float *x, const float *weight, const float *y, const float *dy, int N, int C, int F, int H, int W,
+                              float *dx, float *dw, float *db, scream_stream_t stream);
+
 /* Host-buffer convenience entry point (end-to-end path: H2D copies, forward, D2H copies, one stream
  * synchronise).  All pointers are HOST pointers; device staging is allocated per call and freed.
  * device < 0 uses the current device.  flags: SCREAM_F_RAW, _DENSE, _NOSTREAM, _THINSEED; the others

@@ -256,8 +256,32 @@ def freeze_registration():
         print(f"wrote {name}: n={len(src)} m={m} valid={int(valid.sum())} det(Tw[1])={np.linalg.det(Tw[1, :3, :3].numpy()):+.3f}")
 
 
+def freeze_disc():
+    """tests/golden/disc_stem.npz: the first two modules of the reference's NLayerDiscriminator (gan.py:39),
+    built with input_nc=2, applied to rendered views; forward and the reference's autograd gradients."""
+    from models.gan import NLayerDiscriminator, weights_init           # the real reference (needs only torch)
+    from oracle import disc_stem_oracle as dso
+    torch.manual_seed(5)
+    D = NLayerDiscriminator(input_nc=2, n_layers=3, use_actnorm=False, ndf=64).apply(weights_init)   # loss.py:19-24 with 2 channels
+    conv, act = D.main[0], D.main[1]
+    g = np.load(os.path.join(OUT, "cfg2_ball_fake.npz"))
+    x = torch.from_numpy(g["imgs"][[0, 4]].copy()).requires_grad_(True)  # two [2,64,64] views from the executed reference renderer
+    y = act(conv(x))
+    gy = torch.from_numpy(np.random.default_rng(11).standard_normal(tuple(y.shape)).astype(np.float32))
+    y.backward(gy)
+    want = dso.disc_stem(x.detach(), conv.weight.detach(), conv.bias.detach())
+    assert torch.equal(want, y.detach()), "disc stem restatement differs from the reference modules"
+    np.savez_compressed(os.path.join(OUT, "disc_stem.npz"), x=x.detach().numpy(), weight=conv.weight.detach().numpy(),
+                        bias=conv.bias.detach().numpy(), y=y.detach().numpy(), grad_out=gy.numpy(), grad_x=x.grad.numpy(),
+                        grad_w=conv.weight.grad.numpy(), grad_b=conv.bias.grad.numpy())
+    print(f"wrote disc_stem: x {tuple(x.shape)} -> y {tuple(y.shape)}, restatement == reference modules")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--only-disc" in sys.argv:
+        freeze_disc()
+        return
     if "--only-registration" in sys.argv:
         freeze_registration()
         return
@@ -295,6 +319,7 @@ def main():
     freeze_colorize()
     freeze_half_all()
     freeze_registration()
+    freeze_disc()
     freeze_full()
 
 

@@ -49,6 +49,8 @@ _SIGNATURES = {
     "scream_nearest_target": (C.c_int, [_P, C.c_int64, _P, C.c_int64, C.c_float, _P, _P, _P, C.c_size_t, _P]),
     "scream_rigid_transform": (C.c_int, [_P, _P, _P, _P, _P, C.c_float, C.c_float, C.c_int, C.c_int64, C.c_int64,
                                          _P, _P, C.c_size_t, _P]),
+    "scream_disc_stem_forward": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "scream_disc_stem_backward": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P]),
     "scream_depth_to_rgb8": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
     "scream_render_forward_host": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_double, C.c_uint,
                                              _P, _P, _P, C.c_int]),

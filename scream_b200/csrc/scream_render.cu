@@ -11,6 +11,7 @@
 #include "half_rotate.cuh"
 #include "registration.cuh"
 #include "shard_keys.cuh"
+#include "disc_stem.cuh"
 
 #include <algorithm>
 #include <cstdarg>
@@ -519,6 +520,51 @@ int scream_unpack_keys(const int64_t* keys, int V, int w, float* val, float* img
     const long long total = (long long)V * 2 * w * w;
     unpack_keys_kernel<<<(unsigned)((total + SK_THREADS - 1) / SK_THREADS), SK_THREADS, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const long long*>(keys), total, val, imgs, reinterpret_cast<long long*>(winner_global));
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+static int disc_stem_check(int N, int C, int F, int H, int W) {
+    if (N <= 0 || C <= 0 || F <= 0 || H <= 0 || W <= 0) return fail(SCREAM_E_ARG, "N, C, F, H, W must be positive");
+    if (C > DS_MAX_C || F > DS_MAX_F) return fail(SCREAM_E_UNSUPPORTED, "disc stem: C <= %d and F <= %d (the renderer emits 2 channels, gan.py uses ndf = 64)", DS_MAX_C, DS_MAX_F);
+    if ((H | W) & 1) return fail(SCREAM_E_ARG, "H and W must be even (kernel 4, stride 2, padding 1)");
+    return 0;
+}
+
+int scream_disc_stem_forward(const float* x, const float* weight, const float* bias, int N, int C, int F, int H, int W,
+                             float* y, scream_stream_t stream)
+{
+    if (!x || !weight || !y) return fail(SCREAM_E_ARG, "x/weight/y must not be NULL");
+    if (int rc = disc_stem_check(N, C, F, H, W)) return rc;
+    DiscStemParams P{};
+    P.x = x; P.weight = weight; P.bias = bias; P.y = y; P.N = N; P.C = C; P.F = F; P.H = H; P.W = W;
+    const long long total = (long long)N * (H / 2) * (W / 2);
+    disc_stem_forward_kernel<<<(unsigned)((total + DS_THREADS - 1) / DS_THREADS), DS_THREADS, 0, (cudaStream_t)stream>>>(P);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+int scream_disc_stem_backward(const float* x, const float* weight, const float* y, const float* dy, int N, int C, int F, int H, int W,
+                              float* dx, float* dw, float* db, scream_stream_t stream)
+{
+    if (!x || !weight || !y || !dy) return fail(SCREAM_E_ARG, "x/weight/y/dy must not be NULL");
+    if (int rc = disc_stem_check(N, C, F, H, W)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    DiscStemParams P{};
+    P.x = x; P.weight = weight; P.y = const_cast<float*>(y); P.dy = dy; P.dx = dx; P.dw = dw; P.db = db;
+    P.N = N; P.C = C; P.F = F; P.H = H; P.W = W;
+    if (dx) {
+        const long long total = (long long)N * H * W;
+        disc_stem_dgrad_kernel<<<(unsigned)((total + DS_THREADS - 1) / DS_THREADS), DS_THREADS, 0, st>>>(P);
+    }
+    if (dw) {
+        CUDA_TRY(cudaMemsetAsync(dw, 0, (size_t)F * C * DS_TAPS * sizeof(float), st));
+        if (db) CUDA_TRY(cudaMemsetAsync(db, 0, (size_t)F * sizeof(float), st));
+        const long long chunks = ((long long)N * (H / 2) * (W / 2) + DS_WG_POS - 1) / DS_WG_POS;
+        const long long ctas = std::min<long long>(chunks, 148 * 8);
+        const long long per = (chunks + ctas - 1) / ctas;
+        disc_stem_wgrad_kernel<<<(unsigned)((chunks + per - 1) / per), DS_THREADS, 0, st>>>(P, per);
+    }
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

@@ -22,7 +22,7 @@ def golden_names():
     """Renderer fixtures of the fp32 path (the colouriser's fixture, the fp16-mode fixtures, the NaN case and the
     BASELINE-size "full_*" fixtures have their own tests)."""
     names = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
-    return [n for n in names if not n.startswith(("colorize", "half_", "registration_", "full_", "nan_"))]
+    return [n for n in names if not n.startswith(("colorize", "half_", "registration_", "full_", "nan_", "disc_"))]
 
 
 def full_golden_names():
