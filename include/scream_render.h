@@ -73,6 +73,10 @@ extern "C" {
                                    is unchanged.  The target cloud is sorted once and searched twice.  Not combined
                                    with SCREAM_F_DENSE or SCREAM_F_ZRANGE_IN, nor with giant clouds (SCREAM_E_UNSUPPORTED). */
 
+#define SCREAM_F_DUAL_NOWIN1 128u /* with SCREAM_F_DUAL: no winner map for the posed render (winner is [B,V,2,w,w], the render as
+                                   given only) -- nothing differentiates through the "real" render, and without a map its
+                                   pixels below 2^-26 need no search */
+
 #define SCREAM_F_HALF      64u   /* fp16 (autocast) input mode, SURVEY 8 f2 (train_kitti.py:154-169: under torch.cuda.amp.autocast()
                                    render.py:68's matmul and render.py:31 run in fp16): xyz holds clouds already rotated and
                                    rounded by scream_half_rotate, views is the identity, and the depth weight follows the

@@ -20,6 +20,7 @@ F_NOSTREAM = 8
 F_THINSEED = 16
 F_DUAL = 32
 F_HALF = 64
+F_DUAL_NOWIN1 = 128
 
 _lock = threading.Lock()
 _lib = None

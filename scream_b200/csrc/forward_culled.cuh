@@ -306,6 +306,7 @@ __device__ __forceinline__ void pixel_class(int row, int col, int half, float r2
 }
 
 constexpr unsigned FC_FLAG_DUAL = 32u;                   // SCREAM_F_DUAL
+constexpr unsigned FC_FLAG_NOWIN1 = 128u;                // SCREAM_F_DUAL_NOWIN1
 constexpr unsigned FC_FLAG_HALF = 64u;                   // SCREAM_F_HALF: fp16 depth-weight chain (common.cuh)
 
 __global__ void __launch_bounds__(FC_THREADS, 1)
@@ -370,8 +371,6 @@ forward_culled_kernel(FwdParams P)
     const float s_zero = __fmul_rn(FC_EXP_ZERO, inv_k);   // scores beyond: value exactly 0
     // scores beyond s_far cannot change the OUTPUT: all of them when the value is exactly zero; with the
     // normalised output and no winner map, already when val <= 2^-26 ((val-0.5)/0.5 rounds to -1).
-    const bool minus1_ok = !raw && P.winner == nullptr;
-    const float r2cap_all = minus1_ok ? fminf(s_zero, __fmul_rn(FC_EXP_MINUS1, inv_k)) : s_zero;
     __syncthreads();
 
     FcShared S; S.rec = s_rec; S.start = s_start;
@@ -381,6 +380,11 @@ forward_culled_kernel(FwdParams P)
   for (int pass = pass0; pass < pass1; ++pass) {
     // outputs and depth range of this pass (dual: item pass * B + b of the pose-major outputs)
     const size_t ob = dual ? (size_t)pass * P.B + b : (size_t)b;
+    // winner map of this pass: SCREAM_F_DUAL_NOWIN1 leaves the posed ("real") render of a dual launch without one -- nothing
+    // differentiates through it (train_3d_match.py:198-201), and without it the -1 cap below applies to that render too
+    int32_t* const winner = (dual && pass == 1 && (P.flags & FC_FLAG_NOWIN1)) ? nullptr : P.winner;
+    const bool minus1_ok = !raw && winner == nullptr;
+    const float r2cap_all = minus1_ok ? fminf(s_zero, __fmul_rn(FC_EXP_MINUS1, inv_k)) : s_zero;
     const bool posed = (dual ? pass == 1 : P.pose != nullptr) && c == 0;
     if (P.fuse_zrange) {
         // render.py:30-31 inside this kernel: min / max of the rotated depth over BOTH clouds of the item (order-preserving
@@ -419,7 +423,7 @@ forward_culled_kernel(FwdParams P)
         // is NaN, and torch.max(dim=0) of an all-NaN column is NaN at index 0 (render.py:46,49) -- both clouds, every pixel
         for (int p = tid; p < npix; p += FC_THREADS) {
             P.imgs[img_off + p] = __int_as_float(0x7FC00000);
-            if (P.winner) P.winner[img_off + p] = hi > lo ? 0 : -1;
+            if (winner) winner[img_off + p] = hi > lo ? 0 : -1;
         }
         continue;                                         // uniform over the CTA
     }
@@ -594,11 +598,11 @@ forward_culled_kernel(FwdParams P)
                 const size_t o = img_off + (size_t)row * w + col;
                 if (batch > 0) {
                     const float pb = P.imgs[o];
-                    const int pid = P.winner ? P.winner[o] : 0;
+                    const int pid = winner ? winner[o] : 0;
                     if (!(val > pb || (val == pb && id < pid))) { val = pb; id = pid; }
                 }
                 P.imgs[o] = (raw || !last) ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
-                if (P.winner) P.winner[o] = id;
+                if (winner) winner[o] = id;
             };
             auto geom = [&](int row, int col) {
                 PixelGeom g;
@@ -758,10 +762,10 @@ forward_culled_kernel(FwdParams P)
     } while (c0 < npts);
 
     // empty cloud: the reference would raise; the batched C ABI writes the background and winner -1
-    if (hi <= lo && P.winner) {
+    if (hi <= lo && winner) {
         for (int p = tid; p < npix; p += FC_THREADS) {
             const int vl = lpt_vis((p / w) % FC_TILE) * FC_TILE + (p % w) % FC_TILE;
-            if ((vl >> 5) % nparts == part) P.winner[img_off + p] = -1;      // the pixels this CTA owns
+            if ((vl >> 5) % nparts == part) winner[img_off + p] = -1;      // the pixels this CTA owns
         }
     }
     __syncthreads();

@@ -146,6 +146,7 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
         if (L.stream && !(flags & SCREAM_F_NOSTREAM)) return fail(SCREAM_E_UNSUPPORTED, "SCREAM_F_DUAL with giant clouds: render the two poses separately");
         if ((long long)B * V * 3 > 2147483647LL) return fail(SCREAM_E_UNSUPPORTED, "B*V too large for one launch");
     }
+    if ((flags & SCREAM_F_DUAL_NOWIN1) && !(flags & SCREAM_F_DUAL)) return fail(SCREAM_E_ARG, "SCREAM_F_DUAL_NOWIN1 without SCREAM_F_DUAL");
     if (flags & SCREAM_F_HALF) {
         if (pose || (flags & SCREAM_F_DUAL)) return fail(SCREAM_E_UNSUPPORTED, "SCREAM_F_HALF takes pre-rotated clouds: no pose, no SCREAM_F_DUAL");
         flags |= SCREAM_F_NOSTREAM;           // the giant-cloud pre-filter bounds the fp32 depth weight

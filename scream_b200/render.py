@@ -259,7 +259,7 @@ class _DualRender(torch.autograd.Function):
     transform of the reference is applied to data, not to a prediction).  C ABI: SCREAM_F_DUAL."""
 
     @staticmethod
-    def forward(ctx, xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts):
+    def forward(ctx, xyz, offs, pose, views, w, rho, flags, want_winner, max_item_pts, real_winner):
         _require_cuda(xyz, offs, pose, views)
         lib = _lib.load()
         assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.dim() == 2 and xyz.shape[1] == 3
@@ -270,7 +270,9 @@ class _DualRender(torch.autograd.Function):
         dev = xyz.device
         with torch.cuda.device(dev):
             imgs = _empty((2, B, V, 2, w, w), torch.float32, dev)
-            winner = _empty((2, B, V, 2, w, w) if want_winner else (0,), torch.int32, dev)
+            if want_winner and not real_winner:
+                flags |= _lib.F_DUAL_NOWIN1           # winner map of the render as given only: [1,B,V,2,w,w]
+            winner = _empty((2 if real_winner else 1, B, V, 2, w, w) if want_winner else (0,), torch.int32, dev)
             zrange = _empty((2, B, V, 2), torch.float32, dev)
             nws = _lib.workspace_bytes(B, V, w, total)
             ws = _empty((nws,), torch.uint8, dev)
@@ -291,14 +293,15 @@ class _DualRender(torch.autograd.Function):
         w, rho, flags, max_item_pts, want_winner = ctx.cfg
         if not want_winner:
             raise RuntimeError("render_pair was run without a winner map (need_winner=False)")
-        g = _bwd_impl(xyz, offs, None, views, w, rho, flags, g_fake, winner[0], zrange[0], max_item_pts)
-        return g, None, None, None, None, None, None, None, None
+        g = _bwd_impl(xyz, offs, None, views, w, rho, flags & ~_lib.F_DUAL_NOWIN1, g_fake, winner[0], zrange[0], max_item_pts)
+        return g, None, None, None, None, None, None, None, None, None
 
 
 def render_pair(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho, w: int, pose: torch.Tensor,
-                raw: bool = False, need_winner: Optional[bool] = None, max_item_pts: int = 0):
+                raw: bool = False, need_winner: Optional[bool] = None, max_item_pts: int = 0, real_winner: bool = False):
     """The two renders of a training step in ONE launch: (fake [B,V,2,w,w] = the pairs as given, differentiable w.r.t.
-    xyz; real [B,V,2,w,w] = source clouds posed by pose [B,3,4], no gradient; winner int32 [2,B,V,2,w,w] or empty;
+    xyz; real [B,V,2,w,w] = source clouds posed by pose [B,3,4], no gradient; winner int32 [1,B,V,2,w,w] (the render as given:
+    the one autograd needs; real_winner=True: [2,B,V,2,w,w], the posed render's map as well) or empty;
     zrange [2,B,V,2]).  Bit-identical to render_batch(...) and render_batch(..., pose=pose); the target clouds are
     sorted once.  Not for giant clouds (the C ABI answers SCREAM_E_UNSUPPORTED)."""
     if w < 64 or w % 64:
@@ -307,7 +310,7 @@ def render_pair(xyz: torch.Tensor, offs: torch.Tensor, views: torch.Tensor, rho,
         need_winner = torch.is_grad_enabled() and xyz.requires_grad
     pose = as_pose(pose, (offs.numel() - 1) // 2, xyz.device)
     return _DualRender.apply(xyz, offs, pose, views, int(w), float(rho), int(_lib.F_RAW if raw else 0),
-                             bool(need_winner), int(max_item_pts))
+                             bool(need_winner), int(max_item_pts), bool(real_winner))
 
 
 PAIR_MAX_PTS = 147456          # scream_render_forward_pair's limit (giant pairs take the batched entry point and its pre-filter)

@@ -432,8 +432,12 @@ def test_dual_render_equals_two_calls():
         fake, win, zr = render_batch(x1, offs, views, 24, 64, raw=raw, need_winner=True)
         real, winr, zrr = render_batch(x1.detach(), offs, views, 24, 64, pose=pose, raw=raw, need_winner=True)
         fake.backward(grad)
-        dfake, dreal, dwin, dzr = render_pair(x2, offs, views, 24, 64, pose, raw=raw, need_winner=True)
+        dfake, dreal, dwin, dzr = render_pair(x2, offs, views, 24, 64, pose, raw=raw, need_winner=True, real_winner=True)
         dfake.backward(grad)
+        # default: no winner map for the posed render (SCREAM_F_DUAL_NOWIN1) -- same images, the map of the render as given
+        nfake, nreal, nwin, nzr = render_pair(x2.detach(), offs, views, 24, 64, pose, raw=raw, need_winner=True)
+        assert nwin.shape[0] == 1 and torch.equal(nwin[0], win) and torch.equal(nfake, fake) and torch.equal(nreal, real)
+        assert torch.equal(nzr, dzr)
         assert torch.equal(dzr[0], zr) and torch.equal(dzr[1], zrr)
         assert torch.equal(dfake, fake) and torch.equal(dreal, real)
         assert torch.equal(dwin[0], win) and torch.equal(dwin[1], winr)
