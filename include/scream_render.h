@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define SCREAM_ABI_VERSION 8
+#define SCREAM_ABI_VERSION 9
 
 /* error codes */
 #define SCREAM_OK            0
@@ -108,6 +108,22 @@ int scream_render_forward(const float *xyz, const int64_t *offs, int64_t total_p
                           int B, int V, int w, double rho, unsigned flags,
                           float *imgs, int32_t *winner, float *zrange,
                           void *ws, size_t ws_bytes, scream_stream_t stream);
+
+/* scream_render_forward without a workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, flags, outputs and bits as scream_render_forward; the scratch (the encoded
+ * depth ranges of render.py:30-31) is a static device array of SCREAM_NOALLOC_WS_BYTES inside the library, which every GPU
+ * that loads the library holds until exit.  Limits: the call's workspace (scream_render_workspace_bytes) must fit, i.e.
+ * B*V <= SCREAM_NOALLOC_WS_BYTES / 16 = 4096 (item, view) pairs and fewer than 147456 points per item on average (the
+ * giant-cloud pre-filter needs hundreds of MB: use scream_render_forward); beyond that SCREAM_E_UNSUPPORTED, nothing launched.
+ * The function calls no cudaMalloc / cudaFree / allocating routine.  ALL calls on a device share the one array (it keeps the
+ * last call's contents; every word a call reads is rewritten by that call first): calls that overlap on the GPU -- two
+ * streams, two threads, two processes' worth of streams in one context -- RACE; serialise them on one stream. */
+#define SCREAM_NOALLOC_WS_BYTES 65536
+int scream_render_forward_noalloc(const float *xyz, const int64_t *offs, int64_t total_pts, int64_t max_item_pts,
+                                  const float *pose, const float *views,
+                                  int B, int V, int w, double rho, unsigned flags,
+                                  float *imgs, int32_t *winner, float *zrange, scream_stream_t stream);
 
 /* Backward: replaces the autograd graph of render.py:27-73.  Scatters
  * grad_imgs [B,V,2,w,w] through the saved winner map to grad_xyz [total_pts,3] (overwritten: the

@@ -11,7 +11,7 @@ import threading
 
 from .csrc import build as _build
 
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 F_RAW = 1
 F_DENSE = 2
@@ -21,6 +21,7 @@ F_THINSEED = 16
 F_DUAL = 32
 F_HALF = 64
 F_DUAL_NOWIN1 = 128
+NOALLOC_WS_BYTES = 65536
 
 _lock = threading.Lock()
 _lib = None
@@ -32,6 +33,8 @@ _SIGNATURES = {
     "scream_render_workspace_bytes": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int64, C.POINTER(C.c_size_t)]),
     "scream_render_forward": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, C.c_int, C.c_int, C.c_int,
                                         C.c_double, C.c_uint, _P, _P, _P, _P, C.c_size_t, _P]),
+    "scream_render_forward_noalloc": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, C.c_int, C.c_int, C.c_int,
+                                                C.c_double, C.c_uint, _P, _P, _P, _P]),
     "scream_render_backward": (C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P, C.c_int, C.c_int, C.c_int,
                                          C.c_double, C.c_uint, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "scream_render_forward_pair": (C.c_int, [_P, C.c_int64, _P, C.c_int64, _P, _P, C.c_int, C.c_int, C.c_double, C.c_uint,

@@ -295,6 +295,45 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
                         stream, Shard());
 }
 
+// ---- no-allocation variant (no counterpart in the reference) -------------
+// The scratch of scream_render_forward (the encoded depth ranges that the z-range kernels reduce into and the render kernel
+// reads) lives in a file-scope device array instead of a caller workspace, for callers that cannot cudaMalloc (CUDA graph
+// capture, tight serving loops).  Every GPU that loads the library holds SCREAM_NOALLOC_WS_BYTES until exit.  In host code
+// the array's NAME is a host-side stand-in, not a device address: the address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+static __device__ __align__(256) unsigned char g_noalloc_ws[SCREAM_NOALLOC_WS_BYTES];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+void* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};            // per device, resolved on first use (idempotent: racing threads store the same value)
+}
+
+int scream_render_forward_noalloc(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
+                                  const float* pose, const float* views,
+                                  int B, int V, int w, double rho, unsigned flags,
+                                  float* imgs, int32_t* winner, float* zrange, scream_stream_t stream)
+{
+    if (int rc = check_common(xyz, offs, views, B, V, w, rho, total_pts)) return rc;
+    const size_t need = ws_layout(B, V, w, total_pts).total;
+    if (need > (size_t)SCREAM_NOALLOC_WS_BYTES)
+        return fail(SCREAM_E_UNSUPPORTED, "scream_render_forward_noalloc: this call needs %zu bytes of scratch, the static array holds %d "
+                    "(B*V <= %d and fewer than %lld points per item on average); use scream_render_forward with a caller workspace",
+                    need, SCREAM_NOALLOC_WS_BYTES, SCREAM_NOALLOC_WS_BYTES / 16, (long long)FS_MIN_AVG_PTS);
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail(SCREAM_E_UNSUPPORTED, "device ordinal %d beyond %d", dev, NOALLOC_MAX_DEVICES);
+    void* ptr = g_noalloc_ptr[dev];
+    if (!ptr) {
+        CUDA_TRY(cudaGetSymbolAddress(&ptr, g_noalloc_ws));
+        if (!ptr) return fail(SCREAM_E_CUDA, "cudaGetSymbolAddress returned NULL");
+        g_noalloc_ptr[dev] = ptr;
+    }
+    // nothing in the array has to start at zero: the z-range stage (zrange_init_kernel / zrange_encode_kernel) rewrites every
+    // word the render reads, on the caller's stream, before the render kernel is launched on it
+    return forward_impl(xyz, offs, total_pts, max_item_pts, pose, views, B, V, w, rho, flags, imgs, winner, zrange,
+                        ptr, (size_t)SCREAM_NOALLOC_WS_BYTES, stream, Shard());
+}
+
 int scream_render_forward_sharded(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
                                   const float* views, int B, int V, int w, double rho, unsigned flags,
                                   int stage, int rank, int world,
