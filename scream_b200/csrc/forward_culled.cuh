@@ -309,6 +309,21 @@ constexpr unsigned FC_FLAG_DUAL = 32u;                   // SCREAM_F_DUAL
 constexpr unsigned FC_FLAG_NOWIN1 = 128u;                // SCREAM_F_DUAL_NOWIN1
 constexpr unsigned FC_FLAG_HALF = 64u;                   // SCREAM_F_HALF: fp16 depth-weight chain (common.cuh)
 
+// Phase timeline of a CTA (diagnostic builds only: tools/diag_cfg1_timeline.py compiles with -DFC_TIMELINE): SM cycle
+// counter at the phase boundaries (thread 0, behind the phase's barrier), queue lengths and per-task times.
+#ifdef FC_TIMELINE
+__device__ long long g_fc_marks[1024][16];
+#define FC_MARK(k) do { if (threadIdx.x == 0) g_fc_marks[blockIdx.x & 1023][(k)] = clock64(); } while (0)
+#define FC_COUNT(k, n) atomicAdd(reinterpret_cast<unsigned long long*>(&g_fc_marks[blockIdx.x & 1023][(k)]), (unsigned long long)(n))
+#define FC_MAXOF(k, n) atomicMax(reinterpret_cast<unsigned long long*>(&g_fc_marks[blockIdx.x & 1023][(k)]), (unsigned long long)(n))
+#define FC_CLOCK() clock64()
+#else
+#define FC_MARK(k) do { } while (0)
+#define FC_COUNT(k, n) do { } while (0)
+#define FC_MAXOF(k, n) do { } while (0)
+#define FC_CLOCK() 0ll
+#endif
+
 __global__ void __launch_bounds__(FC_THREADS, 1)
 forward_culled_kernel(FwdParams P)
 {
@@ -326,6 +341,11 @@ forward_culled_kernel(FwdParams P)
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int w = P.w, npix = w * w, half = w / 2;
+#ifdef FC_TIMELINE
+    if (tid < 16) g_fc_marks[blockIdx.x & 1023][tid] = 0;
+    __syncthreads();
+#endif
+    FC_MARK(0);
     // Work of this CTA.  Plain call: image (b, v, c).  SCREAM_F_DUAL (the "fake" and the "real" render of a
     // training step in one launch): outputs carry a leading pose dimension [2][B]... -- 0 = clouds as given, 1 = source
     // posed -- and the CTAs of (b, v) are: source as given, source posed, and ONE for the target, which sorts the target
@@ -409,6 +429,7 @@ forward_culled_kernel(FwdParams P)
         zl = __reduce_min_sync(0xFFFFFFFFu, zl); zh = __reduce_max_sync(0xFFFFFFFFu, zh);
         if (lane == 0) { atomicMin(&s_zr[0], zl); atomicMax(&s_zr[1], zh); }
         __syncthreads();
+        FC_MARK(1);
     }
     const float zmin = dec_f32(P.fuse_zrange ? s_zr[0] : P.zenc[(ob * P.V + v) * 2]);
     const float zmax = dec_f32(P.fuse_zrange ? s_zr[1] : P.zenc[(ob * P.V + v) * 2 + 1]);
@@ -473,6 +494,7 @@ forward_culled_kernel(FwdParams P)
             }
         }
         __syncthreads();
+        FC_MARK(2);
 
         // ---------------- P2: exclusive scan over the cells -----------------------------------
         {
@@ -504,6 +526,7 @@ forward_culled_kernel(FwdParams P)
             if (tid == FC_THREADS - 1) s_start[FC_CELLS] = (unsigned short)run;
         }
         __syncthreads();
+        FC_MARK(3);
 
         // ---------------- P3: occupancy masks + scatter of the records into cell order ---------
         if (tid < (FC_G / 4) * 32) {                      // warp wq builds rows 4wq..4wq+3
@@ -546,6 +569,7 @@ forward_culled_kernel(FwdParams P)
             rx[0] = 0.0f; rx[2] = 0.0f; *rec_c(s_rec, cnt) = INFINITY; *rec_idx(s_rec, cnt) = 0;
         }
         __syncthreads();
+        FC_MARK(4);
 
         // ---------------- P3b: Chebyshev distance transform of the cell occupancy -------------
         // h[i][j] = distance to the nearest occupied cell of row i (bit tricks on the row mask), then
@@ -574,6 +598,7 @@ forward_culled_kernel(FwdParams P)
                 s_ring[cell] = (unsigned char)best;
             }
             __syncthreads();
+            FC_MARK(5);
         }
 
         } else {
@@ -632,6 +657,7 @@ forward_culled_kernel(FwdParams P)
                 }
             }
             __syncthreads();
+            FC_MARK(6);
 
             // ---- disc scan of one queued pixel (far: no candidate; near: the best record of its 3 x 3 window) ----
             auto scan_pixel = [&](int pl, int cand) {
@@ -676,9 +702,12 @@ forward_culled_kernel(FwdParams P)
                 if (lane == 0) t = (int)atomicAdd(&s_work, 1u);
                 t = __shfl_sync(0xFFFFFFFFu, t, 0);
                 if (t >= far_batches + FC_TPIX / 32 / nparts) break;
+                const long long task_t0 = FC_CLOCK(); (void)task_t0;
                 if (t < far_batches) {
                     const int qi = t * far_take + lane;
                     if (lane < far_take && qi < nfar) scan_pixel(s_queue[qi], 0xFFFF);
+                    __syncwarp();
+                    if (lane == 0) { FC_MAXOF(12, FC_CLOCK() - task_t0); FC_COUNT(14, FC_CLOCK() - task_t0); }
                     continue;
                 }
                 // ---- 3 x 3 cells, lane per pixel ----
@@ -716,14 +745,17 @@ forward_culled_kernel(FwdParams P)
                     nb = __shfl_sync(0xFFFFFFFFu, nb, 0);
                     if (near) s_queue[FC_TPIX - 1 - (nb + __popc(nm & ((1u << lane) - 1u)))] = (unsigned short)pl;
                 }
+                if (lane == 0) { FC_MAXOF(13, FC_CLOCK() - task_t0); FC_COUNT(15, FC_CLOCK() - task_t0); }
             }
             __syncthreads();
+            FC_MARK(7);
 
             // ---- the near queue, 32 pixels at a time with all lanes busy: the 5 x 5 window, five row runs in lockstep.
             // Typical case: the winner is a deep point (score offset c > 2.25 cells^2, i.e. pv < 0.53), so the 3 x 3 radius
             // test can never pass although the winner is a cell away; 17 % of the pixels of a unit-ball view, none of them
             // with a best score beyond the 5 x 5 reach of 6.25 cells^2.  What stays open takes the general disc scan.
             const int nnear = (int)s_qnear;
+            if (tid == 0) { FC_COUNT(9, nfar); FC_COUNT(10, nnear); }
             const int near_take = (FC_NEAR_SPREAD || nparts > 1) ? max(1, min(32, (nnear + 31) >> 5)) : 32;
             for (;;) {
                 int qi = 0;
@@ -753,10 +785,12 @@ forward_culled_kernel(FwdParams P)
                     const float val = exact_value(S, E, a1, g, id);
                     put(row, col, val, id);
                 } else {
+                    FC_COUNT(11, 1);
                     scan_pixel(pl, a1 < 0 ? 0xFFFF : a1);
                 }
             }
             __syncthreads();
+            FC_MARK(8);
         }
         c0 += cnt; ++batch;
     } while (c0 < npts);

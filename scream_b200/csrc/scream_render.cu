@@ -295,6 +295,15 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
                         stream, Shard());
 }
 
+#ifdef FC_TIMELINE
+// diagnostic builds only: the phase marks of the last forward_culled_kernel launch (forward_culled.cuh), [1024][16] int64
+int scream_debug_fc_marks(long long* host_out) {
+    CUDA_TRY(cudaDeviceSynchronize());
+    CUDA_TRY(cudaMemcpyFromSymbol(host_out, g_fc_marks, sizeof(long long) * 1024 * 16));
+    return 0;
+}
+#endif
+
 // ---- no-allocation variant (no counterpart in the reference) -------------
 // The scratch of scream_render_forward (the encoded depth ranges that the z-range kernels reduce into and the render kernel
 // reads) lives in a file-scope device array instead of a caller workspace, for callers that cannot cudaMalloc (CUDA graph
