@@ -37,6 +37,7 @@ constexpr int FC_THREADS = 1024;
 constexpr int FC_PPT = 12;                               // points per thread per batch
 constexpr int FC_CAP = FC_THREADS * FC_PPT;              // 12288 points per batch
 constexpr int FC_NEAR_SPREAD = 0;                        // near queue spread over all warps also when the GPU is full (A/B)
+constexpr int FC_COOP_FAR = 4;                           // small grids: far pixels a warp searches together before their values are evaluated side by side
 constexpr int FC_AHEAD = 2;                              // points whose global loads are in flight ahead of the one in work (P1, P3)
 constexpr int FC_G = 64;                                 // cell grid side
 constexpr int FC_CELLS = FC_G * FC_G;
@@ -282,6 +283,48 @@ __device__ __forceinline__ void disc_scan(const FcShared& S, const ExactCtx& E, 
     if (!EXACT) a1 = best_of_pair(S, a1, g);             // the search tracked the best PAIR
 }
 
+// One grid row of the disc of radius rc (cells) around pixel g, fixed radius: the records of the row's column span, the
+// expressions of disc_scan.  The warp-cooperative scan (small grids, see the kernel) gives every lane rows of its own.
+template <bool EXACT>
+__device__ __forceinline__ void row_scan(const FcShared& S, const ExactCtx& E, const PixelGeom& g, int i, float rc, float s_thr,
+                                         float& s1, float& s2, int& a1, float& best, int& arg)
+{
+    const int ci = (int)g.uy;
+    const float dist = i == ci ? 0.0f : (i < ci ? __fsub_rn(g.uy, (float)(i + 1)) : __fsub_rn((float)i, g.uy));
+    if (dist > rc) return;
+    const float h2 = __fmaf_rn(rc, rc, -__fmul_rn(dist, dist));
+    float hw;                                            // sqrt.approx (2 ulp) + 1e-3 cells: still an upper bound of the half width
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(hw) : "f"(fmaxf(h2, 0.0f)));
+    hw += 1e-3f;
+    const int j0 = max(0, (int)floorf(g.ux - hw)), j1 = min(FC_G - 1, (int)floorf(g.ux + hw));
+    if (j0 > j1 || (S.rowmask[i] & col_mask(j0, j1)) == 0ull) return;
+    const int rb = S.start[i * FC_G + j0], re = S.start[i * FC_G + j1 + 1];
+    if (EXACT) {
+#pragma unroll 1
+        for (int p = rb >> 1; p < (re + 1) >> 1; ++p) {
+            const float2 sc = score_pair(S, p, g);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if ((h ? sc.y : sc.x) <= s_thr) {
+                    int id;
+                    const float val = exact_value(S, E, 2 * p + h, g, id);
+                    if (val > best || (val == best && id < arg)) { best = val; arg = id; }
+                }
+            }
+        }
+    } else {
+        bool improved = false;
+        scan_run(S, rb, re, g, s1, s2, a1, improved);
+    }
+}
+// minimum over the warp of scores: non-negative floats or +inf (never NaN: the searches fold scores with fminf), whose bit
+// patterns order like unsigned integers -- one REDUX instead of five shuffle steps.  A NaN operand (a record whose depth
+// weight rounded below zero) is mapped to +inf first.
+__device__ __forceinline__ float warp_min(float v) {
+    const unsigned b = (v == v) ? __float_as_uint(v) & 0x7FFFFFFFu : 0x7F800000u;       // -0 -> +0
+    return __uint_as_float(__reduce_min_sync(0xFFFFFFFFu, b));
+}
+
 // Visiting order of a tile's 64 pixel rows: from the top and bottom edges towards the middle (the pixels farthest from a
 // centred cloud, i.e. the longest disc scans, first).  lpt_row: visiting index -> row; lpt_vis: its inverse.
 __device__ __forceinline__ int lpt_row(int vis) { return vis < 16 ? vis : (vis < 32 ? 79 - vis : (vis < 48 ? vis - 16 : 95 - vis)); }
@@ -312,7 +355,7 @@ constexpr unsigned FC_FLAG_HALF = 64u;                   // SCREAM_F_HALF: fp16 
 // Phase timeline of a CTA (diagnostic builds only: tools/diag_cfg1_timeline.py compiles with -DFC_TIMELINE): SM cycle
 // counter at the phase boundaries (thread 0, behind the phase's barrier), queue lengths and per-task times.
 #ifdef FC_TIMELINE
-__device__ long long g_fc_marks[1024][16];
+__device__ long long g_fc_marks[1024][24];
 #define FC_MARK(k) do { if (threadIdx.x == 0) g_fc_marks[blockIdx.x & 1023][(k)] = clock64(); } while (0)
 #define FC_COUNT(k, n) atomicAdd(reinterpret_cast<unsigned long long*>(&g_fc_marks[blockIdx.x & 1023][(k)]), (unsigned long long)(n))
 #define FC_MAXOF(k, n) atomicMax(reinterpret_cast<unsigned long long*>(&g_fc_marks[blockIdx.x & 1023][(k)]), (unsigned long long)(n))
@@ -342,7 +385,7 @@ forward_culled_kernel(FwdParams P)
     const int tid = threadIdx.x, lane = tid & 31;
     const int w = P.w, npix = w * w, half = w / 2;
 #ifdef FC_TIMELINE
-    if (tid < 16) g_fc_marks[blockIdx.x & 1023][tid] = 0;
+    if (tid < 24) g_fc_marks[blockIdx.x & 1023][tid] = 0;
     __syncthreads();
 #endif
     FC_MARK(0);
@@ -689,21 +732,128 @@ forward_culled_kernel(FwdParams P)
                 put(row, col, val, id);
             };
 
+            // ---- the same for ONE pixel by a whole warp (all lanes call with the same arguments): small grids are bound by
+            // latency, a lane's disc scan is a serial chain of ~1500 dependent instructions (3 us), and three lanes of a warp
+            // in three different scans run one after the other.  Here every lane takes grid rows of the disc (fixed radius from
+            // a first guess), the lanes' (best, runner-up) merge through shuffles, and the exact pass is shared the same way.
+            // Returns (warp-uniform) the winner's record when the search settled the pixel -- the caller evaluates and writes it
+            // (finish_pixel: one lane per pixel, so the L2 round trips of several pixels overlap) -- or -1: written here.
+            auto finish_pixel = [&](int pl, int a) {
+                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                int id;
+                float val = exact_value(S, E, a, geom(row, col), id);
+                if (val == 0.0f) id = 0;                  // all-zero pixel: torch.max returns index 0
+                put(row, col, val, id);
+            };
+            auto search_pixel_warp = [&](int pl, int cand) -> int {
+                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                const PixelGeom g = geom(row, col);
+                const int ci = (int)g.uy, cj = (int)g.ux;
+                const float r2cap = r2cap_all;
+                float sb = cand == 0xFFFF ? INFINITY : score_of(S, cand, g);
+                const long long w_t0 = FC_CLOCK(); (void)w_t0;
+                if (cand == 0xFFFF) {
+                    // first guess: per grid row the occupied cell nearest to the pixel's column, the nearest of those over the
+                    // warp, the best score of its records (any real point bounds the best score from above)
+                    unsigned key = 0xFFFFFFFFu;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int i = lane + 32 * h;
+                        const unsigned long long m = s_rowmask[i];
+                        const unsigned long long ml = m & ((2ull << cj) - 1ull), mr = m >> cj;
+                        int jn = -1;
+                        if (ml) jn = 63 - __clzll((long long)ml);
+                        if (mr) { const int jr = cj + __ffsll((long long)mr) - 1; if (jn < 0 || jr - cj < cj - jn) jn = jr; }
+                        if (jn >= 0) key = min(key, ((unsigned)((i - ci) * (i - ci) + (jn - cj) * (jn - cj)) << 16) | (unsigned)(i * FC_G + jn));
+                    }
+                    key = __reduce_min_sync(0xFFFFFFFFu, key);
+                    if (key != 0xFFFFFFFFu) {
+                        const int cell = (int)(key & 0xFFFFu), r0 = s_start[cell] + lane;
+                        sb = warp_min(r0 < (int)s_start[cell + 1] ? score_of(S, r0, g) : INFINITY);
+                    }
+                }
+                const long long w_t1 = FC_CLOCK(); (void)w_t1;
+                const float r2 = fminf(r2cap, sb + score_margin(sb, inv_k));
+                const float rc = radius_cells(r2);
+                const int reach = (int)fminf(rc, (float)FC_G) + 1;
+                const int i_lo = max(0, ci - reach), i_hi = min(FC_G - 1, ci + reach);
+                float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
+                float val = 0.0f; int id = 0;
+                for (int i = i_lo + lane; i <= i_hi; i += 32) row_scan<false>(S, E, g, i, rc, 0.0f, s1, s2, a1, val, id);
+                __syncwarp();
+                const long long w_t2 = FC_CLOCK(); (void)w_t2;
+                a1 = best_of_pair(S, a1, g);
+                const float m1 = warp_min(s1);
+                const unsigned wm = __ballot_sync(0xFFFFFFFFu, s1 == m1 && a1 >= 0);
+                if (wm != 0u && m1 <= r2cap) {
+                    const int wl = __ffs(wm) - 1;
+                    // runner-up of the disc: the winner lane's own, or the best of any other lane (a second lane with the same
+                    // best score leaves s2 == s1: unresolved, as in the serial search)
+                    const float m2 = warp_min(lane == wl ? s2 : s1);
+                    const int a = __shfl_sync(0xFFFFFFFFu, a1, wl);
+                    float s_thr = m1 + score_margin(m1, inv_k);
+                    const float e1 = __fmul_rn(m1, -P.negk);
+                    if (e1 >= FC_EXP_DENORM) {
+                        const float lu = e1 - 101.2f;
+                        s_thr = lu >= -0.7f ? s_zero : s_thr + 1.5f * expf(lu) * inv_k;
+                    }
+                    if (lane == 0) { FC_COUNT(16, w_t1 - w_t0); FC_COUNT(17, w_t2 - w_t1); FC_COUNT(18, FC_CLOCK() - w_t2); FC_COUNT(19, 1); FC_COUNT(20, reach); }
+                    if (m2 > s_thr) return a;
+                    {
+                        const float r2e = fminf(s_thr, s_zero), rce = radius_cells(r2e);
+                        const int reach_e = (int)fminf(rce, (float)FC_G) + 1;
+                        for (int i = max(0, ci - reach_e) + lane; i <= min(FC_G - 1, ci + reach_e); i += 32)
+                            row_scan<true>(S, E, g, i, rce, r2e, s1, s2, a1, val, id);
+#pragma unroll
+                        for (int d = 16; d > 0; d >>= 1) {                    // (value, lowest index) over the lanes
+                            const float ov = __shfl_xor_sync(0xFFFFFFFFu, val, d);
+                            const int oid = __shfl_xor_sync(0xFFFFFFFFu, id, d);
+                            if (ov > val || (ov == val && oid < id)) { val = ov; id = oid; }
+                        }
+                    }
+                    if (val == 0.0f) id = 0;
+                }
+                if (lane == 0) put(row, col, val, id);
+                return -1;
+            };
+
             // ---- one dynamic work list: the far batches first (long), then the 3 x 3 chunks (short, uniform) fill the
             // gaps -- the heavy scans do not start after a barrier behind the 3 x 3 phase.
             // batch = the queue entries a warp takes at once: 32 when the GPU is full (issue-bound: lanes are what counts);
             // when several CTAs share an image the kernel is latency-bound instead, a warp's time is its slowest lane's
             // serial chain, and the entries are spread over all 32 warps
+            // Small grids (coop): a far pixel is a task of its own, searched by the whole warp, and the 3 x 3 chunks -- now the
+            // long tasks -- go first.
+            const bool coop = nparts > 1;
             const int nfar = (int)s_qfar;
-            const int far_take = nparts > 1 ? max(1, min(32, (nfar + 31) >> 5)) : 32;
+            const int far_take = coop ? FC_COOP_FAR : 32;
             const int far_batches = (nfar + far_take - 1) / far_take;
+            const int nchunks = FC_TPIX / 32 / nparts;
             for (;;) {
                 int t = 0;
                 if (lane == 0) t = (int)atomicAdd(&s_work, 1u);
                 t = __shfl_sync(0xFFFFFFFFu, t, 0);
-                if (t >= far_batches + FC_TPIX / 32 / nparts) break;
+                if (t >= far_batches + nchunks) break;
                 const long long task_t0 = FC_CLOCK(); (void)task_t0;
-                if (t < far_batches) {
+                if (coop) {
+                    if (t >= nchunks) {
+                        int my_pl = 0, my_a = -1, prev_a = -1;
+                        for (int k = 0; k < FC_COOP_FAR; ++k) {
+                            const int qi = (t - nchunks) * FC_COOP_FAR + k;
+                            if (qi >= nfar) break;
+                            const int pl = s_queue[qi];
+                            // the winner of the previous pixel (usually its neighbour in the row) is the first guess of this one
+                            const int a = search_pixel_warp(pl, prev_a >= 0 ? prev_a : 0xFFFF);
+                            prev_a = a;
+                            if (a >= 0 && lane == k) { my_pl = pl; my_a = a; }
+                        }
+                        if (my_a >= 0) finish_pixel(my_pl, my_a);
+                        __syncwarp();
+                        if (lane == 0) { FC_MAXOF(12, FC_CLOCK() - task_t0); FC_COUNT(14, FC_CLOCK() - task_t0); }
+                        continue;
+                    }
+                    t += far_batches;                    // chunk t of the list below
+                } else if (t < far_batches) {
                     const int qi = t * far_take + lane;
                     if (lane < far_take && qi < nfar) scan_pixel(s_queue[qi], 0xFFFF);
                     __syncwarp();
@@ -757,7 +907,61 @@ forward_culled_kernel(FwdParams P)
             const int nnear = (int)s_qnear;
             if (tid == 0) { FC_COUNT(9, nfar); FC_COUNT(10, nnear); }
             const int near_take = (FC_NEAR_SPREAD || nparts > 1) ? max(1, min(32, (nnear + 31) >> 5)) : 32;
-            for (;;) {
+            // Small grids: four pixels per warp, eight lanes each -- five of them take one row run of the 5 x 5 window each, the
+            // (best, runner-up) of the rows merge through shuffles, the group's first lane decides and evaluates.  (Lanes in
+            // lockstep instead of three lanes walking three different windows one after the other.)
+            for (; coop;) {
+                int q0 = 0;
+                if (lane == 0) q0 = (int)atomicAdd(&s_qhead, 4u);
+                q0 = __shfl_sync(0xFFFFFFFFu, q0, 0);
+                if (q0 >= nnear) break;
+                const int grp = lane >> 3, gl = lane & 7, qi = q0 + grp;
+                const bool act = qi < nnear;
+                const int pl = act ? s_queue[FC_TPIX - 1 - qi] : 0;
+                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                const PixelGeom g = geom(row, col);
+                const int ci = (int)g.uy, cj = (int)g.ux;
+                float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
+                bool found = false;
+                const int i = ci - 2 + gl;
+                if (act && gl < 5 && i >= 0 && i < FC_G)
+                    scan_run(S, s_start[i * FC_G + max(cj - 2, 0)], s_start[i * FC_G + min(cj + 2, FC_G - 1) + 1], g, s1, s2, a1, found);
+                a1 = best_of_pair(S, a1, g);
+                float m1 = s1;
+#pragma unroll
+                for (int d = 4; d > 0; d >>= 1) m1 = fminf(m1, __shfl_xor_sync(0xFFFFFFFFu, m1, d));
+                const unsigned wm = (__ballot_sync(0xFFFFFFFFu, s1 == m1 && a1 >= 0) >> (8 * grp)) & 0xFFu;
+                const int wl = 8 * grp + (wm ? __ffs(wm) - 1 : 0);
+                float m2 = (wm && lane == wl) ? s2 : s1;
+#pragma unroll
+                for (int d = 4; d > 0; d >>= 1) m2 = fminf(m2, __shfl_xor_sync(0xFFFFFFFFu, m2, d));
+                const int a = __shfl_sync(0xFFFFFFFFu, a1, wl);
+                int fb_cand = -2;
+                if (act && gl == 0) {
+                    const float fx = g.ux - (float)cj, fy = g.uy - (float)ci;
+                    const float edge = fminf(fminf(fx, 1.0f - fx), fminf(fy, 1.0f - fy));
+                    const float cov = __fmul_rn(2.0f + edge, 1.0f / FC_CELLS_PER_NDC);
+                    const float cov2 = __fmul_rn(__fmul_rn(cov, cov), 0.99999f);
+                    const float m = score_margin(m1, inv_k);
+                    if (wm && (m1 + m < cov2) && (m2 > m1 + m) && (__fmul_rn(m1, -P.negk) < FC_EXP_DENORM)) {
+                        int id;
+                        const float val = exact_value(S, E, a, g, id);
+                        put(row, col, val, id);
+                    } else {
+                        FC_COUNT(11, 1);
+                        fb_cand = wm ? a : 0xFFFF;
+                    }
+                }
+                unsigned fbm = __ballot_sync(0xFFFFFFFFu, fb_cand != -2);
+                while (fbm) {
+                    const int src = __ffs(fbm) - 1;
+                    fbm &= fbm - 1u;
+                    const int fpl = __shfl_sync(0xFFFFFFFFu, pl, src);
+                    const int fa = search_pixel_warp(fpl, __shfl_sync(0xFFFFFFFFu, fb_cand, src));
+                    if (fa >= 0 && lane == 0) finish_pixel(fpl, fa);
+                }
+            }
+            for (; !coop;) {
                 int qi = 0;
                 if (lane == 0) qi = (int)atomicAdd(&s_qhead, (unsigned)near_take);
                 qi = __shfl_sync(0xFFFFFFFFu, qi, 0) + lane;

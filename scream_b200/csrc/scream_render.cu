@@ -296,10 +296,10 @@ int scream_render_forward(const float* xyz, const int64_t* offs, int64_t total_p
 }
 
 #ifdef FC_TIMELINE
-// diagnostic builds only: the phase marks of the last forward_culled_kernel launch (forward_culled.cuh), [1024][16] int64
+// diagnostic builds only: the phase marks of the last forward_culled_kernel launch (forward_culled.cuh), [1024][24] int64
 int scream_debug_fc_marks(long long* host_out) {
     CUDA_TRY(cudaDeviceSynchronize());
-    CUDA_TRY(cudaMemcpyFromSymbol(host_out, g_fc_marks, sizeof(long long) * 1024 * 16));
+    CUDA_TRY(cudaMemcpyFromSymbol(host_out, g_fc_marks, sizeof(long long) * 1024 * 24));
     return 0;
 }
 #endif

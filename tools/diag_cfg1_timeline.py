@@ -25,7 +25,7 @@ for it in range(4):
     with torch.no_grad():
         out = r(src, tgt)
     torch.cuda.synchronize()
-marks = np.zeros((1024, 16), dtype=np.int64)
+marks = np.zeros((1024, 24), dtype=np.int64)
 lib.scream_debug_fc_marks(marks.ctypes.data)
 n = V * 2 * 8
 m = marks[:n]
@@ -38,6 +38,8 @@ print(f"  total     {tot.mean():7.2f} {tot.max():7.2f}")
 print("far pixels per CTA mean/max", m[:, 9].mean(), m[:, 9].max(), " near", m[:, 10].mean(), m[:, 10].max(), " fallback", m[:, 11].mean(), m[:, 11].max())
 print("far batch us: max over CTAs of max", m[:, 12].max() / 1.9e3, "mean of max", m[:, 12].mean() / 1.9e3, " mean task", (m[:, 14].sum() / np.maximum(1, np.ceil(m[:, 9] / np.maximum(1, np.minimum(32, (m[:, 9] + 31) // 32))).sum())) / 1.9e3)
 print("3x3 chunk us: max over CTAs of max", m[:, 13].max() / 1.9e3, "mean of max", m[:, 13].mean() / 1.9e3, " mean task", m[:, 15].sum() / (n * 16) / 1.9e3)
+ns = np.maximum(1, m[:, 19].sum())
+print("warp search per pixel (us): guess", m[:, 16].sum() / ns / 1.9e3, "rows", m[:, 17].sum() / ns / 1.9e3, "merge", m[:, 18].sum() / ns / 1.9e3, " searches per CTA", m[:, 19].mean(), " mean reach (rows)", m[:, 20].sum() / ns)
 worst = np.argsort(-d[:, 7])[:6]
 for cta in worst:
     print(f"  cta {cta}: near phase {d[cta, 7]:.2f} us, near {m[cta, 10]}, fallback {m[cta, 11]}, worklist {d[cta, 6]:.2f}, far {m[cta, 9]}")
