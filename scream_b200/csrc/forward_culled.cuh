@@ -37,7 +37,10 @@ constexpr int FC_THREADS = 1024;
 constexpr int FC_PPT = 12;                               // points per thread per batch
 constexpr int FC_CAP = FC_THREADS * FC_PPT;              // 12288 points per batch
 constexpr int FC_NEAR_SPREAD = 0;                        // near queue spread over all warps also when the GPU is full (A/B)
-constexpr int FC_COOP_FAR = 4;                           // small grids: far pixels a warp searches together before their values are evaluated side by side
+#ifndef FC_COOP_FAR_N
+#define FC_COOP_FAR_N 4
+#endif
+constexpr int FC_COOP_FAR = FC_COOP_FAR_N;                           // small grids: far pixels a warp searches together before their values are evaluated side by side
 constexpr int FC_AHEAD = 2;                              // points whose global loads are in flight ahead of the one in work (P1, P3)
 constexpr int FC_G = 64;                                 // cell grid side
 constexpr int FC_CELLS = FC_G * FC_G;
