@@ -45,7 +45,8 @@ def up_to_date() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and up_to_date():
         return LIB
-    cmd = [find_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + SOURCES
+    # SCREAM_DEFS: extra -D switches of an A/B build (tools/ab_build.sh); the shipped library is built without
+    cmd = [find_nvcc()] + NVCC_FLAGS + os.environ.get("SCREAM_DEFS", "").split() + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + SOURCES
     res = subprocess.run(cmd, cwd=HERE, capture_output=True, text=True)
     if verbose or res.returncode != 0:
         sys.stderr.write(" ".join(cmd) + "\n" + res.stdout + res.stderr)

@@ -37,6 +37,10 @@ constexpr int FC_THREADS = 1024;
 constexpr int FC_PPT = 12;                               // points per thread per batch
 constexpr int FC_CAP = FC_THREADS * FC_PPT;              // 12288 points per batch
 constexpr int FC_NEAR_SPREAD = 0;                        // near queue spread over all warps also when the GPU is full (A/B)
+#ifndef FC_FAR_TAKE_N
+#define FC_FAR_TAKE_N 32
+#endif
+constexpr int FC_FAR_TAKE = FC_FAR_TAKE_N;                 // far pixels a warp takes at once when every image has a CTA of its own
 #ifndef FC_COOP_FAR_N
 #define FC_COOP_FAR_N 4
 #endif
@@ -829,7 +833,7 @@ forward_culled_kernel(FwdParams P)
             // long tasks -- go first.
             const bool coop = nparts > 1;
             const int nfar = (int)s_qfar;
-            const int far_take = coop ? FC_COOP_FAR : 32;
+            const int far_take = coop ? FC_COOP_FAR : FC_FAR_TAKE;
             const int far_batches = (nfar + far_take - 1) / far_take;
             const int nchunks = FC_TPIX / 32 / nparts;
             for (;;) {

@@ -21,13 +21,22 @@ r = R.RegistrationRender(24, 64, device=dev)
 if V != 6:
     r.eulers = r.eulers[:V]
 names = ["start", "zrange", "P1", "P2", "P3", "P3b", "classify", "worklist", "near"]
+BATCH = int(sys.argv[2]) if len(sys.argv) > 2 else 0       # > 0: that many pairs through render_batch (one CTA per image, cfg2's mode)
+if BATCH:
+    xyz = torch.cat([torch.cat([torch.from_numpy(synth.unit_ball(10000, 2 * i + 1)), torch.from_numpy(synth.unit_ball(10000, 2 * i + 2))]) for i in range(BATCH)]).to(dev)
+    offs = R.make_offsets([(10000, 10000)] * BATCH).to(dev)
+    vm = R.view_matrices(r.eulers).to(dev)
+    class _B:
+        def __call__(self, a, b):
+            return R.render_batch(xyz, offs, vm, 24, 64, need_winner=True)[0]
+    r = _B()
 for it in range(4):
     with torch.no_grad():
         out = r(src, tgt)
     torch.cuda.synchronize()
 marks = np.zeros((1024, 24), dtype=np.int64)
 lib.scream_debug_fc_marks(marks.ctypes.data)
-n = V * 2 * 8
+n = min(1024, V * 2 * BATCH) if BATCH else V * 2 * 8
 m = marks[:n]
 d = np.diff(m[:, :9], axis=1) / 1.9e3          # us at ~1.9 GHz
 import time
@@ -46,7 +55,7 @@ tot = (m[:, 8] - m[:, 0]) / 1.9e3
 print(f"  total     {tot.mean():7.2f} {tot.max():7.2f}")
 print("far pixels per CTA mean/max", m[:, 9].mean(), m[:, 9].max(), " near", m[:, 10].mean(), m[:, 10].max(), " fallback", m[:, 11].mean(), m[:, 11].max())
 print("far batch us: max over CTAs of max", m[:, 12].max() / 1.9e3, "mean of max", m[:, 12].mean() / 1.9e3, " mean task", (m[:, 14].sum() / np.maximum(1, np.ceil(m[:, 9] / np.maximum(1, np.minimum(32, (m[:, 9] + 31) // 32))).sum())) / 1.9e3)
-print("3x3 chunk us: max over CTAs of max", m[:, 13].max() / 1.9e3, "mean of max", m[:, 13].mean() / 1.9e3, " mean task", m[:, 15].sum() / (n * 16) / 1.9e3)
+print("3x3 chunk us: max over CTAs of max", m[:, 13].max() / 1.9e3, "mean of max", m[:, 13].mean() / 1.9e3, " mean task", m[:, 15].sum() / (n * (128 if BATCH else 16)) / 1.9e3)
 if m[:, 21].max() > 0:
     print("cluster sort (us, mean): P1 work", ((m[:, 21] - m[:, 1]) / 1.9e3).mean(), "P1 barrier", ((m[:, 2] - m[:, 21]) / 1.9e3).mean(),
           "P3 work", ((m[:, 22] - m[:, 3]) / 1.9e3).mean(), "P3 barrier", ((m[:, 23] - m[:, 22]) / 1.9e3).mean(), "copy", ((m[:, 4] - m[:, 23]) / 1.9e3).mean())
