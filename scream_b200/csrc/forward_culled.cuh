@@ -46,6 +46,7 @@ constexpr int FC_FAR_TAKE = FC_FAR_TAKE_N;                 // far pixels a warp 
 #endif
 constexpr int FC_COOP_FAR = FC_COOP_FAR_N;                           // small grids: far pixels a warp searches together before their values are evaluated side by side
 constexpr int FC_AHEAD = 2;                              // points whose global loads are in flight ahead of the one in work (P1, P3)
+constexpr int FC_DIL_MAX = 31;                           // dilation steps whose masks fit the histogram's memory (31 x 64 x 8 bytes)
 constexpr int FC_G = 64;                                 // cell grid side
 constexpr int FC_CELLS = FC_G * FC_G;
 constexpr int FC_TILE = 64;                              // pixel tile side of P4
@@ -386,8 +387,9 @@ forward_culled_kernel(FwdParams P)
     __shared__ float s_R[9], s_pose[12];
     __shared__ unsigned s_warp_tot[FC_THREADS / 32];
     __shared__ unsigned s_qfar, s_qnear, s_qhead, s_work, s_zr[2];
+    __shared__ int s_kmax;
     __shared__ unsigned long long s_rowmask[FC_G], s_blockmask[FC_G / 4];
-    __shared__ unsigned char s_ring[FC_CELLS];            // Chebyshev distance (cells) to the nearest occupied cell
+    __shared__ __align__(16) unsigned char s_ring[FC_CELLS];            // Chebyshev distance (cells) to the nearest occupied cell
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int w = P.w, npix = w * w, half = w / 2;
@@ -594,6 +596,37 @@ forward_culled_kernel(FwdParams P)
             }
             if (lane == 0) s_blockmask[wq] = bm;
         }
+        // Chebyshev distance (cells) to the nearest occupied cell, by dilation of the row masks: D_k = the cells within k of
+        // an occupied one (row above | row | row below, then x | x << 1 | x >> 1).  ONE warp does the steps while the others
+        // scatter the records (the steps are serial, ~20 instructions each, and nobody waits for them); the masks go to the
+        // histogram's memory, free since P2.  Steps beyond the radius that can matter are not needed: a cell that D_K does
+        // not cover is farther than anything that can change the output.
+        const int need_ring = (int)ceilf(sqrtf(r2cap_all) * FC_CELLS_PER_NDC) + 2;
+        const bool dil = need_ring <= FC_DIL_MAX;         // (a smaller rho reaches farther: the row-wise transform below)
+        unsigned long long* s_dil = reinterpret_cast<unsigned long long*>(s_hist);      // [k - 1][row], k = 1 .. FC_DIL_MAX
+        if (dil && tid < (FC_G / 4 + 1) * 32) {
+            if (tid < (FC_G / 4) * 32) {                  // the mask builders: arrive, do not wait
+                __threadfence_block();
+                asm volatile("bar.arrive 1, %0;" :: "n"((FC_G / 4 + 1) * 32) : "memory");
+            } else {
+                asm volatile("bar.sync 1, %0;" :: "n"((FC_G / 4 + 1) * 32) : "memory");
+                unsigned long long m0 = s_rowmask[2 * lane], m1 = s_rowmask[2 * lane + 1];
+                int kmax = 0;
+                for (int k = 1; k <= need_ring; ++k) {
+                    unsigned long long up = __shfl_up_sync(0xFFFFFFFFu, m1, 1), dn = __shfl_down_sync(0xFFFFFFFFu, m0, 1);
+                    if (lane == 0) up = 0ull;
+                    if (lane == 31) dn = 0ull;
+                    const unsigned long long v0 = up | m0 | m1, v1 = m0 | m1 | dn;
+                    const unsigned long long n0 = v0 | (v0 << 1) | (v0 >> 1), n1 = v1 | (v1 << 1) | (v1 >> 1);
+                    const bool same = n0 == m0 && n1 == m1;
+                    m0 = n0; m1 = n1;
+                    if (__all_sync(0xFFFFFFFFu, same)) break;          // nothing grows any more: all covered, or an empty batch
+                    *reinterpret_cast<ulonglong2*>(s_dil + (k - 1) * FC_G + 2 * lane) = make_ulonglong2(m0, m1);
+                    kmax = k;
+                }
+                if (lane == 0) s_kmax = kmax;
+            }
+        }
         {
             float nx[FC_AHEAD], ny[FC_AHEAD], nz[FC_AHEAD]; int nid[FC_AHEAD];
 #pragma unroll
@@ -626,7 +659,29 @@ forward_culled_kernel(FwdParams P)
         // ring[i][j] = min_i' max(|i-i'|, h[i'][j]), rows outwards with early exit.  Lets empty space be
         // classified without touching the records: a pixel whose ring is >= 2 has nothing in its 3 x 3
         // window, and its nearest point is at least (ring - 1 + edge) cells away.
-        {
+        if (dil) {
+            // ring = the number of steps D_0 .. D_kmax that do not cover the cell (D_k grows with k).  A thread counts for four
+            // neighbouring cells of a row at once: the four mask bits spread into the four bytes of one counter word.
+            const int kmax = s_kmax;
+            {
+                const int i = tid >> 4, j0 = (tid & 15) * 4;
+                unsigned nib = (unsigned)(~s_rowmask[i] >> j0) & 0xFu;
+                unsigned cntw = (nib * 0x00204081u) & 0x01010101u;
+                for (int k = 1; k <= kmax; ++k) {
+                    nib = (unsigned)(~s_dil[(k - 1) * FC_G + i] >> j0) & 0xFu;
+                    cntw += (nib * 0x00204081u) & 0x01010101u;
+                }
+                // still uncovered after the last step: beyond the steps that matter (count = need_ring + 1), or -- the growth
+                // stopped early -- an empty batch: nothing anywhere
+                if (nib != 0u && kmax < need_ring) {
+                    const unsigned far = (nib * 0x00204081u) & 0x01010101u;
+                    cntw = (cntw & ~(far * 0xFFu)) | (far * (unsigned)FC_G);
+                }
+                reinterpret_cast<unsigned*>(s_ring)[tid] = cntw;
+            }
+            __syncthreads();
+            FC_MARK(5);
+        } else {
             unsigned char* s_h = reinterpret_cast<unsigned char*>(s_queue);      // scratch until phase A
             for (int cell = tid; cell < FC_CELLS; cell += FC_THREADS) {
                 const int i = cell >> 6, j = cell & 63;

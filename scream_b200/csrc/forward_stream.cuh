@@ -632,6 +632,10 @@ stream_voxmask_kernel(StreamParams P)
 //      point's cell, then one global atomic per warp and image to reserve list space.
 // Every point that attains a pixel's maximum passes -- all points that tie included -- so rendering the survivors is
 // bit-identical to rendering the cloud.  No block barrier in the loop (queues are per warp, fill levels in registers).
+#ifndef FS_HEAVY_N
+#define FS_HEAVY_N 6
+#endif
+constexpr int FS_HEAVY = FS_HEAVY_N;                     // S3: from this many views on, a point's pairs are queued by the whole warp
 constexpr int FS_WQ = 64;                                // step-2 queue entries per warp: view << 21 | cloud << 20 | point of the chunk
 constexpr int FS_Q1 = 2048;                              // pair queue per warp, a ring (u16: slot << 11 | view << 5 | lane): < 32 left over + 32 * 32 per half round
 constexpr size_t FS_FILTER_SMEM = (size_t)(FS_FILTER_THREADS / 32) * (FS_WQ * sizeof(unsigned) + FS_Q1 * sizeof(unsigned short) + 2 * 96 * sizeof(float))
@@ -845,6 +849,16 @@ stream_filter_kernel(StreamParams P)
                 for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (lane >= d) inc += o; }
                 unsigned pos = q1t + (unsigned)(inc - cnt);
                 q1t += (unsigned)__shfl_sync(0xFFFFFFFFu, inc, 31);
+                // The bit counts are skewed (a rim point passes twenty views, most points none): a lane with many bits has the
+                // whole warp write its pairs in one step (lane v writes view v); the others loop over their few bits.
+                const unsigned heavy = __ballot_sync(0xFFFFFFFFu, cnt >= FS_HEAVY);
+                for (unsigned hm = heavy; hm; hm &= hm - 1u) {
+                    const int L = __ffs(hm) - 1;
+                    const unsigned mL = __shfl_sync(0xFFFFFFFFu, mh, L), pL = __shfl_sync(0xFFFFFFFFu, pos, L);
+                    if ((mL >> lane) & 1u)
+                        q1[(pL + (unsigned)__popc(mL & lt)) & (FS_Q1 - 1)] = (unsigned short)(((unsigned)slot << 11) | ((unsigned)(lane + 32 * half) << 5) | (unsigned)L);
+                }
+                if (cnt >= FS_HEAVY) mh = 0u;
                 while (mh) {
                     const int vv = __ffs(mh) - 1 + 32 * half;
                     mh &= mh - 1u;
