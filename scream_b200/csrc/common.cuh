@@ -68,7 +68,11 @@ __device__ __forceinline__ float rot_row_f16(const float* __restrict__ r, float 
 // render.py:14-16  pixel centre ((j - w//2) + 0.5) / (w//2)  -- exact in fp32 (w/2 is a power of two
 // times at most a 7-bit integer; all intermediate values are multiples of 0.5 below 2^24)
 __device__ __forceinline__ float pixel_centre(int j, int half) {
-    return __fdiv_rn(__fadd_rn(__fsub_rn((float)j, (float)half), 0.5f), (float)half);
+    const float num = __fadd_rn(__fsub_rn((float)j, (float)half), 0.5f);
+    // half a power of two (w = 64, 128, 256, ...): scaling by 2^-e is exact, so the product with the reciprocal -- exponent
+    // arithmetic on the bits of (float)half -- has the bits of the IEEE quotient, without the division's ten instructions
+    if ((half & (half - 1)) == 0) return __fmul_rn(num, __uint_as_float(0x7F000000u - __float_as_uint((float)half)));
+    return __fdiv_rn(num, (float)half);
 }
 
 // render.py:42-43,46  value of one (point, pixel) pair.  negk = -(float)(rho*rho) / 2 ; since /2 is
