@@ -745,7 +745,8 @@ forward_culled_kernel(FwdParams P)
             // ---- classification: background pixels are written, "far" pixels (no occupied cell within the 3 x 3 window:
             // the long disc scans) are queued.  Rows are visited from the tile's top and bottom edges towards its middle,
             // so the pixels farthest from a centred cloud enter the queue first: longest tasks first.
-            for (int ol = tid; ol < FC_TPIX / nparts; ol += FC_THREADS) {
+            const int own_chunks = (FC_TPIX / 32 - part + nparts - 1) / nparts;      // chunks c < 128 with c % nparts == part
+            for (int ol = tid; ol < own_chunks * 32; ol += FC_THREADS) {
                 const int vl = ((ol >> 5) * nparts + part) * 32 + (ol & 31);      // the chunks this CTA owns, in visiting order
                 const int rl = lpt_row(vl / FC_TILE);
                 const int row = trow0 + rl, col = tcol0 + vl % FC_TILE;
@@ -890,7 +891,7 @@ forward_culled_kernel(FwdParams P)
             const int nfar = (int)s_qfar;
             const int far_take = coop ? FC_COOP_FAR : FC_FAR_TAKE;
             const int far_batches = (nfar + far_take - 1) / far_take;
-            const int nchunks = FC_TPIX / 32 / nparts;
+            const int nchunks = own_chunks;
             for (;;) {
                 int t = 0;
                 if (lane == 0) t = (int)atomicAdd(&s_work, 1u);

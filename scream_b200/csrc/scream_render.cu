@@ -16,6 +16,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 using namespace scream;
@@ -83,11 +84,11 @@ int check_common(const void* xyz, const void* offs, const void* views, int B, in
     return 0;
 }
 
-// CTAs per image of the culled kernel: one wave of the 148 SMs (1 CTA / SM) at most, a power of two up to 8
+// CTAs per image of the culled kernel: as many as fill one wave of the 148 SMs (1 CTA / SM) -- every CTA sorts the whole cloud,
+// which is free on SMs that would otherwise idle, and searches 1 / parts of the pixels.  At most 64 (two 32-pixel chunks each).
 int culled_parts(long long images) {
-    int parts = 1;
-    while (parts < 8 && images * parts * 2 <= 148) parts *= 2;
-    return parts;
+    if (const char* e = getenv("SCREAM_MAX_PARTS")) { const int m = atoi(e); if (m >= 1) return (int)std::max<long long>(1, std::min<long long>(m, 148 / std::max<long long>(images, 1))); }
+    return (int)std::max<long long>(1, std::min<long long>(64, 148 / std::max<long long>(images, 1)));
 }
 
 // stage 1: z range of every (item, view) into ws (encoded)

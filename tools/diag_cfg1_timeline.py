@@ -36,7 +36,7 @@ for it in range(4):
     torch.cuda.synchronize()
 marks = np.zeros((1024, 24), dtype=np.int64)
 lib.scream_debug_fc_marks(marks.ctypes.data)
-n = min(1024, V * 2 * BATCH) if BATCH else V * 2 * 8
+n = min(1024, V * 2 * BATCH) if BATCH else V * 2 * min(64, 148 // (V * 2), int(os.environ.get("SCREAM_MAX_PARTS", "64")))
 m = marks[:n]
 d = np.diff(m[:, :9], axis=1) / 1.9e3          # us at ~1.9 GHz
 import time
@@ -55,7 +55,7 @@ tot = (m[:, 8] - m[:, 0]) / 1.9e3
 print(f"  total     {tot.mean():7.2f} {tot.max():7.2f}")
 print("far pixels per CTA mean/max", m[:, 9].mean(), m[:, 9].max(), " near", m[:, 10].mean(), m[:, 10].max(), " fallback", m[:, 11].mean(), m[:, 11].max())
 print("far batch us: max over CTAs of max", m[:, 12].max() / 1.9e3, "mean of max", m[:, 12].mean() / 1.9e3, " mean task", (m[:, 14].sum() / np.maximum(1, np.ceil(m[:, 9] / np.maximum(1, np.minimum(32, (m[:, 9] + 31) // 32))).sum())) / 1.9e3)
-print("3x3 chunk us: max over CTAs of max", m[:, 13].max() / 1.9e3, "mean of max", m[:, 13].mean() / 1.9e3, " mean task", m[:, 15].sum() / (n * (128 if BATCH else 16)) / 1.9e3)
+print("3x3 chunk us: max over CTAs of max", m[:, 13].max() / 1.9e3, "mean of max", m[:, 13].mean() / 1.9e3, " mean task", m[:, 15].sum() / (128 * V * 2 * max(1, BATCH)) / 1.9e3)
 if m[:, 21].max() > 0:
     print("cluster sort (us, mean): P1 work", ((m[:, 21] - m[:, 1]) / 1.9e3).mean(), "P1 barrier", ((m[:, 2] - m[:, 21]) / 1.9e3).mean(),
           "P3 work", ((m[:, 22] - m[:, 3]) / 1.9e3).mean(), "P3 barrier", ((m[:, 23] - m[:, 22]) / 1.9e3).mean(), "copy", ((m[:, 4] - m[:, 23]) / 1.9e3).mean())
