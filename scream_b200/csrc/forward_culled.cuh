@@ -45,7 +45,14 @@ constexpr int FC_FAR_TAKE = FC_FAR_TAKE_N;                 // far pixels a warp 
 #define FC_COOP_FAR_N 4
 #endif
 constexpr int FC_COOP_FAR = FC_COOP_FAR_N;                           // small grids: far pixels a warp searches together before their values are evaluated side by side
-constexpr int FC_AHEAD = 2;                              // points whose global loads are in flight ahead of the one in work (P1, P3)
+#ifndef FC_AHEAD_N
+#define FC_AHEAD_N 2
+#endif
+#ifndef FC_ZFLIGHT_N
+#define FC_ZFLIGHT_N 4
+#endif
+constexpr int FC_ZFLIGHT = FC_ZFLIGHT_N;                   // points in flight per thread in the fused depth-range pass
+constexpr int FC_AHEAD = FC_AHEAD_N;                              // points whose global loads are in flight ahead of the one in work (P1, P3)
 constexpr int FC_DIL_MAX = 31;                           // dilation steps whose masks fit the histogram's memory (31 x 64 x 8 bytes)
 constexpr int FC_G = 64;                                 // cell grid side
 constexpr int FC_CELLS = FC_G * FC_G;
@@ -462,16 +469,16 @@ forward_culled_kernel(FwdParams P)
         // render.py:30-31 inside this kernel: min / max of the rotated depth over BOTH clouds of the item (order-preserving
         // integer codes: exact in any order, so every CTA of the item finds the same bits)
         unsigned zl = 0xFFFFFFFFu, zh = 0u;
-        for (int64_t i0 = sp.src0 + tid; i0 < sp.end; i0 += 4 * FC_THREADS) {      // four points in flight per thread
-            float x[4], y[4], z[4];
+        for (int64_t i0 = sp.src0 + tid; i0 < sp.end; i0 += FC_ZFLIGHT * FC_THREADS) {      // FC_ZFLIGHT points in flight per thread
+            float x[FC_ZFLIGHT], y[FC_ZFLIGHT], z[FC_ZFLIGHT];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < FC_ZFLIGHT; ++u) {
                 const int64_t i = i0 + u * FC_THREADS < sp.end ? i0 + u * FC_THREADS : i0;      // tail: the first point again
                 const float* q = ((i >= sp.tgt0 && P.xyz_t != nullptr) ? P.xyz_t : P.xyz) + (size_t)i * 3;
                 x[u] = __ldg(q); y[u] = __ldg(q + 1); z[u] = __ldg(q + 2);
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < FC_ZFLIGHT; ++u) {
                 const int64_t i = i0 + u * FC_THREADS < sp.end ? i0 + u * FC_THREADS : i0;
                 if (P.pose != nullptr && i < sp.tgt0) apply_pose(s_pose, x[u], y[u], z[u]);
                 const unsigned e = enc_f32(rot_row(s_R + 6, x[u], y[u], z[u]));
