@@ -8,9 +8,10 @@
 //   forward   thread per output pixel, the 2 x 4 x 4 window in registers, all F filters from a shared-memory copy of the
 //             weights (broadcast LDS.128); stores are coalesced per filter plane.  Output-write bound: 4 F bytes per pixel.
 //   backward  dpre = dy * (y > 0 ? 1 : 0.2)  (the reference's LeakyReLU is in-place: autograd differentiates from the OUTPUT)
-//             dx    thread per input pixel: the 2 x 2 output positions that see it x F filters
-//             dW,db one CTA per chunk of output positions: a 64 x 33 outer-product tile accumulated in registers
-//                   (thread = 1 filter x 8 taps), then atomicAdd of the CTA's partial sums
+//             dx    CTA = 8 x 64 input pixels and the 6 x 34 output positions that see them, dpre staged in shared memory
+//                   32 filters at a time; thread = two neighbouring pixels
+//             dW,db persistent CTAs over chunks of 64 output positions: dpre and the im2col patch in shared memory, thread =
+//                   4 filters x 2 taps, four positions per vector load; atomicAdd of the CTA's sums at the end
 #pragma once
 #include "common.cuh"
 
@@ -73,103 +74,150 @@ disc_stem_forward_kernel(DiscStemParams P)
     }
 }
 
-// dx[n,c,iy,ix] = sum over the output positions (oy, ox) with 2 oy - 1 + ky == iy, 2 ox - 1 + kx == ix and all filters
+// dpre of one output element (0 outside the output): the in-place LeakyReLU differentiates from the saved output
+__device__ __forceinline__ float ds_dpre(const DiscStemParams& P, long long n, int f, int oy, int ox, int Ho, int Wo) {
+    if (oy < 0 || oy >= Ho || ox < 0 || ox >= Wo) return 0.0f;
+    const long long o = ((n * P.F + f) * Ho + oy) * Wo + ox;
+    return __ldg(P.dy + o) * (__ldg(P.y + o) > 0.0f ? 1.0f : DS_SLOPE);
+}
+
+// dx[n,c,iy,ix] = sum over the output positions (oy, ox) with 2 oy - 1 + ky == iy, 2 ox - 1 + kx == ix and all filters.
+// grid (ceil(W / 64), ceil(H / 8), N); CTA = 8 input rows x 64 input columns = the 6 x 34 output positions that see them, 32
+// filters at a time in shared memory (each dpre element is read from global memory once per tile instead of once per tap);
+// thread = two neighbouring pixels of a row (even, odd column): 3 x 2 output positions, 16 FMAs per filter for 6 scalar and
+// 4 vector shared loads.
+constexpr int DS_DG_ROWS = 8, DS_DG_COLS = 64, DS_DG_OR = DS_DG_ROWS / 2 + 2, DS_DG_OC = DS_DG_COLS / 2 + 2, DS_DG_F = 32;
 __global__ void __launch_bounds__(DS_THREADS)
 disc_stem_dgrad_kernel(DiscStemParams P)
 {
-    __shared__ float s_w[DS_MAX_F * DS_MAX_C * DS_TAPS];
-    const int taps = P.C * DS_TAPS;
-    for (int t = threadIdx.x; t < P.F * taps; t += DS_THREADS) s_w[t] = P.weight[t];
-    __syncthreads();
-    const int Ho = P.H / 2, Wo = P.W / 2;
-    const long long total = (long long)P.N * P.H * P.W;
-    const long long t = (long long)blockIdx.x * DS_THREADS + threadIdx.x;
-    if (t >= total) return;
-    const int ix = (int)(t % P.W), iy = (int)((t / P.W) % P.H);
-    const long long n = t / ((long long)P.W * P.H);
-    float acc[DS_MAX_C] = {0.0f, 0.0f};
-    // ky = iy + 1 - 2 oy in [0, 4)  ->  oy in {(iy + 1) / 2, (iy + 1) / 2 - 1} (when inside the output)
+    __shared__ float s_d[DS_DG_F][DS_DG_OR][DS_DG_OC + 1];
+    __shared__ __align__(16) float s_w[DS_DG_F * DS_MAX_C * DS_TAPS];
+    const int Ho = P.H / 2, Wo = P.W / 2, taps = P.C * DS_TAPS;
+    const int ix0 = blockIdx.x * DS_DG_COLS, iy0 = blockIdx.y * DS_DG_ROWS;
+    const long long n = blockIdx.z;
+    const int oyb = iy0 / 2 - 1, oxb = ix0 / 2 - 1;       // output position of the tile's corner
+    const int r = threadIdx.x / 32, cp = threadIdx.x % 32;
+    const int iy = iy0 + r, ix = ix0 + 2 * cp;
+    // the two output rows that see input row iy: oy_a = (iy + 1) / 2 with ky_a = iy + 1 - 2 oy_a, and oy_a - 1 with ky_a + 2
+    const int oy_a = (iy + 1) / 2, ky_a = iy + 1 - 2 * oy_a, la = oy_a - oyb;
+    float acc[2][DS_MAX_C] = {{0.0f, 0.0f}, {0.0f, 0.0f}};      // [pixel ix, ix + 1][channel]
+    for (int f0 = 0; f0 < P.F; f0 += DS_DG_F) {
+        const int nf = min(DS_DG_F, P.F - f0);
+        __syncthreads();
+        for (int t = threadIdx.x; t < DS_DG_F * DS_DG_OR * DS_DG_OC; t += DS_THREADS) {
+            const int ff = t / (DS_DG_OR * DS_DG_OC), rr = (t / DS_DG_OC) % DS_DG_OR, cc = t % DS_DG_OC;
+            s_d[ff][rr][cc] = ff < nf ? ds_dpre(P, n, f0 + ff, oyb + rr, oxb + cc, Ho, Wo) : 0.0f;
+        }
+        for (int t = threadIdx.x; t < DS_DG_F * DS_MAX_C * DS_TAPS; t += DS_THREADS) {
+            const int ff = t / (DS_MAX_C * DS_TAPS), cj = t % (DS_MAX_C * DS_TAPS);
+            s_w[t] = (ff < nf && cj < taps) ? __ldg(P.weight + (size_t)(f0 + ff) * taps + cj) : 0.0f;
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (int ff = 0; ff < DS_DG_F; ++ff) {
+            // columns cp, cp + 1, cp + 2 of the tile = ox = ix/2 - 1, ix/2, ix/2 + 1
+            const float a0 = s_d[ff][la][cp], a1 = s_d[ff][la][cp + 1], a2 = s_d[ff][la][cp + 2];
+            const float b0 = s_d[ff][la - 1][cp], b1 = s_d[ff][la - 1][cp + 1], b2 = s_d[ff][la - 1][cp + 2];
 #pragma unroll
-    for (int a = 0; a < 2; ++a) {
-        const int oy = (iy + 1) / 2 - a, ky = iy + 1 - 2 * oy;
-        if (oy < 0 || oy >= Ho) continue;
-#pragma unroll
-        for (int b = 0; b < 2; ++b) {
-            const int ox = (ix + 1) / 2 - b, kx = ix + 1 - 2 * ox;
-            if (ox < 0 || ox >= Wo) continue;
-            const float* yp = P.y + (n * P.F * Ho + oy) * Wo + ox;
-            const float* gp = P.dy + (n * P.F * Ho + oy) * Wo + ox;
-            for (int f = 0; f < P.F; ++f) {
-                const float g = __ldg(gp + (long long)f * Ho * Wo) * (__ldg(yp + (long long)f * Ho * Wo) > 0.0f ? 1.0f : DS_SLOPE);
-#pragma unroll
-                for (int c = 0; c < DS_MAX_C; ++c)
-                    if (c < P.C) acc[c] = __fmaf_rn(g, s_w[(f * P.C + c) * DS_TAPS + ky * DS_K + kx], acc[c]);
+            for (int c = 0; c < DS_MAX_C; ++c) {
+                const float4 wa = *reinterpret_cast<const float4*>(s_w + (ff * DS_MAX_C + c) * DS_TAPS + ky_a * DS_K);
+                const float4 wb = *reinterpret_cast<const float4*>(s_w + (ff * DS_MAX_C + c) * DS_TAPS + (ky_a + 2) * DS_K);
+                // pixel ix (even): kx = 1 with ox = ix/2, kx = 3 with ox = ix/2 - 1;  pixel ix + 1: kx = 0 with ix/2 + 1, kx = 2 with ix/2
+                acc[0][c] = __fmaf_rn(a1, wa.y, acc[0][c]); acc[0][c] = __fmaf_rn(a0, wa.w, acc[0][c]);
+                acc[0][c] = __fmaf_rn(b1, wb.y, acc[0][c]); acc[0][c] = __fmaf_rn(b0, wb.w, acc[0][c]);
+                acc[1][c] = __fmaf_rn(a2, wa.x, acc[1][c]); acc[1][c] = __fmaf_rn(a1, wa.z, acc[1][c]);
+                acc[1][c] = __fmaf_rn(b2, wb.x, acc[1][c]); acc[1][c] = __fmaf_rn(b1, wb.z, acc[1][c]);
             }
         }
     }
-    for (int c = 0; c < P.C; ++c) P.dx[((n * P.C + c) * P.H + iy) * P.W + ix] = acc[c];
+    if (iy < P.H) {
+#pragma unroll
+        for (int c = 0; c < DS_MAX_C; ++c) {
+            if (c < P.C) {
+                float* o = P.dx + ((n * P.C + c) * P.H + iy) * P.W + ix;
+                if (ix < P.W) o[0] = acc[0][c];
+                if (ix + 1 < P.W) o[1] = acc[1][c];
+            }
+        }
+    }
 }
 
-// dW[f,c,ky,kx] = sum_p dpre[f,p] * x[c, 2 oy - 1 + ky, 2 ox - 1 + kx],  db[f] = sum_p dpre[f,p]  over all output positions p.
-// CTA = DS_WG_POS consecutive output positions of one image row block; thread = filter f (tid / 4) x a quarter of the taps.
-constexpr int DS_WG_POS = 64;
+// dW[f,c,ky,kx] = sum_p dpre[f,p] * x[c, 2 oy - 1 + ky, 2 ox - 1 + kx],  db[f] = sum_p dpre[f,p]  over all output positions p:
+// a [F x P] x [P x 32] product.  Persistent CTAs walk chunks of DS_WG_POS positions; per chunk dpre [F][pos] and the im2col
+// patch [tap][pos] go to shared memory (y and dy are read from global memory once), thread = 4 filters x 2 taps over the
+// positions four at a time (6 vector loads for 32 FMAs); the CTA's sums leave through atomicAdd at the end.
+constexpr int DS_WG_POS = 64, DS_WG_LD = DS_WG_POS + 4;
 __global__ void __launch_bounds__(DS_THREADS)
 disc_stem_wgrad_kernel(DiscStemParams P, long long chunks_per_cta)
 {
-    __shared__ float s_g[DS_MAX_F][DS_WG_POS + 1];        // dpre of the chunk
-    __shared__ float s_x[DS_MAX_C * DS_TAPS][DS_WG_POS + 1];   // im2col patch of the chunk
+    __shared__ __align__(16) float s_g[DS_MAX_F][DS_WG_LD];                  // dpre of the chunk
+    __shared__ __align__(16) float s_x[DS_MAX_C * DS_TAPS][DS_WG_LD];       // im2col patch of the chunk
+    __shared__ int4 s_pos[DS_WG_POS];                                         // (image, offset in the plane, oy, ox) of the chunk's positions
     const int Ho = P.H / 2, Wo = P.W / 2, taps = P.C * DS_TAPS;
     const long long total = (long long)P.N * Ho * Wo;
-    const int f = threadIdx.x >> 2, part = threadIdx.x & 3;          // 64 filters x 4 tap groups of 8
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, accb = 0.0f;
+    const int tf = threadIdx.x / 16, tt = threadIdx.x % 16;                  // filters 4 tf .. 4 tf + 3, taps tt and tt + 16
+    float acc[4][2] = {{0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}}, accb[4] = {0.f, 0.f, 0.f, 0.f};
     for (long long ch = 0; ch < chunks_per_cta; ++ch) {
         const long long p0 = ((long long)blockIdx.x * chunks_per_cta + ch) * DS_WG_POS;
         if (p0 >= total) break;
         __syncthreads();
-        for (int t = threadIdx.x; t < P.F * DS_WG_POS; t += DS_THREADS) {
-            const int ff = t / DS_WG_POS, q = t % DS_WG_POS;
-            const long long p = p0 + q;
-            float g = 0.0f;
+        // where the chunk's positions are: image, offset inside the image's output plane, (oy, ox) -- once per position, not
+        // once per element (the 64-bit divisions were most of the fill)
+        if (threadIdx.x < DS_WG_POS) {
+            const long long p = p0 + threadIdx.x;
+            int4 w4 = make_int4(-1, 0, 0, 0);
             if (p < total) {
-                const long long n = p / ((long long)Wo * Ho), r = p % ((long long)Wo * Ho);
-                const long long o = (n * P.F + ff) * Ho * Wo + r;
+                const long long n = p / ((long long)Wo * Ho);
+                const int rr = (int)(p - n * (long long)Wo * Ho);
+                w4 = make_int4((int)n, rr, rr / Wo, rr % Wo);
+            }
+            s_pos[threadIdx.x] = w4;
+        }
+        __syncthreads();
+        for (int t = threadIdx.x; t < DS_MAX_F * DS_WG_POS; t += DS_THREADS) {
+            const int ff = t / DS_WG_POS, q = t % DS_WG_POS;
+            const int4 w4 = s_pos[q];
+            float g = 0.0f;
+            if (w4.x >= 0 && ff < P.F) {
+                const long long o = ((long long)w4.x * P.F + ff) * (Ho * Wo) + w4.y;
                 g = __ldg(P.dy + o) * (__ldg(P.y + o) > 0.0f ? 1.0f : DS_SLOPE);
             }
             s_g[ff][q] = g;
         }
-        for (int t = threadIdx.x; t < taps * DS_WG_POS; t += DS_THREADS) {
+        for (int t = threadIdx.x; t < DS_MAX_C * DS_TAPS * DS_WG_POS; t += DS_THREADS) {
             const int j = t / DS_WG_POS, q = t % DS_WG_POS;
-            const long long p = p0 + q;
+            const int4 w4 = s_pos[q];
             float v = 0.0f;
-            if (p < total) {
-                const int ox = (int)(p % Wo), oy = (int)((p / Wo) % Ho);
-                const long long n = p / ((long long)Wo * Ho);
+            if (w4.x >= 0 && j < taps) {
                 const int c = j / DS_TAPS, ky = (j % DS_TAPS) / DS_K, kx = j % DS_K;
-                const int iy = 2 * oy - 1 + ky, ix = 2 * ox - 1 + kx;
-                if (iy >= 0 && iy < P.H && ix >= 0 && ix < P.W) v = __ldg(P.x + ((n * P.C + c) * P.H + iy) * P.W + ix);
+                const int iy = 2 * w4.z - 1 + ky, ix = 2 * w4.w - 1 + kx;
+                if (iy >= 0 && iy < P.H && ix >= 0 && ix < P.W) v = __ldg(P.x + (((long long)w4.x * P.C + c) * P.H + iy) * P.W + ix);
             }
             s_x[j][q] = v;
         }
         __syncthreads();
-        if (f < P.F) {
-            for (int q = 0; q < DS_WG_POS; ++q) {
-                const float g = s_g[f][q];
-                if (part == 0) accb += g;
+#pragma unroll 2
+        for (int q = 0; q < DS_WG_POS; q += 4) {
+            const float4 x0 = *reinterpret_cast<const float4*>(&s_x[tt][q]), x1 = *reinterpret_cast<const float4*>(&s_x[tt + 16][q]);
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const int j = part * 8 + u;
-                    if (j < taps) acc[u] = __fmaf_rn(g, s_x[j][q], acc[u]);
-                }
+            for (int u = 0; u < 4; ++u) {
+                const float4 g = *reinterpret_cast<const float4*>(&s_g[4 * tf + u][q]);
+                acc[u][0] = __fmaf_rn(g.x, x0.x, acc[u][0]); acc[u][0] = __fmaf_rn(g.y, x0.y, acc[u][0]);
+                acc[u][0] = __fmaf_rn(g.z, x0.z, acc[u][0]); acc[u][0] = __fmaf_rn(g.w, x0.w, acc[u][0]);
+                acc[u][1] = __fmaf_rn(g.x, x1.x, acc[u][1]); acc[u][1] = __fmaf_rn(g.y, x1.y, acc[u][1]);
+                acc[u][1] = __fmaf_rn(g.z, x1.z, acc[u][1]); acc[u][1] = __fmaf_rn(g.w, x1.w, acc[u][1]);
+                if (tt == 0) accb[u] += (g.x + g.y) + (g.z + g.w);
             }
         }
     }
-    if (f < P.F) {
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const int j = part * 8 + u;
-            if (j < taps) atomicAdd(P.dw + f * taps + j, acc[u]);
+    for (int u = 0; u < 4; ++u) {
+        const int f = 4 * tf + u;
+        if (f < P.F) {
+            if (tt < taps) atomicAdd(P.dw + f * taps + tt, acc[u][0]);
+            if (tt + 16 < taps) atomicAdd(P.dw + f * taps + tt + 16, acc[u][1]);
+            if (tt == 0 && P.db) atomicAdd(P.db + f, accb[u]);
         }
-        if (part == 0 && P.db) atomicAdd(P.db + f, accb);
     }
 }
 

@@ -604,8 +604,8 @@ int scream_disc_stem_backward(const float* x, const float* weight, const float* 
     P.x = x; P.weight = weight; P.y = const_cast<float*>(y); P.dy = dy; P.dx = dx; P.dw = dw; P.db = db;
     P.N = N; P.C = C; P.F = F; P.H = H; P.W = W;
     if (dx) {
-        const long long total = (long long)N * H * W;
-        disc_stem_dgrad_kernel<<<(unsigned)((total + DS_THREADS - 1) / DS_THREADS), DS_THREADS, 0, st>>>(P);
+        if ((H + DS_DG_ROWS - 1) / DS_DG_ROWS > 65535 || N > 65535) return fail(SCREAM_E_UNSUPPORTED, "image count or height beyond the dx grid");
+        disc_stem_dgrad_kernel<<<dim3((unsigned)((W + DS_DG_COLS - 1) / DS_DG_COLS), (unsigned)((H + DS_DG_ROWS - 1) / DS_DG_ROWS), (unsigned)N), DS_THREADS, 0, st>>>(P);
     }
     if (dw) {
         CUDA_TRY(cudaMemsetAsync(dw, 0, (size_t)F * C * DS_TAPS * sizeof(float), st));
