@@ -25,6 +25,33 @@ struct BwdParams {
 
 constexpr int BW_THREADS = 256;
 
+// gradient of one pixel w.r.t. its winner point (in the frame of xyz: through R_v^T and, for a posed source point, R_pose^T)
+struct PixelGrad { float g0, g1, g2; };
+__device__ __forceinline__ PixelGrad pixel_grad(const BwdParams& P, const float* __restrict__ R, const float* __restrict__ pose, bool posed,
+                                                float x, float y, float z, float G, float zmin, float range, int p, int w, int half)
+{
+    if (posed) apply_pose(pose, x, y, z);
+    const float xr = rot_row(R, x, y, z), yr = rot_row(R + 3, x, y, z), zr = rot_row(R + 6, x, y, z);
+    const float pv = depth_weight_m(zr, zmin, range, (P.flags & 64u) != 0);   // 64u: SCREAM_F_HALF
+    const float dx = __fsub_rn(xr, pixel_centre(p % w, half)), dy = __fsub_rn(yr, pixel_centre(p / w, half));
+    const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+    const float wgt = expf(__fmul_rn(d2, P.negk));
+    const float gz = -(G * wgt) / range;
+    const float dd2 = G * pv * wgt * P.negk;
+    const float gx = 2.0f * dx * dd2, gy = 2.0f * dy * dd2;
+    PixelGrad g;                                          // R_v^T g
+    g.g0 = R[0] * gx + R[3] * gy + R[6] * gz;
+    g.g1 = R[1] * gx + R[4] * gy + R[7] * gz;
+    g.g2 = R[2] * gx + R[5] * gy + R[8] * gz;
+    if (posed) {
+        const float h0 = pose[0] * g.g0 + pose[4] * g.g1 + pose[8] * g.g2;
+        const float h1 = pose[1] * g.g0 + pose[5] * g.g1 + pose[9] * g.g2;
+        const float h2 = pose[2] * g.g0 + pose[6] * g.g1 + pose[10] * g.g2;
+        g.g0 = h0; g.g1 = h1; g.g2 = h2;
+    }
+    return g;
+}
+
 __global__ void __launch_bounds__(BW_THREADS)
 backward_scatter_kernel(BwdParams P)
 {
@@ -52,31 +79,89 @@ backward_scatter_kernel(BwdParams P)
     const ItemSpan sp = item_span(P.offs, b, P.pair_n, P.pair_m);
     const int64_t gi = (c ? sp.tgt0 : sp.src0) + wi;
     const float* xyz = (c && P.xyz_t != nullptr) ? P.xyz_t : P.xyz;
-    float x = xyz[gi * 3], y = xyz[gi * 3 + 1], z = xyz[gi * 3 + 2];
-    if (posed) apply_pose(s_pose, x, y, z);
-    const float xr = rot_row(s_R, x, y, z), yr = rot_row(s_R + 3, x, y, z), zr = rot_row(s_R + 6, x, y, z);
     const float zmin = P.zrange[((size_t)b * P.V + v) * 2], zmax = P.zrange[((size_t)b * P.V + v) * 2 + 1];
-    const float range = z_range(zmin, zmax);
-    const float pv = depth_weight_m(zr, zmin, range, (P.flags & 64u) != 0);   // 64u: SCREAM_F_HALF
-    const float dx = __fsub_rn(xr, pixel_centre(p % w, half)), dy = __fsub_rn(yr, pixel_centre(p / w, half));
-    const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
-    const float wgt = expf(__fmul_rn(d2, P.negk));
-
-    const float gz = -(G * wgt) / range;
-    const float dd2 = G * pv * wgt * P.negk;
-    const float gx = 2.0f * dx * dd2, gy = 2.0f * dy * dd2;
-    // R_v^T g
-    float g0 = s_R[0] * gx + s_R[3] * gy + s_R[6] * gz;
-    float g1 = s_R[1] * gx + s_R[4] * gy + s_R[7] * gz;
-    float g2 = s_R[2] * gx + s_R[5] * gy + s_R[8] * gz;
-    if (posed) {
-        float h0 = s_pose[0] * g0 + s_pose[4] * g1 + s_pose[8] * g2;
-        float h1 = s_pose[1] * g0 + s_pose[5] * g1 + s_pose[9] * g2;
-        float h2 = s_pose[2] * g0 + s_pose[6] * g1 + s_pose[10] * g2;
-        g0 = h0; g1 = h1; g2 = h2;
-    }
+    const PixelGrad g = pixel_grad(P, s_R, s_pose, posed, xyz[gi * 3], xyz[gi * 3 + 1], xyz[gi * 3 + 2], G, zmin, z_range(zmin, zmax), p, w, half);
     float* dst = ((c && P.grad_t != nullptr) ? P.grad_t : P.grad_xyz) + gi * 3;
-    atomicAdd(dst, g0); atomicAdd(dst + 1, g1); atomicAdd(dst + 2, g2);
+    atomicAdd(dst, g.g0); atomicAdd(dst + 1, g.g1); atomicAdd(dst + 2, g.g2);
+}
+
+// The same sums with the atomics in SHARED memory: one CTA per (item, cloud) walks all V views' pixels of that cloud, adds
+// every pixel's gradient into a shared-memory copy of the cloud's gradient (3 floats per point), and writes it out once,
+// coalesced.  75 M global RED.ADD of a 512-pair step (the scatter kernel sits at 73 % of the L2's throughput) become plain
+// stores.  For grids that fill the GPU (B * 2 >= the SM count); a cloud beyond BG_CAP points takes the scatter's atomics here.
+constexpr int BG_THREADS = 1024;
+constexpr int BG_CAP = 18432;                             // points whose gradient fits 216 KB of shared memory
+
+#ifndef BG_FLIGHT_N
+#define BG_FLIGHT_N 1
+#endif
+constexpr int BG_FLIGHT = BG_FLIGHT_N;                              // pixels in flight per thread
+constexpr int BG_MAXV = 64;                               // views whose constants are staged at once
+
+__global__ void __launch_bounds__(BG_THREADS, 1)
+backward_gather_kernel(BwdParams P, int cap)
+{
+    extern __shared__ __align__(16) float s_acc[];       // [3 * npts]
+    __shared__ float s_Rv[BG_MAXV][12];                  // R_v, zmin, range, -
+    __shared__ float s_pose[12];
+    const int w = P.w, npix = w * w, half = w / 2;
+    const int c = blockIdx.x & 1, b = blockIdx.x >> 1;
+    const ItemSpan sp = item_span(P.offs, b, P.pair_n, P.pair_m);
+    const int64_t lo = c ? sp.tgt0 : sp.src0, hi = c ? sp.end : sp.tgt0;
+    const int64_t npts = hi - lo;
+    const bool local = npts <= (int64_t)cap;              // uniform over the CTA
+    const float* xyz = ((c && P.xyz_t != nullptr) ? P.xyz_t : P.xyz) + lo * 3;
+    float* dst = ((c && P.grad_t != nullptr) ? P.grad_t : P.grad_xyz) + lo * 3;
+    const bool posed = P.pose != nullptr && c == 0;
+    if (posed && threadIdx.x < 12) s_pose[threadIdx.x] = P.pose[(size_t)b * 12 + threadIdx.x];
+    // (the caller does not clear grad_xyz for this kernel: a cloud too large for shared memory clears its own rows first)
+    if (local) for (int t = threadIdx.x; t < 3 * (int)npts; t += BG_THREADS) s_acc[t] = 0.0f;
+    else for (int64_t t = threadIdx.x; t < 3 * npts; t += BG_THREADS) dst[t] = 0.0f;
+    for (int v0 = 0; v0 < P.V; v0 += BG_MAXV) {
+        const int nv = min(BG_MAXV, P.V - v0);
+        __syncthreads();
+        for (int t = threadIdx.x; t < nv * 12; t += BG_THREADS) {
+            const int vv = t / 12, k = t % 12, v = v0 + vv;
+            const float zmin = P.zrange[((size_t)b * P.V + v) * 2], zmax = P.zrange[((size_t)b * P.V + v) * 2 + 1];
+            s_Rv[vv][k] = k < 9 ? P.views[(size_t)v * 9 + k] : (k == 9 ? zmin : (k == 10 ? z_range(zmin, zmax) : 0.0f));
+        }
+        __syncthreads();
+        const size_t o0 = (((size_t)b * P.V + v0) * 2 + c) * npix;       // view v0 + vv: + vv * 2 * npix
+        // BG_FLIGHT pixels per thread and trip: their winner / gradient loads, then the winners' coordinates (a dependent
+        // gather), are in flight together -- one CTA per SM has 24 serial trips of two L2 round trips otherwise
+        for (int t0 = threadIdx.x; t0 < nv * npix; t0 += BG_FLIGHT * BG_THREADS) {
+            int wi[BG_FLIGHT]; float G[BG_FLIGHT], x[BG_FLIGHT], y[BG_FLIGHT], z[BG_FLIGHT];
+#pragma unroll
+            for (int u = 0; u < BG_FLIGHT; ++u) {
+                const int t = t0 + u * BG_THREADS;
+                wi[u] = -1; G[u] = 0.0f;
+                if (t < nv * npix) {
+                    const int vv = t / npix, p = t - vv * npix;
+                    const size_t o = o0 + (size_t)vv * 2 * npix + p;
+                    wi[u] = __ldg(P.winner + o); G[u] = __ldg(P.grad_imgs + o);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < BG_FLIGHT; ++u) {
+                x[u] = y[u] = z[u] = 0.0f;
+                if (wi[u] >= 0 && G[u] != 0.0f) { const float* q = xyz + (size_t)wi[u] * 3; x[u] = __ldg(q); y[u] = __ldg(q + 1); z[u] = __ldg(q + 2); }
+            }
+#pragma unroll
+            for (int u = 0; u < BG_FLIGHT; ++u) {
+                if (wi[u] < 0 || G[u] == 0.0f) continue;
+                const int t = t0 + u * BG_THREADS, vv = t / npix, p = t - vv * npix;
+                const float Gs = (P.flags & 1u) ? G[u] : G[u] * 2.0f;
+                const PixelGrad g = pixel_grad(P, s_Rv[vv], s_pose, posed, x[u], y[u], z[u], Gs, s_Rv[vv][9], s_Rv[vv][10], p, w, half);
+                // (shared memory has no native fp32 add: each of these is a compare-and-swap loop; one 128-bit CAS per point was slower)
+                if (local) { atomicAdd(s_acc + 3 * wi[u], g.g0); atomicAdd(s_acc + 3 * wi[u] + 1, g.g1); atomicAdd(s_acc + 3 * wi[u] + 2, g.g2); }
+                else { float* a = dst + (size_t)wi[u] * 3; atomicAdd(a, g.g0); atomicAdd(a + 1, g.g1); atomicAdd(a + 2, g.g2); }
+            }
+        }
+    }
+    if (local) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < 3 * (int)npts; t += BG_THREADS) dst[t] = s_acc[t];
+    }
 }
 
 }  // namespace scream

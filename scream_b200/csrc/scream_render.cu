@@ -361,7 +361,7 @@ int scream_render_forward_sharded(const float* xyz, const int64_t* offs, int64_t
                         zrange, ws, ws_bytes, stream, sh);
 }
 
-int scream_render_backward(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t /*max_item_pts*/,
+int scream_render_backward(const float* xyz, const int64_t* offs, int64_t total_pts, int64_t max_item_pts,
                            const float* pose, const float* views,
                            int B, int V, int w, double rho, unsigned flags,
                            const float* grad_imgs, const int32_t* winner, const float* zrange,
@@ -370,13 +370,29 @@ int scream_render_backward(const float* xyz, const int64_t* offs, int64_t total_
     if (int rc = check_common(xyz, offs, views, B, V, w, rho, total_pts)) return rc;
     if (!grad_imgs || !winner || !zrange || !grad_xyz) return fail(SCREAM_E_ARG, "grad_imgs/winner/zrange/grad_xyz must not be NULL");
     cudaStream_t st = (cudaStream_t)stream;
-    CUDA_TRY(cudaMemsetAsync(grad_xyz, 0, (size_t)total_pts * 3 * sizeof(float), st));
     BwdParams P;
     P.xyz = xyz; P.offs = offs; P.pose = pose; P.views = views;
     P.B = B; P.V = V; P.w = w;
     P.negk = -(float)(rho * rho) * 0.5f;
     P.flags = flags; P.grad_imgs = grad_imgs; P.winner = winner; P.zrange = zrange; P.grad_xyz = grad_xyz;
     P.xyz_t = nullptr; P.grad_t = nullptr; P.pair_n = P.pair_m = 0;
+    // grids that fill the GPU: one CTA per (item, cloud), the atomics in shared memory (backward.cuh)
+    const char* no_gather = getenv("SCREAM_BWD_SCATTER");
+    if ((long long)B * 2 >= 148 && !(no_gather && no_gather[0] == '1')) {
+        const int cap = (int)((max_item_pts > 0 && max_item_pts < BG_CAP) ? max_item_pts : BG_CAP);
+        const size_t smem = (size_t)cap * 3 * sizeof(float);
+        static thread_local int attr_dev = -1;
+        int dev = 0;
+        CUDA_TRY(cudaGetDevice(&dev));
+        if (attr_dev != dev) {
+            CUDA_TRY(cudaFuncSetAttribute(backward_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(BG_CAP * 3 * sizeof(float))));
+            attr_dev = dev;
+        }
+        backward_gather_kernel<<<(unsigned)(B * 2), BG_THREADS, smem, st>>>(P, cap);
+        CUDA_TRY(cudaGetLastError());
+        return 0;
+    }
+    CUDA_TRY(cudaMemsetAsync(grad_xyz, 0, (size_t)total_pts * 3 * sizeof(float), st));
     const long long grid = (long long)B * V * 2 * (w * w / BW_THREADS);
     backward_scatter_kernel<<<(unsigned)grid, BW_THREADS, 0, st>>>(P);
     CUDA_TRY(cudaGetLastError());

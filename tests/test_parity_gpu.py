@@ -652,6 +652,32 @@ def test_pair_entry_point_equals_batched_render():
         assert torch.equal(raw, want_raw[0, 0])
 
 
+def test_backward_with_shared_memory_sums_equals_the_scatter_kernel(monkeypatch):
+    """Batches that fill the GPU take backward_gather_kernel (one CTA per cloud, the gradient summed in shared memory and
+    written once); SCREAM_BWD_SCATTER=1 forces the global-atomics kernel the parity tests pin against the reference's
+    autograd.  Same sums up to the order of the additions; ragged clouds, a pose, one cloud too large for shared memory."""
+    from scream_b200.render import _bwd_impl
+    rng = np.random.default_rng(12)
+    sizes = [(int(rng.integers(40, 900)), int(rng.integers(40, 900))) for _ in range(79)] + [(19000, 300)]
+    xyz = torch.from_numpy(np.concatenate([np.concatenate([synth.unit_ball(a, 3 * i), synth.room_shell(b, 3 * i + 1)])
+                                           for i, (a, b) in enumerate(sizes)]).astype(np.float32)).to(DEV)
+    offs = make_offsets(sizes).to(DEV)
+    views = view_matrices(RegistrationRender(24, 64, device=DEV).eulers)[:3].to(DEV).contiguous()
+    B, V, w, rho = len(sizes), 3, 64, 24.0
+    g = torch.Generator().manual_seed(1)
+    q, _ = torch.linalg.qr(torch.randn(B, 3, 3, generator=g))
+    pose = torch.cat([q, 0.03 * torch.randn(B, 3, 1, generator=g)], dim=2).float().to(DEV).contiguous()
+    imgs, win, zr = render_batch(xyz, offs, views, rho, w, pose=pose, need_winner=True)
+    grad = torch.randn(imgs.shape, generator=torch.Generator().manual_seed(2)).to(DEV)
+    got = _bwd_impl(xyz, offs, pose, views, w, rho, 0, grad, win, zr, max(a + b for a, b in sizes))
+    got0 = _bwd_impl(xyz, offs, pose, views, w, rho, 0, grad, win, zr, 0)          # bound unknown: full-size shared buffer
+    monkeypatch.setenv("SCREAM_BWD_SCATTER", "1")
+    want = _bwd_impl(xyz, offs, pose, views, w, rho, 0, grad, win, zr, 0)
+    scale = float(want.abs().max())
+    assert scale > 0 and float((got - want).abs().max()) <= 1e-5 * scale
+    assert float((got0 - want).abs().max()) <= 1e-5 * scale
+
+
 def test_counter_based_cloud_is_slice_invariant():
     """bench.py's cfg5 cloud: point i has the same bits in whatever slice it is generated (the N-GPU runs shard the cloud the
     1-GPU run renders)."""
