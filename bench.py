@@ -744,7 +744,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": {"fwd_fake": b_fake, "fwd_real": b_real, "bwd": b_bwd},
                          "ms_per_launch": {"fwd_fake": t_fake, "bwd": t_bwd, "fwd_real": t_real}},
-            "roofline_bwd": {"bound": "hbm", "kernel": "backward_scatter_kernel (L2 RED.ADD.F32 through the winner map)",
+            "roofline_bwd": {"bound": "hbm", "kernel": "backward_gather_kernel (one CTA per cloud: the gradient summed in shared memory through the winner map, stored once; grids below 148 CTAs: backward_scatter_kernel, L2 RED.ADD.F32)",
                              "achieved": b_bwd / (t_bwd / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
                              "frac": b_bwd / (t_bwd / 1e3) / 1e9 / peak},
             "clocks": clocks}
