@@ -140,7 +140,7 @@ int scream_render_backward(const float *xyz, const int64_t *offs, int64_t total_
  * handed the two clouds as two tensors and pointnet.py:39-40 asserts batch 1.  src [n,3], tgt [m,3] are separate device
  * buffers (no torch.cat of render.py:63, no offsets); pose [3,4] or NULL; imgs [V,2,w,w], winner [V,2,w,w] or NULL, zrange
  * [V,2] or NULL (output).  ONE kernel launch: every CTA reduces the depth range of render.py:30-31 itself, and each image is
- * shared by up to 8 CTAs (a 6-view pair fills 96 SMs instead of 12).  Same bits as scream_render_forward on the
+ * shared by as many CTAs as fill one wave of the SMs (a 6-view pair: 12 per image, 144 SMs instead of 12).  Same bits as scream_render_forward on the
  * concatenated pair.  flags: SCREAM_F_RAW, SCREAM_F_HALF.  n + m < 147456 (giant pairs: scream_render_forward). */
 int scream_render_forward_pair(const float *src, int64_t n, const float *tgt, int64_t m,
                                const float *pose, const float *views, int V, int w, double rho, unsigned flags,
