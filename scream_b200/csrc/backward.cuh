@@ -148,13 +148,32 @@ backward_gather_kernel(BwdParams P, int cap)
             }
 #pragma unroll
             for (int u = 0; u < BG_FLIGHT; ++u) {
-                if (wi[u] < 0 || G[u] == 0.0f) continue;
-                const int t = t0 + u * BG_THREADS, vv = t / npix, p = t - vv * npix;
-                const float Gs = (P.flags & 1u) ? G[u] : G[u] * 2.0f;
-                const PixelGrad g = pixel_grad(P, s_Rv[vv], s_pose, posed, x[u], y[u], z[u], Gs, s_Rv[vv][9], s_Rv[vv][10], p, w, half);
-                // (shared memory has no native fp32 add: each of these is a compare-and-swap loop; one 128-bit CAS per point was slower)
-                if (local) { atomicAdd(s_acc + 3 * wi[u], g.g0); atomicAdd(s_acc + 3 * wi[u] + 1, g.g1); atomicAdd(s_acc + 3 * wi[u] + 2, g.g2); }
-                else { float* a = dst + (size_t)wi[u] * 3; atomicAdd(a, g.g0); atomicAdd(a + 1, g.g1); atomicAdd(a + 2, g.g2); }
+                if (t0 + u * BG_THREADS >= nv * npix) break;          // uniform over the warp (npix is a multiple of the CTA size)
+                const bool valid = wi[u] >= 0 && G[u] != 0.0f;
+                PixelGrad g = {0.0f, 0.0f, 0.0f};
+                if (valid) {
+                    const int t = t0 + u * BG_THREADS, vv = t / npix, p = t - vv * npix;
+                    const float Gs = (P.flags & 1u) ? G[u] : G[u] * 2.0f;
+                    g = pixel_grad(P, s_Rv[vv], s_pose, posed, x[u], y[u], z[u], Gs, s_Rv[vv][9], s_Rv[vv][10], p, w, half);
+                }
+                // Neighbouring pixels often share their winner, and lanes of a warp that add to the same word make its
+                // compare-and-swap loop retry once per lane: runs of equal winners are summed over the warp first (segmented
+                // scan: 15 shuffles) and the last lane of a run adds the total.
+                const int key = valid ? wi[u] : -1 - (int)(threadIdx.x & 31);           // invalid lanes: runs of their own
+                const int prev = __shfl_up_sync(0xFFFFFFFFu, key, 1), next = __shfl_down_sync(0xFFFFFFFFu, key, 1);
+                const int lane = threadIdx.x & 31;
+                const unsigned heads = __ballot_sync(0xFFFFFFFFu, lane == 0 || prev != key);
+                const int start = 31 - __clz(heads & (0xFFFFFFFFu >> (31 - lane)));
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const float o0 = __shfl_up_sync(0xFFFFFFFFu, g.g0, d), o1 = __shfl_up_sync(0xFFFFFFFFu, g.g1, d), o2 = __shfl_up_sync(0xFFFFFFFFu, g.g2, d);
+                    if (lane - d >= start) { g.g0 += o0; g.g1 += o1; g.g2 += o2; }
+                }
+                if (valid && (lane == 31 || next != key)) {
+                    // (shared memory has no native fp32 add: each of these is a compare-and-swap loop; one 128-bit CAS per point was slower)
+                    if (local) { atomicAdd(s_acc + 3 * wi[u], g.g0); atomicAdd(s_acc + 3 * wi[u] + 1, g.g1); atomicAdd(s_acc + 3 * wi[u] + 2, g.g2); }
+                    else { float* a = dst + (size_t)wi[u] * 3; atomicAdd(a, g.g0); atomicAdd(a + 1, g.g1); atomicAdd(a + 2, g.g2); }
+                }
             }
         }
     }
