@@ -28,12 +28,12 @@ constexpr int BW_THREADS = 256;
 // gradient of one pixel w.r.t. its winner point (in the frame of xyz: through R_v^T and, for a posed source point, R_pose^T)
 struct PixelGrad { float g0, g1, g2; };
 __device__ __forceinline__ PixelGrad pixel_grad(const BwdParams& P, const float* __restrict__ R, const float* __restrict__ pose, bool posed,
-                                                float x, float y, float z, float G, float zmin, float range, int p, int w, int half)
+                                                float x, float y, float z, float G, float zmin, float range, int row, int col, int half)
 {
     if (posed) apply_pose(pose, x, y, z);
     const float xr = rot_row(R, x, y, z), yr = rot_row(R + 3, x, y, z), zr = rot_row(R + 6, x, y, z);
     const float pv = depth_weight_m(zr, zmin, range, (P.flags & 64u) != 0);   // 64u: SCREAM_F_HALF
-    const float dx = __fsub_rn(xr, pixel_centre(p % w, half)), dy = __fsub_rn(yr, pixel_centre(p / w, half));
+    const float dx = __fsub_rn(xr, pixel_centre(col, half)), dy = __fsub_rn(yr, pixel_centre(row, half));
     const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
     const float wgt = expf(__fmul_rn(d2, P.negk));
     const float gz = -(G * wgt) / range;
@@ -80,7 +80,7 @@ backward_scatter_kernel(BwdParams P)
     const int64_t gi = (c ? sp.tgt0 : sp.src0) + wi;
     const float* xyz = (c && P.xyz_t != nullptr) ? P.xyz_t : P.xyz;
     const float zmin = P.zrange[((size_t)b * P.V + v) * 2], zmax = P.zrange[((size_t)b * P.V + v) * 2 + 1];
-    const PixelGrad g = pixel_grad(P, s_R, s_pose, posed, xyz[gi * 3], xyz[gi * 3 + 1], xyz[gi * 3 + 2], G, zmin, z_range(zmin, zmax), p, w, half);
+    const PixelGrad g = pixel_grad(P, s_R, s_pose, posed, xyz[gi * 3], xyz[gi * 3 + 1], xyz[gi * 3 + 2], G, zmin, z_range(zmin, zmax), p / w, p % w, half);
     float* dst = ((c && P.grad_t != nullptr) ? P.grad_t : P.grad_xyz) + gi * 3;
     atomicAdd(dst, g.g0); atomicAdd(dst + 1, g.g1); atomicAdd(dst + 2, g.g2);
 }
@@ -92,10 +92,6 @@ backward_scatter_kernel(BwdParams P)
 constexpr int BG_THREADS = 1024;
 constexpr int BG_CAP = 18432;                             // points whose gradient fits 216 KB of shared memory
 
-#ifndef BG_FLIGHT_N
-#define BG_FLIGHT_N 1
-#endif
-constexpr int BG_FLIGHT = BG_FLIGHT_N;                              // pixels in flight per thread
 constexpr int BG_MAXV = 64;                               // views whose constants are staged at once
 
 __global__ void __launch_bounds__(BG_THREADS, 1)
@@ -127,54 +123,57 @@ backward_gather_kernel(BwdParams P, int cap)
         }
         __syncthreads();
         const size_t o0 = (((size_t)b * P.V + v0) * 2 + c) * npix;       // view v0 + vv: + vv * 2 * npix
-        // BG_FLIGHT pixels per thread and trip: their winner / gradient loads, then the winners' coordinates (a dependent
-        // gather), are in flight together -- one CTA per SM has 24 serial trips of two L2 round trips otherwise
-        for (int t0 = threadIdx.x; t0 < nv * npix; t0 += BG_FLIGHT * BG_THREADS) {
-            int wi[BG_FLIGHT]; float G[BG_FLIGHT], x[BG_FLIGHT], y[BG_FLIGHT], z[BG_FLIGHT];
-#pragma unroll
-            for (int u = 0; u < BG_FLIGHT; ++u) {
-                const int t = t0 + u * BG_THREADS;
-                wi[u] = -1; G[u] = 0.0f;
-                if (t < nv * npix) {
-                    const int vv = t / npix, p = t - vv * npix;
-                    const size_t o = o0 + (size_t)vv * 2 * npix + p;
-                    wi[u] = __ldg(P.winner + o); G[u] = __ldg(P.grad_imgs + o);
-                }
+        // Three pixels per thread are in flight: the one whose gradient is computed, the next one's winner coordinates (a
+        // dependent gather: a third of the stall samples when exposed), the one after's winner / upstream gradient (a fourth,
+        // with two gathers ahead, measured slower).  Pixel
+        // (view, row, column) follows t = thread + 1024 i incrementally (no division in the loop).
+        const int total = nv * npix, lane = threadIdx.x & 31;
+        const int dcol = BG_THREADS % w, drow = BG_THREADS / w;
+        int vv = 0, row = (int)threadIdx.x / w, col = (int)threadIdx.x % w;      // of the pixel being computed (npix >= 4096 > thread)
+        int wi1 = -1, wi2 = -1; float G1 = 0.0f, G2 = 0.0f, x1 = 0.0f, y1 = 0.0f, z1 = 0.0f;
+        auto load_wg = [&](int t, int& wi, float& G) {
+            wi = -1; G = 0.0f;
+            if (t < total) { const size_t o = o0 + (size_t)(t / npix) * npix + t; wi = __ldg(P.winner + o); G = __ldg(P.grad_imgs + o); }
+        };
+        auto gather = [&](int wi, float G, float& x, float& y, float& z) {
+            x = y = z = 0.0f;
+            if (wi >= 0 && G != 0.0f) { const float* q = xyz + (size_t)wi * 3; x = __ldg(q); y = __ldg(q + 1); z = __ldg(q + 2); }
+        };
+        load_wg(threadIdx.x, wi1, G1);
+        load_wg(threadIdx.x + BG_THREADS, wi2, G2);
+        gather(wi1, G1, x1, y1, z1);
+        for (int t = threadIdx.x; t < total; t += BG_THREADS) {          // uniform over the warp (npix is a multiple of the CTA size)
+            const int wi0 = wi1; const float G0 = G1, x0 = x1, y0 = y1, z0 = z1;
+            wi1 = wi2; G1 = G2;
+            gather(wi1, G1, x1, y1, z1);
+            load_wg(t + 2 * BG_THREADS, wi2, G2);
+            const bool valid = wi0 >= 0 && G0 != 0.0f;
+            PixelGrad g = {0.0f, 0.0f, 0.0f};
+            if (valid) {
+                const float Gs = (P.flags & 1u) ? G0 : G0 * 2.0f;
+                g = pixel_grad(P, s_Rv[vv], s_pose, posed, x0, y0, z0, Gs, s_Rv[vv][9], s_Rv[vv][10], row, col, half);
             }
+            // Neighbouring pixels often share their winner, and lanes of a warp that add to the same word make its
+            // compare-and-swap loop retry once per lane: runs of equal winners are summed over the warp first (segmented
+            // scan: 15 shuffles) and the last lane of a run adds the total.
+            const int key = valid ? wi0 : -1 - lane;                  // invalid lanes: runs of their own
+            const int prev = __shfl_up_sync(0xFFFFFFFFu, key, 1), next = __shfl_down_sync(0xFFFFFFFFu, key, 1);
+            const unsigned heads = __ballot_sync(0xFFFFFFFFu, lane == 0 || prev != key);
+            const int start = 31 - __clz(heads & (0xFFFFFFFFu >> (31 - lane)));
 #pragma unroll
-            for (int u = 0; u < BG_FLIGHT; ++u) {
-                x[u] = y[u] = z[u] = 0.0f;
-                if (wi[u] >= 0 && G[u] != 0.0f) { const float* q = xyz + (size_t)wi[u] * 3; x[u] = __ldg(q); y[u] = __ldg(q + 1); z[u] = __ldg(q + 2); }
+            for (int d = 1; d < 32; d <<= 1) {
+                const float a0 = __shfl_up_sync(0xFFFFFFFFu, g.g0, d), a1 = __shfl_up_sync(0xFFFFFFFFu, g.g1, d), a2 = __shfl_up_sync(0xFFFFFFFFu, g.g2, d);
+                if (lane - d >= start) { g.g0 += a0; g.g1 += a1; g.g2 += a2; }
             }
-#pragma unroll
-            for (int u = 0; u < BG_FLIGHT; ++u) {
-                if (t0 + u * BG_THREADS >= nv * npix) break;          // uniform over the warp (npix is a multiple of the CTA size)
-                const bool valid = wi[u] >= 0 && G[u] != 0.0f;
-                PixelGrad g = {0.0f, 0.0f, 0.0f};
-                if (valid) {
-                    const int t = t0 + u * BG_THREADS, vv = t / npix, p = t - vv * npix;
-                    const float Gs = (P.flags & 1u) ? G[u] : G[u] * 2.0f;
-                    g = pixel_grad(P, s_Rv[vv], s_pose, posed, x[u], y[u], z[u], Gs, s_Rv[vv][9], s_Rv[vv][10], p, w, half);
-                }
-                // Neighbouring pixels often share their winner, and lanes of a warp that add to the same word make its
-                // compare-and-swap loop retry once per lane: runs of equal winners are summed over the warp first (segmented
-                // scan: 15 shuffles) and the last lane of a run adds the total.
-                const int key = valid ? wi[u] : -1 - (int)(threadIdx.x & 31);           // invalid lanes: runs of their own
-                const int prev = __shfl_up_sync(0xFFFFFFFFu, key, 1), next = __shfl_down_sync(0xFFFFFFFFu, key, 1);
-                const int lane = threadIdx.x & 31;
-                const unsigned heads = __ballot_sync(0xFFFFFFFFu, lane == 0 || prev != key);
-                const int start = 31 - __clz(heads & (0xFFFFFFFFu >> (31 - lane)));
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const float o0 = __shfl_up_sync(0xFFFFFFFFu, g.g0, d), o1 = __shfl_up_sync(0xFFFFFFFFu, g.g1, d), o2 = __shfl_up_sync(0xFFFFFFFFu, g.g2, d);
-                    if (lane - d >= start) { g.g0 += o0; g.g1 += o1; g.g2 += o2; }
-                }
-                if (valid && (lane == 31 || next != key)) {
-                    // (shared memory has no native fp32 add: each of these is a compare-and-swap loop; one 128-bit CAS per point was slower)
-                    if (local) { atomicAdd(s_acc + 3 * wi[u], g.g0); atomicAdd(s_acc + 3 * wi[u] + 1, g.g1); atomicAdd(s_acc + 3 * wi[u] + 2, g.g2); }
-                    else { float* a = dst + (size_t)wi[u] * 3; atomicAdd(a, g.g0); atomicAdd(a + 1, g.g1); atomicAdd(a + 2, g.g2); }
-                }
+            if (valid && (lane == 31 || next != key)) {
+                // (shared memory has no native fp32 add: each of these is a compare-and-swap loop; one 128-bit CAS per point was slower)
+                if (local) { atomicAdd(s_acc + 3 * wi0, g.g0); atomicAdd(s_acc + 3 * wi0 + 1, g.g1); atomicAdd(s_acc + 3 * wi0 + 2, g.g2); }
+                else { float* a = dst + (size_t)wi0 * 3; atomicAdd(a, g.g0); atomicAdd(a + 1, g.g1); atomicAdd(a + 2, g.g2); }
             }
+            // the next pixel of this thread: 1024 further on, possibly in the next view
+            col += dcol; row += drow;
+            if (col >= w) { col -= w; ++row; }
+            if (row >= w) { row -= w; ++vv; }
         }
     }
     if (local) {
