@@ -147,7 +147,7 @@ disc_stem_dgrad_kernel(DiscStemParams P)
 // patch [tap][pos] go to shared memory (y and dy are read from global memory once), thread = 4 filters x 2 taps over the
 // positions four at a time (6 vector loads for 32 FMAs); the CTA's sums leave through atomicAdd at the end.
 constexpr int DS_WG_POS = 64, DS_WG_LD = DS_WG_POS + 4;
-__global__ void __launch_bounds__(DS_THREADS)
+__global__ void __launch_bounds__(DS_THREADS, 3)
 disc_stem_wgrad_kernel(DiscStemParams P, long long chunks_per_cta)
 {
     __shared__ __align__(16) float s_g[DS_MAX_F][DS_WG_LD];                  // dpre of the chunk
@@ -174,26 +174,38 @@ disc_stem_wgrad_kernel(DiscStemParams P, long long chunks_per_cta)
             s_pos[threadIdx.x] = w4;
         }
         __syncthreads();
-        for (int t = threadIdx.x; t < DS_MAX_F * DS_WG_POS; t += DS_THREADS) {
-            const int ff = t / DS_WG_POS, q = t % DS_WG_POS;
+        {
+            // a thread's elements all belong to ONE position (256 threads, 64 positions: q = thread % 64), so its place is read
+            // once, and the loads of all its elements are issued before the first store (a shared store between them would
+            // order them one behind the other: 24 exposed round trips per chunk)
+            static_assert(DS_THREADS % DS_WG_POS == 0, "one position per thread");
+            constexpr int FSTEP = DS_THREADS / DS_WG_POS, NG = DS_MAX_F / FSTEP, NX = DS_MAX_C * DS_TAPS / FSTEP;
+            const int q = threadIdx.x % DS_WG_POS, r0 = threadIdx.x / DS_WG_POS;
             const int4 w4 = s_pos[q];
-            float g = 0.0f;
-            if (w4.x >= 0 && ff < P.F) {
-                const long long o = ((long long)w4.x * P.F + ff) * (Ho * Wo) + w4.y;
-                g = __ldg(P.dy + o) * (__ldg(P.y + o) > 0.0f ? 1.0f : DS_SLOPE);
+            float gv[NG], yv[NG], xv[NX];
+#pragma unroll
+            for (int u = 0; u < NG; ++u) {
+                const int ff = r0 + FSTEP * u;
+                gv[u] = 0.0f; yv[u] = 0.0f;
+                if (w4.x >= 0 && ff < P.F) {
+                    const long long o = ((long long)w4.x * P.F + ff) * (Ho * Wo) + w4.y;
+                    gv[u] = __ldg(P.dy + o); yv[u] = __ldg(P.y + o);
+                }
             }
-            s_g[ff][q] = g;
-        }
-        for (int t = threadIdx.x; t < DS_MAX_C * DS_TAPS * DS_WG_POS; t += DS_THREADS) {
-            const int j = t / DS_WG_POS, q = t % DS_WG_POS;
-            const int4 w4 = s_pos[q];
-            float v = 0.0f;
-            if (w4.x >= 0 && j < taps) {
-                const int c = j / DS_TAPS, ky = (j % DS_TAPS) / DS_K, kx = j % DS_K;
-                const int iy = 2 * w4.z - 1 + ky, ix = 2 * w4.w - 1 + kx;
-                if (iy >= 0 && iy < P.H && ix >= 0 && ix < P.W) v = __ldg(P.x + (((long long)w4.x * P.C + c) * P.H + iy) * P.W + ix);
+#pragma unroll
+            for (int u = 0; u < NX; ++u) {
+                const int j = r0 + FSTEP * u;
+                xv[u] = 0.0f;
+                if (w4.x >= 0 && j < taps) {
+                    const int c = j / DS_TAPS, ky = (j % DS_TAPS) / DS_K, kx = j % DS_K;
+                    const int iy = 2 * w4.z - 1 + ky, ix = 2 * w4.w - 1 + kx;
+                    if (iy >= 0 && iy < P.H && ix >= 0 && ix < P.W) xv[u] = __ldg(P.x + (((long long)w4.x * P.C + c) * P.H + iy) * P.W + ix);
+                }
             }
-            s_x[j][q] = v;
+#pragma unroll
+            for (int u = 0; u < NG; ++u) s_g[r0 + FSTEP * u][q] = gv[u] * (yv[u] > 0.0f ? 1.0f : DS_SLOPE);
+#pragma unroll
+            for (int u = 0; u < NX; ++u) s_x[r0 + FSTEP * u][q] = xv[u];
         }
         __syncthreads();
 #pragma unroll 2
