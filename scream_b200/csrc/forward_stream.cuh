@@ -68,6 +68,10 @@ struct StreamParams {
 
 constexpr int FS_VPC = 2;                                // views per CTA task of S1 (2 views x 2 clouds x 32 KB of 64-bit tiles)
 constexpr int FS_VPC_FILTER = 64;                        // ... of S3: one 64-bit voxel mask word covers them
+#ifndef FS_VOX_BIG_MIN_N
+#define FS_VOX_BIG_MIN_N (8 << 20)
+#endif
+constexpr int64_t FS_VOX_BIG_MIN = FS_VOX_BIG_MIN_N;       // points per item from which the 64^3 voxel grid replaces the 32^3 one
 constexpr int FV_G = 64;                                 // voxels per axis of a cloud's bounding box (S2b): g^3 mask words per group of 64 views
 constexpr int FS_TC = (FC_G + 1) * (FC_G + 1);           // cell corners per image
 constexpr float FS_AIM = 6.0f;                            // how far (cells) outside a rim cell its aim lies

@@ -53,7 +53,7 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
     L.zenc_off = take((size_t)B * V * 2 * 2 * sizeof(unsigned));        // two sets: SCREAM_F_DUAL keeps the range of both renders
     L.stream = stream_eligible(B, w, total_pts);
     L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = L.vox_off = L.tab_off = 0;
-    L.vox_g = total_pts / B >= (4 << 20) ? FV_G : FV_G / 2;   // ~100+ points per voxel; the mask kernel costs g^3 x V
+    L.vox_g = total_pts / B >= FS_VOX_BIG_MIN ? FV_G : FV_G / 2;   // the mask kernel costs g^3 x V; the finer grid pays from FS_VOX_BIG_MIN points on
     L.surv2_cap = 1 << 18;
     // rim cells of a solid cloud pass the cell-level test wholesale (~2-3 % of the points): keep room for 1/16
     L.surv_cap = (int)std::min<int64_t>(std::max<int64_t>(FS_SURV_MIN, total_pts / 16), 1 << 26);
