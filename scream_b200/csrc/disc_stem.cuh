@@ -146,13 +146,22 @@ disc_stem_dgrad_kernel(DiscStemParams P)
 // a [F x P] x [P x 32] product.  Persistent CTAs walk chunks of DS_WG_POS positions; per chunk dpre [F][pos] and the im2col
 // patch [tap][pos] go to shared memory (y and dy are read from global memory once), thread = 4 filters x 2 taps over the
 // positions four at a time (6 vector loads for 32 FMAs); the CTA's sums leave through atomicAdd at the end.
-constexpr int DS_WG_POS = 64, DS_WG_LD = DS_WG_POS + 4;
-__global__ void __launch_bounds__(DS_THREADS, 3)
+#ifndef DS_WG_POS_N
+#define DS_WG_POS_N 32
+#endif
+#ifndef DS_WG_MINB_N
+#define DS_WG_MINB_N 8
+#endif
+constexpr int DS_WG_MINB = DS_WG_MINB_N;                  // CTAs per SM the register allocation aims at (32-position chunks)
+constexpr int DS_WG_POS = DS_WG_POS_N, DS_WG_LD = DS_WG_POS + 4;
+constexpr size_t DS_WG_SMEM = (size_t)(DS_MAX_F + DS_MAX_C * DS_TAPS) * DS_WG_LD * sizeof(float) + (size_t)DS_WG_POS * sizeof(int4);
+__global__ void __launch_bounds__(DS_THREADS, (DS_WG_POS <= 32 ? DS_WG_MINB : DS_WG_POS <= 64 ? 3 : 2))
 disc_stem_wgrad_kernel(DiscStemParams P, long long chunks_per_cta)
 {
-    __shared__ __align__(16) float s_g[DS_MAX_F][DS_WG_LD];                  // dpre of the chunk
-    __shared__ __align__(16) float s_x[DS_MAX_C * DS_TAPS][DS_WG_LD];       // im2col patch of the chunk
-    __shared__ int4 s_pos[DS_WG_POS];                                         // (image, offset in the plane, oy, ox) of the chunk's positions
+    extern __shared__ __align__(16) unsigned char s_wg_raw[];
+    float (*s_g)[DS_WG_LD] = reinterpret_cast<float (*)[DS_WG_LD]>(s_wg_raw);                                   // [F][pos] dpre of the chunk
+    float (*s_x)[DS_WG_LD] = reinterpret_cast<float (*)[DS_WG_LD]>(s_wg_raw + (size_t)DS_MAX_F * DS_WG_LD * sizeof(float));   // [tap][pos] im2col patch
+    int4* s_pos = reinterpret_cast<int4*>(s_wg_raw + (size_t)(DS_MAX_F + DS_MAX_C * DS_TAPS) * DS_WG_LD * sizeof(float)); // (image, offset in the plane, oy, ox)
     const int Ho = P.H / 2, Wo = P.W / 2, taps = P.C * DS_TAPS;
     const long long total = (long long)P.N * Ho * Wo;
     const int tf = threadIdx.x / 16, tt = threadIdx.x % 16;                  // filters 4 tf .. 4 tf + 3, taps tt and tt + 16
@@ -163,49 +172,59 @@ disc_stem_wgrad_kernel(DiscStemParams P, long long chunks_per_cta)
         __syncthreads();
         // where the chunk's positions are: image, offset inside the image's output plane, (oy, ox) -- once per position, not
         // once per element (the 64-bit divisions were most of the fill)
-        if (threadIdx.x < DS_WG_POS) {
-            const long long p = p0 + threadIdx.x;
+        for (int t = threadIdx.x; t < DS_WG_POS; t += DS_THREADS) {
+            const long long p = p0 + t;
             int4 w4 = make_int4(-1, 0, 0, 0);
             if (p < total) {
                 const long long n = p / ((long long)Wo * Ho);
                 const int rr = (int)(p - n * (long long)Wo * Ho);
                 w4 = make_int4((int)n, rr, rr / Wo, rr % Wo);
             }
-            s_pos[threadIdx.x] = w4;
+            s_pos[t] = w4;
         }
         __syncthreads();
         {
-            // a thread's elements all belong to ONE position (256 threads, 64 positions: q = thread % 64), so its place is read
-            // once, and the loads of all its elements are issued before the first store (a shared store between them would
-            // order them one behind the other: 24 exposed round trips per chunk)
-            static_assert(DS_THREADS % DS_WG_POS == 0, "one position per thread");
-            constexpr int FSTEP = DS_THREADS / DS_WG_POS, NG = DS_MAX_F / FSTEP, NX = DS_MAX_C * DS_TAPS / FSTEP;
+            // A thread's elements all belong to the same positions (q = thread % positions), so their place is read once; its
+            // loads are issued in groups of up to 16 rows before the group's shared stores (a store between two loads would
+            // order them one behind the other).  A warp reads 128 contiguous bytes of one filter's plane per load; the
+            // larger the chunk, the longer the contiguous piece per plane (the planes of one position are 4 KB apart).
+            constexpr int QPT = DS_WG_POS > DS_THREADS ? DS_WG_POS / DS_THREADS : 1;          // positions per thread
+            constexpr int FSTEP = DS_WG_POS >= DS_THREADS ? 1 : DS_THREADS / DS_WG_POS;       // rows between a thread's elements
+            constexpr int NG = DS_MAX_F / FSTEP, NX = DS_MAX_C * DS_TAPS / FSTEP, GRP = NG < 16 ? NG : 16;
+            static_assert(QPT == 1, "chunks of up to 256 positions");
             const int q = threadIdx.x % DS_WG_POS, r0 = threadIdx.x / DS_WG_POS;
             const int4 w4 = s_pos[q];
-            float gv[NG], yv[NG], xv[NX];
 #pragma unroll
-            for (int u = 0; u < NG; ++u) {
-                const int ff = r0 + FSTEP * u;
-                gv[u] = 0.0f; yv[u] = 0.0f;
-                if (w4.x >= 0 && ff < P.F) {
-                    const long long o = ((long long)w4.x * P.F + ff) * (Ho * Wo) + w4.y;
-                    gv[u] = __ldg(P.dy + o); yv[u] = __ldg(P.y + o);
+            for (int g0 = 0; g0 < NG; g0 += GRP) {
+                float gv[GRP], yv[GRP];
+#pragma unroll
+                for (int u = 0; u < GRP; ++u) {
+                    const int ff = r0 + FSTEP * (g0 + u);
+                    gv[u] = 0.0f; yv[u] = 0.0f;
+                    if (w4.x >= 0 && ff < P.F) {
+                        const long long o = ((long long)w4.x * P.F + ff) * (Ho * Wo) + w4.y;
+                        gv[u] = __ldg(P.dy + o); yv[u] = __ldg(P.y + o);
+                    }
                 }
+#pragma unroll
+                for (int u = 0; u < GRP; ++u) s_g[r0 + FSTEP * (g0 + u)][q] = gv[u] * (yv[u] > 0.0f ? 1.0f : DS_SLOPE);
             }
 #pragma unroll
-            for (int u = 0; u < NX; ++u) {
-                const int j = r0 + FSTEP * u;
-                xv[u] = 0.0f;
-                if (w4.x >= 0 && j < taps) {
-                    const int c = j / DS_TAPS, ky = (j % DS_TAPS) / DS_K, kx = j % DS_K;
-                    const int iy = 2 * w4.z - 1 + ky, ix = 2 * w4.w - 1 + kx;
-                    if (iy >= 0 && iy < P.H && ix >= 0 && ix < P.W) xv[u] = __ldg(P.x + (((long long)w4.x * P.C + c) * P.H + iy) * P.W + ix);
+            for (int g0 = 0; g0 < NX; g0 += (NX < 16 ? NX : 16)) {
+                float xv[(NX < 16 ? NX : 16)];
+#pragma unroll
+                for (int u = 0; u < (NX < 16 ? NX : 16); ++u) {
+                    const int j = r0 + FSTEP * (g0 + u);
+                    xv[u] = 0.0f;
+                    if (w4.x >= 0 && j < taps) {
+                        const int c = j / DS_TAPS, ky = (j % DS_TAPS) / DS_K, kx = j % DS_K;
+                        const int iy = 2 * w4.z - 1 + ky, ix = 2 * w4.w - 1 + kx;
+                        if (iy >= 0 && iy < P.H && ix >= 0 && ix < P.W) xv[u] = __ldg(P.x + (((long long)w4.x * P.C + c) * P.H + iy) * P.W + ix);
+                    }
                 }
+#pragma unroll
+                for (int u = 0; u < (NX < 16 ? NX : 16); ++u) s_x[r0 + FSTEP * (g0 + u)][q] = xv[u];
             }
-#pragma unroll
-            for (int u = 0; u < NG; ++u) s_g[r0 + FSTEP * u][q] = gv[u] * (yv[u] > 0.0f ? 1.0f : DS_SLOPE);
-#pragma unroll
-            for (int u = 0; u < NX; ++u) s_x[r0 + FSTEP * u][q] = xv[u];
         }
         __syncthreads();
 #pragma unroll 2

@@ -629,7 +629,14 @@ int scream_disc_stem_backward(const float* x, const float* weight, const float* 
         const long long chunks = ((long long)N * (H / 2) * (W / 2) + DS_WG_POS - 1) / DS_WG_POS;
         const long long ctas = std::min<long long>(chunks, 148 * 8);
         const long long per = (chunks + ctas - 1) / ctas;
-        disc_stem_wgrad_kernel<<<(unsigned)((chunks + per - 1) / per), DS_THREADS, 0, st>>>(P, per);
+        static thread_local int wg_attr_dev = -1;
+        int dev = 0;
+        CUDA_TRY(cudaGetDevice(&dev));
+        if (wg_attr_dev != dev) {
+            CUDA_TRY(cudaFuncSetAttribute(disc_stem_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DS_WG_SMEM));
+            wg_attr_dev = dev;
+        }
+        disc_stem_wgrad_kernel<<<(unsigned)((chunks + per - 1) / per), DS_THREADS, DS_WG_SMEM, st>>>(P, per);
     }
     CUDA_TRY(cudaGetLastError());
     return 0;
