@@ -86,7 +86,10 @@ __device__ __forceinline__ float ds_dpre(const DiscStemParams& P, long long n, i
 // filters at a time in shared memory (each dpre element is read from global memory once per tile instead of once per tap);
 // thread = two neighbouring pixels of a row (even, odd column): 3 x 2 output positions, 16 FMAs per filter for 6 scalar and
 // 4 vector shared loads.
-constexpr int DS_DG_ROWS = 8, DS_DG_COLS = 64, DS_DG_OR = DS_DG_ROWS / 2 + 2, DS_DG_OC = DS_DG_COLS / 2 + 2, DS_DG_F = 32;
+#ifndef DS_DG_F_N
+#define DS_DG_F_N 32
+#endif
+constexpr int DS_DG_ROWS = 8, DS_DG_COLS = 64, DS_DG_OR = DS_DG_ROWS / 2 + 2, DS_DG_OC = DS_DG_COLS / 2 + 2, DS_DG_F = DS_DG_F_N;
 __global__ void __launch_bounds__(DS_THREADS)
 disc_stem_dgrad_kernel(DiscStemParams P)
 {
