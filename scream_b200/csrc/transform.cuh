@@ -87,7 +87,10 @@ zrange_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ offs,
 // three-input FMNMX3 (sm_100, .NaN: a NaN depth poisons the range like torch.min / torch.max do), against ~10 in the kernel above.  The cloud is read V / ZW_VPG times (from L2
 // when it fits).  Float min / max order -0 < +0 like the integer keys do, so both kernels give the same bits.
 constexpr int ZW_THREADS = 256;
-constexpr int ZW_VPG = 16;
+#ifndef ZW_VPG_N
+#define ZW_VPG_N 16
+#endif
+constexpr int ZW_VPG = ZW_VPG_N;
 constexpr int ZW_PTS_PER_THREAD = 64;
 constexpr int ZW_STAGES = 3;                // cp.async stages per thread (4 points each)
 constexpr int ZW_PTS_PER_CTA = ZW_THREADS * ZW_PTS_PER_THREAD;

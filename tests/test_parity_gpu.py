@@ -244,6 +244,42 @@ def test_culled_equals_dense_bitwise(case):
     assert torch.equal(c[0], (a[0] - 0.5) / 0.5)
 
 
+@pytest.mark.parametrize("seed", range(10))
+def test_random_small_batches_culled_equals_dense_bitwise(seed):
+    """Small grids take other code than full ones: several CTAs per image (any count that fills a wave: 74, 37, 24, 12, ...),
+    far pixels and open near pixels searched by a whole warp, the near queue in 8-lane groups.  Random batch sizes, view
+    counts, cloud sizes and families, rho, w and poses: images, winner maps and depth ranges must equal the dense kernel's
+    bit for bit, with and without the winner map."""
+    rng = np.random.default_rng(100 + seed)
+    B = int(rng.choice([1, 1, 2, 3, 5, 9]))
+    V = int(rng.choice([1, 2, 3, 6]))
+    w = int(rng.choice([64, 64, 128]))
+    rho = float(rng.choice([12, 24, 36, 48]))
+    gens = [lambda n, s: synth.unit_ball(n, s) * np.float32(rng.uniform(0.4, 1.3)), synth.room_shell, synth.kitti_slab]
+    sizes, clouds = [], []
+    for i in range(B):
+        n, m = int(rng.integers(20, 5000)), int(rng.integers(20, 5000))
+        if seed == 3 and i == 0:
+            n = 14000                                                           # two shared-memory batches
+        sizes.append((n, m))
+        clouds += [gens[int(rng.integers(3))](n, 1000 * seed + 2 * i), gens[int(rng.integers(3))](m, 1000 * seed + 2 * i + 1)]
+    xyz = torch.from_numpy(np.concatenate(clouds).astype(np.float32)).to(DEV)
+    offs = make_offsets(sizes).to(DEV)
+    views = torch.from_numpy(synth.random_views(V, 7 + seed)).to(DEV)
+    pose = None
+    if seed % 2:
+        g = torch.Generator().manual_seed(seed)
+        q, _ = torch.linalg.qr(torch.randn(B, 3, 3, generator=g))
+        pose = torch.cat([q, 0.05 * torch.randn(B, 3, 1, generator=g)], dim=2).float().to(DEV).contiguous()
+    a = render_batch(xyz, offs, views, rho, w, pose=pose, raw=True, dense=True, need_winner=True)
+    b = render_batch(xyz, offs, views, rho, w, pose=pose, raw=True, dense=False, need_winner=True)
+    assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels (B={B} V={V} w={w} rho={rho})"
+    assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels (B={B} V={V} w={w} rho={rho})"
+    assert torch.equal(a[2], b[2])
+    c = render_batch(xyz, offs, views, rho, w, pose=pose, raw=False, dense=False, need_winner=False)
+    assert torch.equal(c[0], (a[0] - 0.5) / 0.5)
+
+
 def test_point_sharded_merge_equals_unsharded():
     """SURVEY 8e, giant-cloud mode emulated on one GPU: two point shards rendered with the depth range of the
     whole cloud (SCREAM_F_ZRANGE_IN), merged through the int64 keys -> bit-identical to the unsharded render."""
