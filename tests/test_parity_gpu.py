@@ -714,6 +714,20 @@ def test_backward_with_shared_memory_sums_equals_the_scatter_kernel(monkeypatch)
     assert float((got0 - want).abs().max()) <= 1e-5 * scale
 
 
+@pytest.mark.parametrize("V", [2, 5, 9, 20, 40, 75])
+def test_pair_entry_point_for_any_view_count_equals_dense(V):
+    """One pair per call with V views: 148 // (2 V) CTAs per image (37, 14, 8, 3, 1, 1), the depth range reduced in the
+    kernel -- against the dense kernel of the batched entry point, bit for bit."""
+    from scream_b200.render import _PairRender
+    src = torch.from_numpy(synth.unit_ball(4000 + 37 * V, 70 + V)).to(DEV)
+    tgt = torch.from_numpy(synth.room_shell(3000 + 11 * V, 71 + V)).to(DEV)
+    views = torch.from_numpy(synth.random_views(V, 3 + V)).to(DEV).contiguous()
+    imgs, win, zr = _PairRender.run(src, tgt, views, 64, 24.0, _lib.F_RAW, True)
+    offs = make_offsets([(src.shape[0], tgt.shape[0])]).to(DEV)
+    want = render_batch(torch.cat([src, tgt], 0), offs, views, 24.0, 64, raw=True, dense=True, need_winner=True)
+    assert torch.equal(imgs, want[0][0]) and torch.equal(win, want[1][0]) and torch.equal(zr, want[2][0])
+
+
 def test_counter_based_cloud_is_slice_invariant():
     """bench.py's cfg5 cloud: point i has the same bits in whatever slice it is generated (the N-GPU runs shard the cloud the
     1-GPU run renders)."""
