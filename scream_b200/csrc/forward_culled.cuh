@@ -54,6 +54,10 @@ constexpr int FC_COOP_FAR = FC_COOP_FAR_N;                           // small gr
 constexpr int FC_ZFLIGHT = FC_ZFLIGHT_N;                   // points in flight per thread in the fused depth-range pass
 constexpr int FC_AHEAD = FC_AHEAD_N;                              // points whose global loads are in flight ahead of the one in work (P1, P3)
 constexpr int FC_DIL_MAX = 31;                           // dilation steps whose masks fit the histogram's memory (31 x 64 x 8 bytes)
+#ifndef FC_LINEAR_MAX_N
+#define FC_LINEAR_MAX_N 128
+#endif
+constexpr int FC_LINEAR_MAX = FC_LINEAR_MAX_N;             // batches of up to this many points: every pixel scans all records
 constexpr int FC_G = 64;                                 // cell grid side
 constexpr int FC_CELLS = FC_G * FC_G;
 constexpr int FC_TILE = 64;                              // pixel tile side of P4
@@ -340,6 +344,67 @@ __device__ __forceinline__ float warp_min(float v) {
     return __uint_as_float(__reduce_min_sync(0xFFFFFFFFu, b));
 }
 
+// A cloud of a few points (cnt <= FC_LINEAR_MAX), whole image (forward_tiny_kernel): every pixel scores all records, then the
+// resolution rules of the disc scans (scan_pixel in the kernel): runner-up beyond the rounding margin -> the winner's exact
+// value; else every record within the margin evaluated exactly, (value, lowest index).  Records in point order, compact pair
+// arrays: xy2 [pairs] {x0, x1, y0, y1}, c2 [pairs] {c0, c1}; record s is point s of the cloud.
+constexpr int FT_THREADS = 256, FT_SLICE = 4096;         // forward_tiny_kernel: threads per CTA, pixels per CTA (w % 64 == 0)
+__device__ __forceinline__ void linear_batch(const float4* xy2f, const float2* c2f, const float* xyz, int64_t lo, const float* R,
+                                             const float* pose, bool posed, float zmin, float range, float negk, bool f16, int cnt, int w,
+                                             float r2cap, float s_zero, float inv_k, float* imgs, int32_t* winner, bool keep_raw, int p_begin, int p_end)
+{
+    FcShared S; S.xy2 = (unsigned)__cvta_generic_to_shared(xy2f); S.c2 = (unsigned)__cvta_generic_to_shared(c2f);
+    S.rec = nullptr; S.start = nullptr; S.rowmask = nullptr; S.blockmask = nullptr;
+    const int half = w / 2;
+    auto exact = [&](int s, const PixelGeom& g) {           // exact_value() on the compact arrays
+        const float* q = xyz + (size_t)(lo + s) * 3;
+        float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+        if (posed) apply_pose(pose, x, y, z);
+        const float pv = depth_weight_m(rot_row(R + 6, x, y, z), zmin, range, f16);
+        const float* f = reinterpret_cast<const float*>(xy2f) + ((s >> 1) << 2) + (s & 1);
+        return pair_value(pair_d2(f[0], f[2], g.cx, g.cy), pv, negk);
+    };
+    for (int p = p_begin + threadIdx.x; p < p_end; p += FT_THREADS) {
+        const int row = p / w, col = p - row * w;
+        PixelGeom g;
+        g.cx = pixel_centre(col, half); g.cy = pixel_centre(row, half);
+        g.ux = __fmul_rn(__fadd_rn(g.cx, 1.0f), FC_CELLS_PER_NDC);
+        g.uy = __fmul_rn(__fadd_rn(g.cy, 1.0f), FC_CELLS_PER_NDC);
+        float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
+        bool found = false;
+        scan_run(S, 0, cnt, g, s1, s2, a1, found);
+        a1 = best_of_pair(S, a1, g);
+        float val = 0.0f; int id = 0;
+        if (a1 >= 0 && s1 <= r2cap) {
+            float s_thr = s1 + score_margin(s1, inv_k);
+            const float e1 = __fmul_rn(s1, -negk);
+            if (e1 >= FC_EXP_DENORM) {
+                const float lu = e1 - 101.2f;
+                s_thr = lu >= -0.7f ? s_zero : s_thr + 1.5f * expf(lu) * inv_k;
+            }
+            if (s2 > s_thr) { id = a1; val = exact(a1, g); }
+            else {
+                const float thr = fminf(s_thr, s_zero);
+#pragma unroll 1
+                for (int q = 0; q < (cnt + 1) >> 1; ++q) {
+                    const float2 sc = score_pair(S, q, g);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int s = 2 * q + h;
+                        if (s < cnt && (h ? sc.y : sc.x) <= thr) {
+                            const float ev = exact(s, g);
+                            if (ev > val || (ev == val && s < id)) { val = ev; id = s; }
+                        }
+                    }
+                }
+            }
+            if (val == 0.0f) id = 0;
+        }
+        imgs[p] = keep_raw ? val : __fmul_rn(__fsub_rn(val, 0.5f), 2.0f);
+        if (winner) winner[p] = id;
+    }
+}
+
 // Visiting order of a tile's 64 pixel rows: from the top and bottom edges towards the middle (the pixels farthest from a
 // centred cloud, i.e. the longest disc scans, first).  lpt_row: visiting index -> row; lpt_vis: its inverse.
 __device__ __forceinline__ int lpt_row(int vis) { return vis < 16 ? vis : (vis < 32 ? 79 - vis : (vis < 48 ? vis - 16 : 95 - vis)); }
@@ -445,6 +510,8 @@ forward_culled_kernel(FwdParams P)
             if (n1 <= (unsigned)P.surv1_cap) { surv = P.surv1 + img * (size_t)P.surv1_cap; npts = (int64_t)n1; }
         }
     }
+    // a cloud of a few points is rendered by forward_tiny_kernel (launched next to this one when P.tiny is set)
+    if (P.tiny && npts <= (int64_t)FC_LINEAR_MAX && surv == nullptr) return;
     const bool raw = P.flags & 1u;
     const float inv_k = -P.inv_negk;                      // 1/k, k = rho^2/2
     const float s_zero = __fmul_rn(FC_EXP_ZERO, inv_k);   // scores beyond: value exactly 0
@@ -1078,6 +1145,68 @@ forward_culled_kernel(FwdParams P)
     }
     __syncthreads();
   }
+}
+
+// Clouds of up to FC_LINEAR_MAX points (OpenGG's 6 x 6 DEM against 65536 pixels at w = 256): every pixel of such an image
+// would be a "far" pixel walking the rows of an almost empty grid (~1500 instructions); scoring all records costs ~8 each.
+// One small CTA per (item, view, cloud) image, launched next to forward_culled_kernel (which returns at once for these
+// images, as this kernel does for all others: 2 KB of shared memory, so thousands of them come and go in microseconds):
+// records in point order (no sort), then linear_batch.  A kernel of its own so that the common path keeps its register
+// allocation (the same code inlined, or called, inside it cost cfg2 2.5 %).
+__global__ void __launch_bounds__(FT_THREADS)
+forward_tiny_kernel(FwdParams P)
+{
+    __shared__ float4 s_xy2[FC_LINEAR_MAX / 2 + 1];
+    __shared__ float2 s_c2[FC_LINEAR_MAX / 2 + 1];
+    __shared__ float s_R[9], s_pose[12];
+    // grid: (image, slice of FT_SLICE pixels) -- an image of w = 256 is 16 CTAs
+    const int tid = threadIdx.x, w = P.w, npix = w * w, slices = npix / FT_SLICE;
+    int bid = blockIdx.x;
+    const int slice = bid % slices; bid /= slices;
+    const int c = bid % 2; bid /= 2;
+    const int v = bid % P.V, b = bid / P.V;
+    const ItemSpan sp = item_span(P.offs, b, P.pair_n, P.pair_m);
+    const int64_t lo = c ? sp.tgt0 : sp.src0, hi = c ? sp.end : sp.tgt0;
+    const int64_t npts = hi - lo;
+    if (npts > (int64_t)FC_LINEAR_MAX) return;            // forward_culled_kernel's image
+    const int p_begin = slice * FT_SLICE, p_end = p_begin + FT_SLICE;
+    if (tid < 9) s_R[tid] = P.views[(size_t)v * 9 + tid];
+    const bool posed = P.pose != nullptr && c == 0;
+    if (posed && tid >= 32 && tid < 44) s_pose[tid - 32] = P.pose[(size_t)b * 12 + tid - 32];
+    __syncthreads();
+    const float* xyz_c = (c && P.xyz_t != nullptr) ? P.xyz_t : P.xyz;
+    const float zmin = dec_f32(P.zenc[((size_t)b * P.V + v) * 2]), zmax = dec_f32(P.zenc[((size_t)b * P.V + v) * 2 + 1]);
+    const float range = z_range(zmin, zmax);
+    const size_t img_off = (((size_t)b * P.V + v) * 2 + c) * npix;
+    if (P.zrange && c == 0 && slice == 0 && tid == 0) { P.zrange[((size_t)b * P.V + v) * 2] = zmin; P.zrange[((size_t)b * P.V + v) * 2 + 1] = zmax; }
+    if (zmin != zmin || zmax != zmax) {                   // a NaN coordinate in the pair: see forward_culled_kernel
+        for (int p = p_begin + tid; p < p_end; p += FT_THREADS) {
+            P.imgs[img_off + p] = __int_as_float(0x7FC00000);
+            if (P.winner) P.winner[img_off + p] = hi > lo ? 0 : -1;
+        }
+        return;
+    }
+    const bool raw = P.flags & 1u, f16 = (P.flags & FC_FLAG_HALF) != 0;
+    const float inv_k = -P.inv_negk, s_zero = __fmul_rn(FC_EXP_ZERO, inv_k);
+    const float r2cap = (!raw && P.winner == nullptr) ? fminf(s_zero, __fmul_rn(FC_EXP_MINUS1, inv_k)) : s_zero;
+    const int cnt = (int)npts;
+    float* xyf = reinterpret_cast<float*>(s_xy2); float* cf = reinterpret_cast<float*>(s_c2);
+    for (int t = tid; t < cnt + (cnt & 1); t += FT_THREADS) {     // (the pad behind an odd count: a record that can never win)
+        float xr = 0.0f, yr = 0.0f, cv = INFINITY;
+        if (t < cnt) {
+            const float* q = xyz_c + (size_t)(lo + t) * 3;
+            float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+            if (posed) apply_pose(s_pose, x, y, z);
+            xr = rot_row(s_R, x, y, z); yr = rot_row(s_R + 3, x, y, z);
+            cv = __fmul_rn(logf(depth_weight_m(rot_row(s_R + 6, x, y, z), zmin, range, f16)), P.inv_negk);
+        }
+        xyf[((t >> 1) << 2) + (t & 1)] = xr; xyf[((t >> 1) << 2) + (t & 1) + 2] = yr; cf[t] = cv;
+    }
+    __syncthreads();
+    linear_batch(s_xy2, s_c2, xyz_c, lo, s_R, s_pose, posed, zmin, range, P.negk, f16, cnt, w, r2cap, s_zero, inv_k,
+                 P.imgs + img_off, P.winner ? P.winner + img_off : nullptr, raw, p_begin, p_end);
+    if (hi <= lo && P.winner)                             // empty cloud: the background and winner -1, as the culled kernel does
+        for (int p = p_begin + tid; p < p_end; p += FT_THREADS) P.winner[img_off + p] = -1;
 }
 
 }  // namespace scream

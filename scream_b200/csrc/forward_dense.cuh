@@ -30,6 +30,7 @@ struct FwdParams {
     int64_t pair_n, pair_m;      //   xyz_t + 3 * (pair_n + i) is target point i; the source cloud is xyz
     int nparts;                  // CTAs per image (>= 1): CTA `part` owns the 32-pixel chunks c with c % nparts == part
     int fuse_zrange;             // the CTA reduces the depth range of its (item, view) itself (small grids: two launches less)
+    int tiny;                    // clouds of up to FC_LINEAR_MAX points are left to forward_tiny_kernel
 };
 
 __device__ __forceinline__ float zero_or_cull(float best, float inv_negk) {

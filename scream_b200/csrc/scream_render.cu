@@ -172,7 +172,7 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
     P.flags = flags; P.imgs = imgs; P.winner = winner; P.zrange = (flags & SCREAM_F_ZRANGE_IN) ? nullptr : zrange;
     P.surv = nullptr; P.surv_cnt = nullptr; P.surv_cap = 0;
     P.surv1 = nullptr; P.surv1_cnt = nullptr; P.surv1_cap = 0;
-    P.xyz_t = nullptr; P.pair_n = P.pair_m = 0; P.nparts = 1; P.fuse_zrange = 0;
+    P.xyz_t = nullptr; P.pair_n = P.pair_m = 0; P.nparts = 1; P.fuse_zrange = 0; P.tiny = 0;
     // giant clouds: seed z-buffer -> bounds -> filter, then the culled kernel renders the survivors
     const int zero_radius = (int)ceilf(sqrtf(FC_EXP_ZERO / (0.5f * rho2)) * FC_CELLS_PER_NDC) + 1;
     const bool use_stream = L.stream && !(flags & (SCREAM_F_DENSE | SCREAM_F_NOSTREAM)) && zero_radius <= 32;
@@ -277,7 +277,11 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
         // small grids: several CTAs per image (forward_culled.cuh: nparts), as many as keep the grid within one wave
         const long long images = (long long)B * V * ((flags & SCREAM_F_DUAL) ? 3 : 2);
         if (!(flags & SCREAM_F_DUAL)) P.nparts = culled_parts(images);
+        // grids that fill the GPU: clouds of a few points go to forward_tiny_kernel (one more launch, which returns at once for
+        // every other image; small grids keep the single launch: there the launch is what counts)
+        P.tiny = !(flags & SCREAM_F_DUAL) && P.nparts == 1 && P.surv == nullptr;
         forward_culled_kernel<<<(unsigned)(images * P.nparts), FC_THREADS, FC_SMEM, st>>>(P);
+        if (P.tiny) forward_tiny_kernel<<<(unsigned)(images * ((long long)w * w / FT_SLICE)), FT_THREADS, 0, st>>>(P);
     }
     CUDA_TRY(cudaGetLastError());
     return 0;
@@ -423,7 +427,7 @@ int scream_render_forward_pair(const float* src, int64_t n, const float* tgt, in
     P.surv1 = nullptr; P.surv1_cnt = nullptr; P.surv1_cap = 0;
     // virtual base: xyz_t + 3 * (n + i) is target point i (never dereferenced below 3 * n)
     P.xyz_t = reinterpret_cast<const float*>(reinterpret_cast<uintptr_t>(tgt) - (uintptr_t)n * 12u);
-    P.pair_n = n; P.pair_m = m; P.fuse_zrange = 1;
+    P.pair_n = n; P.pair_m = m; P.fuse_zrange = 1; P.tiny = 0;
     P.nparts = culled_parts((long long)V * 2);
     static thread_local int attr_dev = -1;
     int dev = 0;

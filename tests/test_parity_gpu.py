@@ -280,6 +280,39 @@ def test_random_small_batches_culled_equals_dense_bitwise(seed):
     assert torch.equal(c[0], (a[0] - 0.5) / 0.5)
 
 
+@pytest.mark.parametrize("w,rho", [(64, 24.0), (128, 36.0), (256, 72.0)])
+def test_clouds_of_a_few_points_in_a_full_grid_equal_dense_bitwise(w, rho):
+    """Batches that fill the GPU hand clouds of up to 128 points to forward_tiny_kernel (every pixel scores all records) and
+    the rest to forward_culled_kernel: OpenGG-like patches (a DSM grid against a 6 x 6 DEM), clouds of 1, 2, 127, 128 and 129
+    points, exact ties on the coarse grid, a pose -- against the dense kernel, bit for bit, with and without winner maps."""
+    rng = np.random.default_rng(w)
+    sizes, clouds = [], []
+    for i in range(40):
+        n = [1, 2, 36, 127, 128, 129, 400][i % 7]
+        m = int(rng.integers(1, 300))
+        if i % 5 == 0:
+            dsm, dem = synth.opengg_patch(20, 50 + i)
+            a, b2 = dsm, dem
+        else:
+            a, b2 = synth.unit_ball(n, 900 + i) * np.float32(0.9), synth.room_shell(m, 950 + i)
+        sizes.append((len(a), len(b2))); clouds += [a, b2]
+    xyz = torch.from_numpy(np.concatenate(clouds).astype(np.float32)).to(DEV)
+    offs = make_offsets(sizes).to(DEV)
+    B = len(sizes)
+    views = torch.from_numpy(np.concatenate([np.eye(3, dtype=np.float32)[None], synth.random_views(1, 4)], 0)).to(DEV)   # 160 images
+    g = torch.Generator().manual_seed(w)
+    q, _ = torch.linalg.qr(torch.randn(B, 3, 3, generator=g))
+    pose = torch.cat([q, 0.05 * torch.randn(B, 3, 1, generator=g)], dim=2).float().to(DEV).contiguous()
+    for ps in (None, pose):
+        a = render_batch(xyz, offs, views, rho, w, pose=ps, raw=True, dense=True, need_winner=True)
+        b = render_batch(xyz, offs, views, rho, w, pose=ps, raw=True, dense=False, need_winner=True)
+        assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
+        assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
+        assert torch.equal(a[2], b[2])
+        c = render_batch(xyz, offs, views, rho, w, pose=ps, raw=False, dense=False, need_winner=False)
+        assert torch.equal(c[0], (a[0] - 0.5) / 0.5)
+
+
 def test_point_sharded_merge_equals_unsharded():
     """SURVEY 8e, giant-cloud mode emulated on one GPU: two point shards rendered with the depth range of the
     whole cloud (SCREAM_F_ZRANGE_IN), merged through the int64 keys -> bit-identical to the unsharded render."""
