@@ -64,6 +64,11 @@ struct StreamParams {
     // (all_reduce(SUM): one rank contributes, the others add zeros).  nullptr: seeds are local (P.seed holds point indices).
     float4* seedtab;
     int rank;
+    // w == 128 (lattice passes, scream_render.cu): the image's pixel centres are four 64 x 64 lattices, the w == 64 lattice
+    // moved by -+1/128 along x and y.  A pass filters for ONE of them in the frame that puts it on the cell centres: the
+    // cell coordinate of a point is fl(32 x' + off) with off = 32 +- 0.25 (the additive constant of the same FMA, no extra
+    // rounding) and the NDC position of a seed fl(x' + sh), sh = (off - 32) / 32 = +-1/128.  w == 64: off = 32, sh = 0.
+    float offx, offy, shx, shy;
 };
 
 constexpr int FS_VPC = 2;                                // views per CTA task of S1 (2 views x 2 clouds x 32 KB of 64-bit tiles)
@@ -90,10 +95,10 @@ struct StreamPoint { float pv, d2c; int cell; bool inside; };
 // the safe direction by the callers), home cell = floor of the cell coordinate (clamped like the renderer's grid) and
 // d2c = squared distance, in cells^2, to the pixel centre of that cell (w == 64: pixel = cell).  The cell function
 // need not be bit-identical to the renderer's: S1 and S3 share it, and the bounds of S2 carry slack.
-__device__ __forceinline__ StreamPoint stream_point(float x, float y, float z, const StreamView& W) {
+__device__ __forceinline__ StreamPoint stream_point(float x, float y, float z, const StreamView& W, float offx, float offy) {
     StreamPoint sp;
-    const float ux = __fmaf_rn(rot_row(W.R, x, y, z), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
-    const float uy = __fmaf_rn(rot_row(W.R + 3, x, y, z), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+    const float ux = __fmaf_rn(rot_row(W.R, x, y, z), FC_CELLS_PER_NDC, offx);
+    const float uy = __fmaf_rn(rot_row(W.R + 3, x, y, z), FC_CELLS_PER_NDC, offy);
     sp.pv = __fmaf_rn(-(rot_row(W.R + 6, x, y, z) - W.zmin), W.rcp_range, 1.0f);
     const float jf = fminf(fmaxf(floorf(ux), 0.0f), (float)(FC_G - 1)), jf2 = fminf(fmaxf(floorf(uy), 0.0f), (float)(FC_G - 1));
     sp.inside = ux >= 0.0f && ux < (float)FC_G && uy >= 0.0f && uy < (float)FC_G;     // really inside its cell (not clamped)
@@ -159,7 +164,7 @@ stream_seed_kernel(StreamParams P)
                 const unsigned li = (unsigned)(gi - (c ? sp.tgt0 : sp.src0));
                 if (P.pose != nullptr && c == 0) apply_pose(s_pose, x[u], y[u], z[u]);
                 for (int vv = 0; vv < nv; ++vv) {
-                    const StreamPoint pt = stream_point(x[u], y[u], z[u], s_view[vv]);
+                    const StreamPoint pt = stream_point(x[u], y[u], z[u], s_view[vv], P.offx, P.offy);
                     const float pv_lo = pt.pv - FS_PV_ABS;
                     if (!(pv_lo > 0.0f) || !pt.inside) continue;     // clamped points may be anywhere outside: they cannot seed
                     const float val = pv_lo * home_weight(pt, negkc);
@@ -231,7 +236,7 @@ stream_seedtab_kernel(StreamParams P)
             if (posed) apply_pose(s_pose, x, y, z);
             const float pv_lo = __fmaf_rn(-(rot_row(s_R + 6, x, y, z) - zmin), rcp_range, 1.0f) - FS_PV_ABS;
             if (pv_lo > 0.0f) {
-                sd = make_float4(rot_row(s_R, x, y, z), rot_row(s_R + 3, x, y, z),
+                sd = make_float4(rot_row(s_R, x, y, z) + P.shx, rot_row(s_R + 3, x, y, z) + P.shy,
                                  fmaxf(-logf(pv_lo) * inv_k, 0.0f) * (1.0f + 1e-5f) + 1e-12f, __uint_as_float((unsigned)(key >> 32)));
                 out = (key & 0xFFFFFFFF00000000ull) | (unsigned long long)(0xFFFFFFFFu - (unsigned)P.rank);
             }
@@ -289,7 +294,7 @@ stream_bound_kernel(StreamParams P)
             if (posed) apply_pose(s_pose, x, y, z);
             const float pv_lo = __fmaf_rn(-(rot_row(s_R + 6, x, y, z) - zmin), rcp_range, 1.0f) - FS_PV_ABS;
             if (pv_lo > 0.0f)
-                sd = make_float4(rot_row(s_R, x, y, z), rot_row(s_R + 3, x, y, z),
+                sd = make_float4(rot_row(s_R, x, y, z) + P.shx, rot_row(s_R + 3, x, y, z) + P.shy,
                                  fmaxf(-logf(pv_lo) * inv_k, 0.0f) * (1.0f + 1e-5f) + 1e-12f, 0.f);
         }
         s_seedpt[cell] = sd;
@@ -332,7 +337,7 @@ stream_bound_kernel(StreamParams P)
         if (!(pv_lo > 0.0f)) continue;
         const int slot = atomicAdd(&s_nextra, 1);
         if (slot < FS_EXTRA_MAX)
-            s_extra[slot] = make_float4(rot_row(s_R, x, y, z), rot_row(s_R + 3, x, y, z),
+            s_extra[slot] = make_float4(rot_row(s_R, x, y, z) + P.shx, rot_row(s_R + 3, x, y, z) + P.shy,
                                         fmaxf(-logf(pv_lo) * inv_k, 0.0f) * (1.0f + 1e-5f) + 1e-12f, 0.f);
     }
     __syncthreads();
@@ -378,7 +383,8 @@ stream_bound_kernel(StreamParams P)
         // Denormal range (k U > 80): values are multiples of 2^-149, so scores up to -ln(1 - u)/k <= 1.5 u/k apart
         // (u = 8 * 2^-149 * e^(k U)) may tie or swap; from u >= 1/2 on every non-zero value may.  Same rule as the
         // renderer's exact pass (forward_culled.cuh).
-        float up = best * (1.0f + 6e-6f);
+        // (lattice passes: a seed's x' + sh is rounded once more, <= 3e-8 per coordinate: 2 d 3e-8 <= 1e-7 sqrt(score))
+        float up = best * (1.0f + 6e-6f) + ((P.shx != 0.0f || P.shy != 0.0f) ? 1e-7f * sqrtf(best) : 0.0f);
         const float e1 = up * -P.negk;
         if (e1 >= FC_EXP_DENORM) {
             const float lu = e1 - 101.2f;
@@ -601,8 +607,8 @@ stream_voxmask_kernel(StreamParams P)
     unsigned mask = 0u;
     for (int vv = 0; vv < nv; ++vv) {
         const StreamView& W = s_view[vv];
-        const float uxc = __fmaf_rn(rot_row(W.R, cp[0], cp[1], cp[2]), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
-        const float uyc = __fmaf_rn(rot_row(W.R + 3, cp[0], cp[1], cp[2]), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+        const float uxc = __fmaf_rn(rot_row(W.R, cp[0], cp[1], cp[2]), FC_CELLS_PER_NDC, P.offx);
+        const float uyc = __fmaf_rn(rot_row(W.R + 3, cp[0], cp[1], cp[2]), FC_CELLS_PER_NDC, P.offy);
         const float zc = rot_row(W.R + 6, cp[0], cp[1], cp[2]);
         const float ex = (fabsf(W.R[0]) * hs[0] + fabsf(W.R[1]) * hs[1] + fabsf(W.R[2]) * hs[2] + rnd) * FC_CELLS_PER_NDC + 1e-4f;
         const float ey = (fabsf(W.R[3]) * hs[0] + fabsf(W.R[4]) * hs[1] + fabsf(W.R[5]) * hs[2] + rnd) * FC_CELLS_PER_NDC + 1e-4f;
@@ -656,10 +662,10 @@ __device__ __forceinline__ float ex2_ftz(float x) {
 
 // the transform S1 and S3 share (same arithmetic as stream_point(): they must agree on the home cell)
 struct FilterPoint { float ux, uy, pv_hi, cj, cr; bool inside; int cell; };
-__device__ __forceinline__ FilterPoint filter_point(float x, float y, float z, const StreamViewPacked& W) {
+__device__ __forceinline__ FilterPoint filter_point(float x, float y, float z, const StreamViewPacked& W, float offx, float offy) {
     FilterPoint f;
-    f.ux = __fmaf_rn(__fmaf_rn(W.rx.z, z, __fmaf_rn(W.rx.y, y, __fmul_rn(W.rx.x, x))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
-    f.uy = __fmaf_rn(__fmaf_rn(W.ry.z, z, __fmaf_rn(W.ry.y, y, __fmul_rn(W.ry.x, x))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+    f.ux = __fmaf_rn(__fmaf_rn(W.rx.z, z, __fmaf_rn(W.rx.y, y, __fmul_rn(W.rx.x, x))), FC_CELLS_PER_NDC, offx);
+    f.uy = __fmaf_rn(__fmaf_rn(W.ry.z, z, __fmaf_rn(W.ry.y, y, __fmul_rn(W.ry.x, x))), FC_CELLS_PER_NDC, offy);
     const float zr = __fmaf_rn(W.rz.z, z, __fmaf_rn(W.rz.y, y, __fmul_rn(W.rz.x, x)));
     f.pv_hi = __fmaf_rn(-(zr - W.rx.w), W.ry.w, 1.0f) + FS_PV_ABS;
     const float fj = floorf(f.ux), fi = floorf(f.uy);
@@ -748,6 +754,7 @@ stream_filter_kernel(StreamParams P)
     const int vg = P.vox_g, groups = (P.V + FS_VPC_FILTER - 1) / FS_VPC_FILTER;
     const unsigned long long* vox = P.vox + (((size_t)b * groups + blockIdx.x) * 2 + c) * (size_t)(vg * vg * vg);
     const float inv_k = -1.0f / P.negk;
+    const float offx = P.offx, offy = P.offy;
     const int npts = (int)min((int64_t)P.filter_chunk, cloud1 - base);
     const bool grid_ok = s_grid_ok;
     const float glx = s_grid[0], gly = s_grid[1], glz = s_grid[2], gix = s_grid[3], giy = s_grid[4], giz = s_grid[5];
@@ -769,7 +776,7 @@ stream_filter_kernel(StreamParams P)
                 const float* q = P.xyz + (size_t)(base + pi) * 3;
                 float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
                 if (posed) apply_pose(s_pose, x, y, z);
-                const FilterPoint f = filter_point(x, y, z, s_view[l >> 1]);
+                const FilterPoint f = filter_point(x, y, z, s_view[l >> 1], P.offx, P.offy);
                 li = (int)(base + pi - cloud0);
                 keep = !f.inside || point_may_win(f, P.win + (img0 + l) * (size_t)FC_CELLS * 8, inv_k) != 0;
             }
@@ -803,8 +810,8 @@ stream_filter_kernel(StreamParams P)
         const float px = pt[0], py = pt[32], pz = pt[64];
         const float4 rx = s_vrep[vv * 8 + (lane & 7)], ry = s_vrep[(FS_VPC_FILTER + vv) * 8 + (lane & 7)], rz = s_vrep[(2 * FS_VPC_FILTER + vv) * 8 + (lane & 7)];
         // the transform of filter_point() / stream_point(); sub-cell by integer floor of 3 x the cell coordinate
-        const float ux = __fmaf_rn(__fmaf_rn(rx.z, pz, __fmaf_rn(rx.y, py, __fmul_rn(rx.x, px))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
-        const float uy = __fmaf_rn(__fmaf_rn(ry.z, pz, __fmaf_rn(ry.y, py, __fmul_rn(ry.x, px))), FC_CELLS_PER_NDC, FC_CELLS_PER_NDC);
+        const float ux = __fmaf_rn(__fmaf_rn(rx.z, pz, __fmaf_rn(rx.y, py, __fmul_rn(rx.x, px))), FC_CELLS_PER_NDC, offx);
+        const float uy = __fmaf_rn(__fmaf_rn(ry.z, pz, __fmaf_rn(ry.y, py, __fmul_rn(ry.x, px))), FC_CELLS_PER_NDC, offy);
         const float zr = __fmaf_rn(rz.z, pz, __fmaf_rn(rz.y, py, __fmul_rn(rz.x, px)));
         const float pv_hi = __fmaf_rn(-(zr - rx.w), ry.w, 1.0f) + FS_PV_ABS;
         const int j3 = __float2int_rd(ux * (float)FS_SUB), i3 = __float2int_rd(uy * (float)FS_SUB);
@@ -928,7 +935,7 @@ stream_reseed_kernel(StreamParams P)
         const float* q = P.xyz + (size_t)(C.lo + li) * 3;
         float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
         if (C.posed) apply_pose(s_pose, x, y, z);
-        const StreamPoint pt = stream_point(x, y, z, s_view);
+        const StreamPoint pt = stream_point(x, y, z, s_view, P.offx, P.offy);
         const float pv_lo = pt.pv - FS_PV_ABS;
         if (!(pv_lo > 0.0f) || !pt.inside) continue;
         const float val = pv_lo * home_weight(pt, negkc);
@@ -939,7 +946,7 @@ stream_reseed_kernel(StreamParams P)
         // rim cells: the smallest score at the cell's aim (scores are positive floats: their bits order like uints)
         const float2 a = __ldg(aim + pt.cell);
         if (a.x == a.x) {
-            const float dx = rot_row(s_view.R, x, y, z) - a.x, dy = rot_row(s_view.R + 3, x, y, z) - a.y;
+            const float dx = rot_row(s_view.R, x, y, z) + P.shx - a.x, dy = rot_row(s_view.R + 3, x, y, z) + P.shy - a.y;
             const float sc = __fmaf_rn(dx, dx, __fmaf_rn(dy, dy, -logf(pv_lo) * inv_k));
             const unsigned nb = ~__float_as_uint(fmaxf(sc, 0.0f));
             unsigned long long* slot2 = &s_tile2[pt.cell];
@@ -1003,7 +1010,7 @@ stream_refilter_kernel(StreamParams P)
             const float* q = P.xyz + (size_t)(C.lo + li) * 3;
             float x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
             if (C.posed) apply_pose(s_pose, x, y, z);
-            const FilterPoint f = filter_point(x, y, z, s_view);
+            const FilterPoint f = filter_point(x, y, z, s_view, P.offx, P.offy);
             ux = f.ux; uy = f.uy;
             if (f.pv_hi > 0.0f) {
                 if (!f.inside) code = 2;
@@ -1057,6 +1064,54 @@ stream_refilter_kernel(StreamParams P)
             if (lane == 0) gp = atomicAdd(&P.surv2_cnt[C.img], (unsigned)__popc(km));
             gp = __shfl_sync(0xFFFFFFFFu, gp, 0) + __popc(km & ((1u << lane) - 1u));
             if (keep && gp < (unsigned)P.surv2_cap) P.surv2[C.img * (size_t)P.surv2_cap + gp] = li;
+        }
+    }
+}
+
+// ---- w == 128: the union of the four lattice passes' survivor lists ---------------------------------------------------
+// A pixel of the 128 x 128 image belongs to exactly one of the four lattices, so every point that can win a pixel is in the
+// final list of that lattice's pass; the culled kernel renders the union.  A point usually survives several passes, and a
+// record that appears twice ties with itself (every pixel it wins would take the exact pass): one bit per (item, view,
+// item-local point) keeps the first copy only.  grid (chunks of FS_R2_CHUNK entries, B * V * 2) after every pass.
+// The pass's list: the second round's, else the first round's; neither complete -> the union is marked incomplete (top bit of
+// its counter: the culled kernel then renders the whole cloud, as it does for a w == 64 list that overflowed).
+struct UnionParams {
+    const int64_t* offs; int V;
+    const int* list2; const unsigned* cnt2; int cap2;    // second round (nullptr: none)
+    const int* list1; const unsigned* cnt1; int cap1;    // first round
+    unsigned* bitmap; size_t words;                      // [B][V][words]
+    int* ulist; unsigned* ucnt; int ucap;                // [B][V][2][ucap], [B][V][2]
+};
+__global__ void __launch_bounds__(1024)
+stream_union_kernel(UnionParams M)
+{
+    const size_t img = blockIdx.y;
+    const int c = (int)(img & 1), b = (int)(img / (2 * (size_t)M.V));
+    const int* list = nullptr; unsigned n = 0u;
+    if (M.list2 != nullptr && M.cnt2[img] <= (unsigned)M.cap2) { list = M.list2 + img * (size_t)M.cap2; n = M.cnt2[img]; }
+    else if (M.cnt1[img] <= (unsigned)M.cap1) { list = M.list1 + img * (size_t)M.cap1; n = M.cnt1[img]; }
+    else { if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&M.ucnt[img], 0x80000000u); return; }
+    const unsigned first = blockIdx.x * FS_R2_CHUNK;
+    if (first >= n) return;
+    const unsigned stop = min(n, first + FS_R2_CHUNK);
+    const ItemSpan sp = item_span(M.offs, b);
+    const unsigned local0 = c ? (unsigned)(sp.tgt0 - sp.src0) : 0u;       // item-local index of the cloud's first point
+    unsigned* bits = M.bitmap + (img >> 1) * M.words;
+    const int lane = threadIdx.x & 31;
+    for (unsigned t0 = first + (threadIdx.x - lane); t0 < stop; t0 += 1024) {
+        const unsigned t = t0 + lane;
+        bool fresh = false; int li = 0;
+        if (t < stop) {
+            li = __ldg(list + t);
+            const unsigned g = local0 + (unsigned)li, bit = 1u << (g & 31u);
+            fresh = (atomicOr(bits + (g >> 5), bit) & bit) == 0u;
+        }
+        const unsigned km = __ballot_sync(0xFFFFFFFFu, fresh);
+        if (km) {
+            unsigned gp = 0;
+            if (lane == 0) gp = atomicAdd(&M.ucnt[img], (unsigned)__popc(km));
+            gp = __shfl_sync(0xFFFFFFFFu, gp, 0) + __popc(km & ((1u << lane) - 1u));
+            if (fresh && gp < (unsigned)M.ucap) M.ulist[img * (size_t)M.ucap + gp] = li;
         }
     }
 }

@@ -38,12 +38,15 @@ int fail(int code, const char* fmt, ...) {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, surv2_off, vox_off, tab_off, total; bool stream; int surv_cap, surv2_cap, vox_g; };
+struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, surv2_off, vox_off, tab_off, ucnt_off, ulist_off, ubits_off, total; bool stream; int surv_cap, surv2_cap, vox_g, ucap; };
 
 // The giant-cloud pre-filter (forward_stream.cuh) is used when the AVERAGE item reaches FS_MIN_AVG_PTS points
-// (decided from B and total_pts alone, so the workspace query and the forward call agree) and w == 64.
+// (decided from B and total_pts alone, so the workspace query and the forward call agree) and w == 64 -- or w == 128 and
+// FS_MIN_AVG_PTS_W128 points: that image is four 64 x 64 pixel lattices, filtered one after the other (four passes over the
+// cloud) and rendered from the union of their survivor lists.
+constexpr int64_t FS_MIN_AVG_PTS_W128 = 1 << 20;
 bool stream_eligible(int B, int w, int64_t total_pts) {
-    return w == 64 && total_pts >= FS_MIN_AVG_PTS * (int64_t)B;
+    return (w == 64 && total_pts >= FS_MIN_AVG_PTS * (int64_t)B) || (w == 128 && total_pts >= FS_MIN_AVG_PTS_W128 * (int64_t)B);
 }
 
 WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
@@ -52,9 +55,9 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
     L.zenc_off = take((size_t)B * V * 2 * 2 * sizeof(unsigned));        // two sets: SCREAM_F_DUAL keeps the range of both renders
     L.stream = stream_eligible(B, w, total_pts);
-    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = L.vox_off = L.tab_off = 0;
+    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = L.vox_off = L.tab_off = L.ucnt_off = L.ulist_off = L.ubits_off = 0;
     L.vox_g = total_pts / B >= FS_VOX_BIG_MIN ? FV_G : FV_G / 2;   // the mask kernel costs g^3 x V; the finer grid pays from FS_VOX_BIG_MIN points on
-    L.surv2_cap = 1 << 18;
+    L.surv2_cap = 1 << 18; L.ucap = 0;
     // rim cells of a solid cloud pass the cell-level test wholesale (~2-3 % of the points): keep room for 1/16
     L.surv_cap = (int)std::min<int64_t>(std::max<int64_t>(FS_SURV_MIN, total_pts / 16), 1 << 26);
     if (L.stream) {
@@ -66,6 +69,14 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
         L.surv2_off = take(imgs * (size_t)L.surv2_cap * sizeof(int));
         L.vox_off = take((size_t)B * ((V + FS_VPC_FILTER - 1) / FS_VPC_FILTER) * 2 * (size_t)L.vox_g * L.vox_g * L.vox_g * sizeof(unsigned long long));
         L.tab_off = take(imgs * (size_t)FC_CELLS * sizeof(float4));              // point-sharded clouds: the cross-rank seed table
+        // w == 128: the union of the four passes' lists (a second-round list holds at most 2^18 entries, a first-round list is
+        // final only below 16 M points, where surv_cap < 2^20), its counters, and one bit per (item, view, point of the item)
+        L.ucap = std::min(L.surv_cap, 1 << 20);
+        if (w == 128) {
+            L.ucnt_off = take(imgs * sizeof(unsigned));
+            L.ulist_off = take(imgs * (size_t)L.ucap * sizeof(int));
+            L.ubits_off = take((size_t)B * V * (size_t)((total_pts + 31) / 32) * sizeof(unsigned));
+        }
     }
     L.total = off;
     return L;
@@ -196,7 +207,6 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
         S.surv2 = reinterpret_cast<int*>((char*)ws + L.surv2_off); S.surv2_cap = L.surv2_cap;
         S.bbox = reinterpret_cast<unsigned*>(S.stats + 8);
         S.vox = reinterpret_cast<unsigned long long*>((char*)ws + L.vox_off); S.vox_g = L.vox_g;
-        if (sh.stage <= 1) CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
         const int64_t mi = (max_item_pts <= 0 || max_item_pts > total_pts) ? total_pts : max_item_pts;
         // S1 seeds from a subset of the cloud (at most 4 M points per item: ~1000 per pixel): any subset gives valid bounds.
         // Sharded: the ranks' samples are pooled (seed table), so each rank draws its share of the 4 M.
@@ -224,39 +234,70 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
             }
         }
         if (chunks > 2147483647LL || V * 2 > 65535 || (mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS > 2147483647LL) return fail(SCREAM_E_UNSUPPORTED, "cloud too large for the stream grid");
-        if (sh.stage <= 1)
-            stream_seed_kernel<<<dim3((unsigned)((chunks + FS_SEED_CPB - 1) / FS_SEED_CPB), (unsigned)((V + FS_VPC - 1) / FS_VPC), (unsigned)B), FS_THREADS, FS_SEED_SMEM, st>>>(S);
-        if (sh.stage == 1 || sh.stage == 2) {
-            // stage 1: this rank's seed table + keys (value bits << 32 | ~rank) -> caller: all_reduce(MAX) over the keys
-            // stage 2: entries that are not the cell's best are cleared        -> caller: all_reduce(SUM) over the table
-            if (sh.stage == 1) stream_seedtab_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, 0, st>>>(S);
-            else stream_seedtab_mask_kernel<<<(unsigned)((n_cells + 255) / 256), 256, 0, st>>>(S, (long long)n_cells);
-            CUDA_TRY(cudaGetLastError());
-            if (sh.keys) *sh.keys = reinterpret_cast<int64_t*>(S.seed);
-            if (sh.n_keys) *sh.n_keys = n_cells;
-            if (sh.table) *sh.table = reinterpret_cast<float*>(S.seedtab);
-            if (sh.n_table) *sh.n_table = n_cells * 4;
-            return 0;
-        }
-        stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM, st>>>(S);
-        S.seedtab = nullptr;                              // a second round seeds from this rank's own survivors again
-        stream_bbox_kernel<<<dim3((unsigned)((mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS), (unsigned)B), FV_BBOX_THREADS, 0, st>>>(S);
-        stream_voxmask_kernel<<<dim3((unsigned)((L.vox_g * L.vox_g * L.vox_g + 255) / 256), (unsigned)(vgroups * 2 * 4), (unsigned)B), 256, 0, st>>>(S);
-        stream_filter_kernel<<<dim3((unsigned)vgroups, (unsigned)(fchunks * 2), (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
-        // second round: seeds from the survivors (the true per-cell best), bounds again, survivor lists filtered again.
-        // Pays once the first round's seeds are a thin sample of the cloud (its survivors grow with the stride).
-        // (sharded: the pooled seeds already are the 4 M sample of the whole cloud and a shard's survivor lists are short)
         const bool round2 = S.seed_stride >= 4 && sh.stage == 0;
-        if (round2) {
-            const unsigned r2chunks = (unsigned)((std::min<int64_t>(mi, L.surv_cap) + FS_R2_CHUNK - 1) / FS_R2_CHUNK);
-            CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.cnt_off - L.seed_off, st));
-            const dim3 g2(r2chunks, (unsigned)(V * 2), (unsigned)B);
-            stream_reseed_kernel<<<g2, FS_THREADS, FS_RESEED_SMEM, st>>>(S);
+        // w == 64: one pass in the image's own frame.  w == 128: four passes, one per pixel lattice (StreamParams::offx), each
+        // followed by the merge of its final list into the union.
+        const int passes = w == 128 ? 4 : 1;
+        if (passes > 1 && sh.stage != 0) return fail(SCREAM_E_UNSUPPORTED, "the sharded stages take w == 64 only");
+        UnionParams U;
+        if (passes > 1) {
+            U.offs = offs; U.V = V;
+            U.list2 = round2 ? S.surv2 : nullptr; U.cnt2 = S.surv2_cnt; U.cap2 = L.surv2_cap;
+            U.list1 = S.surv; U.cnt1 = S.surv_cnt; U.cap1 = L.surv_cap;
+            U.bitmap = reinterpret_cast<unsigned*>((char*)ws + L.ubits_off); U.words = (size_t)((mi + 31) / 32);
+            U.ulist = reinterpret_cast<int*>((char*)ws + L.ulist_off); U.ucnt = reinterpret_cast<unsigned*>((char*)ws + L.ucnt_off); U.ucap = L.ucap;
+            CUDA_TRY(cudaMemsetAsync(U.ucnt, 0, (size_t)B * V * 2 * sizeof(unsigned), st));
+            CUDA_TRY(cudaMemsetAsync(U.bitmap, 0, (size_t)B * V * U.words * sizeof(unsigned), st));
+        }
+        for (int pass = 0; pass < passes; ++pass) {
+            // lattice (a, b) of a 128 x 128 image: pixel 2 q + a has the centre of pixel q of the 64 x 64 image + (a - 1/2) / 64,
+            // so the points move by (1/2 - a) / 64 = -+1/128 NDC = -+1/4 cell
+            S.offx = S.offy = FC_CELLS_PER_NDC; S.shx = S.shy = 0.0f;
+            if (passes > 1) {
+                S.shx = (pass & 1) ? -1.0f / 128.0f : 1.0f / 128.0f; S.shy = (pass & 2) ? -1.0f / 128.0f : 1.0f / 128.0f;
+                S.offx = FC_CELLS_PER_NDC + S.shx * FC_CELLS_PER_NDC; S.offy = FC_CELLS_PER_NDC + S.shy * FC_CELLS_PER_NDC;
+                S.seedtab = nullptr;
+            }
+            if (sh.stage <= 1) CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
+            if (sh.stage <= 1)
+                stream_seed_kernel<<<dim3((unsigned)((chunks + FS_SEED_CPB - 1) / FS_SEED_CPB), (unsigned)((V + FS_VPC - 1) / FS_VPC), (unsigned)B), FS_THREADS, FS_SEED_SMEM, st>>>(S);
+            if (sh.stage == 1 || sh.stage == 2) {
+                // stage 1: this rank's seed table + keys (value bits << 32 | ~rank) -> caller: all_reduce(MAX) over the keys
+                // stage 2: entries that are not the cell's best are cleared        -> caller: all_reduce(SUM) over the table
+                if (sh.stage == 1) stream_seedtab_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, 0, st>>>(S);
+                else stream_seedtab_mask_kernel<<<(unsigned)((n_cells + 255) / 256), 256, 0, st>>>(S, (long long)n_cells);
+                CUDA_TRY(cudaGetLastError());
+                if (sh.keys) *sh.keys = reinterpret_cast<int64_t*>(S.seed);
+                if (sh.n_keys) *sh.n_keys = n_cells;
+                if (sh.table) *sh.table = reinterpret_cast<float*>(S.seedtab);
+                if (sh.n_table) *sh.n_table = n_cells * 4;
+                return 0;
+            }
             stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM, st>>>(S);
-            stream_refilter_kernel<<<g2, FS_THREADS, 0, st>>>(S);
+            S.seedtab = nullptr;                              // a second round seeds from this rank's own survivors again
+            stream_bbox_kernel<<<dim3((unsigned)((mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS), (unsigned)B), FV_BBOX_THREADS, 0, st>>>(S);
+            stream_voxmask_kernel<<<dim3((unsigned)((L.vox_g * L.vox_g * L.vox_g + 255) / 256), (unsigned)(vgroups * 2 * 4), (unsigned)B), 256, 0, st>>>(S);
+            stream_filter_kernel<<<dim3((unsigned)vgroups, (unsigned)(fchunks * 2), (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
+            // second round: seeds from the survivors (the true per-cell best), bounds again, survivor lists filtered again.
+            // Pays once the first round's seeds are a thin sample of the cloud (its survivors grow with the stride).
+            // (sharded: the pooled seeds already are the 4 M sample of the whole cloud and a shard's survivor lists are short)
+            if (round2) {
+                const unsigned r2chunks = (unsigned)((std::min<int64_t>(mi, L.surv_cap) + FS_R2_CHUNK - 1) / FS_R2_CHUNK);
+                CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.cnt_off - L.seed_off, st));
+                const dim3 g2(r2chunks, (unsigned)(V * 2), (unsigned)B);
+                stream_reseed_kernel<<<g2, FS_THREADS, FS_RESEED_SMEM, st>>>(S);
+                stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM, st>>>(S);
+                stream_refilter_kernel<<<g2, FS_THREADS, 0, st>>>(S);
+            }
+            if (passes > 1) {
+                const unsigned uchunks = (unsigned)((std::min<int64_t>(mi, L.surv_cap) + FS_R2_CHUNK - 1) / FS_R2_CHUNK);
+                stream_union_kernel<<<dim3(uchunks, (unsigned)(B * V * 2)), 1024, 0, st>>>(U);
+            }
         }
         CUDA_TRY(cudaGetLastError());
-        if (round2) {
+        if (passes > 1) {
+            P.surv = U.ulist; P.surv_cnt = U.ucnt; P.surv_cap = L.ucap;
+        } else if (round2) {
             P.surv = S.surv2; P.surv_cnt = S.surv2_cnt; P.surv_cap = L.surv2_cap;
             P.surv1 = S.surv; P.surv1_cnt = S.surv_cnt; P.surv1_cap = L.surv_cap;
         } else {

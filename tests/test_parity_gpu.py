@@ -427,6 +427,64 @@ def test_giant_cloud_stream_filter_is_exact(case):
     assert torch.equal(c[0], d[0])
 
 
+GIANT_W128_CASES = [
+    # (n, m, rho, kind, V): >= 2^20 points per item, the size from which a w = 128 render takes the lattice passes
+    (700000, 500000, 36, "ball", 3),            # cfg5's second shape (rho 36, w 128)
+    (600000, 560000, 36, "shell", 2),
+    (650000, 450000, 24, "ballx", 2),           # points outside the image
+    (600000, 500000, 36, "cube", 2),            # the square image filled to its edges: the quarter-cell border strips of the shifted frames
+    (640000, 480000, 72, "slab", 2),            # a narrow kernel (rho 72: sigma = 0.9 pixels)
+]
+
+
+@pytest.mark.parametrize("case", GIANT_W128_CASES)
+def test_giant_cloud_w128_lattice_passes_are_exact(case):
+    """BASELINE config 5, second shape (w = 128): the image's pixels are four 64 x 64 lattices; the pre-filter runs once per
+    lattice in a frame shifted by a quarter cell and the culled kernel renders the union of the four survivor lists.  Same
+    bits as rendering every batch of the cloud (SCREAM_F_NOSTREAM), values and winner maps, with and without a pose, with
+    the default and with thin seeds + the second round."""
+    import ctypes as C
+    from scream_b200 import _lib
+    n, m, rho, kind, V = case
+    if kind == "ball":
+        src, tgt = synth.unit_ball(n, 41), synth.unit_ball(m, 42)
+    elif kind == "ballx":
+        src, tgt = synth.unit_ball(n, 43) * np.float32(1.3), synth.unit_ball(m, 44) * np.float32(1.15)
+    elif kind == "shell":
+        src, tgt = synth.room_shell(n, 45), synth.room_shell(m, 46)
+    elif kind == "cube":
+        rng = np.random.default_rng(47)
+        src = (rng.random((n, 3), dtype=np.float32) * 2 - 1).astype(np.float32)
+        tgt = (rng.random((m, 3), dtype=np.float32) * 2 - 1).astype(np.float32)
+    else:
+        src, tgt = synth.kitti_slab(n, 48), synth.kitti_slab(m, 49)
+    # the canonical axis views keep the cube's faces on the image border; random views for the others
+    views = np.concatenate([np.eye(3, dtype=np.float32)[None], synth.random_views(V - 1, 17)], 0)
+    if kind == "cube":
+        views[1] = np.array([[0, 0, 1], [0, 1, 0], [-1, 0, 0]], np.float32)
+    views = torch.from_numpy(views).to(DEV)
+    xyz = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV)
+    offs = make_offsets([(n, m)]).to(DEV)
+    nb64, nb128 = C.c_size_t(0), C.c_size_t(0)
+    lib = _lib.load()
+    assert lib.scream_render_workspace_bytes(1, V, 128, n + m, C.byref(nb128)) == 0
+    assert lib.scream_render_workspace_bytes(1, V, 128, 1 << 19, C.byref(nb64)) == 0
+    assert nb128.value > 64 * nb64.value, "w = 128 at this size must take the pre-filter (workspace with survivor lists)"
+    pose = torch.from_numpy(synth.random_pose(5))[None].contiguous().to(DEV)
+    for p in (None, pose):
+        a = render_batch(xyz, offs, views, rho, 128, pose=p, raw=True, need_winner=True, no_stream=True)
+        b = render_batch(xyz, offs, views, rho, 128, pose=p, raw=True, need_winner=True)
+        assert torch.equal(a[2], b[2])
+        assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
+        assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
+        t = render_batch(xyz, offs, views, rho, 128, pose=p, raw=True, need_winner=True, thin_seed=True)
+        assert torch.equal(a[0], t[0]), f"thin seed: values differ at {(a[0] != t[0]).sum().item()} pixels"
+        assert torch.equal(a[1], t[1]), f"thin seed: winners differ at {(a[1] != t[1]).sum().item()} pixels"
+    c = render_batch(xyz, offs, views, rho, 128, need_winner=False)
+    d = render_batch(xyz, offs, views, rho, 128, need_winner=False, no_stream=True)
+    assert torch.equal(c[0], d[0])
+
+
 @pytest.mark.parametrize("posed", [False, True])
 def test_depth_range_of_large_clouds_bit_exact(posed, c_oracle):
     """Items of >= 2^18 points take the views-in-registers z-range kernel (transform.cuh, zrange_wide_kernel):
