@@ -293,7 +293,16 @@ def streaming_leg(dev, peak_gbs: float, n: int = 100_000_000, n_views: int = 64,
                                 "views moves fewer bytes, so this is not physical HBM utilisation)",
                         "frac_of_compulsory_traffic": STREAM_PASSES * 12 * n / ms / 1e6 / peak_gbs},
            "hash": image_hash(out[0][0], out[1][0])}
-    del xyz, out
+    del out
+    # cfg5's second shape (rho 36, w 128) on the same cloud: four lattice passes of the pre-filter + the union render
+    run2 = lambda: render_batch(xyz, offs, views, 36, 128, raw=True, need_winner=True, max_item_pts=n)
+    ms2, _ = _timed(run2, max(2, steps // 2), dev, warm=2)
+    alg2 = n_views * 12 * n + n_views * 2 * 128 * 128 * 8
+    res["w128_rho36"] = {"ms_per_step": ms2, "gpoint_views_per_sec": n_views * n / ms2 / 1e6, "images_per_sec": 2 * n_views / ms2 * 1e3,
+                         "roofline": {"bound": "hbm", "achieved": alg2 / ms2 / 1e6, "peak": peak_gbs, "unit": "GB/s",
+                                      "frac": alg2 / ms2 / 1e6 / peak_gbs, "algorithmic_bytes_per_step": alg2,
+                                      "note": "per-view accounting, as above"}}
+    del xyz
     torch.cuda.empty_cache()
     return res
 

@@ -745,11 +745,12 @@ def test_sixteen_million_points_default_path_equals_rendering_every_batch():
     del d
     offs = make_offsets([(n, n)]).to(DEV)
     views = torch.from_numpy(synth.random_views(2, 21)).to(DEV)
-    a = render_batch(xyz, offs, views, 24, 64, raw=True, need_winner=True, max_item_pts=2 * n)
-    b = render_batch(xyz, offs, views, 24, 64, raw=True, need_winner=True, max_item_pts=2 * n, no_stream=True)
-    assert torch.equal(a[2], b[2])
-    assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
-    assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
+    for rho, w in ((24, 64), (36, 128)):            # w = 128: the same path once per pixel lattice, lists merged
+        a = render_batch(xyz, offs, views, rho, w, raw=True, need_winner=True, max_item_pts=2 * n)
+        b = render_batch(xyz, offs, views, rho, w, raw=True, need_winner=True, max_item_pts=2 * n, no_stream=True)
+        assert torch.equal(a[2], b[2])
+        assert torch.equal(a[0], b[0]), f"w {w}: values differ at {(a[0] != b[0]).sum().item()} pixels"
+        assert torch.equal(a[1], b[1]), f"w {w}: winners differ at {(a[1] != b[1]).sum().item()} pixels"
 
 
 def test_pair_entry_point_equals_batched_render():

@@ -1,0 +1,32 @@
+"""Diagnostics (GPU): survivor counts of the w = 128 lattice passes (last pass's rounds, the union) beside w = 64.
+    python tools/surv_count_w128.py <n_points> [views]"""
+import os, sys, numpy as np, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench
+from scream_b200 import _lib, synth
+from scream_b200.render import make_offsets
+n = int(sys.argv[1]); V = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+dev = torch.device('cuda:0')
+xyz = torch.cat([bench.counter_ball(0, n // 2, 9000, dev), bench.counter_ball(0, n - n // 2, 9500, dev)], 0)
+offs = make_offsets([(n // 2, n - n // 2)]).to(dev); views = torch.from_numpy(synth.random_views(V, 5)).to(dev)
+lib = _lib.load()
+al = lambda x: (x + 255) // 256 * 256
+for w, rho in ((64, 24.0), (128, 36.0), (128, 24.0)):
+    nws = _lib.workspace_bytes(1, V, w, n); ws = torch.zeros(nws, dtype=torch.uint8, device=dev)
+    imgs = torch.empty((1, V, 2, w, w), device=dev); win = torch.empty((1, V, 2, w, w), dtype=torch.int32, device=dev); zr = torch.empty((1, V, 2), device=dev)
+    rc = lib.scream_render_forward(xyz.data_ptr(), offs.data_ptr(), n, n, None, views.data_ptr(), 1, V, w, rho, 1, imgs.data_ptr(), win.data_ptr(), zr.data_ptr(), ws.data_ptr(), nws, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize(); assert rc == 0
+    I = V * 2
+    cnt_off = al(I * 2 * 4) + al(I * 4096 * 16)
+    cnt = ws[cnt_off:cnt_off + I * 4].view(torch.int32).cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+    cnt2 = ws[cnt_off + I * 4:cnt_off + I * 8].view(torch.int32).cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+    print(f"w {w} rho {rho}: (last pass) round-1 mean {cnt.mean():.0f} max {cnt.max()}  round-2 mean {cnt2.mean():.0f} max {cnt2.max()}")
+    if w == 128:
+        S1 = min(max(49152, n // 16), 1 << 26); S2 = 1 << 18; g = 64 if n >= (4 << 20) else 32
+        thr_off = cnt_off + al(I * 8 + 64 + 48); surv_off = thr_off + al(I * 4096 * 45 * 4); surv2_off = surv_off + al(I * S1 * 4)
+        vox_off = surv2_off + al(I * S2 * 4); tab_off = vox_off + al(2 * g ** 3 * 8); ucnt_off = tab_off + al(I * 4096 * 16)
+        uc = ws[ucnt_off:ucnt_off + I * 4].view(torch.int32).cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+        print(f"   union: mean {uc.mean():.0f} max {uc.max()} (cap {min(S1, 1 << 20)})")
+    wn = win[0].cpu().numpy()
+    print("   distinct winners per image (mean)", np.mean([len(np.unique(wn[v, c])) for v in range(V) for c in range(2)]))
+    del ws, imgs, win
