@@ -61,7 +61,7 @@ extern "C" {
                                     caller (point-sharded clouds: every shard must normalise with the range of
                                     the WHOLE cloud, scream_b200/shard.py); the z-range kernel is skipped */
 
-#define SCREAM_F_NOSTREAM   8u   /* giant clouds (average item >= 147456 points, w == 64): skip the streaming pre-filter and
+#define SCREAM_F_NOSTREAM   8u   /* giant clouds (average item >= 147456 points at w == 64, >= 1048576 at w == 128): skip the streaming pre-filter and
                                     render every batch of the cloud (testing / diagnostics; same bits, slower) */
 
 #define SCREAM_F_THINSEED  16u   /* giant clouds: seed the pre-filter from every 4th chunk only and always run its second
