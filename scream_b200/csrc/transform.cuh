@@ -103,6 +103,16 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
     float r; asm("max.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r;
 }
 
+// packed fp32 x 2 (FMUL2 / FFMA2, sm_100): both halves rounded like the scalar instructions
+#ifndef ZW_PACKED
+#define ZW_PACKED 1
+#endif
+typedef unsigned long long f32x2_t;
+__device__ __forceinline__ f32x2_t zw_pack(float lo, float hi) { f32x2_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void zw_unpack(f32x2_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2_t zw_mul2(f32x2_t a, f32x2_t b) { f32x2_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2_t zw_fma2(f32x2_t a, f32x2_t b, f32x2_t c) { f32x2_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
 __global__ void __launch_bounds__(ZW_THREADS)
 zrange_wide_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ offs,
                    const float* __restrict__ pose, const float* __restrict__ views,
@@ -126,6 +136,16 @@ zrange_wide_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ of
         r[v][0] = __ldg(R); r[v][1] = __ldg(R + 1); r[v][2] = __ldg(R + 2);
         lo[v] = INFINITY; hi[v] = -INFINITY;
     }
+#if ZW_PACKED
+    // the z rows of two views side by side: one FMUL2 + two FFMA2 give a point's depth in both (the point's coordinate
+    // is the same in both halves), half the FMA-pipe instructions of the scalar form and the same bits
+    static_assert(ZW_VPG % 2 == 0, "views are paired");
+    f32x2_t rp[ZW_VPG / 2][3];
+#pragma unroll
+    for (int v = 0; v < ZW_VPG / 2; ++v)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) rp[v][k] = zw_pack(r[2 * v][k], r[2 * v + 1][k]);
+#endif
     __syncthreads();
 
     // The points come through shared memory with cp.async, ZW_STAGES - 1 iterations ahead (the loop is otherwise bound
@@ -166,6 +186,22 @@ zrange_wide_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ of
                 if (i < nsrc) apply_pose(s_pose, px[u], py[u], pz[u]);
             }
         }
+#if ZW_PACKED
+        f32x2_t X[4], Y[4], Z[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { X[u] = zw_pack(px[u], px[u]); Y[u] = zw_pack(py[u], py[u]); Z[u] = zw_pack(pz[u], pz[u]); }
+#pragma unroll
+        for (int v = 0; v < ZW_VPG / 2; ++v) {
+            float z0[4], z1[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)                       // rot_row(): fmaf(r2, z, fmaf(r1, y, r0 * x)) in both halves
+                zw_unpack(zw_fma2(rp[v][2], Z[u], zw_fma2(rp[v][1], Y[u], zw_mul2(rp[v][0], X[u]))), z0[u], z1[u]);
+            lo[2 * v] = fmin3(fmin3(lo[2 * v], z0[0], z0[1]), z0[2], z0[3]);
+            hi[2 * v] = fmax3(fmax3(hi[2 * v], z0[0], z0[1]), z0[2], z0[3]);
+            lo[2 * v + 1] = fmin3(fmin3(lo[2 * v + 1], z1[0], z1[1]), z1[2], z1[3]);
+            hi[2 * v + 1] = fmax3(fmax3(hi[2 * v + 1], z1[0], z1[1]), z1[2], z1[3]);
+        }
+#else
 #pragma unroll
         for (int v = 0; v < ZW_VPG; ++v) {
             const float za = rot_row(r[v], px[0], py[0], pz[0]), zb = rot_row(r[v], px[1], py[1], pz[1]);
@@ -173,6 +209,7 @@ zrange_wide_kernel(const float* __restrict__ xyz, const int64_t* __restrict__ of
             lo[v] = fmin3(fmin3(lo[v], za, zb), zc, zd);
             hi[v] = fmax3(fmax3(hi[v], za, zb), zc, zd);
         }
+#endif
     }
 #pragma unroll
     for (int v = 0; v < ZW_VPG; ++v) {
