@@ -258,7 +258,8 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
                 S.offx = FC_CELLS_PER_NDC + S.shx * FC_CELLS_PER_NDC; S.offy = FC_CELLS_PER_NDC + S.shy * FC_CELLS_PER_NDC;
                 S.seedtab = nullptr;
             }
-            if (sh.stage <= 1) CUDA_TRY(cudaMemsetAsync(S.seed, 0, L.thr_off - L.seed_off, st));          // seed image + survivor counters
+            // seed image + survivor counters (+ the clouds' bounding-box keys: computed by the first pass, kept by the others)
+            if (sh.stage <= 1) CUDA_TRY(cudaMemsetAsync(S.seed, 0, pass == 0 ? L.thr_off - L.seed_off : (size_t)((char*)S.bbox - (char*)S.seed), st));
             if (sh.stage <= 1)
                 stream_seed_kernel<<<dim3((unsigned)((chunks + FS_SEED_CPB - 1) / FS_SEED_CPB), (unsigned)((V + FS_VPC - 1) / FS_VPC), (unsigned)B), FS_THREADS, FS_SEED_SMEM, st>>>(S);
             if (sh.stage == 1 || sh.stage == 2) {
@@ -275,7 +276,7 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
             }
             stream_bound_kernel<<<dim3((unsigned)(V * 2), (unsigned)B), 1024, FS_BOUND_SMEM, st>>>(S);
             S.seedtab = nullptr;                              // a second round seeds from this rank's own survivors again
-            stream_bbox_kernel<<<dim3((unsigned)((mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS), (unsigned)B), FV_BBOX_THREADS, 0, st>>>(S);
+            if (pass == 0) stream_bbox_kernel<<<dim3((unsigned)((mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS), (unsigned)B), FV_BBOX_THREADS, 0, st>>>(S);
             stream_voxmask_kernel<<<dim3((unsigned)((L.vox_g * L.vox_g * L.vox_g + 255) / 256), (unsigned)(vgroups * 2 * 4), (unsigned)B), 256, 0, st>>>(S);
             stream_filter_kernel<<<dim3((unsigned)vgroups, (unsigned)(fchunks * 2), (unsigned)B), FS_FILTER_THREADS, FS_FILTER_SMEM, st>>>(S);
             // second round: seeds from the survivors (the true per-cell best), bounds again, survivor lists filtered again.

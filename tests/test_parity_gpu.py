@@ -485,6 +485,24 @@ def test_giant_cloud_w128_lattice_passes_are_exact(case):
     assert torch.equal(c[0], d[0])
 
 
+def test_giant_w128_batch_of_items_and_more_than_64_views():
+    """The lattice passes with B = 2 items of different sizes and 66 views (two voxel-mask words, the second group partial):
+    the union lists and their bit maps are per (item, view, cloud)."""
+    sizes = [(700000, 600000), (520000, 380000)]
+    clouds = []
+    for k, (n, m) in enumerate(sizes):
+        clouds += [synth.unit_ball(n, 61 + 2 * k) * np.float32(0.9 + 0.1 * k), synth.room_shell(m, 62 + 2 * k)]
+    xyz = torch.from_numpy(np.concatenate(clouds, 0)).to(DEV)
+    offs = make_offsets(sizes).to(DEV)
+    views = torch.from_numpy(synth.random_views(66, 23)).to(DEV)
+    pose = torch.from_numpy(np.stack([synth.random_pose(7), synth.random_pose(8)])).contiguous().to(DEV)
+    a = render_batch(xyz, offs, views, 36, 128, pose=pose, raw=True, need_winner=True, no_stream=True)
+    b = render_batch(xyz, offs, views, 36, 128, pose=pose, raw=True, need_winner=True)
+    assert torch.equal(a[2], b[2])
+    assert torch.equal(a[0], b[0]), f"values differ at {(a[0] != b[0]).sum().item()} pixels"
+    assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
+
+
 @pytest.mark.parametrize("posed", [False, True])
 def test_depth_range_of_large_clouds_bit_exact(posed, c_oracle):
     """Items of >= 2^18 points take the views-in-registers z-range kernel (transform.cuh, zrange_wide_kernel):
