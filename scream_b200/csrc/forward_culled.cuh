@@ -447,8 +447,12 @@ __device__ long long g_fc_marks[1024][24];
 #define FC_CLOCK() 0ll
 #endif
 
+// PSTEP 1: every pixel of the image (forward_culled_kernel).  PSTEP 2: only the pixels (2 r + P.prow0, 2 c + P.pcol0) of a
+// w == 128 image, one of its four 64 x 64 lattices, as ONE tile (forward_culled_lattice_kernel: giant clouds, one launch per
+// lattice pass of the pre-filter).  A template, so that the common kernel keeps its register allocation.
+template <int PSTEP>
 __global__ void __launch_bounds__(FC_THREADS, 1)
-forward_culled_kernel(FwdParams P)
+forward_culled_kernel_t(FwdParams P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     unsigned char* s_rec = smem_raw + FC_OFF_REC;
@@ -791,9 +795,11 @@ forward_culled_kernel(FwdParams P)
         }
 
         // ---------------- P4: per-pixel search, one 64 x 64 pixel tile at a time ---------------
-        const int tiles_side = w / FC_TILE;
+        // (lattice mode, P.pstep == 2: one "tile" of 64 x 64 pixels two apart, starting at (P.prow0, P.pcol0))
+        constexpr int pstep = PSTEP;
+        const int tiles_side = pstep == 2 ? 1 : w / FC_TILE;
         for (int tile = 0; tile < tiles_side * tiles_side; ++tile) {
-            const int trow0 = (tile / tiles_side) * FC_TILE, tcol0 = (tile % tiles_side) * FC_TILE;
+            const int trow0 = pstep == 2 ? P.prow0 : (tile / tiles_side) * FC_TILE, tcol0 = pstep == 2 ? P.pcol0 : (tile % tiles_side) * FC_TILE;
             if (tid == 0) { s_qfar = 0u; s_qnear = 0u; s_qhead = 0u; s_work = 0u; }
             __syncthreads();
 
@@ -823,7 +829,7 @@ forward_culled_kernel(FwdParams P)
             for (int ol = tid; ol < own_chunks * 32; ol += FC_THREADS) {
                 const int vl = ((ol >> 5) * nparts + part) * 32 + (ol & 31);      // the chunks this CTA owns, in visiting order
                 const int rl = lpt_row(vl / FC_TILE);
-                const int row = trow0 + rl, col = tcol0 + vl % FC_TILE;
+                const int row = trow0 + rl * pstep, col = tcol0 + (vl % FC_TILE) * pstep;
                 int ring; bool blank;
                 pixel_class(row, col, half, r2cap_all, s_ring, ring, blank);
                 if (blank) put(row, col, 0.0f, 0);        // background: value 0 (index 0), or what earlier batches found
@@ -841,7 +847,7 @@ forward_culled_kernel(FwdParams P)
 
             // ---- disc scan of one queued pixel (far: no candidate; near: the best record of its 3 x 3 window) ----
             auto scan_pixel = [&](int pl, int cand) {
-                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                const int row = trow0 + (pl / FC_TILE) * pstep, col = tcol0 + (pl % FC_TILE) * pstep;
                 const PixelGeom g = geom(row, col);
                 // nothing beyond r2cap can change the output of this pixel
                 const float r2cap = r2cap_all;
@@ -876,14 +882,14 @@ forward_culled_kernel(FwdParams P)
             // Returns (warp-uniform) the winner's record when the search settled the pixel -- the caller evaluates and writes it
             // (finish_pixel: one lane per pixel, so the L2 round trips of several pixels overlap) -- or -1: written here.
             auto finish_pixel = [&](int pl, int a) {
-                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                const int row = trow0 + (pl / FC_TILE) * pstep, col = tcol0 + (pl % FC_TILE) * pstep;
                 int id;
                 float val = exact_value(S, E, a, geom(row, col), id);
                 if (val == 0.0f) id = 0;                  // all-zero pixel: torch.max returns index 0
                 put(row, col, val, id);
             };
             auto search_pixel_warp = [&](int pl, int cand) -> int {
-                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                const int row = trow0 + (pl / FC_TILE) * pstep, col = tcol0 + (pl % FC_TILE) * pstep;
                 const PixelGeom g = geom(row, col);
                 const int ci = (int)g.uy, cj = (int)g.ux;
                 const float r2cap = r2cap_all;
@@ -1000,7 +1006,7 @@ forward_culled_kernel(FwdParams P)
                 // ---- 3 x 3 cells, lane per pixel ----
                 const int vl = ((t - far_batches) * nparts + part) * 32 + lane;   // same chunks, same visiting order: a pixel
                 const int pl = lpt_row(vl / FC_TILE) * FC_TILE + vl % FC_TILE;    // belongs to ONE CTA in every batch of a cloud
-                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                const int row = trow0 + (pl / FC_TILE) * pstep, col = tcol0 + (pl % FC_TILE) * pstep;
                 const PixelGeom g = geom(row, col);
                 const int ci = (int)g.uy, cj = (int)g.ux;
                 const float fx = g.ux - (float)cj, fy = g.uy - (float)ci;
@@ -1055,7 +1061,7 @@ forward_culled_kernel(FwdParams P)
                 const int grp = lane >> 3, gl = lane & 7, qi = q0 + grp;
                 const bool act = qi < nnear;
                 const int pl = act ? s_queue[FC_TPIX - 1 - qi] : 0;
-                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                const int row = trow0 + (pl / FC_TILE) * pstep, col = tcol0 + (pl % FC_TILE) * pstep;
                 const PixelGeom g = geom(row, col);
                 const int ci = (int)g.uy, cj = (int)g.ux;
                 float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
@@ -1105,7 +1111,7 @@ forward_culled_kernel(FwdParams P)
                 if (qi - lane >= nnear) break;
                 if (lane >= near_take || qi >= nnear) continue;
                 const int pl = s_queue[FC_TPIX - 1 - qi];
-                const int row = trow0 + pl / FC_TILE, col = tcol0 + pl % FC_TILE;
+                const int row = trow0 + (pl / FC_TILE) * pstep, col = tcol0 + (pl % FC_TILE) * pstep;
                 const PixelGeom g = geom(row, col);
                 const int ci = (int)g.uy, cj = (int)g.ux;
                 const float fx = g.ux - (float)cj, fy = g.uy - (float)ci;
@@ -1146,6 +1152,8 @@ forward_culled_kernel(FwdParams P)
     __syncthreads();
   }
 }
+static const auto forward_culled_kernel = &forward_culled_kernel_t<1>;
+static const auto forward_culled_lattice_kernel = &forward_culled_kernel_t<2>;
 
 // Clouds of up to FC_LINEAR_MAX points (OpenGG's 6 x 6 DEM against 65536 pixels at w = 256): every pixel of such an image
 // would be a "far" pixel walking the rows of an almost empty grid (~1500 instructions); scoring all records costs ~8 each.

@@ -31,6 +31,8 @@ struct FwdParams {
     int nparts;                  // CTAs per image (>= 1): CTA `part` owns the 32-pixel chunks c with c % nparts == part
     int fuse_zrange;             // the CTA reduces the depth range of its (item, view) itself (small grids: two launches less)
     int tiny;                    // clouds of up to FC_LINEAR_MAX points are left to forward_tiny_kernel
+    int prow0 = 0, pcol0 = 0;    // forward_culled_lattice_kernel: (b, a) = it renders the pixels (2 r + b, 2 c + a) of a w == 128 image, one of
+                                 // its four 64 x 64 lattices (giant clouds: one launch per lattice pass, scream_render.cu)
 };
 
 __device__ __forceinline__ float zero_or_cull(float best, float inv_negk) {

@@ -65,7 +65,8 @@ struct StreamParams {
     float4* seedtab;
     int rank;
     // w == 128 (lattice passes, scream_render.cu): the image's pixel centres are four 64 x 64 lattices, the w == 64 lattice
-    // moved by -+1/128 along x and y.  A pass filters for ONE of them in the frame that puts it on the cell centres: the
+    // moved by -+1/128 along x and y.  A pass filters for ONE of them in the frame that puts it on the cell centres (and
+    // forward_culled_lattice_kernel then renders that lattice's pixels from the pass's lists): the
     // cell coordinate of a point is fl(32 x' + off) with off = 32 +- 0.25 (the additive constant of the same FMA, no extra
     // rounding) and the NDC position of a seed fl(x' + sh), sh = (off - 32) / 32 = +-1/128.  w == 64: off = 32, sh = 0.
     float offx, offy, shx, shy;
@@ -1064,54 +1065,6 @@ stream_refilter_kernel(StreamParams P)
             if (lane == 0) gp = atomicAdd(&P.surv2_cnt[C.img], (unsigned)__popc(km));
             gp = __shfl_sync(0xFFFFFFFFu, gp, 0) + __popc(km & ((1u << lane) - 1u));
             if (keep && gp < (unsigned)P.surv2_cap) P.surv2[C.img * (size_t)P.surv2_cap + gp] = li;
-        }
-    }
-}
-
-// ---- w == 128: the union of the four lattice passes' survivor lists ---------------------------------------------------
-// A pixel of the 128 x 128 image belongs to exactly one of the four lattices, so every point that can win a pixel is in the
-// final list of that lattice's pass; the culled kernel renders the union.  A point usually survives several passes, and a
-// record that appears twice ties with itself (every pixel it wins would take the exact pass): one bit per (item, view,
-// item-local point) keeps the first copy only.  grid (chunks of FS_R2_CHUNK entries, B * V * 2) after every pass.
-// The pass's list: the second round's, else the first round's; neither complete -> the union is marked incomplete (top bit of
-// its counter: the culled kernel then renders the whole cloud, as it does for a w == 64 list that overflowed).
-struct UnionParams {
-    const int64_t* offs; int V;
-    const int* list2; const unsigned* cnt2; int cap2;    // second round (nullptr: none)
-    const int* list1; const unsigned* cnt1; int cap1;    // first round
-    unsigned* bitmap; size_t words;                      // [B][V][words]
-    int* ulist; unsigned* ucnt; int ucap;                // [B][V][2][ucap], [B][V][2]
-};
-__global__ void __launch_bounds__(1024)
-stream_union_kernel(UnionParams M)
-{
-    const size_t img = blockIdx.y;
-    const int c = (int)(img & 1), b = (int)(img / (2 * (size_t)M.V));
-    const int* list = nullptr; unsigned n = 0u;
-    if (M.list2 != nullptr && M.cnt2[img] <= (unsigned)M.cap2) { list = M.list2 + img * (size_t)M.cap2; n = M.cnt2[img]; }
-    else if (M.cnt1[img] <= (unsigned)M.cap1) { list = M.list1 + img * (size_t)M.cap1; n = M.cnt1[img]; }
-    else { if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&M.ucnt[img], 0x80000000u); return; }
-    const unsigned first = blockIdx.x * FS_R2_CHUNK;
-    if (first >= n) return;
-    const unsigned stop = min(n, first + FS_R2_CHUNK);
-    const ItemSpan sp = item_span(M.offs, b);
-    const unsigned local0 = c ? (unsigned)(sp.tgt0 - sp.src0) : 0u;       // item-local index of the cloud's first point
-    unsigned* bits = M.bitmap + (img >> 1) * M.words;
-    const int lane = threadIdx.x & 31;
-    for (unsigned t0 = first + (threadIdx.x - lane); t0 < stop; t0 += 1024) {
-        const unsigned t = t0 + lane;
-        bool fresh = false; int li = 0;
-        if (t < stop) {
-            li = __ldg(list + t);
-            const unsigned g = local0 + (unsigned)li, bit = 1u << (g & 31u);
-            fresh = (atomicOr(bits + (g >> 5), bit) & bit) == 0u;
-        }
-        const unsigned km = __ballot_sync(0xFFFFFFFFu, fresh);
-        if (km) {
-            unsigned gp = 0;
-            if (lane == 0) gp = atomicAdd(&M.ucnt[img], (unsigned)__popc(km));
-            gp = __shfl_sync(0xFFFFFFFFu, gp, 0) + __popc(km & ((1u << lane) - 1u));
-            if (fresh && gp < (unsigned)M.ucap) M.ulist[img * (size_t)M.ucap + gp] = li;
         }
     }
 }

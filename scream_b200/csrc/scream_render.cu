@@ -38,12 +38,12 @@ int fail(int code, const char* fmt, ...) {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, surv2_off, vox_off, tab_off, ucnt_off, ulist_off, ubits_off, total; bool stream; int surv_cap, surv2_cap, vox_g, ucap; };
+struct WsLayout { size_t zenc_off, seed_off, thr_off, cnt_off, surv_off, surv2_off, vox_off, tab_off, total; bool stream; int surv_cap, surv2_cap, vox_g; };
 
 // The giant-cloud pre-filter (forward_stream.cuh) is used when the AVERAGE item reaches FS_MIN_AVG_PTS points
 // (decided from B and total_pts alone, so the workspace query and the forward call agree) and w == 64 -- or w == 128 and
-// FS_MIN_AVG_PTS_W128 points: that image is four 64 x 64 pixel lattices, filtered one after the other (four passes over the
-// cloud) and rendered from the union of their survivor lists.
+// FS_MIN_AVG_PTS_W128 points: that image is four 64 x 64 pixel lattices, each filtered (a pass over the cloud) and rendered
+// from its own survivor lists, one after the other.
 constexpr int64_t FS_MIN_AVG_PTS_W128 = 1 << 20;
 bool stream_eligible(int B, int w, int64_t total_pts) {
     return (w == 64 && total_pts >= FS_MIN_AVG_PTS * (int64_t)B) || (w == 128 && total_pts >= FS_MIN_AVG_PTS_W128 * (int64_t)B);
@@ -55,9 +55,9 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
     L.zenc_off = take((size_t)B * V * 2 * 2 * sizeof(unsigned));        // two sets: SCREAM_F_DUAL keeps the range of both renders
     L.stream = stream_eligible(B, w, total_pts);
-    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = L.vox_off = L.tab_off = L.ucnt_off = L.ulist_off = L.ubits_off = 0;
+    L.seed_off = L.thr_off = L.cnt_off = L.surv_off = L.surv2_off = L.vox_off = L.tab_off = 0;
     L.vox_g = total_pts / B >= FS_VOX_BIG_MIN ? FV_G : FV_G / 2;   // the mask kernel costs g^3 x V; the finer grid pays from FS_VOX_BIG_MIN points on
-    L.surv2_cap = 1 << 18; L.ucap = 0;
+    L.surv2_cap = 1 << 18;
     // rim cells of a solid cloud pass the cell-level test wholesale (~2-3 % of the points): keep room for 1/16
     L.surv_cap = (int)std::min<int64_t>(std::max<int64_t>(FS_SURV_MIN, total_pts / 16), 1 << 26);
     if (L.stream) {
@@ -69,14 +69,6 @@ WsLayout ws_layout(int B, int V, int w, int64_t total_pts) {
         L.surv2_off = take(imgs * (size_t)L.surv2_cap * sizeof(int));
         L.vox_off = take((size_t)B * ((V + FS_VPC_FILTER - 1) / FS_VPC_FILTER) * 2 * (size_t)L.vox_g * L.vox_g * L.vox_g * sizeof(unsigned long long));
         L.tab_off = take(imgs * (size_t)FC_CELLS * sizeof(float4));              // point-sharded clouds: the cross-rank seed table
-        // w == 128: the union of the four passes' lists (a second-round list holds at most 2^18 entries, a first-round list is
-        // final only below 16 M points, where surv_cap < 2^20), its counters, and one bit per (item, view, point of the item)
-        L.ucap = std::min(L.surv_cap, 1 << 20);
-        if (w == 128) {
-            L.ucnt_off = take(imgs * sizeof(unsigned));
-            L.ulist_off = take(imgs * (size_t)L.ucap * sizeof(int));
-            L.ubits_off = take((size_t)B * V * (size_t)((total_pts + 31) / 32) * sizeof(unsigned));
-        }
     }
     L.total = off;
     return L;
@@ -139,6 +131,19 @@ int scream_render_workspace_bytes(int B, int V, int w, int64_t total_pts, size_t
 }  // extern "C"
 
 namespace {
+// the culled kernels' dynamic shared memory (once per device and thread)
+int culled_attr() {
+    static thread_local int attr_dev = -1;
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (attr_dev != dev) {
+        CUDA_TRY(cudaFuncSetAttribute(forward_culled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FC_SMEM));
+        CUDA_TRY(cudaFuncSetAttribute(forward_culled_lattice_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FC_SMEM));
+        attr_dev = dev;
+    }
+    return 0;
+}
+
 // Exchange points of the point-sharded protocol (scream_render_forward_sharded): the whole call, or one of its three stages.
 struct Shard { int stage = 0, rank = 0, world = 1; int64_t** keys = nullptr; size_t* n_keys = nullptr; float** table = nullptr; size_t* n_table = nullptr; };
 
@@ -186,6 +191,7 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
     P.xyz_t = nullptr; P.pair_n = P.pair_m = 0; P.nparts = 1; P.fuse_zrange = 0; P.tiny = 0;
     // giant clouds: seed z-buffer -> bounds -> filter, then the culled kernel renders the survivors
     const int zero_radius = (int)ceilf(sqrtf(FC_EXP_ZERO / (0.5f * rho2)) * FC_CELLS_PER_NDC) + 1;
+    bool lattice_done = false;
     const bool use_stream = L.stream && !(flags & (SCREAM_F_DENSE | SCREAM_F_NOSTREAM)) && zero_radius <= 32;
     if (sh.stage != 0 && !use_stream) return fail(SCREAM_E_UNSUPPORTED, "the sharded stages need the giant-cloud path (w == 64, >= 147456 points per item, no DENSE / NOSTREAM)");
     if (use_stream) {
@@ -236,19 +242,10 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
         if (chunks > 2147483647LL || V * 2 > 65535 || (mi + FV_BBOX_PTS - 1) / FV_BBOX_PTS > 2147483647LL) return fail(SCREAM_E_UNSUPPORTED, "cloud too large for the stream grid");
         const bool round2 = S.seed_stride >= 4 && sh.stage == 0;
         // w == 64: one pass in the image's own frame.  w == 128: four passes, one per pixel lattice (StreamParams::offx), each
-        // followed by the merge of its final list into the union.
+        // followed by the render of that lattice's pixels from the pass's survivor lists (a pixel belongs to exactly one
+        // lattice, so every point that can win it is in that pass's list).
         const int passes = w == 128 ? 4 : 1;
         if (passes > 1 && sh.stage != 0) return fail(SCREAM_E_UNSUPPORTED, "the sharded stages take w == 64 only");
-        UnionParams U;
-        if (passes > 1) {
-            U.offs = offs; U.V = V;
-            U.list2 = round2 ? S.surv2 : nullptr; U.cnt2 = S.surv2_cnt; U.cap2 = L.surv2_cap;
-            U.list1 = S.surv; U.cnt1 = S.surv_cnt; U.cap1 = L.surv_cap;
-            U.bitmap = reinterpret_cast<unsigned*>((char*)ws + L.ubits_off); U.words = (size_t)((mi + 31) / 32);
-            U.ulist = reinterpret_cast<int*>((char*)ws + L.ulist_off); U.ucnt = reinterpret_cast<unsigned*>((char*)ws + L.ucnt_off); U.ucap = L.ucap;
-            CUDA_TRY(cudaMemsetAsync(U.ucnt, 0, (size_t)B * V * 2 * sizeof(unsigned), st));
-            CUDA_TRY(cudaMemsetAsync(U.bitmap, 0, (size_t)B * V * U.words * sizeof(unsigned), st));
-        }
         for (int pass = 0; pass < passes; ++pass) {
             // lattice (a, b) of a 128 x 128 image: pixel 2 q + a has the centre of pixel q of the 64 x 64 image + (a - 1/2) / 64,
             // so the points move by (1/2 - a) / 64 = -+1/128 NDC = -+1/4 cell
@@ -291,13 +288,21 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
                 stream_refilter_kernel<<<g2, FS_THREADS, 0, st>>>(S);
             }
             if (passes > 1) {
-                const unsigned uchunks = (unsigned)((std::min<int64_t>(mi, L.surv_cap) + FS_R2_CHUNK - 1) / FS_R2_CHUNK);
-                stream_union_kernel<<<dim3(uchunks, (unsigned)(B * V * 2)), 1024, 0, st>>>(U);
+                FwdParams Q = P;
+                if (round2) {
+                    Q.surv = S.surv2; Q.surv_cnt = S.surv2_cnt; Q.surv_cap = L.surv2_cap;
+                    Q.surv1 = S.surv; Q.surv1_cnt = S.surv_cnt; Q.surv1_cap = L.surv_cap;
+                } else {
+                    Q.surv = S.surv; Q.surv_cnt = S.surv_cnt; Q.surv_cap = L.surv_cap;
+                }
+                Q.pcol0 = pass & 1; Q.prow0 = (pass >> 1) & 1;
+                if (int rc = culled_attr()) return rc;
+                forward_culled_lattice_kernel<<<(unsigned)((long long)B * V * 2), FC_THREADS, FC_SMEM, st>>>(Q);
             }
         }
         CUDA_TRY(cudaGetLastError());
         if (passes > 1) {
-            P.surv = U.ulist; P.surv_cnt = U.ucnt; P.surv_cap = L.ucap;
+            lattice_done = true;
         } else if (round2) {
             P.surv = S.surv2; P.surv_cnt = S.surv2_cnt; P.surv_cap = L.surv2_cap;
             P.surv1 = S.surv; P.surv1_cnt = S.surv_cnt; P.surv1_cap = L.surv_cap;
@@ -305,17 +310,13 @@ int forward_impl(const float* xyz, const int64_t* offs, int64_t total_pts, int64
             P.surv = S.surv; P.surv_cnt = S.surv_cnt; P.surv_cap = L.surv_cap;
         }
     }
-    if (flags & SCREAM_F_DENSE) {
+    if (lattice_done) {
+        // w == 128 giant cloud: every lattice pass has rendered its pixels
+    } else if (flags & SCREAM_F_DENSE) {
         const long long grid = (long long)B * V * 2 * (w * w / FD_TILE);
         forward_dense_kernel<<<(unsigned)grid, FD_THREADS, 0, st>>>(P);
     } else {
-        static thread_local int attr_dev = -1;
-        int dev = 0;
-        CUDA_TRY(cudaGetDevice(&dev));
-        if (attr_dev != dev) {
-            CUDA_TRY(cudaFuncSetAttribute(forward_culled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FC_SMEM));
-            attr_dev = dev;
-        }
+        if (int rc = culled_attr()) return rc;
         // small grids: several CTAs per image (forward_culled.cuh: nparts), as many as keep the grid within one wave
         const long long images = (long long)B * V * ((flags & SCREAM_F_DUAL) ? 3 : 2);
         if (!(flags & SCREAM_F_DUAL)) P.nparts = culled_parts(images);

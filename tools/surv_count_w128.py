@@ -1,4 +1,4 @@
-"""Diagnostics (GPU): survivor counts of the w = 128 lattice passes (last pass's rounds, the union) beside w = 64.
+"""Diagnostics (GPU): survivor counts of the w = 128 lattice passes (the last pass's two rounds) beside w = 64.
     python tools/surv_count_w128.py <n_points> [views]"""
 import os, sys, numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -21,12 +21,6 @@ for w, rho in ((64, 24.0), (128, 36.0), (128, 24.0)):
     cnt = ws[cnt_off:cnt_off + I * 4].view(torch.int32).cpu().numpy().astype(np.int64) & 0xFFFFFFFF
     cnt2 = ws[cnt_off + I * 4:cnt_off + I * 8].view(torch.int32).cpu().numpy().astype(np.int64) & 0xFFFFFFFF
     print(f"w {w} rho {rho}: (last pass) round-1 mean {cnt.mean():.0f} max {cnt.max()}  round-2 mean {cnt2.mean():.0f} max {cnt2.max()}")
-    if w == 128:
-        S1 = min(max(49152, n // 16), 1 << 26); S2 = 1 << 18; g = 64 if n >= (4 << 20) else 32
-        thr_off = cnt_off + al(I * 8 + 64 + 48); surv_off = thr_off + al(I * 4096 * 45 * 4); surv2_off = surv_off + al(I * S1 * 4)
-        vox_off = surv2_off + al(I * S2 * 4); tab_off = vox_off + al(2 * g ** 3 * 8); ucnt_off = tab_off + al(I * 4096 * 16)
-        uc = ws[ucnt_off:ucnt_off + I * 4].view(torch.int32).cpu().numpy().astype(np.int64) & 0xFFFFFFFF
-        print(f"   union: mean {uc.mean():.0f} max {uc.max()} (cap {min(S1, 1 << 20)})")
     wn = win[0].cpu().numpy()
     print("   distinct winners per image (mean)", np.mean([len(np.unique(wn[v, c])) for v in range(V) for c in range(2)]))
     del ws, imgs, win
