@@ -662,7 +662,16 @@ __device__ __forceinline__ float ex2_ftz(float x) {
 }
 
 // the transform S1 and S3 share (same arithmetic as stream_point(): they must agree on the home cell)
-struct FilterPoint { float ux, uy, pv_hi, cj, cr; bool inside; int cell; };
+// Points outside the cell grid (outside the image; in a lattice pass of a w == 128 render also the quarter-cell strip that the
+// shifted frame leaves out): every pixel centre lies inside the grid, a convex box, so the point's projection onto the box is
+// at least as close to EVERY pixel as the point itself -- a point whose projection (same depth weight) cannot reach U anywhere
+// cannot either.  They are tested at the projected position (ux, uy clamped into the border cell), not kept wholesale: at
+// w == 128 a third of a unit ball's final lists were strip points, hundreds of records in a few border cells that every far
+// pixel near them walked.  NaN coordinates are kept (the renderer writes the NaN image by itself).
+#ifndef FS_CLAMP_OUTSIDE
+#define FS_CLAMP_OUTSIDE 1
+#endif
+struct FilterPoint { float ux, uy, pv_hi, cj, cr; bool inside, nan; int cell; };
 __device__ __forceinline__ FilterPoint filter_point(float x, float y, float z, const StreamViewPacked& W, float offx, float offy) {
     FilterPoint f;
     f.ux = __fmaf_rn(__fmaf_rn(W.rx.z, z, __fmaf_rn(W.rx.y, y, __fmul_rn(W.rx.x, x))), FC_CELLS_PER_NDC, offx);
@@ -672,7 +681,14 @@ __device__ __forceinline__ FilterPoint filter_point(float x, float y, float z, c
     const float fj = floorf(f.ux), fi = floorf(f.uy);
     f.cj = fminf(fmaxf(fj, 0.0f), (float)(FC_G - 1)); f.cr = fminf(fmaxf(fi, 0.0f), (float)(FC_G - 1));
     f.inside = (f.cj == fj) && (f.cr == fi);             // really inside its cell (not clamped, not NaN)
+    f.nan = !(f.ux == f.ux) || !(f.uy == f.uy);
     f.cell = (int)f.cr * FC_G + (int)f.cj;
+#if FS_CLAMP_OUTSIDE
+    if (!f.inside && !f.nan) {                           // the projection onto the grid, inside the (closed) border cell
+        f.ux = fminf(fmaxf(f.ux, f.cj), f.cj + 1.0f); f.uy = fminf(fmaxf(f.uy, f.cr), f.cr + 1.0f);
+        f.inside = true;
+    }
+#endif
     return f;
 }
 
@@ -816,9 +832,16 @@ stream_filter_kernel(StreamParams P)
         const float zr = __fmaf_rn(rz.z, pz, __fmaf_rn(rz.y, py, __fmul_rn(rz.x, px)));
         const float pv_hi = __fmaf_rn(-(zr - rx.w), ry.w, 1.0f) + FS_PV_ABS;
         const int j3 = __float2int_rd(ux * (float)FS_SUB), i3 = __float2int_rd(uy * (float)FS_SUB);
+#if FS_CLAMP_OUTSIDE
+        // outside points: the sub-cell of their projection onto the grid (see FilterPoint); NaN coordinates pass
+        const bool inside = (ux == ux) && (uy == uy);
+        const int j3c = min(max(j3, 0), FS_SUB * FC_G - 1), i3c = min(max(i3, 0), FS_SUB * FC_G - 1);
+        const float lim = __ldg(lpv0 + (size_t)vv * (2 * FS_SUB * FC_G * FS_SUB * FC_G) + (inside ? i3c * (FS_SUB * FC_G) + j3c : 0));
+#else
         const bool inside = (unsigned)j3 < (unsigned)(FS_SUB * FC_G) && (unsigned)i3 < (unsigned)(FS_SUB * FC_G);
         const float lim = __ldg(lpv0 + (size_t)vv * (2 * FS_SUB * FC_G * FS_SUB * FC_G) + (inside ? i3 * (FS_SUB * FC_G) + j3 : 0));
-        const bool pass = live && pv_hi > 0.0f && (pv_hi >= lim || !inside);         // clamped points are never dropped here
+#endif
+        const bool pass = live && pv_hi > 0.0f && (pv_hi >= lim || !inside);         // NaN (and, without the projection, clamped) points are never dropped here
         const unsigned pm = __ballot_sync(0xFFFFFFFFu, pass);
         if (pm) {
             // the pair's point: entries are at most one round old, the other slot holds the round before
@@ -1018,8 +1041,15 @@ stream_refilter_kernel(StreamParams P)
                 else {
                     // the sub-cell threshold of THIS round's bounds first (4 bytes): most of the list fails it
                     const int j3 = __float2int_rd(f.ux * (float)FS_SUB), i3 = __float2int_rd(f.uy * (float)FS_SUB);
+#if FS_CLAMP_OUTSIDE
+                    const bool in3 = true;               // a projected point may sit on the grid's far edge: the last sub-cell
+                    const int j3c = min(max(j3, 0), FS_SUB * FC_G - 1), i3c = min(max(i3, 0), FS_SUB * FC_G - 1);
+                    const float lim = __ldg(P.lpv9 + C.img * (size_t)(FS_SUB * FC_G * FS_SUB * FC_G) + i3c * (FS_SUB * FC_G) + j3c);
+#else
                     const bool in3 = (unsigned)j3 < (unsigned)(FS_SUB * FC_G) && (unsigned)i3 < (unsigned)(FS_SUB * FC_G);
                     const float lim = in3 ? __ldg(P.lpv9 + C.img * (size_t)(FS_SUB * FC_G * FS_SUB * FC_G) + i3 * (FS_SUB * FC_G) + j3) : 0.0f;
+#endif
+                    (void)in3;
                     if (f.pv_hi >= lim) code = point_may_win(f, P.win + C.img * (size_t)FC_CELLS * 8, inv_k, &thr);
                 }
             }
