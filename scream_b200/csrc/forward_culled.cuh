@@ -967,7 +967,13 @@ forward_culled_kernel_t(FwdParams P)
             // serial chain, and the entries are spread over all 32 warps
             // Small grids (coop): a far pixel is a task of its own, searched by the whole warp, and the 3 x 3 chunks -- now the
             // long tasks -- go first.
-            const bool coop = nparts > 1;
+#ifndef FC_LATTICE_COOP
+#define FC_LATTICE_COOP 1
+#endif
+            // (lattice renders of a giant cloud's survivor lists, PSTEP 2: warp-cooperative searches too -- their corner pixels sit in the
+            // last e-folds above zero at rho 36, where EVERY record of the band is evaluated exactly from its point in a 10^8-point
+            // cloud: lane per pixel, a batch of them ran for 2.9 ms of serial DRAM round trips while the CTA waited)
+            const bool coop = nparts > 1 || (FC_LATTICE_COOP && PSTEP == 2);
             const int nfar = (int)s_qfar;
             const int far_take = coop ? FC_COOP_FAR : FC_FAR_TAKE;
             const int far_batches = (nfar + far_take - 1) / far_take;
@@ -1000,7 +1006,7 @@ forward_culled_kernel_t(FwdParams P)
                     const int qi = t * far_take + lane;
                     if (lane < far_take && qi < nfar) scan_pixel(s_queue[qi], 0xFFFF);
                     __syncwarp();
-                    if (lane == 0) { FC_MAXOF(12, FC_CLOCK() - task_t0); FC_COUNT(14, FC_CLOCK() - task_t0); }
+                    if (lane == 0) { FC_MAXOF(12, ((FC_CLOCK() - task_t0) << 20) | ((long long)batch << 16) | (long long)s_queue[t * far_take]); FC_COUNT(14, FC_CLOCK() - task_t0); }
                     continue;
                 }
                 // ---- 3 x 3 cells, lane per pixel ----

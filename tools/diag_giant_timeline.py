@@ -31,5 +31,7 @@ m = marks[:V * 2]
 us = lambda x: x / 1.9e3
 print(f"n {n} w {w} rho {rho} raw {raw}: CTAs {len(m)}, CTA total us mean {us(m[:, 8] - m[:, 0]).mean():.0f} max {us(m[:, 8] - m[:, 0]).max():.0f}")
 print("  far pixels per CTA (all batches, tiles) mean", m[:, 9].mean(), " near", m[:, 10].mean(), " near->disc fallback", m[:, 11].mean())
-print("  far tasks: warp-time sum per CTA (us) mean", us(m[:, 14]).mean(), " longest task (us) max", us(m[:, 12]).max())
+print("  far tasks: warp-time sum per CTA (us) mean", us(m[:, 14]).mean(), " longest task (us) max", us(m[:, 12] >> 20).max())
+order = np.argsort(-(m[:, 12] >> 20))[:8]
+print("  longest far task per CTA (us, batch, first pixel row, col):", [(int(us(m[i, 12] >> 20)), int((m[i, 12] >> 16) & 15), int((m[i, 12] & 0xFFFF) // 64), int((m[i, 12] & 0xFFFF) % 64)) for i in order])
 print("  3x3 chunks: warp-time sum per CTA (us) mean", us(m[:, 15]).mean(), " longest (us) max", us(m[:, 13]).max())
