@@ -846,7 +846,9 @@ forward_culled_kernel_t(FwdParams P)
             FC_MARK(6);
 
             // ---- disc scan of one queued pixel (far: no candidate; near: the best record of its 3 x 3 window) ----
-            auto scan_pixel = [&](int pl, int cand) {
+            // (defer, lattice renders only: a pixel that needs the exact pass over a band of records is handed back -- the winner's
+            // record is returned, nothing is written -- and the caller settles it with the whole warp)
+            auto scan_pixel = [&](int pl, int cand, bool defer) -> int {
                 const int row = trow0 + (pl / FC_TILE) * pstep, col = tcol0 + (pl % FC_TILE) * pstep;
                 const PixelGeom g = geom(row, col);
                 // nothing beyond r2cap can change the output of this pixel
@@ -868,11 +870,13 @@ forward_culled_kernel_t(FwdParams P)
                     if (s2 > s_thr) {
                         val = exact_value(S, E, a1, g, id);
                     } else {
+                        if (PSTEP == 2 && defer) return a1;
                         disc_scan<true>(S, E, g, fminf(s_thr, s_zero), inv_k, s1, s2, a1, val, id);
                     }
                     if (val == 0.0f) id = 0;              // all-zero pixel: torch.max returns index 0
                 }
                 put(row, col, val, id);
+                return -1;
             };
 
             // ---- the same for ONE pixel by a whole warp (all lanes call with the same arguments): small grids are bound by
@@ -968,12 +972,15 @@ forward_culled_kernel_t(FwdParams P)
             // Small grids (coop): a far pixel is a task of its own, searched by the whole warp, and the 3 x 3 chunks -- now the
             // long tasks -- go first.
 #ifndef FC_LATTICE_COOP
-#define FC_LATTICE_COOP 1
+#define FC_LATTICE_COOP 2
 #endif
-            // (lattice renders of a giant cloud's survivor lists, PSTEP 2: warp-cooperative searches too -- their corner pixels sit in the
-            // last e-folds above zero at rho 36, where EVERY record of the band is evaluated exactly from its point in a 10^8-point
-            // cloud: lane per pixel, a batch of them ran for 2.9 ms of serial DRAM round trips while the CTA waited)
-            const bool coop = nparts > 1 || (FC_LATTICE_COOP && PSTEP == 2);
+            // Lattice renders of a giant cloud's survivor lists (PSTEP 2): their corner pixels sit in the last e-folds above zero at
+            // rho 36, where EVERY record of the band is evaluated exactly from its point in a 10^8-point cloud -- lane per pixel, a
+            // batch of them ran for 2.9 ms of serial DRAM round trips while the CTA waited.  FC_LATTICE_COOP 1: all far pixels by
+            // whole warps (1.8 ms per launch, but 3 lanes per instruction on the ordinary ones); 2: lane per pixel, and the pixels
+            // that need the exact pass over a band are handed to the whole warp afterwards.
+            const bool coop = nparts > 1 || (FC_LATTICE_COOP == 1 && PSTEP == 2);
+            const bool coop_near = coop || PSTEP == 2;
             const int nfar = (int)s_qfar;
             const int far_take = coop ? FC_COOP_FAR : FC_FAR_TAKE;
             const int far_batches = (nfar + far_take - 1) / far_take;
@@ -1004,8 +1011,19 @@ forward_culled_kernel_t(FwdParams P)
                     t += far_batches;                    // chunk t of the list below
                 } else if (t < far_batches) {
                     const int qi = t * far_take + lane;
-                    if (lane < far_take && qi < nfar) scan_pixel(s_queue[qi], 0xFFFF);
+                    int dpl = 0, dcand = -1;
+                    if (lane < far_take && qi < nfar) { dpl = s_queue[qi]; dcand = scan_pixel(dpl, 0xFFFF, true); }
                     __syncwarp();
+                    if (PSTEP == 2) {
+                        unsigned dm = __ballot_sync(0xFFFFFFFFu, dcand >= 0);
+                        while (dm) {
+                            const int src = __ffs(dm) - 1;
+                            dm &= dm - 1u;
+                            const int fpl = __shfl_sync(0xFFFFFFFFu, dpl, src);
+                            const int fa = search_pixel_warp(fpl, __shfl_sync(0xFFFFFFFFu, dcand, src));
+                            if (fa >= 0 && lane == 0) finish_pixel(fpl, fa);
+                        }
+                    }
                     if (lane == 0) { FC_MAXOF(12, ((FC_CLOCK() - task_t0) << 20) | ((long long)batch << 16) | (long long)s_queue[t * far_take]); FC_COUNT(14, FC_CLOCK() - task_t0); }
                     continue;
                 }
@@ -1059,7 +1077,7 @@ forward_culled_kernel_t(FwdParams P)
             // Small grids: four pixels per warp, eight lanes each -- five of them take one row run of the 5 x 5 window each, the
             // (best, runner-up) of the rows merge through shuffles, the group's first lane decides and evaluates.  (Lanes in
             // lockstep instead of three lanes walking three different windows one after the other.)
-            for (; coop;) {
+            for (; coop_near;) {
                 int q0 = 0;
                 if (lane == 0) q0 = (int)atomicAdd(&s_qhead, 4u);
                 q0 = __shfl_sync(0xFFFFFFFFu, q0, 0);
@@ -1110,7 +1128,7 @@ forward_culled_kernel_t(FwdParams P)
                     if (fa >= 0 && lane == 0) finish_pixel(fpl, fa);
                 }
             }
-            for (; !coop;) {
+            for (; !coop_near;) {
                 int qi = 0;
                 if (lane == 0) qi = (int)atomicAdd(&s_qhead, (unsigned)near_take);
                 qi = __shfl_sync(0xFFFFFFFFu, qi, 0) + lane;
@@ -1139,7 +1157,7 @@ forward_culled_kernel_t(FwdParams P)
                     put(row, col, val, id);
                 } else {
                     FC_COUNT(11, 1);
-                    scan_pixel(pl, a1 < 0 ? 0xFFFF : a1);
+                    scan_pixel(pl, a1 < 0 ? 0xFFFF : a1, false);
                 }
             }
             __syncthreads();
