@@ -78,7 +78,10 @@ constexpr int FS_VPC_FILTER = 64;                        // ... of S3: one 64-bi
 #define FS_VOX_BIG_MIN_N (8 << 20)
 #endif
 constexpr int64_t FS_VOX_BIG_MIN = FS_VOX_BIG_MIN_N;       // points per item from which the 64^3 voxel grid replaces the 32^3 one
-constexpr int FV_G = 64;                                 // voxels per axis of a cloud's bounding box (S2b): g^3 mask words per group of 64 views
+#ifndef FV_G_N
+#define FV_G_N 64
+#endif
+constexpr int FV_G = FV_G_N;                                 // voxels per axis of a cloud's bounding box (S2b): g^3 mask words per group of 64 views
 constexpr int FS_TC = (FC_G + 1) * (FC_G + 1);           // cell corners per image
 constexpr float FS_AIM = 6.0f;                            // how far (cells) outside a rim cell its aim lies
 constexpr int FS_SUB = 3;                                // S3 step 1 thresholds per cell and axis (odd: the pixel centre in the middle sub-cell)
