@@ -45,6 +45,20 @@ def test_workspace_query_and_argument_errors():
         _lib.check(rc, "x")
 
 
+def test_giant_cloud_path_is_chosen_by_size_and_image_side():
+    """Host logic (no GPU): the workspace query tells which calls take the giant-cloud pre-filter -- w = 64 from 147,456
+    points per item, w = 128 (four lattice passes) from 2^20, other image sides never; the same sizes decide in the forward call."""
+    small = _lib.workspace_bytes(1, 8, 64, 147455)
+    assert small < 4096                                          # the encoded depth ranges only
+    assert _lib.workspace_bytes(1, 8, 64, 147456) > 100 * small  # seed images, bound tables, survivor lists
+    assert _lib.workspace_bytes(2, 8, 64, 2 * 147456 - 1) == _lib.workspace_bytes(2, 8, 64, 1000)   # the AVERAGE item decides
+    assert _lib.workspace_bytes(1, 8, 128, (1 << 20) - 1) == small
+    big128 = _lib.workspace_bytes(1, 8, 128, 1 << 20)
+    assert big128 > 100 * small
+    assert big128 == _lib.workspace_bytes(1, 8, 64, 1 << 20)     # the passes reuse one set of buffers: no union lists, no bit maps
+    assert _lib.workspace_bytes(1, 8, 192, 1 << 24) == small and _lib.workspace_bytes(1, 8, 256, 1 << 24) == small
+
+
 def test_module_surface_matches_reference():
     r = RegistrationRender(24, 64, device="cpu")
     assert r.state_dict() == {} and list(r.parameters()) == [] and list(r.buffers()) == []
