@@ -364,9 +364,13 @@ def leg_cfg1(dev, peak, cpu: bool):
             r(s, tgt).backward(g)
         f_dev, f_wall = _timed(fwd, 200, dev, warm=20)
         b_dev, b_wall = _timed(fwd_bwd, 200, dev, warm=20)
+        # the same with the autograd engine on the calling thread (a user-level switch of torch: no hop to the device's worker thread)
+        with torch.autograd.set_multithreading_enabled(False):
+            s_dev, s_wall = _timed(fwd_bwd, 200, dev, warm=20)
         fb, bb = _alg_bytes(1, N_PTS, N_PTS, V, W_IMG, winner=False)
         out[f"views_{V}"] = {"fwd_us_device": 1e3 * f_dev, "fwd_us_wall": 1e3 * f_wall, "fwd_bwd_us_device": 1e3 * b_dev,
-                             "fwd_bwd_us_wall": 1e3 * b_wall, "images_per_sec_fwd": 2 * V / (f_dev / 1e3),
+                             "fwd_bwd_us_wall": 1e3 * b_wall, "fwd_bwd_us_wall_autograd_on_calling_thread": 1e3 * s_wall,
+                             "images_per_sec_fwd": 2 * V / (f_dev / 1e3),
                              "roofline": {"bound": "hbm", "achieved": fb / (f_dev / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
                                           "frac": fb / (f_dev / 1e3) / 1e9 / peak, "algorithmic_bytes": fb,
                                           "note": "one call = 0.27 MB (V=1): 42 ns at the HBM peak; a call is launch-latency bound"}}
