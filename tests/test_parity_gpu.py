@@ -503,6 +503,30 @@ def test_giant_w128_batch_of_items_and_more_than_64_views():
     assert torch.equal(a[1], b[1]), f"winners differ at {(a[1] != b[1]).sum().item()} pixels"
 
 
+def test_module_on_a_giant_pair_at_w128_forward_and_backward():
+    """The drop-in module on a pair of 1.2 M points at w = 128, rho = 36 (the viewer's shape, visualize_depth_image.py:20, at
+    cfg5's size): the call takes the lattice passes; images and the gradient through the winner maps equal those of rendering
+    every batch (SCREAM_F_NOSTREAM): images bit for bit, gradients up to the order of the fp32 atomic sums (the backward is a
+    function of (winner, z range) only)."""
+    n, m = 640000, 560000
+    src, tgt = synth.unit_ball(n, 81), synth.room_shell(m, 82)
+    r = RegistrationRender(36, 128, view="single", device=DEV)
+    s = torch.from_numpy(src).to(DEV).requires_grad_(True)
+    t = torch.from_numpy(tgt).to(DEV).requires_grad_(True)
+    imgs = r(s, t)
+    assert imgs.shape == (1, 2, 128, 128)
+    g = torch.from_numpy(np.random.default_rng(3).standard_normal(tuple(imgs.shape)).astype(np.float32)).to(DEV)
+    imgs.backward(g)
+    x = torch.from_numpy(np.concatenate([src, tgt], 0)).to(DEV).requires_grad_(True)
+    offs = make_offsets([(n, m)]).to(DEV)
+    want, win, zr = render_batch(x, offs, view_matrices(r.eulers).to(DEV), 36, 128, need_winner=True, no_stream=True)
+    assert torch.equal(imgs, want[0])
+    want.backward(g[None])
+    got = torch.cat([s.grad, t.grad], 0)
+    scale = float(x.grad.abs().max())
+    assert scale > 0 and float((got - x.grad).abs().max()) <= 1e-5 * scale   # same winners, fp32 atomic sums in any order
+
+
 @pytest.mark.parametrize("posed", [False, True])
 def test_depth_range_of_large_clouds_bit_exact(posed, c_oracle):
     """Items of >= 2^18 points take the views-in-registers z-range kernel (transform.cuh, zrange_wide_kernel):
