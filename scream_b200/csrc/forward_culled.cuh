@@ -1128,36 +1128,58 @@ forward_culled_kernel_t(FwdParams P)
                     if (fa >= 0 && lane == 0) finish_pixel(fpl, fa);
                 }
             }
+#ifndef FC_NEAR_DEFER
+#define FC_NEAR_DEFER 1
+#endif
+            // (FC_NEAR_DEFER: the pixels the 5 x 5 window leaves open are settled afterwards by the whole warp, one at a time -- rows of
+            // the disc per lane -- instead of by their own lanes inside the lockstep batch, where each is a serial chain of ~1500
+            // dependent instructions that the other lanes of the batch, and the barrier behind this phase, wait for)
             for (; !coop_near;) {
                 int qi = 0;
                 if (lane == 0) qi = (int)atomicAdd(&s_qhead, (unsigned)near_take);
                 qi = __shfl_sync(0xFFFFFFFFu, qi, 0) + lane;
                 if (qi - lane >= nnear) break;
-                if (lane >= near_take || qi >= nnear) continue;
-                const int pl = s_queue[FC_TPIX - 1 - qi];
-                const int row = trow0 + (pl / FC_TILE) * pstep, col = tcol0 + (pl % FC_TILE) * pstep;
-                const PixelGeom g = geom(row, col);
-                const int ci = (int)g.uy, cj = (int)g.ux;
-                const float fx = g.ux - (float)cj, fy = g.uy - (float)ci;
-                const float edge = fminf(fminf(fx, 1.0f - fx), fminf(fy, 1.0f - fy));
-                float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
-                bool found = false;
-                {
-                    const int j0 = max(cj - 2, 0), j1 = min(cj + 2, FC_G - 1);
-                    for (int i = max(ci - 2, 0); i <= min(ci + 2, FC_G - 1); ++i)
-                        scan_run(S, s_start[i * FC_G + j0], s_start[i * FC_G + j1 + 1], g, s1, s2, a1, found);
+                const bool act = lane < near_take && qi < nnear;
+                if (!FC_NEAR_DEFER && !act) continue;
+                int fb_cand = -2, pl = 0;
+                if (act) {
+                    pl = s_queue[FC_TPIX - 1 - qi];
+                    const int row = trow0 + (pl / FC_TILE) * pstep, col = tcol0 + (pl % FC_TILE) * pstep;
+                    const PixelGeom g = geom(row, col);
+                    const int ci = (int)g.uy, cj = (int)g.ux;
+                    const float fx = g.ux - (float)cj, fy = g.uy - (float)ci;
+                    const float edge = fminf(fminf(fx, 1.0f - fx), fminf(fy, 1.0f - fy));
+                    float s1 = INFINITY, s2 = INFINITY; int a1 = -1;
+                    bool found = false;
+                    {
+                        const int j0 = max(cj - 2, 0), j1 = min(cj + 2, FC_G - 1);
+                        for (int i = max(ci - 2, 0); i <= min(ci + 2, FC_G - 1); ++i)
+                            scan_run(S, s_start[i * FC_G + j0], s_start[i * FC_G + j1 + 1], g, s1, s2, a1, found);
+                    }
+                    a1 = best_of_pair(S, a1, g);
+                    const float cov = __fmul_rn(2.0f + edge, 1.0f / FC_CELLS_PER_NDC);
+                    const float cov2 = __fmul_rn(__fmul_rn(cov, cov), 0.99999f);
+                    const float m = score_margin(s1, inv_k);
+                    if ((s1 + m < cov2) && (s2 > s1 + m) && (__fmul_rn(s1, -P.negk) < FC_EXP_DENORM)) {
+                        int id;
+                        const float val = exact_value(S, E, a1, g, id);
+                        put(row, col, val, id);
+                    } else {
+                        FC_COUNT(11, 1);
+                        if (FC_NEAR_DEFER) fb_cand = a1 < 0 ? 0xFFFF : a1;
+                        else scan_pixel(pl, a1 < 0 ? 0xFFFF : a1, false);
+                    }
                 }
-                a1 = best_of_pair(S, a1, g);
-                const float cov = __fmul_rn(2.0f + edge, 1.0f / FC_CELLS_PER_NDC);
-                const float cov2 = __fmul_rn(__fmul_rn(cov, cov), 0.99999f);
-                const float m = score_margin(s1, inv_k);
-                if ((s1 + m < cov2) && (s2 > s1 + m) && (__fmul_rn(s1, -P.negk) < FC_EXP_DENORM)) {
-                    int id;
-                    const float val = exact_value(S, E, a1, g, id);
-                    put(row, col, val, id);
-                } else {
-                    FC_COUNT(11, 1);
-                    scan_pixel(pl, a1 < 0 ? 0xFFFF : a1, false);
+                if (FC_NEAR_DEFER) {
+                    __syncwarp();
+                    unsigned fbm = __ballot_sync(0xFFFFFFFFu, fb_cand != -2);
+                    while (fbm) {
+                        const int src = __ffs(fbm) - 1;
+                        fbm &= fbm - 1u;
+                        const int fpl = __shfl_sync(0xFFFFFFFFu, pl, src);
+                        const int fa = search_pixel_warp(fpl, __shfl_sync(0xFFFFFFFFu, fb_cand, src));
+                        if (fa >= 0 && lane == 0) finish_pixel(fpl, fa);
+                    }
                 }
             }
             __syncthreads();
