@@ -36,7 +36,10 @@ namespace scream {
 constexpr int FC_THREADS = 1024;
 constexpr int FC_PPT = 12;                               // points per thread per batch
 constexpr int FC_CAP = FC_THREADS * FC_PPT;              // 12288 points per batch
-constexpr int FC_NEAR_SPREAD = 0;                        // near queue spread over all warps also when the GPU is full (A/B)
+#ifndef FC_NEAR_SPREAD_N
+#define FC_NEAR_SPREAD_N 0
+#endif
+constexpr int FC_NEAR_SPREAD = FC_NEAR_SPREAD_N;                        // near queue spread over all warps also when the GPU is full (A/B)
 #ifndef FC_FAR_TAKE_N
 #define FC_FAR_TAKE_N 32
 #endif
