@@ -91,7 +91,9 @@ const char *scream_last_error(void);
 
 /* Bytes of scratch the forward/backward calls need for a batch of B items, V views, image side w and
  * total_pts points in all.  (No reference counterpart: the reference lets torch allocate N x 4096
- * temporaries, render.py:42.) */
+ * temporaries, render.py:42.)  16 bytes per (item, view) for ordinary batches; giant clouds -- total_pts >= 147456 * B at
+ * w == 64, >= 1048576 * B at w == 128 -- take an exact pre-filter (seed images, bound tables, survivor lists) whose scratch is
+ * included: query with the SAME (B, V, w, total_pts) as the forward call. */
 int scream_render_workspace_bytes(int B, int V, int w, int64_t total_pts, size_t *out_bytes);
 
 /* Forward render of a batch: replaces RegistrationRender.forward / .render, render.py:27-73, for B
